@@ -1,0 +1,78 @@
+"""ctypes binding of ``include/coderag_b200.h``.
+
+There is no fallback: if the CUDA library has not been built (``python -m
+githubrepostorag_b200.build``) loading raises, and every entry point raises ``RuntimeError``
+with the library's message on a non-zero return (the reference propagates Python exceptions,
+``rag_worker/src/worker/services/agent_graph.py:276-278``).  ctypes drops the GIL for the
+duration of each call, which is what lets the worker's thread pool
+(``rag_worker/src/worker/worker.py:136-139``) overlap searches.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from pathlib import Path
+from typing import Optional
+
+_LIB_PATH = Path(__file__).resolve().parent / "_lib" / "libcoderag_b200.so"
+_lib: Optional[C.CDLL] = None
+
+ABI_VERSION = 1
+METRIC_COSINE = 0
+METRIC_IP = 1
+FILT_ANY = -1
+FILT_IMPOSSIBLE = -2
+CODE_MISSING = -1
+MAX_KEYS = 8
+MAX_TOPK = 128
+MAX_DIM = 4096
+
+# every symbol include/coderag_b200.h declares: name -> (restype, argtypes)
+_vp, _i32, _i64, _sz = C.c_void_p, C.c_int32, C.c_int64, C.c_size_t
+PROTOTYPES = {
+    "crb_abi_version": (C.c_int, []),
+    "crb_last_error": (C.c_char_p, []),
+    "crb_index_create": (C.c_int, [C.POINTER(_vp), _vp, _vp, _vp, _i64, _i32, _i32, _i64, _i32]),
+    "crb_index_destroy": (C.c_int, [_vp]),
+    "crb_encode_rows": (C.c_int, [_vp, _vp, _vp, _i64, _i32, _i32, _vp]),
+    "crb_row_inv_norms": (C.c_int, [_vp, _vp, _i64, _i32, _i32, _vp]),
+    "crb_workspace_bytes": (_sz, [_vp, _i32, _i32, _i32]),
+    "crb_search": (C.c_int, [_vp, _vp, _i32, _i32, _i32, _vp, _vp, _vp, _vp, _vp, _vp, _sz, _i32, _vp]),
+    "crb_search_host": (C.c_int, [_vp, _vp, _i32, _i32, _i32, _vp, _vp, _vp, _vp, _i32]),
+    "crb_merge_keys": (C.c_int, [_vp, _i32, _i32, _i32, _i32, _vp, _i32, _vp, _vp, _vp, _vp, _i32, _vp]),
+    "crb_fetch_rows_host": (C.c_int, [_vp, _vp, _i32, _vp]),
+    "crb_launch_count": (_i64, []),
+}
+
+
+def lib_path() -> Path:
+    return _LIB_PATH
+
+
+def load() -> C.CDLL:
+    """Load the library once; raise loudly when it is missing or of another ABI."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not _LIB_PATH.exists():
+        raise RuntimeError(
+            f"{_LIB_PATH} is missing: build it with `python -m githubrepostorag_b200.build` "
+            "(nvcc, sm_100a). There is no CPU fallback for the retrieval path.")
+    lib = C.CDLL(str(_LIB_PATH))
+    for name, (res, args) in PROTOTYPES.items():
+        fn = getattr(lib, name)  # AttributeError here == header and library disagree
+        fn.restype = res
+        fn.argtypes = args
+    if lib.crb_abi_version() != ABI_VERSION:
+        raise RuntimeError(f"ABI mismatch: library {lib.crb_abi_version()} != binding {ABI_VERSION}")
+    _lib = lib
+    return lib
+
+
+def check(rc: int) -> None:
+    if rc != 0:
+        msg = load().crb_last_error()
+        raise RuntimeError("coderag_b200: " + (msg.decode("utf-8", "replace") if msg else f"error {rc}"))
+
+
+def launch_count() -> int:
+    return int(load().crb_launch_count())

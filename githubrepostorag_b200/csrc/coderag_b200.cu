@@ -1,0 +1,622 @@
+// C ABI of the retrieval hot path (include/coderag_b200.h) and the host-side launch planning.
+// Built for sm_100a only; there is no CPU or multi-backend fallback.
+#include "../../include/coderag_b200.h"
+
+#include <algorithm>
+#include <array>
+#include <atomic>
+#include <condition_variable>
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <map>
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "common.cuh"
+#include "k1_stream.cuh"
+#include "k3_filter.cuh"
+#include "topk.cuh"
+
+namespace crb {
+
+// ---------------------------------------------------------------------------------------------
+// errors, device guard, launch counter
+// ---------------------------------------------------------------------------------------------
+static thread_local std::string g_err;
+static std::atomic<int64_t> g_launches{0};
+
+static int fail(const char* fmt, ...) {
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof buf, fmt, ap);
+    va_end(ap);
+    g_err = buf;
+    return 1;
+}
+
+#define CRB_CUDA(expr)                                                                         \
+    do {                                                                                       \
+        cudaError_t _e = (expr);                                                               \
+        if (_e != cudaSuccess)                                                                 \
+            return crb::fail("%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e), __FILE__, \
+                             __LINE__);                                                        \
+    } while (0)
+
+#define CRB_LAUNCH_CHECK()                                                                  \
+    do {                                                                                    \
+        crb::g_launches.fetch_add(1, std::memory_order_relaxed);                            \
+        cudaError_t _e = cudaGetLastError();                                                \
+        if (_e != cudaSuccess)                                                              \
+            return crb::fail("kernel launch failed: %s (%s:%d)", cudaGetErrorString(_e),    \
+                             __FILE__, __LINE__);                                           \
+    } while (0)
+
+struct DeviceGuard {
+    int prev = -1;
+    bool switched = false;
+    cudaError_t status = cudaSuccess;
+    explicit DeviceGuard(int dev) {
+        status = cudaGetDevice(&prev);
+        if (status == cudaSuccess && prev != dev) {
+            status = cudaSetDevice(dev);
+            switched = (status == cudaSuccess);
+        }
+    }
+    ~DeviceGuard() {
+        if (switched) cudaSetDevice(prev);
+    }
+};
+
+static int env_int(const char* name, int dflt) {
+    const char* v = getenv(name);
+    return (v && *v) ? atoi(v) : dflt;
+}
+
+// ---------------------------------------------------------------------------------------------
+// workspace layout
+// ---------------------------------------------------------------------------------------------
+constexpr size_t kWsHeaderBytes = 4096;   // counters [kMaxGroups] u32 @0, list counts @1024
+constexpr size_t kWsCountsOffset = 1024;
+constexpr size_t kWsCandBytes = size_t(8) << 20;  // per-CTA candidate lists of one launch
+
+static inline int64_t round_up(int64_t v, int64_t m) { return (v + m - 1) / m * m; }
+
+struct Lane {
+    cudaStream_t stream = nullptr;
+    void* d_ws = nullptr;
+    size_t ws_cap = 0;
+    void* d_io = nullptr;
+    size_t d_io_cap = 0;
+    void* h_pin = nullptr;
+    size_t h_cap = 0;
+    bool busy = false;
+};
+
+}  // namespace crb
+
+struct crb_index {
+    const __half* rows = nullptr;
+    const float* inv_norm = nullptr;
+    const int32_t* codes = nullptr;
+    int64_t n_rows = 0;
+    int32_t dim = 0;
+    int32_t n_keys = 0;
+    int64_t row_offset = 0;
+    int32_t device = 0;
+    int32_t sm_count = 148;
+    std::mutex mu;
+    std::condition_variable cv;
+    std::vector<crb::Lane> lanes;
+};
+
+namespace crb {
+
+static int64_t list_stride_of(const crb_index* ix) { return round_up(std::max<int64_t>(ix->n_rows, 1), 64); }
+
+// ---------------------------------------------------------------------------------------------
+// K1 dispatch
+// ---------------------------------------------------------------------------------------------
+typedef void (*K1Fn)(const K1Params);
+
+template <int NQ, int CH, int R>
+static K1Fn k1_pick_kpl(int k) {
+    if (k <= 32) return k1_stream_kernel<NQ, CH, R, 1>;
+    return k1_stream_kernel<NQ, CH, R, 4>;
+}
+template <int NQ, int R>
+static K1Fn k1_pick_ch(int ch, int k) {
+    switch (ch) {
+        case 1: return k1_pick_kpl<NQ, 1, R>(k);
+        case 2: return k1_pick_kpl<NQ, 2, R>(k);
+        case 3: if constexpr (NQ <= 2) return k1_pick_kpl<NQ, 3, R>(k); else return nullptr;
+        case 4: if constexpr (NQ <= 2) return k1_pick_kpl<NQ, 4, R>(k); else return nullptr;
+    }
+    return nullptr;
+}
+static K1Fn k1_pick(int nq, int ch, int r1, int k) {
+    if (nq == 1) return r1 == 2 ? k1_pick_ch<1, 2>(ch, k) : k1_pick_ch<1, 4>(ch, k);
+    if (nq == 2) return k1_pick_ch<2, 2>(ch, k);
+    return k1_pick_ch<4, 2>(ch, k);
+}
+static K1Fn k1_pick_generic(int k) {
+    if (k <= 32) return k1_stream_generic_kernel<2, 1>;
+    return k1_stream_generic_kernel<2, 4>;
+}
+
+// resident CTAs per SM of a kernel (cached)
+static int k1_occupancy(K1Fn fn, size_t dyn_smem) {
+    static std::mutex mu;
+    static std::map<std::pair<const void*, size_t>, int> cache;
+    std::lock_guard<std::mutex> lk(mu);
+    auto key = std::make_pair(reinterpret_cast<const void*>(fn), dyn_smem);
+    auto it = cache.find(key);
+    if (it != cache.end()) return it->second;
+    int n = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, fn, kK1Threads, dyn_smem) != cudaSuccess || n < 1) n = 1;
+    cache[key] = n;
+    return n;
+}
+
+struct QueryGroup {
+    std::vector<int> queries;
+    int filter;  // index into the call's distinct-filter table, -1 = none
+};
+
+// Launch K1 for `groups` (all with at most `nq` queries, filter slots already remapped to the
+// lists currently in the workspace).
+static int launch_k1(const crb_index* ix, const float* d_queries, int k, int metric,
+                     const std::vector<QueryGroup>& groups, const std::vector<int>& slot_of_filter,
+                     int nq, uint8_t* ws, float* d_scores, int64_t* d_rows, int32_t* d_n_valid,
+                     uint64_t* d_keys, cudaStream_t stream) {
+    const int chunks = ix->dim / 8;
+    const int ch = (chunks + 31) / 32;
+    const bool generic = ch > 4;
+    const int r1 = env_int("CODERAG_B200_K1_ROWS", 4) == 2 ? 2 : 4;
+    K1Fn fn = generic ? k1_pick_generic(k) : k1_pick(nq, ch, r1, k);
+    if (!fn) return fail("internal: no K1 instantiation for nq=%d ch=%d", nq, ch);
+    const size_t dyn = generic ? size_t(ix->dim) * sizeof(float) : 0;
+    const int rows_per_warp_iter = generic ? 2 : (nq == 1 ? r1 : 2);
+    const int resident = k1_occupancy(fn, dyn) * ix->sm_count;
+
+    for (size_t g0 = 0; g0 < groups.size(); g0 += kMaxGroups) {
+        const int ng = static_cast<int>(std::min<size_t>(kMaxGroups, groups.size() - g0));
+        K1Params p;
+        memset(&p, 0, sizeof p);
+        p.rows = ix->rows;
+        p.inv_norm = ix->inv_norm;
+        p.queries = d_queries;
+        p.lists = reinterpret_cast<const uint32_t*>(ws + kWsHeaderBytes + kWsCandBytes);
+        p.list_counts = reinterpret_cast<const uint32_t*>(ws + kWsCountsOffset);
+        p.cand = reinterpret_cast<uint64_t*>(ws + kWsHeaderBytes);
+        p.counters = reinterpret_cast<unsigned*>(ws);
+        p.out_scores = d_scores;
+        p.out_rows = d_rows;
+        p.out_nvalid = d_n_valid;
+        p.out_keys = d_keys;
+        p.n_rows = ix->n_rows;
+        p.list_stride = list_stride_of(ix);
+        p.row_offset = static_cast<uint32_t>(ix->row_offset);
+        p.dim = ix->dim;
+        p.k = k;
+        p.metric = metric;
+        for (int g = 0; g < ng; ++g) {
+            const QueryGroup& qg = groups[g0 + g];
+            for (int q = 0; q < kK1MaxQ; ++q)
+                p.groups[g].q_idx[q] = q < static_cast<int>(qg.queries.size()) ? qg.queries[q] : -1;
+            p.groups[g].filter = qg.filter < 0 ? -1 : slot_of_filter[qg.filter];
+        }
+        // grid.x: fill the machine once across all groups, but never more CTAs than there is
+        // work for, and never more per-CTA lists than the scratch region or the merge can hold.
+        const int64_t work = (ix->n_rows + int64_t(kK1Warps) * rows_per_warp_iter * 2 - 1) /
+                             (int64_t(kK1Warps) * rows_per_warp_iter * 2);
+        int64_t gx = std::max<int64_t>(resident / ng, 16);
+        gx = std::min<int64_t>(gx, std::max<int64_t>(work, 1));
+        gx = std::min<int64_t>(gx, kK1MaxGridX);
+        const int64_t cand_lists = int64_t(kWsCandBytes) / (int64_t(k) * 8);
+        gx = std::min<int64_t>(gx, std::max<int64_t>(cand_lists / (int64_t(ng) * (generic ? 1 : nq)), 1));
+        dim3 grid(static_cast<unsigned>(gx), static_cast<unsigned>(ng));
+        fn<<<grid, kK1Threads, dyn, stream>>>(p);
+        CRB_LAUNCH_CHECK();
+    }
+    return 0;
+}
+
+// ---------------------------------------------------------------------------------------------
+// the search plan: dedup filters, build survivor lists, group queries, launch
+// ---------------------------------------------------------------------------------------------
+static int search_impl(crb_index* ix, const float* d_queries, int batch, int k, int metric,
+                       const int32_t* h_filt, float* d_scores, int64_t* d_rows,
+                       int32_t* d_n_valid, uint64_t* d_keys, void* d_workspace,
+                       size_t workspace_bytes, int algo, cudaStream_t stream) {
+    (void)algo;
+    uint8_t* ws = static_cast<uint8_t*>(d_workspace);
+    const int M = ix->n_keys;
+
+    // distinct filters of the batch
+    std::vector<std::array<int32_t, kMaxKeys>> filters;
+    std::vector<int> fid(batch, -1);
+    if (h_filt && M > 0) {
+        for (int b = 0; b < batch; ++b) {
+            std::array<int32_t, kMaxKeys> f;
+            f.fill(CRB_FILT_ANY);
+            bool any = false;
+            for (int m = 0; m < M; ++m) {
+                f[m] = h_filt[size_t(b) * M + m];
+                if (f[m] < CRB_FILT_IMPOSSIBLE) return fail("filter code %d out of range", f[m]);
+                any |= (f[m] != CRB_FILT_ANY);
+            }
+            if (!any) continue;
+            int id = -1;
+            for (size_t i = 0; i < filters.size(); ++i)
+                if (filters[i] == f) { id = static_cast<int>(i); break; }
+            if (id < 0) { id = static_cast<int>(filters.size()); filters.push_back(f); }
+            fid[b] = id;
+        }
+    }
+    const int F = static_cast<int>(filters.size());
+    const int64_t stride = list_stride_of(ix);
+    const size_t fixed = kWsHeaderBytes + kWsCandBytes;
+    if (workspace_bytes < fixed) return fail("workspace too small: %zu < %zu", workspace_bytes, fixed);
+    int lists_fit = static_cast<int>(std::min<size_t>((workspace_bytes - fixed) / (size_t(stride) * 4), kMaxFilters));
+    if (F > 0 && lists_fit < 1)
+        return fail("workspace too small for one survivor list: need %zu bytes", fixed + size_t(stride) * 4);
+
+    const int chunks = ix->dim / 8;
+    const int ch = (chunks + 31) / 32;
+    const int nq_cap = ch > 4 ? 1 : (ch <= 2 ? 4 : 2);
+
+    // rounds: round 0 serves the unfiltered queries together with the first block of filters
+    int f_lo = 0;
+    bool first = true;
+    while (first || f_lo < F) {
+        const int f_hi = std::min(F, f_lo + std::max(lists_fit, 1));
+        std::vector<int> slot_of_filter(std::max(F, 1), -1);
+        if (f_hi > f_lo) {
+            K3Params kp;
+            memset(&kp, 0, sizeof kp);
+            kp.codes = ix->codes;
+            kp.lists = reinterpret_cast<uint32_t*>(ws + fixed);
+            kp.counts = reinterpret_cast<uint32_t*>(ws + kWsCountsOffset);
+            kp.n_rows = ix->n_rows;
+            kp.list_stride = stride;
+            kp.n_keys = M;
+            kp.n_filters = f_hi - f_lo;
+            for (int f = f_lo; f < f_hi; ++f) {
+                slot_of_filter[f] = f - f_lo;
+                for (int m = 0; m < kMaxKeys; ++m) {
+                    kp.want[f - f_lo][m] = m < M ? filters[f][m] : CRB_FILT_ANY;
+                    if (m < M && filters[f][m] != CRB_FILT_ANY) kp.used_keys |= (1u << m);
+                }
+            }
+            CRB_CUDA(cudaMemsetAsync(ws + kWsCountsOffset, 0, kMaxFilters * sizeof(uint32_t), stream));
+            const int64_t rows_per_block = int64_t(kK3Threads) * kK3RowsPerThread;
+            const unsigned blocks = static_cast<unsigned>((ix->n_rows + rows_per_block - 1) / rows_per_block);
+            if (blocks > 0) {
+                k3_filter_kernel<<<blocks, kK3Threads, 0, stream>>>(kp);
+                CRB_LAUNCH_CHECK();
+            }
+        }
+        // groups of this round
+        std::vector<QueryGroup> groups;
+        int max_group = 1;
+        {
+            std::map<int, std::vector<int>> by_filter;
+            for (int b = 0; b < batch; ++b) {
+                const int f = fid[b];
+                const bool mine = (f < 0) ? first : (f >= f_lo && f < f_hi);
+                if (mine) by_filter[f].push_back(b);
+            }
+            for (auto& kv : by_filter) {
+                const std::vector<int>& qs = kv.second;
+                for (size_t i = 0; i < qs.size(); i += nq_cap) {
+                    QueryGroup g;
+                    g.filter = kv.first;
+                    g.queries.assign(qs.begin() + i, qs.begin() + std::min(qs.size(), i + nq_cap));
+                    max_group = std::max<int>(max_group, static_cast<int>(g.queries.size()));
+                    groups.push_back(std::move(g));
+                }
+            }
+        }
+        if (!groups.empty()) {
+            const int nq = max_group <= 1 ? 1 : (max_group <= 2 ? 2 : 4);
+            int rc = launch_k1(ix, d_queries, k, metric, groups, slot_of_filter, nq, ws, d_scores,
+                               d_rows, d_n_valid, d_keys, stream);
+            if (rc) return rc;
+        }
+        first = false;
+        f_lo = f_hi;
+    }
+    return 0;
+}
+
+// ---------------------------------------------------------------------------------------------
+// cross-shard merge
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) merge_keys_kernel(const uint64_t* __restrict__ keys_in,
+                                                         int n_lists, int batch, int k, int metric,
+                                                         const float* __restrict__ queries, int dim,
+                                                         float* scores, int64_t* rows,
+                                                         int32_t* n_valid, uint64_t* keys_out) {
+    __shared__ uint64_t xchg[2][32];
+    __shared__ float s_invq;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int b = blockIdx.x;
+    if (warp == 0) {
+        const float iq = (metric == 0) ? warp_inv_qnorm(queries + static_cast<int64_t>(b) * dim, dim, lane) : 1.0f;
+        if (lane == 0) s_invq = iq;
+    }
+    __syncthreads();
+    TopKSink sink;
+    sink.scores = scores + static_cast<int64_t>(b) * k;
+    sink.rows = rows + static_cast<int64_t>(b) * k;
+    sink.n_valid = n_valid + b;
+    sink.keys = keys_out ? keys_out + static_cast<int64_t>(b) * k : nullptr;
+    sink.scale = s_invq;
+    block_merge_sorted_lists<4>(keys_in + static_cast<int64_t>(b) * k, n_lists, k,
+                                static_cast<int64_t>(batch) * k, sink, xchg, lane, warp, 8);
+}
+
+// ---------------------------------------------------------------------------------------------
+// lanes for the host-buffer entry points
+// ---------------------------------------------------------------------------------------------
+static Lane* checkout_lane(crb_index* ix) {
+    std::unique_lock<std::mutex> lk(ix->mu);
+    for (;;) {
+        for (auto& l : ix->lanes)
+            if (!l.busy) { l.busy = true; return &l; }
+        ix->cv.wait(lk);
+    }
+}
+static void checkin_lane(crb_index* ix, Lane* l) {
+    {
+        std::lock_guard<std::mutex> lk(ix->mu);
+        l->busy = false;
+    }
+    ix->cv.notify_one();
+}
+struct LaneHold {
+    crb_index* ix;
+    Lane* lane;
+    ~LaneHold() { checkin_lane(ix, lane); }
+};
+
+static int lane_reserve(Lane* l, size_t ws_bytes, size_t io_bytes, size_t pin_bytes) {
+    if (!l->stream) CRB_CUDA(cudaStreamCreateWithFlags(&l->stream, cudaStreamNonBlocking));
+    if (l->ws_cap < ws_bytes) {
+        if (l->d_ws) CRB_CUDA(cudaFree(l->d_ws));
+        l->d_ws = nullptr; l->ws_cap = 0;
+        CRB_CUDA(cudaMalloc(&l->d_ws, ws_bytes));
+        CRB_CUDA(cudaMemsetAsync(l->d_ws, 0, kWsHeaderBytes, l->stream));
+        l->ws_cap = ws_bytes;
+    }
+    if (l->d_io_cap < io_bytes) {
+        if (l->d_io) CRB_CUDA(cudaFree(l->d_io));
+        l->d_io = nullptr; l->d_io_cap = 0;
+        CRB_CUDA(cudaMalloc(&l->d_io, io_bytes));
+        l->d_io_cap = io_bytes;
+    }
+    if (l->h_cap < pin_bytes) {
+        if (l->h_pin) CRB_CUDA(cudaFreeHost(l->h_pin));
+        l->h_pin = nullptr; l->h_cap = 0;
+        CRB_CUDA(cudaMallocHost(&l->h_pin, pin_bytes));
+        l->h_cap = pin_bytes;
+    }
+    return 0;
+}
+
+static int count_distinct_filters(const int32_t* h_filt, int batch, int M) {
+    if (!h_filt || M <= 0) return 0;
+    std::vector<std::vector<int32_t>> seen;
+    for (int b = 0; b < batch; ++b) {
+        std::vector<int32_t> f(h_filt + size_t(b) * M, h_filt + size_t(b + 1) * M);
+        bool any = false;
+        for (int32_t v : f) any |= (v != CRB_FILT_ANY);
+        if (!any) continue;
+        if (std::find(seen.begin(), seen.end(), f) == seen.end()) seen.push_back(f);
+    }
+    return static_cast<int>(seen.size());
+}
+
+static int validate_search(const crb_index* ix, int batch, int k, int metric) {
+    if (!ix) return fail("index is NULL");
+    if (batch < 1) return fail("batch must be >= 1 (got %d)", batch);
+    if (k < 1 || k > CRB_MAX_TOPK) return fail("k must be in [1, %d] (got %d)", CRB_MAX_TOPK, k);
+    if (metric != CRB_METRIC_COSINE && metric != CRB_METRIC_IP) return fail("unknown metric %d", metric);
+    return 0;
+}
+
+}  // namespace crb
+
+// =============================================================================================
+// extern "C"
+// =============================================================================================
+using namespace crb;
+
+extern "C" int crb_abi_version(void) { return CRB_ABI_VERSION; }
+extern "C" const char* crb_last_error(void) { return g_err.c_str(); }
+extern "C" int64_t crb_launch_count(void) { return g_launches.load(); }
+
+extern "C" int crb_index_create(crb_index** out, const void* d_rows_f16, const float* d_inv_norm,
+                                const int32_t* d_codes, int64_t n_rows, int32_t dim, int32_t n_keys,
+                                int64_t row_offset, int32_t device) {
+    if (!out) return fail("out is NULL");
+    *out = nullptr;
+    if (n_rows < 0) return fail("n_rows must be >= 0");
+    if (dim < 8 || dim % 8 != 0 || dim > CRB_MAX_DIM)
+        return fail("dim must be a multiple of 8 in [8, %d] (got %d)", CRB_MAX_DIM, dim);
+    if (n_keys < 0 || n_keys > CRB_MAX_KEYS) return fail("n_keys must be in [0, %d]", CRB_MAX_KEYS);
+    if (n_rows > 0 && (!d_rows_f16 || !d_inv_norm)) return fail("rows / inv_norm pointers are NULL");
+    if (n_keys > 0 && n_rows > 0 && !d_codes) return fail("codes pointer is NULL with n_keys > 0");
+    if (reinterpret_cast<uintptr_t>(d_rows_f16) % 16 != 0) return fail("rows must be 16-byte aligned");
+    if (row_offset < 0 || row_offset + n_rows > int64_t(0xffffffffll))
+        return fail("row_offset + n_rows must fit in 32 bits");
+    DeviceGuard guard(device);
+    CRB_CUDA(guard.status);
+    cudaDeviceProp prop;
+    CRB_CUDA(cudaGetDeviceProperties(&prop, device));
+    if (prop.major != 10)
+        return fail("device %d is sm_%d%d; this library is built for sm_100a (B200) only", device,
+                    prop.major, prop.minor);
+    crb_index* ix = new crb_index();
+    ix->rows = static_cast<const __half*>(d_rows_f16);
+    ix->inv_norm = d_inv_norm;
+    ix->codes = d_codes;
+    ix->n_rows = n_rows;
+    ix->dim = dim;
+    ix->n_keys = n_keys;
+    ix->row_offset = row_offset;
+    ix->device = device;
+    ix->sm_count = prop.multiProcessorCount;
+    ix->lanes.resize(std::max(1, env_int("CODERAG_B200_LANES", 4)));
+    *out = ix;
+    return 0;
+}
+
+extern "C" int crb_index_destroy(crb_index* ix) {
+    if (!ix) return 0;
+    DeviceGuard guard(ix->device);
+    for (auto& l : ix->lanes) {
+        if (l.stream) cudaStreamSynchronize(l.stream);
+        if (l.d_ws) cudaFree(l.d_ws);
+        if (l.d_io) cudaFree(l.d_io);
+        if (l.h_pin) cudaFreeHost(l.h_pin);
+        if (l.stream) cudaStreamDestroy(l.stream);
+    }
+    delete ix;
+    return 0;
+}
+
+extern "C" int crb_encode_rows(const float* d_src_f32, void* d_dst_f16, float* d_inv_norm,
+                               int64_t n_rows, int32_t dim, int32_t device, void* stream) {
+    if (dim < 8 || dim % 8 != 0) return fail("dim must be a positive multiple of 8");
+    if (n_rows <= 0) return 0;
+    DeviceGuard guard(device);
+    CRB_CUDA(guard.status);
+    const unsigned blocks = static_cast<unsigned>(std::min<int64_t>((n_rows + 7) / 8, 148 * 16));
+    encode_rows_kernel<<<blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+        d_src_f32, static_cast<__half*>(d_dst_f16), d_inv_norm, n_rows, dim);
+    CRB_LAUNCH_CHECK();
+    return 0;
+}
+
+extern "C" int crb_row_inv_norms(const void* d_rows_f16, float* d_inv_norm, int64_t n_rows,
+                                 int32_t dim, int32_t device, void* stream) {
+    if (dim < 8 || dim % 8 != 0) return fail("dim must be a positive multiple of 8");
+    if (n_rows <= 0) return 0;
+    DeviceGuard guard(device);
+    CRB_CUDA(guard.status);
+    const unsigned blocks = static_cast<unsigned>(std::min<int64_t>((n_rows + 7) / 8, 148 * 16));
+    row_inv_norms_kernel<<<blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+        static_cast<const __half*>(d_rows_f16), d_inv_norm, n_rows, dim);
+    CRB_LAUNCH_CHECK();
+    return 0;
+}
+
+extern "C" size_t crb_workspace_bytes(const crb_index* ix, int32_t batch, int32_t k, int32_t n_filters) {
+    (void)batch; (void)k;
+    if (!ix) return 0;
+    const int lists = std::min<int>(std::max<int>(n_filters, 0), kMaxFilters);
+    return kWsHeaderBytes + kWsCandBytes + size_t(lists) * size_t(list_stride_of(ix)) * 4;
+}
+
+extern "C" int crb_search(crb_index* ix, const float* d_queries, int32_t batch, int32_t k,
+                          int32_t metric, const int32_t* h_filt, float* d_scores, int64_t* d_rows,
+                          int32_t* d_n_valid, uint64_t* d_keys, void* d_workspace,
+                          size_t workspace_bytes, int32_t algo, void* stream) {
+    if (int rc = validate_search(ix, batch, k, metric)) return rc;
+    if (!d_queries || !d_scores || !d_rows || !d_n_valid || !d_workspace)
+        return fail("NULL device pointer passed to crb_search");
+    DeviceGuard guard(ix->device);
+    CRB_CUDA(guard.status);
+    return search_impl(ix, d_queries, batch, k, metric, h_filt, d_scores, d_rows, d_n_valid, d_keys,
+                       d_workspace, workspace_bytes, algo, static_cast<cudaStream_t>(stream));
+}
+
+extern "C" int crb_search_host(crb_index* ix, const float* h_queries, int32_t batch, int32_t k,
+                               int32_t metric, const int32_t* h_filt, float* h_scores,
+                               int64_t* h_rows, int32_t* h_n_valid, int32_t algo) {
+    if (int rc = validate_search(ix, batch, k, metric)) return rc;
+    if (!h_queries || !h_scores || !h_rows || !h_n_valid) return fail("NULL host pointer passed to crb_search_host");
+    DeviceGuard guard(ix->device);
+    CRB_CUDA(guard.status);
+    LaneHold hold{ix, checkout_lane(ix)};
+    Lane* l = hold.lane;
+
+    const size_t q_bytes = size_t(batch) * ix->dim * sizeof(float);
+    const size_t s_bytes = size_t(batch) * k * sizeof(float);
+    const size_t r_bytes = size_t(batch) * k * sizeof(int64_t);
+    const size_t v_bytes = size_t(batch) * sizeof(int32_t);
+    // device io: [queries | rows (8B aligned) | scores | n_valid]; pinned mirrors the same layout
+    const size_t off_rows = round_up(q_bytes, 256);
+    const size_t off_scores = off_rows + round_up(r_bytes, 256);
+    const size_t off_valid = off_scores + round_up(s_bytes, 256);
+    const size_t io_bytes = off_valid + round_up(v_bytes, 256);
+    const size_t ws_bytes = crb_workspace_bytes(ix, batch, k, count_distinct_filters(h_filt, batch, ix->n_keys));
+    if (int rc = lane_reserve(l, ws_bytes, io_bytes, io_bytes)) return rc;
+
+    uint8_t* d_io = static_cast<uint8_t*>(l->d_io);
+    uint8_t* h_io = static_cast<uint8_t*>(l->h_pin);
+    memcpy(h_io, h_queries, q_bytes);
+    CRB_CUDA(cudaMemcpyAsync(d_io, h_io, q_bytes, cudaMemcpyHostToDevice, l->stream));
+    int rc = search_impl(ix, reinterpret_cast<const float*>(d_io), batch, k, metric, h_filt,
+                         reinterpret_cast<float*>(d_io + off_scores),
+                         reinterpret_cast<int64_t*>(d_io + off_rows),
+                         reinterpret_cast<int32_t*>(d_io + off_valid), nullptr, l->d_ws, l->ws_cap,
+                         algo, l->stream);
+    if (rc) { cudaStreamSynchronize(l->stream); return rc; }
+    CRB_CUDA(cudaMemcpyAsync(h_io + off_rows, d_io + off_rows, io_bytes - off_rows, cudaMemcpyDeviceToHost, l->stream));
+    CRB_CUDA(cudaStreamSynchronize(l->stream));
+    memcpy(h_rows, h_io + off_rows, r_bytes);
+    memcpy(h_scores, h_io + off_scores, s_bytes);
+    memcpy(h_n_valid, h_io + off_valid, v_bytes);
+    return 0;
+}
+
+extern "C" int crb_merge_keys(const uint64_t* d_keys_in, int32_t n_lists, int32_t batch, int32_t k,
+                              int32_t metric, const float* d_queries, int32_t dim, float* d_scores,
+                              int64_t* d_rows, int32_t* d_n_valid, uint64_t* d_keys_out,
+                              int32_t device, void* stream) {
+    if (n_lists < 1 || n_lists > 1024) return fail("n_lists must be in [1, 1024]");
+    if (batch < 1) return fail("batch must be >= 1");
+    if (k < 1 || k > CRB_MAX_TOPK) return fail("k must be in [1, %d]", CRB_MAX_TOPK);
+    if (!d_keys_in || !d_scores || !d_rows || !d_n_valid) return fail("NULL pointer passed to crb_merge_keys");
+    if (metric == CRB_METRIC_COSINE && !d_queries) return fail("cosine merge needs the queries");
+    DeviceGuard guard(device);
+    CRB_CUDA(guard.status);
+    merge_keys_kernel<<<batch, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+        d_keys_in, n_lists, batch, k, metric, d_queries, dim, d_scores, d_rows, d_n_valid, d_keys_out);
+    CRB_LAUNCH_CHECK();
+    return 0;
+}
+
+extern "C" int crb_fetch_rows_host(crb_index* ix, const int64_t* h_rows_idx, int32_t n, float* h_out) {
+    if (!ix) return fail("index is NULL");
+    if (n <= 0) return 0;
+    if (!h_rows_idx || !h_out) return fail("NULL pointer passed to crb_fetch_rows_host");
+    for (int i = 0; i < n; ++i)
+        if (h_rows_idx[i] < 0 || h_rows_idx[i] >= ix->n_rows)
+            return fail("row index %lld out of range [0, %lld)", (long long)h_rows_idx[i], (long long)ix->n_rows);
+    DeviceGuard guard(ix->device);
+    CRB_CUDA(guard.status);
+    LaneHold hold{ix, checkout_lane(ix)};
+    Lane* l = hold.lane;
+    const size_t idx_bytes = round_up(size_t(n) * sizeof(int64_t), 256);
+    const size_t out_bytes = size_t(n) * ix->dim * sizeof(float);
+    if (int rc = lane_reserve(l, 0, idx_bytes + out_bytes, idx_bytes + out_bytes)) return rc;
+    uint8_t* d_io = static_cast<uint8_t*>(l->d_io);
+    uint8_t* h_io = static_cast<uint8_t*>(l->h_pin);
+    memcpy(h_io, h_rows_idx, size_t(n) * sizeof(int64_t));
+    CRB_CUDA(cudaMemcpyAsync(d_io, h_io, size_t(n) * sizeof(int64_t), cudaMemcpyHostToDevice, l->stream));
+    const unsigned blocks = static_cast<unsigned>(std::min<int64_t>((int64_t(n) * ix->dim + 255) / 256, 148 * 8));
+    fetch_rows_kernel<<<blocks, 256, 0, l->stream>>>(ix->rows, reinterpret_cast<const int64_t*>(d_io), n,
+                                                     ix->dim, reinterpret_cast<float*>(d_io + idx_bytes));
+    CRB_LAUNCH_CHECK();
+    CRB_CUDA(cudaMemcpyAsync(h_io + idx_bytes, d_io + idx_bytes, out_bytes, cudaMemcpyDeviceToHost, l->stream));
+    CRB_CUDA(cudaStreamSynchronize(l->stream));
+    memcpy(h_out, h_io + idx_bytes, out_bytes);
+    return 0;
+}

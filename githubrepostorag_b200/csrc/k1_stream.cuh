@@ -1,0 +1,298 @@
+// K1 -- HBM-streaming exact scorer with fused per-warp top-k and last-block merge.
+//
+// Replaces the scoring that the reference delegates to Cassandra's SAI ANN
+// (`ORDER BY vector ANN OF ? LIMIT k`, reached from
+// rag_worker/src/worker/services/graph_rag_retrievers.py:104-134) with an exact scan of the
+// fp16 shard resident in HBM.  One warp scores one row at a time with 16-byte coalesced loads
+// (R rows in flight per warp), fp32 accumulation in the library's canonical order
+// (common.cuh), so a K1 score *is* the final score: no rescore pass follows.
+//
+// A launch covers up to kMaxGroups "groups" (blockIdx.y).  A group is up to NQ queries that
+// share one row set: either the whole shard or the survivor list K3 built for their filter.
+// Bound: HBM.  Algorithmic bytes per group = items * dim * 2 (+ 4 B/row inverse norm,
+// + 4 B/survivor list entry).
+#pragma once
+#include "topk.cuh"
+
+namespace crb {
+
+constexpr int kK1Threads = 256;
+constexpr int kK1Warps = kK1Threads / 32;
+constexpr int kK1MaxQ = 4;
+constexpr int kK1MergeLPT = 4;  // last-block merge: lists per thread -> grid.x <= 1024
+constexpr int kK1MaxGridX = kK1Threads * kK1MergeLPT;
+
+struct K1Group {
+    int32_t q_idx[kK1MaxQ];  // query index in the batch, -1 = unused slot
+    int32_t filter;          // -1 = whole shard, else survivor list slot
+};
+
+struct K1Params {
+    const __half* rows;
+    const float* inv_norm;
+    const float* queries;          // [batch, dim] fp32
+    const uint32_t* lists;         // [n_filters, list_stride] local row indices
+    const uint32_t* list_counts;   // [n_filters]
+    uint64_t* cand;                // [groups, NQ, grid.x, k] per-CTA sorted lists (scratch)
+    unsigned* counters;            // [groups] arrival counters, zero between launches
+    float* out_scores;             // [batch, k]
+    int64_t* out_rows;             // [batch, k]
+    int32_t* out_nvalid;           // [batch]
+    uint64_t* out_keys;            // [batch, k] or nullptr
+    int64_t n_rows;
+    int64_t list_stride;
+    uint32_t row_offset;
+    int32_t dim;
+    int32_t k;
+    int32_t metric;
+    K1Group groups[kMaxGroups];
+};
+
+template <int NQ, int CH, int R, int KPL>
+__global__ void __launch_bounds__(kK1Threads)
+k1_stream_kernel(const __grid_constant__ K1Params p) {
+    __shared__ uint64_t xchg[2][32];
+    __shared__ float s_invq;
+    __shared__ int s_last;
+
+    const int lane = threadIdx.x & 31;
+    const int warp = threadIdx.x >> 5;
+    const K1Group& G = p.groups[blockIdx.y];
+    const int chunks = p.dim >> 3;
+    const bool cosine = (p.metric == 0);
+
+    // ---- query chunks this lane needs, in registers ----
+    float qr[NQ][CH][8];
+#pragma unroll
+    for (int q = 0; q < NQ; ++q) {
+#pragma unroll
+        for (int c = 0; c < CH; ++c) {
+            const int ch = lane + 32 * c;
+            if (G.q_idx[q] >= 0 && ch < chunks) {
+                const float4* src = reinterpret_cast<const float4*>(
+                    p.queries + static_cast<int64_t>(G.q_idx[q]) * p.dim + ch * 8);
+                const float4 a = __ldg(src), b = __ldg(src + 1);
+                qr[q][c][0] = a.x; qr[q][c][1] = a.y; qr[q][c][2] = a.z; qr[q][c][3] = a.w;
+                qr[q][c][4] = b.x; qr[q][c][5] = b.y; qr[q][c][6] = b.z; qr[q][c][7] = b.w;
+            } else {
+#pragma unroll
+                for (int e = 0; e < 8; ++e) qr[q][c][e] = 0.f;
+            }
+        }
+    }
+
+    WarpTopK<KPL> top[NQ];
+#pragma unroll
+    for (int q = 0; q < NQ; ++q) top[q].init(p.k, lane);
+
+    // ---- row set of this group ----
+    const bool use_list = G.filter >= 0;
+    int64_t n_items = p.n_rows;
+    const uint32_t* list = nullptr;
+    if (use_list) {
+        const int64_t cnt = static_cast<int64_t>(p.list_counts[G.filter]);
+        n_items = cnt < p.n_rows ? cnt : p.n_rows;
+        list = p.lists + static_cast<int64_t>(G.filter) * p.list_stride;
+    }
+    const int64_t stride = static_cast<int64_t>(gridDim.x) * kK1Warps * R;
+    int64_t item0 = (static_cast<int64_t>(blockIdx.x) * kK1Warps + warp) * R;
+
+    uint32_t idx_next = 0u;
+    if (use_list && lane < R && item0 + lane < n_items) idx_next = list[item0 + lane];
+
+    for (; item0 < n_items; item0 += stride) {
+        const uint32_t idx_cur = idx_next;
+        idx_next = 0u;
+        if (use_list && lane < R && item0 + stride + lane < n_items)
+            idx_next = list[item0 + stride + lane];
+
+        int64_t row[R];
+        bool ok[R];
+#pragma unroll
+        for (int j = 0; j < R; ++j) {
+            ok[j] = (item0 + j) < n_items;
+            const uint32_t li = __shfl_sync(CRB_FULL_MASK, idx_cur, j);
+            row[j] = use_list ? static_cast<int64_t>(li) : (item0 + j);
+            if (!ok[j]) row[j] = 0;
+        }
+
+        uint4 v[R][CH];
+        float invn[R];
+#pragma unroll
+        for (int j = 0; j < R; ++j) {
+            const __half* rp = p.rows + row[j] * p.dim;
+#pragma unroll
+            for (int c = 0; c < CH; ++c) {
+                const int ch = lane + 32 * c;
+                if (ch < chunks) v[j][c] = ld_stream_16(rp + ch * 8);
+            }
+        }
+#pragma unroll
+        for (int j = 0; j < R; ++j) invn[j] = cosine ? __ldg(p.inv_norm + row[j]) : 1.0f;
+
+        float acc[NQ][R];
+#pragma unroll
+        for (int q = 0; q < NQ; ++q)
+#pragma unroll
+            for (int j = 0; j < R; ++j) acc[q][j] = 0.f;
+#pragma unroll
+        for (int c = 0; c < CH; ++c) {
+            if (lane + 32 * c < chunks) {
+#pragma unroll
+                for (int j = 0; j < R; ++j)
+#pragma unroll
+                    for (int q = 0; q < NQ; ++q) acc[q][j] = chunk_fma(v[j][c], qr[q][c], acc[q][j]);
+            }
+        }
+#pragma unroll
+        for (int j = 0; j < R; ++j) {
+            const bool row_ok = ok[j] && !(cosine && invn[j] == 0.f);
+#pragma unroll
+            for (int q = 0; q < NQ; ++q) {
+                const float s = warp_butterfly_sum(acc[q][j]) * invn[j];
+                if (row_ok && G.q_idx[q] >= 0 && s == s) {
+                    const uint64_t key = make_key(s, p.row_offset + static_cast<uint32_t>(row[j]));
+                    if (key > top[q].thr) top[q].insert(key, lane);
+                }
+            }
+        }
+    }
+
+    // ---- per-CTA lists -> scratch ----
+#pragma unroll
+    for (int q = 0; q < NQ; ++q) {
+        if (G.q_idx[q] < 0) continue;
+        uint64_t* out = p.cand +
+            ((static_cast<int64_t>(blockIdx.y) * NQ + q) * gridDim.x + blockIdx.x) * p.k;
+        block_extract_topk<KPL>(top[q], p.k, out, xchg, lane, warp, kK1Warps);
+    }
+
+    // ---- the last CTA of the group merges all per-CTA lists and writes the results ----
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence();
+        const unsigned t = atomicAdd(&p.counters[blockIdx.y], 1u);
+        s_last = (t == gridDim.x - 1) ? 1 : 0;
+    }
+    __syncthreads();
+    if (!s_last) return;
+    __threadfence();
+
+#pragma unroll
+    for (int q = 0; q < NQ; ++q) {
+        const int qi = G.q_idx[q];
+        if (qi < 0) continue;
+        if (warp == 0) {
+            const float iq = cosine ? warp_inv_qnorm(p.queries + static_cast<int64_t>(qi) * p.dim, p.dim, lane) : 1.0f;
+            if (lane == 0) s_invq = iq;
+        }
+        __syncthreads();
+        TopKSink sink;
+        sink.scores = p.out_scores + static_cast<int64_t>(qi) * p.k;
+        sink.rows = p.out_rows + static_cast<int64_t>(qi) * p.k;
+        sink.n_valid = p.out_nvalid + qi;
+        sink.keys = p.out_keys ? p.out_keys + static_cast<int64_t>(qi) * p.k : nullptr;
+        sink.scale = s_invq;
+        const uint64_t* lists = p.cand + (static_cast<int64_t>(blockIdx.y) * NQ + q) * gridDim.x * p.k;
+        block_merge_sorted_lists<kK1MergeLPT>(lists, gridDim.x, p.k, p.k, sink, xchg, lane, warp, kK1Warps);
+    }
+    if (threadIdx.x == 0) p.counters[blockIdx.y] = 0u;
+}
+
+// Generic-dimension variant (dim up to CRB_MAX_DIM, one query per group): the query lives in
+// shared memory and chunks are walked with a runtime loop; same canonical summation order.
+template <int R, int KPL>
+__global__ void __launch_bounds__(kK1Threads)
+k1_stream_generic_kernel(const __grid_constant__ K1Params p) {
+    extern __shared__ float s_q[];  // [dim]
+    __shared__ uint64_t xchg[2][32];
+    __shared__ float s_invq;
+    __shared__ int s_last;
+
+    const int lane = threadIdx.x & 31;
+    const int warp = threadIdx.x >> 5;
+    const K1Group& G = p.groups[blockIdx.y];
+    const int chunks = p.dim >> 3;
+    const bool cosine = (p.metric == 0);
+    const int qi = G.q_idx[0];
+
+    for (int i = threadIdx.x; i < p.dim; i += kK1Threads)
+        s_q[i] = p.queries[static_cast<int64_t>(qi) * p.dim + i];
+    __syncthreads();
+
+    WarpTopK<KPL> top;
+    top.init(p.k, lane);
+
+    const bool use_list = G.filter >= 0;
+    int64_t n_items = p.n_rows;
+    const uint32_t* list = nullptr;
+    if (use_list) {
+        const int64_t cnt = static_cast<int64_t>(p.list_counts[G.filter]);
+        n_items = cnt < p.n_rows ? cnt : p.n_rows;
+        list = p.lists + static_cast<int64_t>(G.filter) * p.list_stride;
+    }
+    const int64_t stride = static_cast<int64_t>(gridDim.x) * kK1Warps * R;
+    for (int64_t item0 = (static_cast<int64_t>(blockIdx.x) * kK1Warps + warp) * R; item0 < n_items;
+         item0 += stride) {
+        int64_t row[R];
+        bool ok[R];
+        float acc[R];
+#pragma unroll
+        for (int j = 0; j < R; ++j) {
+            ok[j] = (item0 + j) < n_items;
+            row[j] = ok[j] ? (use_list ? static_cast<int64_t>(list[item0 + j]) : item0 + j) : 0;
+            acc[j] = 0.f;
+        }
+        for (int ch = lane; ch < chunks; ch += 32) {
+            uint4 v[R];
+#pragma unroll
+            for (int j = 0; j < R; ++j) v[j] = ld_stream_16(p.rows + row[j] * p.dim + ch * 8);
+            float q8[8];
+            const float4 a = *reinterpret_cast<const float4*>(s_q + ch * 8);
+            const float4 b = *reinterpret_cast<const float4*>(s_q + ch * 8 + 4);
+            q8[0] = a.x; q8[1] = a.y; q8[2] = a.z; q8[3] = a.w;
+            q8[4] = b.x; q8[5] = b.y; q8[6] = b.z; q8[7] = b.w;
+#pragma unroll
+            for (int j = 0; j < R; ++j) acc[j] = chunk_fma(v[j], q8, acc[j]);
+        }
+#pragma unroll
+        for (int j = 0; j < R; ++j) {
+            const float invn = cosine ? __ldg(p.inv_norm + row[j]) : 1.0f;
+            const float s = warp_butterfly_sum(acc[j]) * invn;
+            if (ok[j] && !(cosine && invn == 0.f) && s == s) {
+                const uint64_t key = make_key(s, p.row_offset + static_cast<uint32_t>(row[j]));
+                if (key > top.thr) top.insert(key, lane);
+            }
+        }
+    }
+
+    uint64_t* out = p.cand + (static_cast<int64_t>(blockIdx.y) * gridDim.x + blockIdx.x) * p.k;
+    block_extract_topk<KPL>(top, p.k, out, xchg, lane, warp, kK1Warps);
+
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence();
+        const unsigned t = atomicAdd(&p.counters[blockIdx.y], 1u);
+        s_last = (t == gridDim.x - 1) ? 1 : 0;
+    }
+    __syncthreads();
+    if (!s_last) return;
+    __threadfence();
+
+    if (warp == 0) {
+        const float iq = cosine ? warp_inv_qnorm(s_q, p.dim, lane) : 1.0f;
+        if (lane == 0) s_invq = iq;
+    }
+    __syncthreads();
+    TopKSink sink;
+    sink.scores = p.out_scores + static_cast<int64_t>(qi) * p.k;
+    sink.rows = p.out_rows + static_cast<int64_t>(qi) * p.k;
+    sink.n_valid = p.out_nvalid + qi;
+    sink.keys = p.out_keys ? p.out_keys + static_cast<int64_t>(qi) * p.k : nullptr;
+    sink.scale = s_invq;
+    const uint64_t* lists = p.cand + static_cast<int64_t>(blockIdx.y) * gridDim.x * p.k;
+    block_merge_sorted_lists<kK1MergeLPT>(lists, gridDim.x, p.k, p.k, sink, xchg, lane, warp, kK1Warps);
+    if (threadIdx.x == 0) p.counters[blockIdx.y] = 0u;
+}
+
+}  // namespace crb

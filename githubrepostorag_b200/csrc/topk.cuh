@@ -1,0 +1,151 @@
+// Top-k primitives: per-warp running lists, block extraction, S-way merge of sorted lists.
+#pragma once
+#include "common.cuh"
+
+namespace crb {
+
+// Running top-k of one warp for one query.  Slot s (= lane + 32*i) is live when s < k.
+// The list is unsorted; `thr` is the smallest live slot (0 while any live slot is empty), so
+// "key > thr" is the warp-uniform admission test.
+template <int KPL>
+struct WarpTopK {
+    uint64_t slot[KPL];
+    uint64_t thr;
+
+    CRB_DEVINL void init(int k, int lane) {
+#pragma unroll
+        for (int i = 0; i < KPL; ++i) slot[i] = (lane + 32 * i < k) ? 0ull : ~0ull;
+        thr = 0ull;
+    }
+    // Warp-uniform call with key > thr: replace the smallest live slot.
+    CRB_DEVINL void insert(uint64_t key, int lane) {
+        int which = -1;
+#pragma unroll
+        for (int i = 0; i < KPL; ++i)
+            if (slot[i] == thr) which = i;
+        const unsigned holders = __ballot_sync(CRB_FULL_MASK, which >= 0);
+        const int owner = __ffs(holders) - 1;
+        if (lane == owner) {
+#pragma unroll
+            for (int i = 0; i < KPL; ++i)
+                if (i == which) slot[i] = key;
+        }
+        uint64_t m = slot[0];
+#pragma unroll
+        for (int i = 1; i < KPL; ++i) m = slot[i] < m ? slot[i] : m;
+        thr = warp_min_u64(m);
+    }
+    CRB_DEVINL void retire_dead_slots() {
+#pragma unroll
+        for (int i = 0; i < KPL; ++i)
+            if (slot[i] == ~0ull) slot[i] = 0ull;
+    }
+    CRB_DEVINL uint64_t local_max() const {
+        uint64_t m = slot[0];
+#pragma unroll
+        for (int i = 1; i < KPL; ++i) m = slot[i] > m ? slot[i] : m;
+        return m;
+    }
+    CRB_DEVINL void remove(uint64_t key) {
+#pragma unroll
+        for (int i = 0; i < KPL; ++i)
+            if (slot[i] == key) slot[i] = 0ull;
+    }
+};
+
+// Block-wide maximum of one u64 per thread.  `xchg` is a [2][32] shared array, `round` picks
+// the buffer so consecutive calls need only one barrier each.
+CRB_DEVINL uint64_t block_max_u64(uint64_t v, uint64_t (*xchg)[32], int round, int lane, int warp,
+                                  int nwarps) {
+    const uint64_t wm = warp_max_u64(v);
+    if (lane == 0) xchg[round & 1][warp] = wm;
+    __syncthreads();
+    const uint64_t o = (lane < nwarps) ? xchg[round & 1][lane] : 0ull;
+    return warp_max_u64(o);
+}
+
+// Merge the per-warp lists of a block into k keys, descending, written by thread 0 to
+// `out[0..k)` (zero padded).  Keys are unique (they embed the row) so each round's winner is
+// held by exactly one thread.
+template <int KPL>
+CRB_DEVINL void block_extract_topk(WarpTopK<KPL>& w, int k, uint64_t* __restrict__ out,
+                                   uint64_t (*xchg)[32], int lane, int warp, int nwarps) {
+    w.retire_dead_slots();
+    int r = 0;
+    for (; r < k; ++r) {
+        const uint64_t best = block_max_u64(w.local_max(), xchg, r, lane, warp, nwarps);
+        if (best == 0ull) break;
+        w.remove(best);
+        if (threadIdx.x == 0) out[r] = best;
+    }
+    if (threadIdx.x == 0)
+        for (; r < k; ++r) out[r] = 0ull;
+    __syncthreads();
+}
+
+// Output of one finished query: scores (times inv_qnorm), global rows, n_valid, keys.
+struct TopKSink {
+    float* scores;      // [k]
+    int64_t* rows;      // [k]
+    int32_t* n_valid;   // [1]
+    uint64_t* keys;     // [k] or nullptr
+    float scale;        // 1/||q|| for cosine, 1 for inner product
+    CRB_DEVINL void emit(int r, uint64_t key) const {
+        if (key != 0ull) {
+            scores[r] = key_score(key) * scale;
+            rows[r] = static_cast<int64_t>(key_row(key));
+        } else {
+            scores[r] = __uint_as_float(0xff800000u);  // -inf
+            rows[r] = -1;
+        }
+        if (keys) keys[r] = key;
+    }
+};
+
+// S-way merge of `n_lists` descending lists of k keys (list l starts at lists + l*stride) by k
+// rounds of "best head wins".  Thread t owns lists t, t+T, ...; LPT bounds lists per thread.
+// Heads are read with ld.cg (they were written by other CTAs of the same grid).
+template <int LPT>
+CRB_DEVINL void block_merge_sorted_lists(const uint64_t* __restrict__ lists, int n_lists, int k,
+                                         int64_t stride, const TopKSink& sink,
+                                         uint64_t (*xchg)[32], int lane, int warp, int nwarps) {
+    const int T = nwarps * 32;
+    uint64_t head[LPT], nxt[LPT];
+    int pos[LPT];
+#pragma unroll
+    for (int j = 0; j < LPT; ++j) {
+        const int l = threadIdx.x + j * T;
+        pos[j] = 0;
+        head[j] = 0ull;
+        nxt[j] = 0ull;
+        if (l < n_lists) {
+            head[j] = ld_cg_u64(lists + l * stride);
+            if (k > 1) nxt[j] = ld_cg_u64(lists + l * stride + 1);
+        }
+    }
+    int r = 0;
+    for (; r < k; ++r) {
+        uint64_t m = head[0];
+#pragma unroll
+        for (int j = 1; j < LPT; ++j) m = head[j] > m ? head[j] : m;
+        const uint64_t best = block_max_u64(m, xchg, r, lane, warp, nwarps);
+        if (best == 0ull) break;
+#pragma unroll
+        for (int j = 0; j < LPT; ++j) {
+            if (head[j] == best) {
+                const int l = threadIdx.x + j * T;
+                head[j] = nxt[j];
+                pos[j] += 1;
+                nxt[j] = (pos[j] + 1 < k) ? ld_cg_u64(lists + l * stride + pos[j] + 1) : 0ull;
+            }
+        }
+        if (threadIdx.x == 0) sink.emit(r, best);
+    }
+    if (threadIdx.x == 0) {
+        *sink.n_valid = r;
+        for (; r < k; ++r) sink.emit(r, 0ull);
+    }
+    __syncthreads();
+}
+
+}  // namespace crb

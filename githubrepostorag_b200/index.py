@@ -1,0 +1,279 @@
+"""Device-resident corpus shard and the host half of the search call.
+
+A :class:`DeviceShard` is what one ``LCCassandra(table_name=...)`` store stands for in the
+reference (``rag_worker/src/worker/services/graph_rag_retrievers.py:68-80``): the rows of one
+embeddings table (``helm/templates/cassandra-initdb-configmap.yaml:86-102``) laid out in HBM as
+
+* ``rows``      fp16 ``[n_rows, dim]`` row-major (the north star's corpus dtype),
+* ``inv_norm``  fp32 ``[n_rows]``,
+* ``codes``     int32 ``[n_keys, n_rows]`` dictionary codes of the filterable ``metadata_s`` entries.
+
+torch owns the device memory and streams; every computation goes through the C ABI
+(``include/coderag_b200.h``) by raw pointer.  There is no CPU fallback.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import threading
+from typing import Dict, Iterable, List, Mapping, Optional, Sequence, Tuple
+
+import numpy as np
+import torch
+
+from . import _native as N
+
+UPLOAD_BLOCK_ROWS = 1 << 18
+
+
+def _ptr(t: Optional[torch.Tensor]) -> Optional[int]:
+    return None if t is None else t.data_ptr()
+
+
+def _np_ptr(a: Optional[np.ndarray]):
+    return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+class MetadataDictionary:
+    """Dictionary encoding of the filterable metadata keys (one int32 code per key per row).
+
+    The reference stores every metadata value as text in ``metadata_s MAP<TEXT,TEXT>``
+    (``ingest/src/app/services/vector_write_service.py:45-98``) and filters by equality on the
+    allow-listed keys (``:28-34,143``).  Values are coerced with ``str()`` exactly as the writer
+    does; a row lacking a key gets ``CODE_MISSING`` and can never match a filter on it.
+    """
+
+    def __init__(self, keys: Sequence[str]):
+        if len(keys) > N.MAX_KEYS:
+            raise ValueError(f"at most {N.MAX_KEYS} filterable keys (got {len(keys)})")
+        self.keys: List[str] = list(keys)
+        self._pos = {k: i for i, k in enumerate(self.keys)}
+        self.values: List[Dict[str, int]] = [dict() for _ in self.keys]
+
+    @property
+    def n_keys(self) -> int:
+        return len(self.keys)
+
+    def encode_row(self, metadata: Mapping[str, object]) -> List[int]:
+        out = []
+        for i, k in enumerate(self.keys):
+            v = metadata.get(k)
+            if v is None:
+                out.append(N.CODE_MISSING)
+                continue
+            table = self.values[i]
+            out.append(table.setdefault(str(v), len(table)))
+        return out
+
+    def encode_rows(self, metadatas: Sequence[Mapping[str, object]]) -> np.ndarray:
+        codes = np.empty((self.n_keys, len(metadatas)), dtype=np.int32)
+        for r, md in enumerate(metadatas):
+            codes[:, r] = self.encode_row(md)
+        return codes
+
+    def register_vocab(self, key: str, values: Sequence[str]) -> None:
+        """Pre-register values so code ``i`` means ``values[i]`` (synthetic corpora)."""
+        table = self.values[self._pos[key]]
+        for v in values:
+            table.setdefault(str(v), len(table))
+
+    def encode_filter(self, flt: Optional[Mapping[str, object]]) -> np.ndarray:
+        """``{key: value}`` (AND of equalities, the only shape the reference emits:
+        ``agent_graph.py:198-239,357-364,532-534``) -> int32 ``[n_keys]``.  An unknown key or an
+        unknown value can match no row, as with Cassandra's ``metadata_s['k']='v'``."""
+        row = np.full(self.n_keys, N.FILT_ANY, dtype=np.int32)
+        if not flt:
+            return row
+        for k, v in flt.items():
+            i = self._pos.get(k)
+            if i is None or v is None:
+                row[:] = N.FILT_IMPOSSIBLE
+                return row
+            code = self.values[i].get(str(v))
+            row[i] = N.FILT_IMPOSSIBLE if code is None else code
+        return row
+
+
+class DeviceShard:
+    """One row-shard of a corpus resident on one GPU."""
+
+    def __init__(self, rows: torch.Tensor, inv_norm: torch.Tensor, codes: Optional[torch.Tensor],
+                 row_offset: int = 0):
+        lib = N.load()
+        if not rows.is_cuda or rows.dtype != torch.float16 or rows.dim() != 2 or not rows.is_contiguous():
+            raise ValueError("rows must be a contiguous fp16 CUDA tensor [n_rows, dim]")
+        n_rows, dim = rows.shape
+        if inv_norm.dtype != torch.float32 or inv_norm.numel() != n_rows or not inv_norm.is_cuda:
+            raise ValueError("inv_norm must be fp32 CUDA [n_rows]")
+        n_keys = 0
+        if codes is not None:
+            if codes.dtype != torch.int32 or codes.dim() != 2 or codes.shape[1] != n_rows or not codes.is_contiguous():
+                raise ValueError("codes must be a contiguous int32 CUDA tensor [n_keys, n_rows]")
+            n_keys = codes.shape[0]
+        self.rows, self.inv_norm, self.codes = rows, inv_norm, codes
+        self.n_rows, self.dim, self.n_keys = int(n_rows), int(dim), int(n_keys)
+        self.row_offset = int(row_offset)
+        self.device = rows.device
+        handle = C.c_void_p()
+        N.check(lib.crb_index_create(C.byref(handle), _ptr(rows), _ptr(inv_norm), _ptr(codes),
+                                     self.n_rows, self.dim, self.n_keys, self.row_offset,
+                                     self.device.index or 0))
+        self._h = handle
+        self._lib = lib
+        self._ws_lock = threading.Lock()
+        self._ws: Optional[torch.Tensor] = None
+
+    # ---- construction ------------------------------------------------------------------
+    @classmethod
+    def from_host(cls, embeddings: np.ndarray, codes: Optional[np.ndarray] = None, *,
+                  device: int | torch.device = 0, row_offset: int = 0) -> "DeviceShard":
+        """Upload host rows.  fp32 input is rounded to fp16 on the device (``crb_encode_rows``);
+        fp16 input is copied as is and its inverse norms are computed on the device."""
+        lib = N.load()
+        dev = torch.device("cuda", device) if isinstance(device, int) else device
+        emb = np.ascontiguousarray(embeddings)
+        if emb.ndim != 2:
+            raise ValueError("embeddings must be [n_rows, dim]")
+        n, d = emb.shape
+        rows = torch.empty((n, d), dtype=torch.float16, device=dev)
+        inv = torch.empty((n,), dtype=torch.float32, device=dev)
+        stream = torch.cuda.current_stream(dev).cuda_stream
+        for lo in range(0, n, UPLOAD_BLOCK_ROWS):
+            hi = min(n, lo + UPLOAD_BLOCK_ROWS)
+            blk = torch.from_numpy(emb[lo:hi])
+            if emb.dtype == np.float16:
+                rows[lo:hi].copy_(blk, non_blocking=False)
+            elif emb.dtype == np.float32:
+                stage = blk.to(dev)
+                N.check(lib.crb_encode_rows(stage.data_ptr(), rows[lo:hi].data_ptr(), inv[lo:hi].data_ptr(),
+                                            hi - lo, d, dev.index or 0, stream))
+                torch.cuda.current_stream(dev).synchronize()
+            else:
+                raise ValueError("embeddings must be float16 or float32")
+        if emb.dtype == np.float16 and n > 0:
+            N.check(lib.crb_row_inv_norms(rows.data_ptr(), inv.data_ptr(), n, d, dev.index or 0, stream))
+        codes_t = None
+        if codes is not None and codes.shape[0] > 0:
+            codes_t = torch.from_numpy(np.ascontiguousarray(codes, dtype=np.int32)).to(dev)
+        torch.cuda.current_stream(dev).synchronize()
+        return cls(rows, inv, codes_t, row_offset)
+
+    @classmethod
+    def from_device(cls, rows: torch.Tensor, codes: Optional[torch.Tensor] = None, *,
+                    row_offset: int = 0) -> "DeviceShard":
+        """Wrap fp16 rows already in HBM; computes the inverse norms on the device."""
+        lib = N.load()
+        n, d = rows.shape
+        inv = torch.empty((n,), dtype=torch.float32, device=rows.device)
+        if n > 0:
+            N.check(lib.crb_row_inv_norms(rows.data_ptr(), inv.data_ptr(), n, d, rows.device.index or 0,
+                                          torch.cuda.current_stream(rows.device).cuda_stream))
+        return cls(rows, inv, codes, row_offset)
+
+    def close(self) -> None:
+        if getattr(self, "_h", None):
+            self._lib.crb_index_destroy(self._h)
+            self._h = None
+
+    def __del__(self):  # pragma: no cover
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # ---- search -------------------------------------------------------------------------
+    @staticmethod
+    def _metric(metric: str | int) -> int:
+        if metric in (N.METRIC_COSINE, "cosine", "default", "cos"):
+            return N.METRIC_COSINE
+        if metric in (N.METRIC_IP, "ip", "dot_product", "dot"):
+            return N.METRIC_IP
+        raise ValueError(f"unsupported metric {metric!r} (cosine and inner product only)")
+
+    def _filt(self, filt: Optional[np.ndarray], batch: int) -> Optional[np.ndarray]:
+        if filt is None or self.n_keys == 0:
+            if filt is not None and self.n_keys == 0 and np.any(np.asarray(filt) != N.FILT_ANY):
+                raise ValueError("filter given but the shard has no filterable keys")
+            return None
+        f = np.ascontiguousarray(filt, dtype=np.int32)
+        if f.shape != (batch, self.n_keys):
+            raise ValueError(f"filt must be [{batch}, {self.n_keys}] (got {f.shape})")
+        return f
+
+    def search_host(self, queries: np.ndarray, k: int, *, metric: str | int = "cosine",
+                    filt: Optional[np.ndarray] = None, algo: int = 0
+                    ) -> Tuple[np.ndarray, np.ndarray, np.ndarray]:
+        """Host buffers in, host buffers out (``crb_search_host``): the per-``invoke`` call."""
+        q = np.ascontiguousarray(queries, dtype=np.float32)
+        if q.ndim == 1:
+            q = q[None, :]
+        if q.shape[1] != self.dim:
+            raise ValueError(f"query dimension {q.shape[1]} != index dimension {self.dim}")
+        b = q.shape[0]
+        f = self._filt(filt, b)
+        scores = np.empty((b, k), dtype=np.float32)
+        rows = np.empty((b, k), dtype=np.int64)
+        n_valid = np.empty((b,), dtype=np.int32)
+        N.check(self._lib.crb_search_host(self._h, _np_ptr(q), b, k, self._metric(metric), _np_ptr(f),
+                                          _np_ptr(scores), _np_ptr(rows), _np_ptr(n_valid), algo))
+        return scores, rows, n_valid
+
+    def workspace_bytes(self, batch: int, k: int, n_filters: int) -> int:
+        return int(self._lib.crb_workspace_bytes(self._h, batch, k, n_filters))
+
+    def new_workspace(self, batch: int, k: int, n_filters: int) -> torch.Tensor:
+        """Zero-filled scratch for :meth:`search_device` (the header must start at zero)."""
+        return torch.zeros(self.workspace_bytes(batch, k, n_filters), dtype=torch.uint8, device=self.device)
+
+    def search_device(self, queries: torch.Tensor, k: int, *, metric: str | int = "cosine",
+                      filt: Optional[np.ndarray] = None, algo: int = 0,
+                      out: Optional[Tuple[torch.Tensor, torch.Tensor, torch.Tensor]] = None,
+                      keys_out: Optional[torch.Tensor] = None,
+                      workspace: Optional[torch.Tensor] = None):
+        """Device-resident queries and results, asynchronous on torch's current stream."""
+        if not queries.is_cuda or queries.dtype != torch.float32 or not queries.is_contiguous():
+            raise ValueError("queries must be a contiguous fp32 CUDA tensor [batch, dim]")
+        b, d = queries.shape
+        if d != self.dim:
+            raise ValueError(f"query dimension {d} != index dimension {self.dim}")
+        f = self._filt(filt, b)
+        if out is None:
+            out = (torch.empty((b, k), dtype=torch.float32, device=self.device),
+                   torch.empty((b, k), dtype=torch.int64, device=self.device),
+                   torch.empty((b,), dtype=torch.int32, device=self.device))
+        scores, rows, n_valid = out
+        if workspace is None:
+            nf = 0 if f is None else len({tuple(r) for r in f.tolist() if any(c != N.FILT_ANY for c in r)})
+            need = self.workspace_bytes(b, k, nf)
+            with self._ws_lock:
+                if self._ws is None or self._ws.numel() < need:
+                    self._ws = torch.zeros(need, dtype=torch.uint8, device=self.device)
+                workspace = self._ws
+        stream = torch.cuda.current_stream(self.device).cuda_stream
+        N.check(self._lib.crb_search(self._h, queries.data_ptr(), b, k, self._metric(metric), _np_ptr(f),
+                                     scores.data_ptr(), rows.data_ptr(), n_valid.data_ptr(), _ptr(keys_out),
+                                     workspace.data_ptr(), workspace.numel(), algo, stream))
+        return scores, rows, n_valid
+
+    def fetch_rows(self, local_rows: Sequence[int]) -> np.ndarray:
+        idx = np.ascontiguousarray(local_rows, dtype=np.int64)
+        out = np.empty((len(idx), self.dim), dtype=np.float32)
+        if len(idx):
+            N.check(self._lib.crb_fetch_rows_host(self._h, _np_ptr(idx), len(idx), _np_ptr(out)))
+        return out
+
+
+def merge_keys(keys_in: torch.Tensor, queries: torch.Tensor, k: int, metric: str | int = "cosine"):
+    """Cross-shard merge of all-gathered keys ``[n_lists, batch, k]`` (``crb_merge_keys``)."""
+    lib = N.load()
+    n_lists, b, kk = keys_in.shape
+    assert kk == k and keys_in.dtype == torch.int64 or keys_in.dtype == torch.uint64
+    dev = keys_in.device
+    scores = torch.empty((b, k), dtype=torch.float32, device=dev)
+    rows = torch.empty((b, k), dtype=torch.int64, device=dev)
+    n_valid = torch.empty((b,), dtype=torch.int32, device=dev)
+    keys_out = torch.empty((b, k), dtype=torch.int64, device=dev)
+    N.check(lib.crb_merge_keys(keys_in.data_ptr(), n_lists, b, k, DeviceShard._metric(metric),
+                               queries.data_ptr(), queries.shape[1], scores.data_ptr(), rows.data_ptr(),
+                               n_valid.data_ptr(), keys_out.data_ptr(), dev.index or 0,
+                               torch.cuda.current_stream(dev).cuda_stream))
+    return scores, rows, n_valid, keys_out

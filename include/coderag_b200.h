@@ -1,0 +1,139 @@
+/*
+ * coderag_b200.h -- C ABI of the B200-native retrieval hot path for CodeRAG.
+ *
+ * The reference (jasonbuchanan145/GithubReposToRag) has no FFI of its own: its boundary is a
+ * duck-typed Python vector-store object.  These entry points are what a
+ * ctypes/cffi binding behind that object binds; every one cites the reference interface it
+ * stands in for.  Plain pointers and sizes only -- no torch, no CUDA types (streams travel as
+ * `void*` holding a `cudaStream_t`).
+ *
+ * Conventions
+ *   - every function returns 0 on success, non-zero on failure; `crb_last_error()` returns the
+ *     calling thread's last message (the reference propagates Python exceptions,
+ *     rag_worker/src/worker/services/agent_graph.py:276-278 -- the Python host raises
+ *     RuntimeError with this text);
+ *   - fewer than k survivors is NOT an error: the short list is returned, padded with
+ *     score = -inf, row = -1, and `n_valid[b]` tells how many slots are real (Cassandra LIMIT
+ *     semantics; agent_graph.py:249,253 tolerate short/empty lists);
+ *   - `d_` pointers are device memory on the index's device, `h_` pointers are host memory;
+ *   - an index borrows the corpus buffers for its lifetime (the store object owns them,
+ *     mirroring GraphRetrieverFactory.close(), graph_rag_retrievers.py:136-140);
+ *   - all entry points are re-entrant: up to `max_jobs=10` worker threads share one store
+ *     (rag_worker/src/worker/worker.py:136-139,185).
+ */
+#ifndef CODERAG_B200_H
+#define CODERAG_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define CRB_ABI_VERSION 1
+
+/* similarity modes: VectorStoreQueryMode.DEFAULT (cosine; the SAI index is created with
+ * similarity_function cosine, helm/templates/cassandra-initdb-configmap.yaml:99-102) and
+ * inner product. */
+#define CRB_METRIC_COSINE 0
+#define CRB_METRIC_IP 1
+
+/* filter codes in a `filt[B][n_keys]` table */
+#define CRB_FILT_ANY (-1)        /* key not constrained */
+#define CRB_FILT_IMPOSSIBLE (-2) /* unknown key or value: no row can match (a Cassandra row
+                                    lacking the map entry never matches metadata_s['k']='v') */
+#define CRB_CODE_MISSING (-1)    /* row has no value for this key */
+
+#define CRB_MAX_KEYS 8    /* filterable metadata keys per index */
+#define CRB_MAX_TOPK 128  /* largest k (reference uses k <= 10, agent_graph.py:171-176) */
+#define CRB_MAX_DIM 4096
+
+typedef struct crb_index crb_index;
+
+int crb_abi_version(void);
+const char *crb_last_error(void);
+
+/* ---- corpus side: what LCCassandra(table) stands for (graph_rag_retrievers.py:68-80) and the
+ *      row layout of helm/templates/cassandra-initdb-configmap.yaml:86-102 ------------------ */
+
+/* Wrap a resident shard: rows fp16 [n_rows, dim] row-major (dim % 8 == 0, 16-byte aligned),
+ * inv_norm fp32 [n_rows] (1/||row||, 0 for a zero row), codes int32 [n_keys, n_rows]
+ * (dictionary codes of the filterable metadata_s entries, CRB_CODE_MISSING where absent; may
+ * be NULL when n_keys == 0).  `row_offset` is the global index of local row 0 (row-sharding).
+ * `device` is the CUDA ordinal that owns the buffers. */
+int crb_index_create(crb_index **out, const void *d_rows_f16, const float *d_inv_norm,
+                     const int32_t *d_codes, int64_t n_rows, int32_t dim, int32_t n_keys,
+                     int64_t row_offset, int32_t device);
+int crb_index_destroy(crb_index *index);
+
+/* Ingest-side conversion (stands for the embedding column write of
+ * ingest/src/app/services/vector_write_service.py:158-159): fp32 rows -> fp16 rows and their
+ * inverse norms (norm taken of the fp16-rounded row, which is the corpus searched). */
+int crb_encode_rows(const float *d_src_f32, void *d_dst_f16, float *d_inv_norm, int64_t n_rows,
+                    int32_t dim, int32_t device, void *stream);
+/* Inverse norms of rows that are already fp16. */
+int crb_row_inv_norms(const void *d_rows_f16, float *d_inv_norm, int64_t n_rows, int32_t dim,
+                      int32_t device, void *stream);
+
+/* ---- query side: VectorStore.query(VectorStoreQuery) -> VectorStoreQueryResult
+ *      (rest_api/src/app/health.py:104-107) and
+ *      LCCassandra.similarity_search_with_embedding_id_by_vector(embedding, k, filter)
+ *      (call sites graph_rag_retrievers.py:104-134 via GraphRetriever.invoke,
+ *      agent_graph.py:249,268) ----------------------------------------------------------- */
+
+/* Scratch bytes `crb_search` needs for a batch of `batch` queries with `n_filters` distinct
+ * non-trivial filters. */
+size_t crb_workspace_bytes(const crb_index *index, int32_t batch, int32_t k, int32_t n_filters);
+
+/* Top-k search, queries and results resident on the device; asynchronous on `stream`.
+ *   d_queries  fp32 [batch, dim]
+ *   h_filt     int32 [batch, n_keys] on the HOST (NULL = no filter): AND of equalities, one
+ *              code per key (CRB_FILT_ANY / CRB_FILT_IMPOSSIBLE as above).  Rows with the same
+ *              filter share one survivor list ("many q, one filter"); distinct filters on one
+ *              query vector are the graph-retriever adjacent() fan-out ("one q, many filters").
+ *   d_scores   fp32 [batch, k]   similarity, descending (raw cosine or inner product)
+ *   d_rows     int64 [batch, k]  global row index (row_offset + local), -1 padding
+ *   d_n_valid  int32 [batch]
+ *   d_keys     uint64 [batch, k] or NULL: order-preserving (score, row) keys, the payload of
+ *              the cross-shard all-gather (see crb_merge_keys)
+ *   d_workspace / workspace_bytes  scratch of at least crb_workspace_bytes(...).  Its first
+ *              4096 bytes must be ZERO before the first call that uses it (cudaMemset /
+ *              torch.zeros); the kernels leave them zero again.  One workspace serves one call
+ *              at a time (concurrent calls need one workspace each).
+ *   algo       0 = choose by batch size, 1 = force the streaming kernel, 2 = force the
+ *              tensor-core kernel */
+int crb_search(crb_index *index, const float *d_queries, int32_t batch, int32_t k, int32_t metric,
+               const int32_t *h_filt, float *d_scores, int64_t *d_rows, int32_t *d_n_valid,
+               uint64_t *d_keys, void *d_workspace, size_t workspace_bytes, int32_t algo,
+               void *stream);
+
+/* Same search through HOST buffers: copies the queries in, runs, copies the results out and
+ * returns when they are in the caller's arrays.  This is the call the Python store makes per
+ * retriever.invoke(); it uses an internal pool of streams/staging buffers, one per concurrent
+ * caller. */
+int crb_search_host(crb_index *index, const float *h_queries, int32_t batch, int32_t k,
+                    int32_t metric, const int32_t *h_filt, float *h_scores, int64_t *h_rows,
+                    int32_t *h_n_valid, int32_t algo);
+
+/* Cross-shard merge (no reference counterpart in-tree: the reference runs `replicas: 1`,
+ * helm/values.yaml:113; this is the k-way merge a row-sharded store needs after the
+ * all-gather of per-shard keys).  d_keys_in uint64 [n_lists, batch, k] -> the best k per
+ * query.  d_queries (fp32 [batch, dim]) supplies the query norm for cosine scores. */
+int crb_merge_keys(const uint64_t *d_keys_in, int32_t n_lists, int32_t batch, int32_t k,
+                   int32_t metric, const float *d_queries, int32_t dim, float *d_scores,
+                   int64_t *d_rows, int32_t *d_n_valid, uint64_t *d_keys_out, int32_t device,
+                   void *stream);
+
+/* Fetch stored rows as fp32 (the `embedding` member of the (Document, embedding, id) triples
+ * LCCassandra returns; graph-retriever re-scores from it).  h_rows_idx are LOCAL row indices. */
+int crb_fetch_rows_host(crb_index *index, const int64_t *h_rows_idx, int32_t n, float *h_out);
+
+/* Number of kernels this library has launched in the calling process (bench.py's
+ * `gpu_launches`). */
+int64_t crb_launch_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CODERAG_B200_H */

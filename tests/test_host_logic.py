@@ -1,0 +1,120 @@
+"""CPU tests: the C-ABI library loads and exports what the header declares, and the host
+logic above it (dictionary encoding, filter translation, store bookkeeping) behaves like the
+reference's boundary.  No compute calls: there is no GPU here."""
+import ctypes as C
+import re
+from pathlib import Path
+
+import numpy as np
+import pytest
+
+ROOT = Path(__file__).resolve().parents[1]
+
+
+@pytest.fixture(scope="module")
+def lib():
+    from githubrepostorag_b200 import _native, build
+    build.build()
+    return _native.load()
+
+
+def _declared_symbols():
+    text = (ROOT / "include" / "coderag_b200.h").read_text()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(crb_[a-z0-9_]+)\s*\(", text)))
+
+
+def test_header_symbols_exported_and_bound(lib):
+    from githubrepostorag_b200 import _native
+    declared = _declared_symbols()
+    assert len(declared) >= 12
+    for name in declared:
+        assert hasattr(lib, name), f"{name} declared in include/coderag_b200.h but not exported"
+        assert name in _native.PROTOTYPES, f"{name} has no ctypes prototype"
+    assert set(_native.PROTOTYPES) == set(declared)
+    assert lib.crb_abi_version() == _native.ABI_VERSION
+
+
+def test_argument_errors_are_reported_not_crashed(lib):
+    from githubrepostorag_b200 import _native
+    h = C.c_void_p()
+    rc = lib.crb_index_create(C.byref(h), None, None, None, 10, 12, 0, 0, 0)   # dim % 8 != 0
+    assert rc != 0 and b"dim" in lib.crb_last_error()
+    rc = lib.crb_index_create(C.byref(h), None, None, None, 10, 16, 99, 0, 0)  # too many keys
+    assert rc != 0 and b"n_keys" in lib.crb_last_error()
+    rc = lib.crb_index_create(C.byref(h), None, None, None, 10, 16, 0, 2**32, 0)
+    assert rc != 0
+    with pytest.raises(RuntimeError, match="coderag_b200"):
+        _native.check(rc)
+    assert lib.crb_search(None, None, 1, 5, 0, None, None, None, None, None, None, 0, 0, None) != 0
+    assert b"NULL" in lib.crb_last_error()
+    assert lib.crb_merge_keys(None, 0, 1, 5, 0, None, 8, None, None, None, None, 0, None) != 0
+    assert lib.crb_index_destroy(None) == 0
+    assert lib.crb_workspace_bytes(None, 1, 1, 0) == 0
+
+
+def test_missing_library_fails_loudly(monkeypatch, tmp_path):
+    from githubrepostorag_b200 import _native
+    monkeypatch.setattr(_native, "_lib", None)
+    monkeypatch.setattr(_native, "_LIB_PATH", tmp_path / "nope.so")
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        _native.load()
+
+
+def test_metadata_dictionary_codes_and_filters(lib):
+    from githubrepostorag_b200 import _native as N
+    from githubrepostorag_b200.index import MetadataDictionary
+    d = MetadataDictionary(["namespace", "repo", "branch"])
+    codes = d.encode_rows([{"namespace": "default", "repo": "a"},
+                           {"namespace": "acme", "repo": "a", "branch": "dev"},
+                           {"repo": 7}])
+    assert codes.dtype == np.int32 and codes.shape == (3, 3)
+    assert codes[:, 0].tolist() == [0, 0, N.CODE_MISSING]
+    assert codes[:, 1].tolist() == [1, 0, 0]
+    assert codes[:, 2].tolist() == [N.CODE_MISSING, 1, N.CODE_MISSING]   # repo=7 stored as "7"
+    assert d.encode_filter(None).tolist() == [N.FILT_ANY] * 3
+    assert d.encode_filter({"repo": "a"}).tolist() == [N.FILT_ANY, 0, N.FILT_ANY]
+    assert d.encode_filter({"repo": "7", "namespace": "acme"}).tolist() == [1, 1, N.FILT_ANY]
+    assert d.encode_filter({"repo": "zzz"}).tolist() == [N.FILT_ANY, N.FILT_IMPOSSIBLE, N.FILT_ANY]
+    assert d.encode_filter({"owner": "x"}).tolist() == [N.FILT_IMPOSSIBLE] * 3
+    with pytest.raises(ValueError):
+        MetadataDictionary([str(i) for i in range(9)])
+
+
+def test_store_host_bookkeeping(lib):
+    from githubrepostorag_b200.types import MetadataFilter, MetadataFilters, TextNode, VectorStoreQuery
+    from githubrepostorag_b200.vector_store import B200VectorStore
+    st = B200VectorStore(dim=8)
+    assert st.stores_text and st.is_embedding_query and st.client is st
+    nodes = [TextNode(text=f"t{i}", metadata={"repo": "a" if i % 2 else "b", "skip": None}, id_=f"n{i}",
+                      embedding=[float(i)] * 8) for i in range(5)]
+    assert st.add(nodes) == [f"n{i}" for i in range(5)]
+    assert len(st) == 5
+    st.add([TextNode(text="new", metadata={"repo": "c"}, id_="n2", embedding=[9.0] * 8)])   # upsert
+    assert len(st) == 5 and st.get_by_document_id("n2").page_content == "new"
+    st.delete("n0")
+    assert len(st) == 4 and st.get_by_document_id("n0") is None
+    st.delete("does-not-exist")
+    with pytest.raises(ValueError):
+        st.add_embeddings(["x"], np.zeros((1, 16), np.float32))
+    f = MetadataFilters(filters=[MetadataFilter(key="repo", value="a"), MetadataFilter(key="namespace", value="n")])
+    assert st._filters_to_dict(f) == {"repo": "a", "namespace": "n"}
+    with pytest.raises(NotImplementedError):
+        st.query(VectorStoreQuery(query_embedding=[0.0] * 8, similarity_top_k=1, node_ids=["n1"]))
+    with pytest.raises(ValueError):
+        st.query(VectorStoreQuery(query_embedding=None, similarity_top_k=1))
+
+
+def test_synthetic_generator_is_block_stable():
+    from githubrepostorag_b200 import synthetic as S
+    full = S.corpus(1001, 5000, 16)
+    part = S.corpus(1001, 5000, 16, lo=1234, hi=4321)
+    assert full.dtype == np.float16 and np.array_equal(full[1234:4321], part)
+    c_full = S.metadata_codes(1001, 5000)
+    c_part = S.metadata_codes(1001, 5000, lo=100, hi=900)
+    for k in S.FILTER_KEYS:
+        assert np.array_equal(c_full[k][100:900], c_part[k])
+    flt, sel = S.pick_filter(c_full, ("namespace", "component_kind"), 0.10)
+    assert set(flt) == {"namespace", "component_kind"} and 0.0 < sel < 0.5
+    md = S.metadata_dicts({k: v[:3] for k, v in c_full.items()})
+    assert all(isinstance(v, str) for row in md for v in row.values())
