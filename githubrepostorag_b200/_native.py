@@ -25,6 +25,7 @@ CODE_MISSING = -1
 MAX_KEYS = 8
 MAX_TOPK = 128
 MAX_DIM = 4096
+NOALLOC_MAX_BATCH = 4
 
 # every symbol include/coderag_b200.h declares: name -> (restype, argtypes)
 _vp, _i32, _i64, _sz = C.c_void_p, C.c_int32, C.c_int64, C.c_size_t
@@ -40,6 +41,7 @@ PROTOTYPES = {
     "crb_search_host": (C.c_int, [_vp, _vp, _i32, _i32, _i32, _vp, _vp, _vp, _vp, _i32]),
     "crb_merge_keys": (C.c_int, [_vp, _i32, _i32, _i32, _i32, _vp, _i32, _vp, _vp, _vp, _vp, _i32, _vp]),
     "crb_fetch_rows_host": (C.c_int, [_vp, _vp, _i32, _vp]),
+    "crb_search_noalloc": (C.c_int, [_vp, _vp, _i32, _i32, _i32, _vp, _vp, _vp, _vp]),
     "crb_launch_count": (_i64, []),
 }
 

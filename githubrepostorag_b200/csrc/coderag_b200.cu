@@ -620,3 +620,111 @@ extern "C" int crb_fetch_rows_host(crb_index* ix, const int64_t* h_rows_idx, int
     memcpy(h_out, h_io + idx_bytes, out_bytes);
     return 0;
 }
+
+// =============================================================================================
+// Allocation-free search (see the comment on crb_search_noalloc in include/coderag_b200.h)
+// =============================================================================================
+// The scratch itself, at file scope: part of the library image, present on every GPU that loads
+// it.  In host code this name is only a stand-in for the symbol -- the address a kernel can use
+// comes from cudaGetSymbolAddress on the device in question.
+static __device__ __align__(256) unsigned char g_noalloc_scratch[CRB_NOALLOC_SCRATCH_BYTES];
+
+namespace crb {
+
+constexpr size_t kNoAllocHeaderBytes = 4096;               // arrival counters of the K1 groups
+constexpr size_t kNoAllocCandBytes = size_t(1) << 20;      // per-CTA candidate lists
+static_assert(kNoAllocHeaderBytes + kNoAllocCandBytes == CRB_NOALLOC_SCRATCH_BYTES, "header and source disagree");
+
+constexpr int kNoAllocMaxDevices = 64;
+static std::mutex g_noalloc_mu;
+static unsigned char* g_noalloc_ptr[kNoAllocMaxDevices] = {};
+
+// Device address of the scratch array on `device`, which must be the current device.  Looked up
+// once per device; later calls return the cached pointer.
+static int noalloc_scratch(int device, unsigned char** out) {
+    if (device < 0 || device >= kNoAllocMaxDevices) return fail("device ordinal %d out of range", device);
+    std::lock_guard<std::mutex> lk(g_noalloc_mu);
+    if (!g_noalloc_ptr[device]) {
+        unsigned char* ptr = nullptr;
+        CRB_CUDA(cudaGetSymbolAddress((void**)&ptr, g_noalloc_scratch));
+        if (!ptr) return fail("cudaGetSymbolAddress returned a null scratch address on device %d", device);
+        g_noalloc_ptr[device] = ptr;
+    }
+    *out = g_noalloc_ptr[device];
+    return 0;
+}
+
+}  // namespace crb
+
+extern "C" int crb_search_noalloc(crb_index* ix, const float* d_queries, int32_t batch, int32_t k,
+                                  int32_t metric, float* d_scores, int64_t* d_rows,
+                                  int32_t* d_n_valid, void* stream_) {
+    if (int rc = validate_search(ix, batch, k, metric)) return rc;
+    if (batch > CRB_NOALLOC_MAX_BATCH)
+        return fail("crb_search_noalloc: batch %d exceeds CRB_NOALLOC_MAX_BATCH (%d); its scratch is a fixed "
+                    "%d-byte array -- use crb_search with a caller-provided workspace for larger batches",
+                    batch, CRB_NOALLOC_MAX_BATCH, CRB_NOALLOC_SCRATCH_BYTES);
+    if (!d_queries || !d_scores || !d_rows || !d_n_valid) return fail("NULL device pointer passed to crb_search_noalloc");
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    DeviceGuard guard(ix->device);
+    CRB_CUDA(guard.status);
+    unsigned char* scratch = nullptr;
+    if (int rc = noalloc_scratch(ix->device, &scratch)) return rc;
+
+    // plan: consecutive queries share a group of up to nq_cap (no filters here)
+    const int chunks = ix->dim / 8;
+    const int ch = (chunks + 31) / 32;
+    const bool generic = ch > 4;
+    const int nq_cap = generic ? 1 : (ch <= 2 ? 4 : 2);
+    const int ng = (batch + nq_cap - 1) / nq_cap;
+    const int widest = std::min<int>(batch, nq_cap);
+    const int nq = widest <= 1 ? 1 : (widest <= 2 ? 2 : 4);
+    K1Fn fn = generic ? k1_pick_generic(k) : k1_pick(nq, ch, 4, k);
+    if (!fn) return fail("internal: no K1 instantiation for nq=%d ch=%d", nq, ch);
+    const size_t dyn = generic ? size_t(ix->dim) * sizeof(float) : 0;
+    const int rows_per_warp_iter = generic ? 2 : (nq == 1 ? 4 : 2);
+    int per_sm = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fn, kK1Threads, dyn) != cudaSuccess || per_sm < 1) per_sm = 1;
+    const int resident = per_sm * ix->sm_count;
+
+    K1Params p;
+    memset(&p, 0, sizeof p);
+    p.rows = ix->rows;
+    p.inv_norm = ix->inv_norm;
+    p.queries = d_queries;
+    p.cand = reinterpret_cast<uint64_t*>(scratch + kNoAllocHeaderBytes);
+    p.counters = reinterpret_cast<unsigned*>(scratch);
+    p.out_scores = d_scores;
+    p.out_rows = d_rows;
+    p.out_nvalid = d_n_valid;
+    p.n_rows = ix->n_rows;
+    p.list_stride = 0;
+    p.row_offset = static_cast<uint32_t>(ix->row_offset);
+    p.dim = ix->dim;
+    p.k = k;
+    p.metric = metric;
+    for (int g = 0; g < ng; ++g) {
+        for (int q = 0; q < kK1MaxQ; ++q) {
+            const int b = g * nq_cap + q;
+            p.groups[g].q_idx[q] = (q < nq_cap && b < batch) ? b : -1;
+        }
+        p.groups[g].filter = -1;
+    }
+    const int64_t work = (ix->n_rows + int64_t(kK1Warps) * rows_per_warp_iter * 2 - 1) /
+                         (int64_t(kK1Warps) * rows_per_warp_iter * 2);
+    int64_t gx = std::max<int64_t>(resident / ng, 16);
+    gx = std::min<int64_t>(gx, std::max<int64_t>(work, 1));
+    gx = std::min<int64_t>(gx, kK1MaxGridX);
+    const int64_t cand_lists = int64_t(kNoAllocCandBytes) / (int64_t(k) * 8);
+    gx = std::min<int64_t>(gx, std::max<int64_t>(cand_lists / (int64_t(ng) * (generic ? 1 : nq)), 1));
+    if (int64_t(ng) * (generic ? 1 : nq) * gx * k * 8 > int64_t(kNoAllocCandBytes))
+        return fail("crb_search_noalloc: batch %d with k %d does not fit the %d-byte scratch", batch, k,
+                    CRB_NOALLOC_SCRATCH_BYTES);
+
+    // The array still holds the previous call's lists and counters: the counters must start at 0.
+    CRB_CUDA(cudaMemsetAsync(scratch, 0, kNoAllocHeaderBytes, stream));
+    dim3 grid(static_cast<unsigned>(gx), static_cast<unsigned>(ng));
+    fn<<<grid, kK1Threads, dyn, stream>>>(p);
+    CRB_LAUNCH_CHECK();
+    return 0;
+}

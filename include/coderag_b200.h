@@ -129,6 +129,38 @@ int crb_merge_keys(const uint64_t *d_keys_in, int32_t n_lists, int32_t batch, in
  * LCCassandra returns; graph-retriever re-scores from it).  h_rows_idx are LOCAL row indices. */
 int crb_fetch_rows_host(crb_index *index, const int64_t *h_rows_idx, int32_t n, float *h_out);
 
+/* Search that allocates nothing -- no counterpart in the reference (the reference never manages
+ * device memory; this exists for hosts of this library that do).
+ *
+ * Who needs it: a serving process that has already given the whole card to the corpus and to its
+ * own memory pool has nothing left for cudaMalloc to hand out, and a plugin host that owns the
+ * device-memory budget may forbid its plugins from allocating at all; in a request path an
+ * allocation is also a device-wide synchronisation point that stalls every other stream.  Those
+ * callers cannot provide or grow a workspace for crb_search and cannot use crb_search_host (its
+ * lanes cudaMalloc their staging buffers).  For them this entry runs the same streaming kernel
+ * with its scratch (per-CTA candidate lists + arrival counters) in a fixed array that is part
+ * of the library image: CRB_NOALLOC_SCRATCH_BYTES of HBM on every GPU that loads the library,
+ * held until the process exits.  The caller passes only inputs and outputs, all on the index's
+ * device:
+ *   d_queries fp32 [batch, dim];  d_scores fp32 [batch, k];  d_rows int64 [batch, k];
+ *   d_n_valid int32 [batch].  Unfiltered search only (survivor lists do not fit the array).
+ *
+ * Limits: batch <= CRB_NOALLOC_MAX_BATCH and k <= CRB_MAX_TOPK; anything larger is refused with
+ * an error, never truncated.  Results are identical to crb_search on the same inputs.
+ *
+ * Set-up: the first call on each device looks up the array's device address (once per device,
+ * with that device current).  Make that first call before starting any stream capture.
+ * Sharing: every call on a device uses the same array, which still holds the previous call's
+ * lists; the entry clears the counters it needs zeroed at the start of each call.  Two calls
+ * whose kernels overlap on the GPU (different streams, or different threads) race on the array
+ * and return garbage -- serialise them on one stream.
+ * It calls no cudaMalloc / cudaFree / cudaMallocHost or any other allocating routine. */
+#define CRB_NOALLOC_MAX_BATCH 4
+#define CRB_NOALLOC_SCRATCH_BYTES (4096 + (1 << 20))
+int crb_search_noalloc(crb_index *index, const float *d_queries, int32_t batch, int32_t k,
+                       int32_t metric, float *d_scores, int64_t *d_rows, int32_t *d_n_valid,
+                       void *stream);
+
 /* Number of kernels this library has launched in the calling process (bench.py's
  * `gpu_launches`). */
 int64_t crb_launch_count(void);
