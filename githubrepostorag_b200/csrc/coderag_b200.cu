@@ -17,6 +17,7 @@
 
 #include "common.cuh"
 #include "k1_stream.cuh"
+#include "k2_gemm.cuh"
 #include "k3_filter.cuh"
 #include "topk.cuh"
 
@@ -85,6 +86,18 @@ constexpr size_t kWsCandBytes = size_t(8) << 20;  // per-CTA candidate lists of 
 
 static inline int64_t round_up(int64_t v, int64_t m) { return (v + m - 1) / m * m; }
 
+constexpr int kK2MaxChunk = kK2MaxMTiles * kK2BlockM;   // queries per K2 launch
+constexpr int64_t kK2MinRows = 16384;                   // below this K1 is always used
+
+// k' (candidates kept per query per CTA) for a requested k
+// (shared memory holds k' x 128 keys next to >= 2 pipeline stages, which caps k' at 120)
+constexpr int kK2MaxKPrime = 120;
+static inline int k2_kprime(int k) {
+    if (k <= 10) return 16;
+    return std::min<int>(kK2MaxKPrime, static_cast<int>(round_up(k + k / 2, 8)));
+}
+static inline bool k2_supports_k(int k) { return k2_kprime(k) >= k + 4; }
+
 struct Lane {
     cudaStream_t stream = nullptr;
     void* d_ws = nullptr;
@@ -108,6 +121,9 @@ struct crb_index {
     int64_t row_offset = 0;
     int32_t device = 0;
     int32_t sm_count = 148;
+    float max_norm = 0.f;          // largest row norm (K5 inner-product margin)
+    bool k2_ok = false;            // corpus tensor map encoded
+    CUtensorMap map_rows;          // fp16 [n_rows, dim], box 64 x 256, 128 B swizzle
     std::mutex mu;
     std::condition_variable cv;
     std::vector<crb::Lane> lanes;
@@ -116,6 +132,62 @@ struct crb_index {
 namespace crb {
 
 static int64_t list_stride_of(const crb_index* ix) { return round_up(std::max<int64_t>(ix->n_rows, 1), 64); }
+static int64_t mask_stride_of(const crb_index* ix) { return round_up((std::max<int64_t>(ix->n_rows, 1) + 31) / 32, 64); }
+
+// Workspace layout: [header 4 KB][K1 candidate lists 8 MB][K2 region][survivor lists][pass masks]
+struct WsLayout {
+    size_t cand = kWsHeaderBytes;
+    size_t k2 = 0;          // K2 region start
+    size_t q16 = 0, invq = 0, eps = 0, qmap = 0, flagged = 0, nflag = 0, cand2 = 0;   // inside the K2 region
+    size_t filt = 0;        // survivor lists start; masks follow the lists
+    size_t per_filter = 0;  // bytes one more filter costs
+};
+static WsLayout ws_layout(const crb_index* ix, int batch, int k) {
+    WsLayout L;
+    L.k2 = kWsHeaderBytes + kWsCandBytes;
+    const size_t nmax = static_cast<size_t>(std::min(batch, kK2MaxChunk));
+    size_t o = L.k2;
+    L.q16 = o;     o += round_up(nmax * ix->dim * 2, 1024);
+    L.invq = o;    o += round_up(nmax * 4, 256);
+    L.eps = o;     o += round_up(nmax * 4, 256);
+    L.qmap = o;    o += round_up(nmax * 4, 256);
+    L.flagged = o; o += round_up(nmax * 4, 256);
+    L.nflag = o;   o += 256;
+    L.cand2 = o;   o += round_up(std::min<size_t>(nmax, kK2BlockM) * ix->sm_count * k2_kprime(k) * 8 + nmax * k2_kprime(k) * 8, 1024);
+    L.filt = o;
+    L.per_filter = size_t(list_stride_of(ix)) * 4 + size_t(mask_stride_of(ix)) * 4;
+    return L;
+}
+
+// cuTensorMapEncodeTiled through the runtime's driver entry point (no link-time libcuda).
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static EncodeTiledFn encode_tiled_fn() {
+    static EncodeTiledFn fn = []() -> EncodeTiledFn {
+        void* f = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &f, cudaEnableDefault, &q) != cudaSuccess ||
+            q != cudaDriverEntryPointSuccess)
+            return nullptr;
+        return reinterpret_cast<EncodeTiledFn>(f);
+    }();
+    return fn;
+}
+// fp16 [rows, dim] row-major -> 2-D map, box = 64 elements (128 B, one swizzle row) x box_rows
+static int make_map_f16(CUtensorMap* map, const void* base, int64_t rows, int dim, int box_rows) {
+    EncodeTiledFn enc = encode_tiled_fn();
+    if (!enc) return fail("cuTensorMapEncodeTiled is unavailable in this driver");
+    const cuuint64_t gdim[2] = {static_cast<cuuint64_t>(dim), static_cast<cuuint64_t>(std::max<int64_t>(rows, 1))};
+    const cuuint64_t gstride[1] = {static_cast<cuuint64_t>(dim) * 2};
+    const cuuint32_t box[2] = {static_cast<cuuint32_t>(kK2BlockK), static_cast<cuuint32_t>(box_rows)};
+    const cuuint32_t estr[2] = {1, 1};
+    const CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, const_cast<void*>(base), gdim, gstride, box, estr,
+                           CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                           CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return fail("cuTensorMapEncodeTiled failed with CUresult %d", static_cast<int>(r));
+    return 0;
+}
 
 // ---------------------------------------------------------------------------------------------
 // K1 dispatch
@@ -170,8 +242,8 @@ struct QueryGroup {
 // lists currently in the workspace).
 static int launch_k1(const crb_index* ix, const float* d_queries, int k, int metric,
                      const std::vector<QueryGroup>& groups, const std::vector<int>& slot_of_filter,
-                     int nq, uint8_t* ws, float* d_scores, int64_t* d_rows, int32_t* d_n_valid,
-                     uint64_t* d_keys, cudaStream_t stream) {
+                     int nq, uint8_t* ws, const uint32_t* lists, float* d_scores, int64_t* d_rows,
+                     int32_t* d_n_valid, uint64_t* d_keys, cudaStream_t stream) {
     const int chunks = ix->dim / 8;
     const int ch = (chunks + 31) / 32;
     const bool generic = ch > 4;
@@ -189,7 +261,7 @@ static int launch_k1(const crb_index* ix, const float* d_queries, int k, int met
         p.rows = ix->rows;
         p.inv_norm = ix->inv_norm;
         p.queries = d_queries;
-        p.lists = reinterpret_cast<const uint32_t*>(ws + kWsHeaderBytes + kWsCandBytes);
+        p.lists = lists;
         p.list_counts = reinterpret_cast<const uint32_t*>(ws + kWsCountsOffset);
         p.cand = reinterpret_cast<uint64_t*>(ws + kWsHeaderBytes);
         p.counters = reinterpret_cast<unsigned*>(ws);
@@ -226,15 +298,121 @@ static int launch_k1(const crb_index* ix, const float* d_queries, int k, int met
 }
 
 // ---------------------------------------------------------------------------------------------
-// the search plan: dedup filters, build survivor lists, group queries, launch
+// K2 launch: tensor-core candidates + K5 exact rescore for one set of queries sharing a row set
+// ---------------------------------------------------------------------------------------------
+// `queries` are indices into the caller's batch; `mask` is the pass-bit array of their common
+// filter (nullptr = whole shard).  Queries K5 cannot prove exact are appended to `unproven`
+// (the caller re-runs them through K1).  Synchronises the stream once to read the flag count.
+static int launch_k2(crb_index* ix, const float* d_queries, int batch, int k, int metric,
+                     const std::vector<int>& queries, const uint32_t* mask, uint8_t* ws, const WsLayout& L,
+                     float* d_scores, int64_t* d_rows, int32_t* d_n_valid, uint64_t* d_keys,
+                     std::vector<int>* unproven, cudaStream_t stream) {
+    const int kprime = k2_kprime(k);
+    const size_t list_bytes = size_t(kprime) * 128 * 8;
+    const size_t tail_bytes = 2 * kK2BlockN * 4 + 256;
+    int stages = static_cast<int>((size_t(227) * 1024 - 1024 - list_bytes - tail_bytes) / kK2StageBytes);
+    stages = std::min(stages, 4);
+    if (stages < 2) return fail("internal: K2 does not fit shared memory for k'=%d", kprime);
+    const size_t smem = 1024 + size_t(stages) * kK2StageBytes + list_bytes + tail_bytes;
+    static std::once_flag attr_once;
+    static cudaError_t attr_err = cudaSuccess;
+    std::call_once(attr_once, [] {
+        attr_err = cudaFuncSetAttribute(k2_gemm_topk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    });
+    CRB_CUDA(attr_err);
+
+    __half* q16 = reinterpret_cast<__half*>(ws + L.q16);
+    float* invq = reinterpret_cast<float*>(ws + L.invq);
+    float* eps = reinterpret_cast<float*>(ws + L.eps);
+    int32_t* qmap = reinterpret_cast<int32_t*>(ws + L.qmap);
+    int32_t* flagged = reinterpret_cast<int32_t*>(ws + L.flagged);
+    int32_t* nflag = reinterpret_cast<int32_t*>(ws + L.nflag);
+    uint64_t* cand2 = reinterpret_cast<uint64_t*>(ws + L.cand2);
+
+    for (size_t c0 = 0; c0 < queries.size(); c0 += kK2MaxChunk) {
+        const int n = static_cast<int>(std::min<size_t>(kK2MaxChunk, queries.size() - c0));
+        bool identity = (c0 == 0);
+        for (int i = 0; i < n && identity; ++i) identity = (queries[c0 + i] == static_cast<int>(c0) + i);
+        const int32_t* d_qmap = nullptr;
+        if (!identity) {
+            CRB_CUDA(cudaMemcpyAsync(qmap, queries.data() + c0, size_t(n) * 4, cudaMemcpyHostToDevice, stream));
+            d_qmap = qmap;
+        }
+        k2_prep_queries_kernel<<<n, 128, 0, stream>>>(d_queries, d_qmap, n, ix->dim, q16, invq, eps);
+        CRB_LAUNCH_CHECK();
+
+        CUtensorMap map_q;
+        if (int rc = make_map_f16(&map_q, q16, n, ix->dim, kK2BlockM)) return rc;
+        K2Params kp;
+        memset(&kp, 0, sizeof kp);
+        kp.inv_norm = ix->inv_norm;
+        kp.mask = mask;
+        kp.cand = cand2;
+        kp.n_rows = ix->n_rows;
+        kp.batch = n;
+        kp.dim = ix->dim;
+        kp.kprime = kprime;
+        kp.metric = metric;
+        kp.m_tiles = (n + kK2BlockM - 1) / kK2BlockM;
+        kp.slots = std::max(1, ix->sm_count / kp.m_tiles);
+        const int64_t n_tiles = (ix->n_rows + kK2BlockN - 1) / kK2BlockN;
+        kp.slots = static_cast<int>(std::min<int64_t>(kp.slots, std::max<int64_t>(n_tiles, 1)));
+        kp.stages = stages;
+        k2_gemm_topk_kernel<<<kp.m_tiles * kp.slots, kK2Threads, smem, stream>>>(map_q, ix->map_rows, kp);
+        CRB_LAUNCH_CHECK();
+
+        CRB_CUDA(cudaMemsetAsync(nflag, 0, 4, stream));
+        K5Params rp;
+        memset(&rp, 0, sizeof rp);
+        rp.rows = ix->rows;
+        rp.inv_norm = ix->inv_norm;
+        rp.queries = d_queries;
+        rp.q_map = d_qmap;
+        rp.cand = cand2;
+        rp.invq = invq;
+        rp.eps = eps;
+        rp.out_scores = d_scores;
+        rp.out_rows = d_rows;
+        rp.out_nvalid = d_n_valid;
+        rp.out_keys = d_keys;
+        rp.flagged = flagged;
+        rp.n_flagged = nflag;
+        rp.max_norm = ix->max_norm;
+        rp.row_offset = static_cast<uint32_t>(ix->row_offset);
+        rp.dim = ix->dim;
+        rp.k = k;
+        rp.kprime = kprime;
+        rp.slots = kp.slots;
+        rp.metric = metric;
+        const size_t dyn = size_t(ix->dim) * sizeof(float);
+        if (k <= 32) k5_rescore_kernel<1><<<n, 256, dyn, stream>>>(rp);
+        else k5_rescore_kernel<4><<<n, 256, dyn, stream>>>(rp);
+        CRB_LAUNCH_CHECK();
+
+        int32_t h_nflag = 0;
+        CRB_CUDA(cudaMemcpyAsync(&h_nflag, nflag, 4, cudaMemcpyDeviceToHost, stream));
+        CRB_CUDA(cudaStreamSynchronize(stream));
+        if (h_nflag > 0) {
+            std::vector<int32_t> h_flag(h_nflag);
+            CRB_CUDA(cudaMemcpyAsync(h_flag.data(), flagged, size_t(h_nflag) * 4, cudaMemcpyDeviceToHost, stream));
+            CRB_CUDA(cudaStreamSynchronize(stream));
+            for (int32_t slot_q : h_flag) unproven->push_back(queries[c0 + slot_q]);
+        }
+    }
+    (void)batch;
+    return 0;
+}
+
+// ---------------------------------------------------------------------------------------------
+// the search plan: dedup filters, build survivor lists, group queries, choose K1 / K2, launch
 // ---------------------------------------------------------------------------------------------
 static int search_impl(crb_index* ix, const float* d_queries, int batch, int k, int metric,
                        const int32_t* h_filt, float* d_scores, int64_t* d_rows,
                        int32_t* d_n_valid, uint64_t* d_keys, void* d_workspace,
                        size_t workspace_bytes, int algo, cudaStream_t stream) {
-    (void)algo;
     uint8_t* ws = static_cast<uint8_t*>(d_workspace);
     const int M = ix->n_keys;
+    if (algo < 0 || algo > 2) return fail("algo must be 0 (auto), 1 (streaming) or 2 (tensor core)");
 
     // distinct filters of the batch
     std::vector<std::array<int32_t, kMaxKeys>> filters;
@@ -258,16 +436,20 @@ static int search_impl(crb_index* ix, const float* d_queries, int batch, int k, 
         }
     }
     const int F = static_cast<int>(filters.size());
+    const WsLayout L = ws_layout(ix, batch, k);
     const int64_t stride = list_stride_of(ix);
-    const size_t fixed = kWsHeaderBytes + kWsCandBytes;
-    if (workspace_bytes < fixed) return fail("workspace too small: %zu < %zu", workspace_bytes, fixed);
-    int lists_fit = static_cast<int>(std::min<size_t>((workspace_bytes - fixed) / (size_t(stride) * 4), kMaxFilters));
+    const int64_t mstride = mask_stride_of(ix);
+    if (workspace_bytes < L.filt) return fail("workspace too small: %zu < %zu", workspace_bytes, L.filt);
+    int lists_fit = static_cast<int>(std::min<size_t>((workspace_bytes - L.filt) / L.per_filter, kMaxFilters));
     if (F > 0 && lists_fit < 1)
-        return fail("workspace too small for one survivor list: need %zu bytes", fixed + size_t(stride) * 4);
+        return fail("workspace too small for one survivor list: need %zu bytes", L.filt + L.per_filter);
+    uint32_t* lists = reinterpret_cast<uint32_t*>(ws + L.filt);
+    uint32_t* masks = reinterpret_cast<uint32_t*>(ws + L.filt + size_t(std::max(lists_fit, 0)) * size_t(stride) * 4);
 
     const int chunks = ix->dim / 8;
     const int ch = (chunks + 31) / 32;
     const int nq_cap = ch > 4 ? 1 : (ch <= 2 ? 4 : 2);
+    const bool k2_possible = ix->k2_ok && ix->n_rows >= kK2MinRows && algo != 1 && k2_supports_k(k);
 
     // rounds: round 0 serves the unfiltered queries together with the first block of filters
     int f_lo = 0;
@@ -275,12 +457,31 @@ static int search_impl(crb_index* ix, const float* d_queries, int batch, int k, 
     while (first || f_lo < F) {
         const int f_hi = std::min(F, f_lo + std::max(lists_fit, 1));
         std::vector<int> slot_of_filter(std::max(F, 1), -1);
+
+        // queries of this round by filter
+        std::map<int, std::vector<int>> by_filter;
+        for (int b = 0; b < batch; ++b) {
+            const int f = fid[b];
+            const bool mine = (f < 0) ? first : (f >= f_lo && f < f_hi);
+            if (mine) by_filter[f].push_back(b);
+        }
+        // which row sets go to the tensor-core kernel
+        std::map<int, bool> use_k2;
+        bool any_k2_filtered = false;
+        for (auto& kv : by_filter) {
+            const bool big = static_cast<int>(kv.second.size()) > nq_cap;
+            use_k2[kv.first] = k2_possible && (algo == 2 || big);
+            any_k2_filtered |= (use_k2[kv.first] && kv.first >= 0);
+        }
+
         if (f_hi > f_lo) {
             K3Params kp;
             memset(&kp, 0, sizeof kp);
             kp.codes = ix->codes;
-            kp.lists = reinterpret_cast<uint32_t*>(ws + fixed);
+            kp.lists = lists;
             kp.counts = reinterpret_cast<uint32_t*>(ws + kWsCountsOffset);
+            kp.masks = any_k2_filtered ? masks : nullptr;
+            kp.mask_stride = mstride;
             kp.n_rows = ix->n_rows;
             kp.list_stride = stride;
             kp.n_keys = M;
@@ -300,30 +501,34 @@ static int search_impl(crb_index* ix, const float* d_queries, int batch, int k, 
                 CRB_LAUNCH_CHECK();
             }
         }
-        // groups of this round
+
+        // tensor-core row sets first; what K5 cannot prove joins the streaming groups
+        std::map<int, std::vector<int>> k1_sets;
+        for (auto& kv : by_filter) {
+            if (!use_k2[kv.first]) { k1_sets[kv.first] = kv.second; continue; }
+            const uint32_t* mask = kv.first < 0 ? nullptr : masks + size_t(slot_of_filter[kv.first]) * size_t(mstride);
+            std::vector<int> unproven;
+            if (int rc = launch_k2(ix, d_queries, batch, k, metric, kv.second, mask, ws, L, d_scores, d_rows,
+                                   d_n_valid, d_keys, &unproven, stream))
+                return rc;
+            if (!unproven.empty()) k1_sets[kv.first] = unproven;
+        }
+
         std::vector<QueryGroup> groups;
         int max_group = 1;
-        {
-            std::map<int, std::vector<int>> by_filter;
-            for (int b = 0; b < batch; ++b) {
-                const int f = fid[b];
-                const bool mine = (f < 0) ? first : (f >= f_lo && f < f_hi);
-                if (mine) by_filter[f].push_back(b);
-            }
-            for (auto& kv : by_filter) {
-                const std::vector<int>& qs = kv.second;
-                for (size_t i = 0; i < qs.size(); i += nq_cap) {
-                    QueryGroup g;
-                    g.filter = kv.first;
-                    g.queries.assign(qs.begin() + i, qs.begin() + std::min(qs.size(), i + nq_cap));
-                    max_group = std::max<int>(max_group, static_cast<int>(g.queries.size()));
-                    groups.push_back(std::move(g));
-                }
+        for (auto& kv : k1_sets) {
+            const std::vector<int>& qs = kv.second;
+            for (size_t i = 0; i < qs.size(); i += nq_cap) {
+                QueryGroup g;
+                g.filter = kv.first;
+                g.queries.assign(qs.begin() + i, qs.begin() + std::min(qs.size(), i + nq_cap));
+                max_group = std::max<int>(max_group, static_cast<int>(g.queries.size()));
+                groups.push_back(std::move(g));
             }
         }
         if (!groups.empty()) {
             const int nq = max_group <= 1 ? 1 : (max_group <= 2 ? 2 : 4);
-            int rc = launch_k1(ix, d_queries, k, metric, groups, slot_of_filter, nq, ws, d_scores,
+            int rc = launch_k1(ix, d_queries, k, metric, groups, slot_of_filter, nq, ws, lists, d_scores,
                                d_rows, d_n_valid, d_keys, stream);
             if (rc) return rc;
         }
@@ -472,6 +677,28 @@ extern "C" int crb_index_create(crb_index** out, const void* d_rows_f16, const f
     ix->device = device;
     ix->sm_count = prop.multiProcessorCount;
     ix->lanes.resize(std::max(1, env_int("CODERAG_B200_LANES", 4)));
+    // tensor-core path set-up: corpus tensor map and the largest row norm
+    if (n_rows > 0 && make_map_f16(&ix->map_rows, d_rows_f16, n_rows, dim, kK2BlockN) == 0) {
+        unsigned* d_bits = nullptr;
+        const unsigned inf_bits = 0x7f800000u;
+        unsigned h_bits = inf_bits;
+        cudaError_t e = cudaMalloc(&d_bits, sizeof(unsigned));
+        if (e == cudaSuccess) e = cudaMemcpy(d_bits, &inf_bits, sizeof(unsigned), cudaMemcpyHostToDevice);
+        if (e == cudaSuccess) {
+            min_pos_inv_norm_kernel<<<std::min<int64_t>((n_rows + 255) / 256, 148 * 8), 256>>>(d_inv_norm, n_rows, d_bits);
+            g_launches.fetch_add(1, std::memory_order_relaxed);
+            e = cudaMemcpy(&h_bits, d_bits, sizeof(unsigned), cudaMemcpyDeviceToHost);
+        }
+        if (d_bits) cudaFree(d_bits);
+        if (e != cudaSuccess) {
+            delete ix;
+            return fail("index set-up failed: %s", cudaGetErrorString(e));
+        }
+        float min_inv;
+        memcpy(&min_inv, &h_bits, 4);
+        ix->max_norm = (h_bits == inf_bits || !(min_inv > 0.f)) ? 0.f : 1.0f / min_inv;
+        ix->k2_ok = true;
+    }
     *out = ix;
     return 0;
 }
@@ -517,10 +744,10 @@ extern "C" int crb_row_inv_norms(const void* d_rows_f16, float* d_inv_norm, int6
 }
 
 extern "C" size_t crb_workspace_bytes(const crb_index* ix, int32_t batch, int32_t k, int32_t n_filters) {
-    (void)batch; (void)k;
     if (!ix) return 0;
     const int lists = std::min<int>(std::max<int>(n_filters, 0), kMaxFilters);
-    return kWsHeaderBytes + kWsCandBytes + size_t(lists) * size_t(list_stride_of(ix)) * 4;
+    const WsLayout L = ws_layout(ix, std::max(batch, 1), std::min(std::max(k, 1), CRB_MAX_TOPK));
+    return L.filt + size_t(lists) * L.per_filter;
 }
 
 extern "C" int crb_search(crb_index* ix, const float* d_queries, int32_t batch, int32_t k,

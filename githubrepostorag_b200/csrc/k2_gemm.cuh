@@ -1,0 +1,486 @@
+// K2 -- tensor-core candidate generation: TMA-staged tcgen05.mma fp16 Q x C^T with the
+// accumulators in TMEM and a fused per-query top-k' epilogue; K5 -- exact rescore.
+//
+// Replaces the same Cassandra ANN scoring as K1 (graph_rag_retrievers.py:104-134) for query
+// batches: the graph-traversal fan-out and query expansion of the reference produce natural
+// batches (agent_graph.py:249-278).  The B x N score matrix is never
+// materialised: each epilogue thread owns one query row of the 128 x 256 accumulator tile,
+// scales by the row's inverse norm, and keeps a private k'-entry candidate list in shared
+// memory across all corpus tiles its CTA visits.
+//
+// K2 scores are APPROXIMATE (the query is rounded to fp16 after normalisation); K5 re-scores
+// every candidate with the library's canonical fp32 order (common.cuh) and proves the result
+// exact with a margin test, flagging the rare query that needs the K1 fallback:
+//   any row NOT kept by a full slot list has approx <= tau_slot, hence exact <= tau_max + eps,
+//   eps = ||q_hat - fp16(q_hat)||_2 (Cauchy-Schwarz, rigorous) + 2^-16 (tensor-core fp32
+//   accumulation allowance, cosine units; scaled by max row norm for inner product).
+//   The exact top-k is proven when its k-th score exceeds tau_max + eps.
+//
+// Bound: tensor pipe for batch >= ~256 (2*B*N*d flop), HBM below that (N*d*2 bytes).
+#pragma once
+#include <cuda.h>
+
+#include "topk.cuh"
+
+namespace crb {
+
+constexpr int kK2BlockM = 128;   // queries per tile (UMMA M)
+constexpr int kK2BlockN = 256;   // corpus rows per tile (UMMA N)
+constexpr int kK2BlockK = 64;    // fp16 elements per k-block = one 128 B swizzle row
+constexpr int kK2UmmaK = 16;
+constexpr int kK2Threads = 192;  // warp 0 TMA, warp 1 MMA + TMEM alloc, warps 2..5 epilogue
+constexpr int kK2StageBytesA = kK2BlockM * kK2BlockK * 2;   // 16 KB
+constexpr int kK2StageBytesB = kK2BlockN * kK2BlockK * 2;   // 32 KB
+constexpr int kK2StageBytes = kK2StageBytesA + kK2StageBytesB;
+constexpr int kK2TmemCols = 512;                            // 2 accumulator buffers x 256 columns
+constexpr int kK2MaxMTiles = 16;
+
+struct K2Params {
+    const float* inv_norm;      // [n_rows]
+    const uint32_t* mask;       // [ceil(n_rows/32)] pass bits or nullptr
+    uint64_t* cand;             // [batch, slots, kprime] approximate keys (local row in low 32 bits)
+    int64_t n_rows;
+    int32_t batch;
+    int32_t dim;
+    int32_t kprime;
+    int32_t metric;
+    int32_t m_tiles;
+    int32_t slots;              // CTAs per m-tile; grid = m_tiles * slots
+    int32_t stages;
+};
+
+// ---- PTX wrappers ------------------------------------------------------------------------------
+CRB_DEVINL uint32_t smem_u32(const void* p) { return static_cast<uint32_t>(__cvta_generic_to_shared(p)); }
+
+CRB_DEVINL void mbar_init(uint64_t* bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+CRB_DEVINL void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+CRB_DEVINL void mbar_arrive(uint64_t* bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+CRB_DEVINL void mbar_wait(uint64_t* bar, uint32_t parity) {
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "WAIT_LOOP:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+        "@p bra WAIT_DONE;\n\t"
+        "bra WAIT_LOOP;\n\t"
+        "WAIT_DONE:\n\t"
+        "}" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+CRB_DEVINL void tma_load_2d(const CUtensorMap* map, void* smem_dst, uint64_t* bar, int32_t c0, int32_t c1) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+        ::"r"(smem_u32(smem_dst)), "l"(reinterpret_cast<uint64_t>(map)), "r"(smem_u32(bar)), "r"(c0), "r"(c1)
+        : "memory");
+}
+CRB_DEVINL void tmem_alloc(uint32_t* smem_dst, uint32_t cols) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(smem_dst)), "r"(cols));
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::);
+}
+CRB_DEVINL void tmem_dealloc(uint32_t taddr, uint32_t cols) {
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(cols));
+}
+CRB_DEVINL void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+CRB_DEVINL void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+CRB_DEVINL void umma_f16(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t"
+        "}" ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate) : "memory");
+}
+CRB_DEVINL void umma_commit(uint64_t* bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+CRB_DEVINL void tmem_ld32(uint32_t taddr, uint32_t (&v)[32]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+        : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+          "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]),
+          "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]),
+          "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+        : "r"(taddr));
+}
+CRB_DEVINL void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+CRB_DEVINL void epi_bar_sync() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
+
+// K-major, 128-byte-swizzled shared-memory matrix descriptor (sm_100 format): start address and
+// offsets in 16-byte units; SBO = 1024 B between 8-row groups; LBO unused for swizzled K-major;
+// version 1; layout type 2 = SWIZZLE_128B.
+CRB_DEVINL uint64_t umma_desc_sw128(uint32_t smem_addr) {
+    return static_cast<uint64_t>((smem_addr >> 4) & 0x3fffu) | (1ull << 16) | (64ull << 32) | (1ull << 46) | (2ull << 61);
+}
+// kind::f16 instruction descriptor: D = f32, A = B = f16, both K-major, M = 128, N = 256.
+constexpr uint32_t kK2IDesc = (1u << 4) | ((kK2BlockN >> 3) << 17) | ((kK2BlockM >> 4) << 24);
+
+// Insert `key` into a thread-private unsorted k'-entry list (entry i at list[i*128]); returns the
+// new {admission threshold bits, count | minpos << 16}.  Kept out of line: the epilogue has 32
+// call sites per TMEM chunk and the call is rare after warm-up.
+__device__ __noinline__ uint2 k2_list_insert(uint64_t* list, uint64_t key, uint32_t state, float thr, int kprime) {
+    int count = static_cast<int>(state & 0xffffu);
+    int minpos = static_cast<int>(state >> 16);
+    if (count < kprime) {
+        list[count * 128] = key;
+        ++count;
+    } else {
+        list[minpos * 128] = key;
+    }
+    if (count == kprime) {
+        uint64_t m = list[0];
+        int mp = 0;
+        for (int i = 1; i < kprime; ++i) {
+            const uint64_t e = list[i * 128];
+            if (e < m) { m = e; mp = i; }
+        }
+        minpos = mp;
+        thr = key_score(m);
+    }
+    return make_uint2(__float_as_uint(thr), static_cast<uint32_t>(count) | (static_cast<uint32_t>(minpos) << 16));
+}
+
+// ---- query preparation -------------------------------------------------------------------------
+// q_hat = q / ||q|| (canonical norm), q16 = fp16(q_hat); eps = ||q_hat - q16||_2 + 2^-16.
+__global__ void __launch_bounds__(128) k2_prep_queries_kernel(const float* __restrict__ queries,
+                                                              const int32_t* __restrict__ q_map, int n,
+                                                              int dim, __half* __restrict__ q16,
+                                                              float* __restrict__ invq,
+                                                              float* __restrict__ eps) {
+    __shared__ float s_iq;
+    __shared__ float s_part[4];
+    const int slot = blockIdx.x;
+    if (slot >= n) return;
+    const float* q = queries + static_cast<int64_t>(q_map ? q_map[slot] : slot) * dim;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (warp == 0) {
+        const float iq = warp_inv_qnorm(q, dim, lane);
+        if (lane == 0) s_iq = iq;
+    }
+    __syncthreads();
+    const float iq = s_iq;
+    float err = 0.f;
+    for (int i = threadIdx.x; i < dim; i += blockDim.x) {
+        const float qh = q[i] * iq;
+        const __half h = __float2half_rn(qh);
+        q16[static_cast<int64_t>(slot) * dim + i] = h;
+        const float d = qh - __half2float(h);
+        err = fmaf(d, d, err);
+    }
+    err = warp_butterfly_sum(err);
+    if (lane == 0) s_part[warp] = err;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        const float e2 = s_part[0] + s_part[1] + s_part[2] + s_part[3];
+        invq[slot] = iq;
+        eps[slot] = sqrtf(e2) * 1.0001f + 1.52587890625e-05f;
+    }
+}
+
+// ---- the GEMM + top-k' kernel ------------------------------------------------------------------
+// grid = m_tiles * slots persistent CTAs (1 per SM).  CTA c serves query tile c % m_tiles and
+// corpus tiles  c / m_tiles + i * slots.
+__global__ void __launch_bounds__(kK2Threads, 1)
+k2_gemm_topk_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant__ CUtensorMap map_c,
+                    const __grid_constant__ K2Params p) {
+    extern __shared__ __align__(1024) uint8_t smem_raw[];
+    // carve: [stages x (A | B)] [lists kprime x 128 u64] [s_inv 2 x 256 f32] [barriers] [tmem ptr]
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint8_t* stage_base = smem;
+    uint64_t* lists = reinterpret_cast<uint64_t*>(smem + static_cast<size_t>(p.stages) * kK2StageBytes);
+    float* s_inv = reinterpret_cast<float*>(lists + static_cast<size_t>(p.kprime) * 128);
+    uint64_t* bars = reinterpret_cast<uint64_t*>(s_inv + 2 * kK2BlockN);
+    uint64_t* full_bar = bars;                       // [stages]
+    uint64_t* empty_bar = bars + p.stages;           // [stages]
+    uint64_t* tfull_bar = bars + 2 * p.stages;       // [2]
+    uint64_t* tempty_bar = bars + 2 * p.stages + 2;  // [2]
+    uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 2 * p.stages + 4);
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+    const int m_tile = blockIdx.x % p.m_tiles;
+    const int slot = blockIdx.x / p.m_tiles;
+    const int64_t n_tiles = (p.n_rows + kK2BlockN - 1) / kK2BlockN;
+    const int k_blocks = (p.dim + kK2BlockK - 1) / kK2BlockK;
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < p.stages; ++s) {
+            mbar_init(&full_bar[s], 1);
+            mbar_init(&empty_bar[s], 1);
+        }
+        for (int b = 0; b < 2; ++b) {
+            mbar_init(&tfull_bar[b], 1);
+            mbar_init(&tempty_bar[b], 128);
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 1) tmem_alloc(tmem_ptr, kK2TmemCols);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_ptr;
+
+    if (warp == 0) {
+        // ===== TMA producer =====
+        if (lane == 0) {
+            int st = 0;
+            uint32_t ph = 0;
+            for (int64_t t = slot; t < n_tiles; t += p.slots) {
+                for (int kb = 0; kb < k_blocks; ++kb) {
+                    mbar_wait(&empty_bar[st], ph ^ 1u);
+                    uint8_t* a = stage_base + static_cast<size_t>(st) * kK2StageBytes;
+                    uint8_t* b = a + kK2StageBytesA;
+                    mbar_expect_tx(&full_bar[st], kK2StageBytes);
+                    tma_load_2d(&map_q, a, &full_bar[st], kb * kK2BlockK, m_tile * kK2BlockM);
+                    tma_load_2d(&map_c, b, &full_bar[st], kb * kK2BlockK, static_cast<int32_t>(t * kK2BlockN));
+                    if (++st == p.stages) { st = 0; ph ^= 1u; }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ===== MMA issuer =====
+        if (lane == 0) {
+            int st = 0;
+            uint32_t ph = 0;
+            int64_t it = 0;
+            for (int64_t t = slot; t < n_tiles; t += p.slots, ++it) {
+                const int buf = static_cast<int>(it & 1);
+                const uint32_t use = static_cast<uint32_t>(it >> 1);
+                mbar_wait(&tempty_bar[buf], (use & 1u) ^ 1u);
+                tc_fence_after();
+                const uint32_t d_tmem = tmem_base + static_cast<uint32_t>(buf * kK2BlockN);
+                for (int kb = 0; kb < k_blocks; ++kb) {
+                    mbar_wait(&full_bar[st], ph);
+                    tc_fence_after();
+                    const uint32_t a_addr = smem_u32(stage_base + static_cast<size_t>(st) * kK2StageBytes);
+                    const uint32_t b_addr = a_addr + kK2StageBytesA;
+#pragma unroll
+                    for (int k = 0; k < kK2BlockK / kK2UmmaK; ++k) {
+                        const uint64_t da = umma_desc_sw128(a_addr + k * kK2UmmaK * 2);
+                        const uint64_t db = umma_desc_sw128(b_addr + k * kK2UmmaK * 2);
+                        umma_f16(d_tmem, da, db, kK2IDesc, (kb | k) != 0 ? 1u : 0u);
+                    }
+                    umma_commit(&empty_bar[st]);   // frees the smem stage when these MMAs retire
+                    if (++st == p.stages) { st = 0; ph ^= 1u; }
+                }
+                umma_commit(&tfull_bar[buf]);      // accumulator tile complete
+            }
+        }
+    } else {
+        // ===== epilogue: 4 warps = 128 TMEM lanes = 128 query rows =====
+        const int quarter = warp & 3;                 // TMEM lane quarter this warp may access
+        const int row = quarter * 32 + lane;          // query row inside the tile
+        const int et = row;                           // list column of this thread
+        const int tid_e = threadIdx.x - 64;           // 0..127 (staging role only)
+        const bool q_valid = (m_tile * kK2BlockM + row) < p.batch;
+        const bool cosine = (p.metric == 0);
+        uint64_t* my_list = lists + et;               // entry i at my_list[i * 128]
+        uint32_t state = 0;                           // count | minpos << 16
+        float thr = q_valid ? __uint_as_float(0xff800000u) : __uint_as_float(0x7f800000u);  // -inf / +inf
+        const float qnan = __uint_as_float(0x7fc00000u);
+
+        int64_t it = 0;
+        for (int64_t t = slot; t < n_tiles; t += p.slots, ++it) {
+            const int buf = static_cast<int>(it & 1);
+            const uint32_t use = static_cast<uint32_t>(it >> 1);
+            const int64_t n0 = t * kK2BlockN;
+            // stage per-column scale: inv_norm (cosine) or 1 (ip); NaN = "this column is not a hit"
+            float* inv = s_inv + buf * kK2BlockN;
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                const int c = tid_e + h * 128;
+                const int64_t n = n0 + c;
+                float v = qnan;
+                if (n < p.n_rows) {
+                    bool pass = true;
+                    if (p.mask) pass = (p.mask[n >> 5] >> (n & 31)) & 1u;
+                    if (pass) {
+                        if (cosine) {
+                            const float in = __ldg(p.inv_norm + n);
+                            v = in > 0.f ? in : qnan;
+                        } else {
+                            v = 1.0f;
+                        }
+                    }
+                }
+                inv[c] = v;
+            }
+            epi_bar_sync();
+            mbar_wait(&tfull_bar[buf], use & 1u);
+            tc_fence_after();
+            const uint32_t t_row = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) +
+                                   static_cast<uint32_t>(buf * kK2BlockN);
+#pragma unroll 1
+            for (int c = 0; c < kK2BlockN / 32; ++c) {
+                uint32_t v[32];
+                tmem_ld32(t_row + c * 32, v);
+                tmem_ld_wait();
+#pragma unroll
+                for (int j = 0; j < 32; ++j) {
+                    const float s = __uint_as_float(v[j]) * inv[c * 32 + j];
+                    if (s > thr) {
+                        const uint2 r = k2_list_insert(my_list, make_key(s, static_cast<uint32_t>(n0 + c * 32 + j)),
+                                                       state, thr, p.kprime);
+                        thr = __uint_as_float(r.x);
+                        state = r.y;
+                    }
+                }
+            }
+            tc_fence_before();
+            mbar_arrive(&tempty_bar[buf]);
+        }
+        // flush this CTA's list for the query
+        if (q_valid) {
+            uint64_t* out = p.cand + (static_cast<int64_t>(m_tile * kK2BlockM + row) * p.slots + slot) * p.kprime;
+            const int count = static_cast<int>(state & 0xffffu);
+            for (int i = 0; i < p.kprime; ++i) out[i] = i < count ? my_list[i * 128] : 0ull;
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, kK2TmemCols);
+    }
+}
+
+// ---- K5: exact rescore of the candidates, final top-k, proof of exactness ------------------------
+struct K5Params {
+    const __half* rows;
+    const float* inv_norm;
+    const float* queries;       // [*, dim] fp32 originals
+    const int32_t* q_map;       // slot -> query index in the caller's batch (or nullptr = identity)
+    const uint64_t* cand;       // [n, slots, kprime]
+    const float* invq;          // [n]
+    const float* eps;           // [n]
+    float* out_scores;
+    int64_t* out_rows;
+    int32_t* out_nvalid;
+    uint64_t* out_keys;
+    int32_t* flagged;           // [n] slots whose result is not proven
+    int32_t* n_flagged;
+    float max_norm;             // largest row norm (inner-product margin)
+    uint32_t row_offset;
+    int32_t dim;
+    int32_t k;
+    int32_t kprime;
+    int32_t slots;
+    int32_t metric;
+};
+
+template <int KPL>
+__global__ void __launch_bounds__(256) k5_rescore_kernel(const __grid_constant__ K5Params p) {
+    extern __shared__ float s_q[];   // [dim]
+    __shared__ uint64_t xchg[2][32];
+    __shared__ uint64_t s_out[kMaxTopK];
+    __shared__ float s_tau[8];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int slot_q = blockIdx.x;
+    const int qi = p.q_map ? p.q_map[slot_q] : slot_q;
+    const bool cosine = (p.metric == 0);
+    const int chunks = p.dim >> 3;
+    for (int i = threadIdx.x; i < p.dim; i += 256) s_q[i] = p.queries[static_cast<int64_t>(qi) * p.dim + i];
+    __syncthreads();
+
+    const uint64_t* cand = p.cand + static_cast<int64_t>(slot_q) * p.slots * p.kprime;
+    const int n_cand = p.slots * p.kprime;
+
+    // tau_max: the best "k'-th approximate score" among FULL slot lists
+    float tau = __uint_as_float(0xff800000u);
+    for (int s = threadIdx.x; s < p.slots; s += 256) {
+        bool full = true;
+        uint64_t m = ~0ull;
+        for (int i = 0; i < p.kprime; ++i) {
+            const uint64_t e = cand[s * p.kprime + i];
+            full &= (e != 0ull);
+            m = e < m ? e : m;
+        }
+        if (full) tau = fmaxf(tau, key_score(m));
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) tau = fmaxf(tau, __shfl_xor_sync(CRB_FULL_MASK, tau, o));
+    if (lane == 0) s_tau[warp] = tau;
+
+    // exact canonical score of every candidate (warp per candidate)
+    WarpTopK<KPL> top;
+    top.init(p.k, lane);
+    for (int c = warp; c < n_cand; c += 8) {
+        const uint64_t e = cand[c];
+        if (e == 0ull) continue;                       // warp-uniform
+        const uint32_t row = key_row(e);
+        const __half* rp = p.rows + static_cast<int64_t>(row) * p.dim;
+        float acc = 0.f;
+        for (int ch = lane; ch < chunks; ch += 32) {
+            const uint4 v = ld_stream_16(rp + ch * 8);
+            float q8[8];
+            const float4 a = *reinterpret_cast<const float4*>(s_q + ch * 8);
+            const float4 b = *reinterpret_cast<const float4*>(s_q + ch * 8 + 4);
+            q8[0] = a.x; q8[1] = a.y; q8[2] = a.z; q8[3] = a.w;
+            q8[4] = b.x; q8[5] = b.y; q8[6] = b.z; q8[7] = b.w;
+            acc = chunk_fma(v, q8, acc);
+        }
+        const float invn = cosine ? __ldg(p.inv_norm + row) : 1.0f;
+        const float s = warp_butterfly_sum(acc) * invn;
+        if (!(cosine && invn == 0.f) && s == s) {
+            const uint64_t key = make_key(s, p.row_offset + row);
+            if (key > top.thr) top.insert(key, lane);
+        }
+    }
+    block_extract_topk<KPL>(top, p.k, s_out, xchg, lane, warp, 8);
+
+    if (threadIdx.x == 0) {
+        float tau_max = s_tau[0];
+        for (int w = 1; w < 8; ++w) tau_max = fmaxf(tau_max, s_tau[w]);
+        const float iq = p.invq[slot_q];
+        TopKSink sink;
+        sink.scores = p.out_scores + static_cast<int64_t>(qi) * p.k;
+        sink.rows = p.out_rows + static_cast<int64_t>(qi) * p.k;
+        sink.n_valid = p.out_nvalid + qi;
+        sink.keys = p.out_keys ? p.out_keys + static_cast<int64_t>(qi) * p.k : nullptr;
+        sink.scale = cosine ? iq : 1.0f;
+        int nv = 0;
+        for (int r = 0; r < p.k; ++r) {
+            sink.emit(r, s_out[r]);
+            nv += (s_out[r] != 0ull);
+        }
+        *sink.n_valid = nv;
+        // proof: every non-candidate row has exact (normalised) score <= tau_max + margin
+        bool proven;
+        if (tau_max == __uint_as_float(0xff800000u)) {
+            proven = true;                              // no slot list overflowed: nothing was dropped
+        } else if (nv < p.k) {
+            proven = false;
+        } else {
+            const float margin = p.eps[slot_q] * (cosine ? 1.0f : p.max_norm);
+            const float kth = key_score(s_out[p.k - 1]) * iq;   // same units as the approximate scores
+            proven = kth > tau_max + margin;
+        }
+        if (!proven) {
+            const int at = atomicAdd(p.n_flagged, 1);
+            p.flagged[at] = slot_q;
+        }
+    }
+}
+
+// Largest row norm = 1 / smallest positive inverse norm (inner-product margin of K5).
+__global__ void __launch_bounds__(256) min_pos_inv_norm_kernel(const float* __restrict__ inv_norm, int64_t n,
+                                                               unsigned* __restrict__ out_bits) {
+    float m = __uint_as_float(0x7f800000u);
+    for (int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < n;
+         i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
+        const float v = inv_norm[i];
+        if (v > 0.f) m = fminf(m, v);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) m = fminf(m, __shfl_xor_sync(CRB_FULL_MASK, m, o));
+    if ((threadIdx.x & 31) == 0) atomicMin(out_bits, __float_as_uint(m));   // positive floats order as uints
+}
+
+}  // namespace crb

@@ -20,6 +20,8 @@ struct K3Params {
     const int32_t* codes;  // [n_keys, n_rows]
     uint32_t* lists;       // [n_filters, list_stride]
     uint32_t* counts;      // [n_filters], zero on entry
+    uint32_t* masks;       // [n_filters, mask_stride] one pass bit per row (for K2), or nullptr
+    int64_t mask_stride;
     int64_t n_rows;
     int64_t list_stride;
     int32_t n_keys;
@@ -88,7 +90,10 @@ __global__ void __launch_bounds__(kK3Threads) k3_filter_kernel(const __grid_cons
         for (int j = 0; j < kK3RowsPerThread; ++j) {
             const uint32_t bit = (pass[j] >> f) & 1u;
             const uint32_t b = __ballot_sync(CRB_FULL_MASK, bit);
-            if (bit) list[off + __popc(b & lt)] = static_cast<uint32_t>(blk0 + j * kK3Threads + threadIdx.x);
+            const int64_t row = blk0 + j * kK3Threads + threadIdx.x;
+            if (bit) list[off + __popc(b & lt)] = static_cast<uint32_t>(row);
+            // the warp's 32 rows are consecutive and 32-aligned: one mask word per ballot
+            if (p.masks && lane == 0 && row < p.n_rows) p.masks[static_cast<int64_t>(f) * p.mask_stride + (row >> 5)] = b;
             off += __popc(b);
         }
     }

@@ -1,0 +1,117 @@
+"""GPU tests of the tensor-core path (K2 candidates + K5 exact rescore) through the C ABI.
+K2 must return exactly what the streaming kernel (K1) returns -- same rows, same score bits --
+because every returned score comes from the canonical exact scorer; and both must match the
+oracle within the stated tolerance."""
+import numpy as np
+import pytest
+
+import oracle
+from githubrepostorag_b200 import synthetic as S
+from tests.test_gpu_parity import _check, _mode_name, _shard
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def torch_cuda():
+    import torch
+    assert torch.cuda.is_available()
+    return torch
+
+
+def _both(sh, torch, q, k, mode, filt=None):
+    qd = torch.from_numpy(q).cuda()
+    r1 = [t.clone() for t in sh.search_device(qd, k, metric=_mode_name(mode), filt=filt, algo=1)]
+    r2 = [t.clone() for t in sh.search_device(qd, k, metric=_mode_name(mode), filt=filt, algo=2)]
+    torch.cuda.synchronize()
+    return r1, r2
+
+
+@pytest.mark.parametrize("n,d", [(100_000, 768), (70_001, 384), (40_000, 1024), (33_000, 264)])
+def test_k2_equals_k1_bitwise_and_matches_oracle(torch_cuda, n, d):
+    torch = torch_cuda
+    rows16 = S.corpus(300 + d, n, d)
+    sh = _shard(torch, rows16)
+    for mode in (oracle.MODE_COSINE, oracle.MODE_DOT):
+        for batch, k in ((1, 10), (5, 10), (130, 20), (300, 5), (64, 100), (3, 128)):
+            q = S.queries(1000 + batch + k, batch, d)
+            (s1, r1, v1), (s2, r2, v2) = _both(sh, torch, q, k, mode)
+            assert torch.equal(r1, r2), f"rows differ n={n} d={d} B={batch} k={k} {mode}"
+            assert torch.equal(v1, v2)
+            assert torch.equal(s1.view(torch.int32), s2.view(torch.int32))
+            nq = min(batch, 3)
+            _check(q[:nq], rows16, s2.cpu().numpy()[:nq], r2.cpu().numpy()[:nq], v2.cpu().numpy()[:nq], k, mode,
+                   what=f"K2 n={n} d={d} B={batch} k={k} {mode}")
+    sh.close()
+
+
+def test_k2_with_filters_and_mixed_batch(torch_cuda):
+    torch = torch_cuda
+    n, d, k = 120_000, 384, 10
+    seed = S.BASE_SEEDS["C4"]
+    rows16 = S.corpus(seed, n, d)
+    codes = S.metadata_codes(seed, n)
+    code_mat = np.stack([codes[kk] for kk in S.FILTER_KEYS]).astype(np.int32)
+    sh = _shard(torch, rows16, code_mat)
+    batch = 200
+    q = S.queries(seed, batch, d)
+    filt = np.full((batch, 4), -1, np.int32)
+    filt[:120] = [0, -1, -1, -1]          # 120 queries share namespace=default
+    filt[120:150] = [1, -1, 1, -1]        # 30 share namespace=acme AND branch=dev
+    filt[150:153] = [-1, 7, -1, -1]       # 3 with a selective repo filter (streaming kernel)
+    filt[153] = [-1, -2, -1, -1]          # impossible
+    (s1, r1, v1), (s2, r2, v2) = _both(sh, torch, q, k, oracle.MODE_COSINE, filt=filt)
+    assert torch.equal(r1, r2) and torch.equal(v1, v2) and torch.equal(s1.view(torch.int32), s2.view(torch.int32))
+    keep = np.ones((batch, n), dtype=bool)
+    for b in range(batch):
+        for m in range(4):
+            if filt[b, m] == -2:
+                keep[b] = False
+            elif filt[b, m] >= 0:
+                keep[b] &= code_mat[m] == filt[b, m]
+    pick = [0, 119, 120, 149, 150, 153, 154, 199]
+    _check(q[pick], rows16, s2.cpu().numpy()[pick], r2.cpu().numpy()[pick], v2.cpu().numpy()[pick], k,
+           oracle.MODE_COSINE, keep=keep[pick], what="K2 filtered")
+    # default dispatch (algo 0) gives the same answer
+    s0, r0, v0 = sh.search_host(q, k, filt=filt)
+    assert np.array_equal(r0, r2.cpu().numpy()) and np.array_equal(s0, s2.cpu().numpy())
+    sh.close()
+
+
+def test_k2_unprovable_queries_fall_back_to_streaming(torch_cuda):
+    """Ties at the k-th boundary cannot be proven by the margin test: the library must notice and
+    re-run those queries exactly."""
+    torch = torch_cuda
+    n, d, k = 50_000, 128, 10
+    rng = np.random.default_rng(17)
+    rows16 = rng.standard_normal((n, d), dtype=np.float32).astype(np.float16)
+    rows16[1000:30_000] = rows16[1000]      # 29k bit-identical rows
+    q = np.stack([rows16[1000].astype(np.float32), rng.standard_normal(d, dtype=np.float32)] * 3)
+    sh = _shard(torch, rows16)
+    (s1, r1, v1), (s2, r2, v2) = _both(sh, torch, q, k, oracle.MODE_COSINE)
+    assert torch.equal(r1, r2) and torch.equal(s1.view(torch.int32), s2.view(torch.int32))
+    assert r2[0].tolist() == list(range(29_999, 29_989, -1))
+    sh.close()
+
+
+def test_k2_sharded_equals_unsharded(torch_cuda):
+    torch = torch_cuda
+    from githubrepostorag_b200.index import merge_keys
+    n, d, k, b = 90_000, 384, 10, 40
+    rows16 = S.corpus(88, n, d)
+    q = S.queries(88, b, d)
+    qd = torch.from_numpy(q).cuda()
+    whole = _shard(torch, rows16)
+    s0, r0, v0 = [t.clone() for t in whole.search_device(qd, k, algo=2)]
+    cuts = [0, 40_000, n]
+    keys = torch.empty((2, b, k), dtype=torch.int64, device="cuda")
+    shards = []
+    for i in range(2):
+        sh = _shard(torch, rows16[cuts[i]:cuts[i + 1]], row_offset=cuts[i])
+        sh.search_device(qd, k, keys_out=keys[i], algo=2)
+        shards.append(sh)
+    s1, r1, v1, _ = merge_keys(keys, qd, k)
+    torch.cuda.synchronize()
+    assert torch.equal(r0, r1) and torch.equal(s0.view(torch.int32), s1.view(torch.int32))
+    for sh in shards + [whole]:
+        sh.close()
