@@ -124,6 +124,7 @@ struct crb_index {
     float max_norm = 0.f;          // largest row norm (K5 inner-product margin)
     bool k2_ok = false;            // corpus tensor map encoded
     CUtensorMap map_rows;          // fp16 [n_rows, dim], box 64 x 256, 128 B swizzle
+    CUtensorMap map_rows_half;     // same, box 64 x 128 (one CTA's half tile in the pair kernel)
     std::mutex mu;
     std::condition_variable cv;
     std::vector<crb::Lane> lanes;
@@ -310,16 +311,20 @@ static int launch_k2(crb_index* ix, const float* d_queries, int batch, int k, in
     const int kprime = k2_kprime(k);
     const size_t list_bytes = size_t(kprime) * 128 * 8;
     const size_t tail_bytes = 2 * kK2BlockN * 4 + 256;
-    int stages = static_cast<int>((size_t(227) * 1024 - 1024 - list_bytes - tail_bytes) / kK2StageBytes);
-    stages = std::min(stages, 4);
-    if (stages < 2) return fail("internal: K2 does not fit shared memory for k'=%d", kprime);
-    const size_t smem = 1024 + size_t(stages) * kK2StageBytes + list_bytes + tail_bytes;
+    const size_t smem_room = size_t(227) * 1024 - 1024 - list_bytes - tail_bytes;
+    const int stages1 = static_cast<int>(std::min<size_t>(smem_room / kK2StageBytes, 4));
+    const int stages2 = static_cast<int>(std::min<size_t>(smem_room / kK2PairStageBytes, 8));
+    if (stages1 < 2) return fail("internal: K2 does not fit shared memory for k'=%d", kprime);
     static std::once_flag attr_once;
     static cudaError_t attr_err = cudaSuccess;
     std::call_once(attr_once, [] {
         attr_err = cudaFuncSetAttribute(k2_gemm_topk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+        if (attr_err == cudaSuccess)
+            attr_err = cudaFuncSetAttribute(k2_gemm_topk_pair_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
     });
     CRB_CUDA(attr_err);
+    // CTA pairs (cta_group::2) pay off once there are >= 2 query tiles; CODERAG_B200_K2_PAIR=0/1 forces.
+    const int pair_env = env_int("CODERAG_B200_K2_PAIR", -1);
 
     __half* q16 = reinterpret_cast<__half*>(ws + L.q16);
     float* invq = reinterpret_cast<float*>(ws + L.invq);
@@ -353,12 +358,25 @@ static int launch_k2(crb_index* ix, const float* d_queries, int batch, int k, in
         kp.dim = ix->dim;
         kp.kprime = kprime;
         kp.metric = metric;
-        kp.m_tiles = (n + kK2BlockM - 1) / kK2BlockM;
-        kp.slots = std::max(1, ix->sm_count / kp.m_tiles);
         const int64_t n_tiles = (ix->n_rows + kK2BlockN - 1) / kK2BlockN;
-        kp.slots = static_cast<int>(std::min<int64_t>(kp.slots, std::max<int64_t>(n_tiles, 1)));
-        kp.stages = stages;
-        k2_gemm_topk_kernel<<<kp.m_tiles * kp.slots, kK2Threads, smem, stream>>>(map_q, ix->map_rows, kp);
+        const bool use_pair = pair_env >= 0 ? (pair_env != 0) : (n > kK2BlockM);
+        kp.prefetch = env_int("CODERAG_B200_K2_PREFETCH", 0);
+        kp.debug = env_int("CODERAG_B200_K2_DEBUG", 0);
+        if (use_pair) {
+            kp.m_tiles = (n + 255) / 256;                       // query tile PAIRS
+            kp.slots = std::max(1, (ix->sm_count / 2) / kp.m_tiles);
+            kp.slots = static_cast<int>(std::min<int64_t>(kp.slots, std::max<int64_t>(n_tiles, 1)));
+            kp.stages = stages2;
+            const size_t smem = 1024 + size_t(stages2) * kK2PairStageBytes + list_bytes + tail_bytes;
+            k2_gemm_topk_pair_kernel<<<2 * kp.m_tiles * kp.slots, kK2Threads, smem, stream>>>(map_q, ix->map_rows_half, kp);
+        } else {
+            kp.m_tiles = (n + kK2BlockM - 1) / kK2BlockM;
+            kp.slots = std::max(1, ix->sm_count / kp.m_tiles);
+            kp.slots = static_cast<int>(std::min<int64_t>(kp.slots, std::max<int64_t>(n_tiles, 1)));
+            kp.stages = stages1;
+            const size_t smem = 1024 + size_t(stages1) * kK2StageBytes + list_bytes + tail_bytes;
+            k2_gemm_topk_kernel<<<kp.m_tiles * kp.slots, kK2Threads, smem, stream>>>(map_q, ix->map_rows, kp);
+        }
         CRB_LAUNCH_CHECK();
 
         CRB_CUDA(cudaMemsetAsync(nflag, 0, 4, stream));
@@ -678,7 +696,8 @@ extern "C" int crb_index_create(crb_index** out, const void* d_rows_f16, const f
     ix->sm_count = prop.multiProcessorCount;
     ix->lanes.resize(std::max(1, env_int("CODERAG_B200_LANES", 4)));
     // tensor-core path set-up: corpus tensor map and the largest row norm
-    if (n_rows > 0 && make_map_f16(&ix->map_rows, d_rows_f16, n_rows, dim, kK2BlockN) == 0) {
+    if (n_rows > 0 && make_map_f16(&ix->map_rows, d_rows_f16, n_rows, dim, kK2BlockN) == 0 &&
+        make_map_f16(&ix->map_rows_half, d_rows_f16, n_rows, dim, kK2BlockN / 2) == 0) {
         unsigned* d_bits = nullptr;
         const unsigned inf_bits = 0x7f800000u;
         unsigned h_bits = inf_bits;

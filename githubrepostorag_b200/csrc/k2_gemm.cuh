@@ -47,6 +47,8 @@ struct K2Params {
     int32_t m_tiles;
     int32_t slots;              // CTAs per m-tile; grid = m_tiles * slots
     int32_t stages;
+    int32_t prefetch;           // L2-prefetch the next corpus tile
+    int32_t debug;              // timing experiments only: 1 = no TMA after the first fill, 2 = no epilogue math
 };
 
 // ---- PTX wrappers ------------------------------------------------------------------------------
@@ -77,6 +79,10 @@ CRB_DEVINL void tma_load_2d(const CUtensorMap* map, void* smem_dst, uint64_t* ba
         "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
         ::"r"(smem_u32(smem_dst)), "l"(reinterpret_cast<uint64_t>(map)), "r"(smem_u32(bar)), "r"(c0), "r"(c1)
         : "memory");
+}
+CRB_DEVINL void tma_prefetch_l2_2d(const CUtensorMap* map, int32_t c0, int32_t c1) {
+    asm volatile("cp.async.bulk.prefetch.tensor.2d.L2.global.tile [%0, {%1, %2}];"
+                 ::"l"(reinterpret_cast<uint64_t>(map)), "r"(c0), "r"(c1) : "memory");
 }
 CRB_DEVINL void tmem_alloc(uint32_t* smem_dst, uint32_t cols) {
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(smem_dst)), "r"(cols));
@@ -121,29 +127,76 @@ CRB_DEVINL uint64_t umma_desc_sw128(uint32_t smem_addr) {
 // kind::f16 instruction descriptor: D = f32, A = B = f16, both K-major, M = 128, N = 256.
 constexpr uint32_t kK2IDesc = (1u << 4) | ((kK2BlockN >> 3) << 17) | ((kK2BlockM >> 4) << 24);
 
-// Insert `key` into a thread-private unsorted k'-entry list (entry i at list[i*128]); returns the
-// new {admission threshold bits, count | minpos << 16}.  Kept out of line: the epilogue has 32
-// call sites per TMEM chunk and the call is rare after warm-up.
+// Insert `key` into a thread-private k'-entry candidate list (entry i at list[i*128]); returns the
+// new {admission threshold bits, count}.  The list fills as a plain array, is turned into a
+// binary MIN-heap when it reaches k' entries, and from then on an admitted key replaces the root
+// and sifts down (O(log k')).  Kept out of line: the epilogue has 32 call sites per chunk and the
+// call is rare after warm-up.
+CRB_DEVINL void k2_sift_down(uint64_t* list, int i, int n, uint64_t key) {
+    for (;;) {
+        int c = 2 * i + 1;
+        if (c >= n) break;
+        uint64_t cv = list[c * 128];
+        if (c + 1 < n) {
+            const uint64_t rv = list[(c + 1) * 128];
+            if (rv < cv) { cv = rv; ++c; }
+        }
+        if (cv >= key) break;
+        list[i * 128] = cv;
+        i = c;
+    }
+    list[i * 128] = key;
+}
 __device__ __noinline__ uint2 k2_list_insert(uint64_t* list, uint64_t key, uint32_t state, float thr, int kprime) {
-    int count = static_cast<int>(state & 0xffffu);
-    int minpos = static_cast<int>(state >> 16);
+    int count = static_cast<int>(state);
     if (count < kprime) {
         list[count * 128] = key;
         ++count;
-    } else {
-        list[minpos * 128] = key;
-    }
-    if (count == kprime) {
-        uint64_t m = list[0];
-        int mp = 0;
-        for (int i = 1; i < kprime; ++i) {
-            const uint64_t e = list[i * 128];
-            if (e < m) { m = e; mp = i; }
+        if (count == kprime) {
+            for (int i = kprime / 2 - 1; i >= 0; --i) k2_sift_down(list, i, kprime, list[i * 128]);
+            thr = key_score(list[0]);
         }
-        minpos = mp;
-        thr = key_score(m);
+    } else {
+        k2_sift_down(list, 0, kprime, key);
+        thr = key_score(list[0]);
     }
-    return make_uint2(__float_as_uint(thr), static_cast<uint32_t>(count) | (static_cast<uint32_t>(minpos) << 16));
+    return make_uint2(__float_as_uint(thr), static_cast<uint32_t>(count));
+}
+
+CRB_DEVINL float4 lds_f4(uint32_t saddr) {
+    float4 r;
+    asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "r"(saddr));
+    return r;
+}
+
+// Examine one 32-column chunk of this thread's accumulator row: scale, and admit columns that
+// beat the thread's threshold.  `inv_saddr` is the shared-window address of the chunk's scales.
+CRB_DEVINL float k2_scan_chunk(const uint32_t (&v)[32], uint32_t inv_saddr, float thr, uint32_t& state,
+                               uint64_t* my_list, int64_t n_first, int kprime) {
+    float s[32];
+#pragma unroll
+    for (int g = 0; g < 8; ++g) {
+        const float4 w = lds_f4(inv_saddr + g * 16);
+        s[4 * g + 0] = __uint_as_float(v[4 * g + 0]) * w.x;
+        s[4 * g + 1] = __uint_as_float(v[4 * g + 1]) * w.y;
+        s[4 * g + 2] = __uint_as_float(v[4 * g + 2]) * w.z;
+        s[4 * g + 3] = __uint_as_float(v[4 * g + 3]) * w.w;
+    }
+    // fmaxf drops NaNs (masked / out-of-range columns), so `best` is the largest real score
+    float best = s[0];
+#pragma unroll
+    for (int j = 1; j < 32; ++j) best = fmaxf(best, s[j]);
+    if (best > thr) {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+            if (s[j] > thr) {
+                const uint2 r = k2_list_insert(my_list, make_key(s[j], static_cast<uint32_t>(n_first + j)), state, thr, kprime);
+                thr = __uint_as_float(r.x);
+                state = r.y;
+            }
+        }
+    }
+    return thr;
 }
 
 // ---- query preparation -------------------------------------------------------------------------
@@ -232,13 +285,23 @@ k2_gemm_topk_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_cons
             int st = 0;
             uint32_t ph = 0;
             for (int64_t t = slot; t < n_tiles; t += p.slots) {
+                // One CTA of each slot pulls the slot's NEXT corpus tile into L2 a whole tile-time
+                // ahead, so the demand loads below (and those of the other query tiles) hit L2.
+                if (p.prefetch && m_tile == 0 && t + p.slots < n_tiles) {
+                    for (int kb = 0; kb < k_blocks; ++kb)
+                        tma_prefetch_l2_2d(&map_c, kb * kK2BlockK, static_cast<int32_t>((t + p.slots) * kK2BlockN));
+                }
                 for (int kb = 0; kb < k_blocks; ++kb) {
                     mbar_wait(&empty_bar[st], ph ^ 1u);
                     uint8_t* a = stage_base + static_cast<size_t>(st) * kK2StageBytes;
                     uint8_t* b = a + kK2StageBytesA;
-                    mbar_expect_tx(&full_bar[st], kK2StageBytes);
-                    tma_load_2d(&map_q, a, &full_bar[st], kb * kK2BlockK, m_tile * kK2BlockM);
-                    tma_load_2d(&map_c, b, &full_bar[st], kb * kK2BlockK, static_cast<int32_t>(t * kK2BlockN));
+                    if ((p.debug & 1) && (t != slot || kb >= p.stages)) {
+                        mbar_arrive(&full_bar[st]);
+                    } else {
+                        mbar_expect_tx(&full_bar[st], kK2StageBytes);
+                        tma_load_2d(&map_q, a, &full_bar[st], kb * kK2BlockK, m_tile * kK2BlockM);
+                        tma_load_2d(&map_c, b, &full_bar[st], kb * kK2BlockK, static_cast<int32_t>(t * kK2BlockN));
+                    }
                     if (++st == p.stages) { st = 0; ph ^= 1u; }
                 }
             }
@@ -281,56 +344,57 @@ k2_gemm_topk_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_cons
         const bool q_valid = (m_tile * kK2BlockM + row) < p.batch;
         const bool cosine = (p.metric == 0);
         uint64_t* my_list = lists + et;               // entry i at my_list[i * 128]
-        uint32_t state = 0;                           // count | minpos << 16
+        uint32_t state = 0;                           // entries in the list
         float thr = q_valid ? __uint_as_float(0xff800000u) : __uint_as_float(0x7f800000u);  // -inf / +inf
         const float qnan = __uint_as_float(0x7fc00000u);
+        auto column_scale = [&](int64_t n) -> float {
+            if (n >= p.n_rows) return qnan;
+            if (p.mask && !((p.mask[n >> 5] >> (n & 31)) & 1u)) return qnan;
+            if (!cosine) return 1.0f;
+            const float in = __ldg(p.inv_norm + n);
+            return in > 0.f ? in : qnan;
+        };
+        float pre[2] = {qnan, qnan};
 
         int64_t it = 0;
         for (int64_t t = slot; t < n_tiles; t += p.slots, ++it) {
             const int buf = static_cast<int>(it & 1);
             const uint32_t use = static_cast<uint32_t>(it >> 1);
             const int64_t n0 = t * kK2BlockN;
-            // stage per-column scale: inv_norm (cosine) or 1 (ip); NaN = "this column is not a hit"
+            // per-column scale: inv_norm (cosine) or 1 (ip); NaN = "this column is not a hit".
+            // The values for THIS tile were fetched from global memory during the previous tile.
             float* inv = s_inv + buf * kK2BlockN;
-#pragma unroll
-            for (int h = 0; h < 2; ++h) {
-                const int c = tid_e + h * 128;
-                const int64_t n = n0 + c;
-                float v = qnan;
-                if (n < p.n_rows) {
-                    bool pass = true;
-                    if (p.mask) pass = (p.mask[n >> 5] >> (n & 31)) & 1u;
-                    if (pass) {
-                        if (cosine) {
-                            const float in = __ldg(p.inv_norm + n);
-                            v = in > 0.f ? in : qnan;
-                        } else {
-                            v = 1.0f;
-                        }
-                    }
-                }
-                inv[c] = v;
+            if (it == 0) { pre[0] = column_scale(n0 + tid_e); pre[1] = column_scale(n0 + tid_e + 128); }
+            inv[tid_e] = pre[0];
+            inv[tid_e + 128] = pre[1];
+            if (t + p.slots < n_tiles) {
+                const int64_t nn = (t + p.slots) * kK2BlockN;
+                pre[0] = column_scale(nn + tid_e);
+                pre[1] = column_scale(nn + tid_e + 128);
             }
             epi_bar_sync();
             mbar_wait(&tfull_bar[buf], use & 1u);
             tc_fence_after();
             const uint32_t t_row = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) +
                                    static_cast<uint32_t>(buf * kK2BlockN);
-#pragma unroll 1
-            for (int c = 0; c < kK2BlockN / 32; ++c) {
-                uint32_t v[32];
-                tmem_ld32(t_row + c * 32, v);
+            // TMEM -> registers one 32-column chunk ahead of the chunk being examined.  The common
+            // case per chunk is: 8 broadcast LDS.128 of the column scales, 32 FMUL, a max tree and
+            // ONE branch; only a chunk that holds a new candidate walks its 32 columns.
+            const uint32_t inv_s = smem_u32(inv);
+            const int n_chunks = (p.debug & 2) ? 0 : kK2BlockN / 32;
+            uint32_t va[32], vb[32];
+            if (n_chunks > 0) {
+                tmem_ld32(t_row, va);
                 tmem_ld_wait();
-#pragma unroll
-                for (int j = 0; j < 32; ++j) {
-                    const float s = __uint_as_float(v[j]) * inv[c * 32 + j];
-                    if (s > thr) {
-                        const uint2 r = k2_list_insert(my_list, make_key(s, static_cast<uint32_t>(n0 + c * 32 + j)),
-                                                       state, thr, p.kprime);
-                        thr = __uint_as_float(r.x);
-                        state = r.y;
-                    }
-                }
+            }
+#pragma unroll 1
+            for (int c = 0; c < n_chunks; c += 2) {
+                tmem_ld32(t_row + (c + 1) * 32, vb);
+                thr = k2_scan_chunk(va, inv_s + c * 128, thr, state, my_list, n0 + c * 32, p.kprime);
+                tmem_ld_wait();
+                if (c + 2 < n_chunks) tmem_ld32(t_row + (c + 2) * 32, va);
+                thr = k2_scan_chunk(vb, inv_s + (c + 1) * 128, thr, state, my_list, n0 + (c + 1) * 32, p.kprime);
+                tmem_ld_wait();
             }
             tc_fence_before();
             mbar_arrive(&tempty_bar[buf]);
@@ -338,7 +402,7 @@ k2_gemm_topk_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_cons
         // flush this CTA's list for the query
         if (q_valid) {
             uint64_t* out = p.cand + (static_cast<int64_t>(m_tile * kK2BlockM + row) * p.slots + slot) * p.kprime;
-            const int count = static_cast<int>(state & 0xffffu);
+            const int count = static_cast<int>(state);
             for (int i = 0; i < p.kprime; ++i) out[i] = i < count ? my_list[i * 128] : 0ull;
         }
     }
@@ -348,6 +412,229 @@ k2_gemm_topk_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_cons
     if (warp == 1) {
         tc_fence_after();
         tmem_dealloc(tmem_base, kK2TmemCols);
+    }
+}
+
+// ---- the CTA-pair variant (cta_group::2) ---------------------------------------------------------
+// Two CTAs of a cluster (one TPC) share one 256 x 256 MMA: each CTA stages its own 128 query rows
+// (A) and HALF of the corpus tile (128 rows of B), so a CTA moves 32 KB per k-block instead of
+// 48 KB for the same flops and the ring holds 6 stages instead of 4.  The leader (cluster rank 0)
+// issues tcgen05.mma.cta_group::2; each CTA's TMEM receives the accumulator rows of its own
+// queries, so the epilogue is the single-CTA one.
+//   full[st]   (leader's, count 2): leader arrive.expect_tx(64 KB) + peer remote arrive; both
+//              CTAs' TMA loads complete_tx on it
+//   empty[st]  (own, count 1):     leader's tcgen05.commit multicast to both CTAs
+//   tfull[b]   (own, count 1):     leader's tcgen05.commit multicast to both CTAs
+//   tempty[b]  (leader's, count 256): all epilogue threads of both CTAs
+constexpr int kK2PairStageBytesB = (kK2BlockN / 2) * kK2BlockK * 2;      // 16 KB: this CTA's half of B
+constexpr int kK2PairStageBytes = kK2StageBytesA + kK2PairStageBytesB;   // 32 KB
+constexpr uint32_t kK2PairIDesc = (1u << 4) | ((kK2BlockN >> 3) << 17) | ((256u >> 4) << 24);
+
+CRB_DEVINL uint32_t cluster_ctarank() {
+    uint32_t r;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+    return r;
+}
+CRB_DEVINL uint32_t mapa_u32(uint32_t saddr, uint32_t rank) {
+    uint32_t r;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(saddr), "r"(rank));
+    return r;
+}
+CRB_DEVINL void mbar_arrive_cluster(uint32_t cluster_addr) {
+    asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+}
+CRB_DEVINL void cluster_sync_all() {
+    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+CRB_DEVINL void tma_load_2d_pair(const CUtensorMap* map, void* smem_dst, uint32_t bar_cluster_addr, int32_t c0, int32_t c1) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+        ::"r"(smem_u32(smem_dst)), "l"(reinterpret_cast<uint64_t>(map)), "r"(bar_cluster_addr), "r"(c0), "r"(c1)
+        : "memory");
+}
+CRB_DEVINL void tmem_alloc_pair(uint32_t* smem_dst, uint32_t cols) {
+    asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(smem_dst)), "r"(cols));
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::);
+}
+CRB_DEVINL void tmem_dealloc_pair(uint32_t taddr, uint32_t cols) {
+    asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(cols));
+}
+CRB_DEVINL void umma_f16_pair(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t"
+        "}" ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate) : "memory");
+}
+CRB_DEVINL void umma_commit_pair(uint64_t* bar) {
+    asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+                 ::"r"(smem_u32(bar)), "h"(static_cast<uint16_t>(3)) : "memory");
+}
+
+// grid = 2 * m_pairs * slots CTAs in clusters of 2.  Pair P serves query rows
+// [ (P % m_pairs) * 256, +256 ) and corpus tiles  P / m_pairs + i * slots.  (p.m_tiles = m_pairs.)
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kK2Threads, 1)
+k2_gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant__ CUtensorMap map_c,
+                         const __grid_constant__ K2Params p) {
+    extern __shared__ __align__(1024) uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint8_t* stage_base = smem;
+    uint64_t* lists = reinterpret_cast<uint64_t*>(smem + static_cast<size_t>(p.stages) * kK2PairStageBytes);
+    float* s_inv = reinterpret_cast<float*>(lists + static_cast<size_t>(p.kprime) * 128);
+    uint64_t* bars = reinterpret_cast<uint64_t*>(s_inv + 2 * kK2BlockN);
+    uint64_t* full_bar = bars;
+    uint64_t* empty_bar = bars + p.stages;
+    uint64_t* tfull_bar = bars + 2 * p.stages;
+    uint64_t* tempty_bar = bars + 2 * p.stages + 2;
+    uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 2 * p.stages + 4);
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+    const uint32_t rank = cluster_ctarank();
+    const bool leader = (rank == 0);
+    const int pair = blockIdx.x >> 1;
+    const int m_pair = pair % p.m_tiles;
+    const int slot = pair / p.m_tiles;
+    const int m_row0 = m_pair * 256 + static_cast<int>(rank) * kK2BlockM;   // first query row of this CTA
+    const int64_t n_tiles = (p.n_rows + kK2BlockN - 1) / kK2BlockN;
+    const int k_blocks = (p.dim + kK2BlockK - 1) / kK2BlockK;
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < p.stages; ++s) {
+            mbar_init(&full_bar[s], 2);
+            mbar_init(&empty_bar[s], 1);
+        }
+        for (int b = 0; b < 2; ++b) {
+            mbar_init(&tfull_bar[b], 1);
+            mbar_init(&tempty_bar[b], 256);
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 1) tmem_alloc_pair(tmem_ptr, kK2TmemCols);
+    tc_fence_before();
+    cluster_sync_all();          // barriers of BOTH CTAs are initialised before anyone signals them
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_ptr;
+
+    if (warp == 0) {
+        // ===== TMA producer (one per CTA): own A rows + own half of the corpus tile =====
+        if (lane == 0) {
+            int st = 0;
+            uint32_t ph = 0;
+            for (int64_t t = slot; t < n_tiles; t += p.slots) {
+                for (int kb = 0; kb < k_blocks; ++kb) {
+                    mbar_wait(&empty_bar[st], ph ^ 1u);
+                    uint8_t* a = stage_base + static_cast<size_t>(st) * kK2PairStageBytes;
+                    uint8_t* b = a + kK2StageBytesA;
+                    const uint32_t full_leader = mapa_u32(smem_u32(&full_bar[st]), 0);
+                    if (leader) mbar_expect_tx(&full_bar[st], 2 * kK2PairStageBytes);
+                    tma_load_2d_pair(&map_q, a, full_leader, kb * kK2BlockK, m_row0);
+                    tma_load_2d_pair(&map_c, b, full_leader, kb * kK2BlockK,
+                                     static_cast<int32_t>(t * kK2BlockN + rank * (kK2BlockN / 2)));
+                    if (!leader) mbar_arrive_cluster(full_leader);
+                    if (++st == p.stages) { st = 0; ph ^= 1u; }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ===== MMA issuer: the leader CTA only =====
+        if (leader && lane == 0) {
+            int st = 0;
+            uint32_t ph = 0;
+            int64_t it = 0;
+            for (int64_t t = slot; t < n_tiles; t += p.slots, ++it) {
+                const int buf = static_cast<int>(it & 1);
+                const uint32_t use = static_cast<uint32_t>(it >> 1);
+                mbar_wait(&tempty_bar[buf], (use & 1u) ^ 1u);
+                tc_fence_after();
+                const uint32_t d_tmem = tmem_base + static_cast<uint32_t>(buf * kK2BlockN);
+                for (int kb = 0; kb < k_blocks; ++kb) {
+                    mbar_wait(&full_bar[st], ph);
+                    tc_fence_after();
+                    const uint32_t a_addr = smem_u32(stage_base + static_cast<size_t>(st) * kK2PairStageBytes);
+                    const uint32_t b_addr = a_addr + kK2StageBytesA;
+#pragma unroll
+                    for (int k = 0; k < kK2BlockK / kK2UmmaK; ++k) {
+                        const uint64_t da = umma_desc_sw128(a_addr + k * kK2UmmaK * 2);
+                        const uint64_t db = umma_desc_sw128(b_addr + k * kK2UmmaK * 2);
+                        umma_f16_pair(d_tmem, da, db, kK2PairIDesc, (kb | k) != 0 ? 1u : 0u);
+                    }
+                    umma_commit_pair(&empty_bar[st]);
+                    if (++st == p.stages) { st = 0; ph ^= 1u; }
+                }
+                umma_commit_pair(&tfull_bar[buf]);
+            }
+        }
+    } else {
+        // ===== epilogue: identical to the single-CTA kernel, on this CTA's 128 query rows =====
+        const int quarter = warp & 3;
+        const int row = quarter * 32 + lane;
+        const int tid_e = threadIdx.x - 64;
+        const bool q_valid = (m_row0 + row) < p.batch;
+        const bool cosine = (p.metric == 0);
+        uint64_t* my_list = lists + row;
+        uint32_t state = 0;
+        float thr = q_valid ? __uint_as_float(0xff800000u) : __uint_as_float(0x7f800000u);
+        const float qnan = __uint_as_float(0x7fc00000u);
+        auto column_scale = [&](int64_t n) -> float {
+            if (n >= p.n_rows) return qnan;
+            if (p.mask && !((p.mask[n >> 5] >> (n & 31)) & 1u)) return qnan;
+            if (!cosine) return 1.0f;
+            const float in = __ldg(p.inv_norm + n);
+            return in > 0.f ? in : qnan;
+        };
+        float pre[2] = {qnan, qnan};
+        int64_t it = 0;
+        for (int64_t t = slot; t < n_tiles; t += p.slots, ++it) {
+            const int buf = static_cast<int>(it & 1);
+            const uint32_t use = static_cast<uint32_t>(it >> 1);
+            const int64_t n0 = t * kK2BlockN;
+            float* inv = s_inv + buf * kK2BlockN;
+            if (it == 0) { pre[0] = column_scale(n0 + tid_e); pre[1] = column_scale(n0 + tid_e + 128); }
+            inv[tid_e] = pre[0];
+            inv[tid_e + 128] = pre[1];
+            if (t + p.slots < n_tiles) {
+                const int64_t nn = (t + p.slots) * kK2BlockN;
+                pre[0] = column_scale(nn + tid_e);
+                pre[1] = column_scale(nn + tid_e + 128);
+            }
+            epi_bar_sync();
+            mbar_wait(&tfull_bar[buf], use & 1u);
+            tc_fence_after();
+            const uint32_t t_row = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) +
+                                   static_cast<uint32_t>(buf * kK2BlockN);
+            const uint32_t inv_s = smem_u32(inv);
+            const int n_chunks = (p.debug & 2) ? 0 : kK2BlockN / 32;
+            uint32_t va[32], vb[32];
+            if (n_chunks > 0) {
+                tmem_ld32(t_row, va);
+                tmem_ld_wait();
+            }
+#pragma unroll 1
+            for (int c = 0; c < n_chunks; c += 2) {
+                tmem_ld32(t_row + (c + 1) * 32, vb);
+                thr = k2_scan_chunk(va, inv_s + c * 128, thr, state, my_list, n0 + c * 32, p.kprime);
+                tmem_ld_wait();
+                if (c + 2 < n_chunks) tmem_ld32(t_row + (c + 2) * 32, va);
+                thr = k2_scan_chunk(vb, inv_s + (c + 1) * 128, thr, state, my_list, n0 + (c + 1) * 32, p.kprime);
+                tmem_ld_wait();
+            }
+            tc_fence_before();
+            mbar_arrive_cluster(mapa_u32(smem_u32(&tempty_bar[buf]), 0));
+        }
+        if (q_valid) {
+            uint64_t* out = p.cand + (static_cast<int64_t>(m_row0 + row) * p.slots + slot) * p.kprime;
+            const int count = static_cast<int>(state);
+            for (int i = 0; i < p.kprime; ++i) out[i] = i < count ? my_list[i * 128] : 0ull;
+        }
+    }
+
+    tc_fence_before();
+    cluster_sync_all();          // the peer may still be reading this CTA's smem / signalling its barriers
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc_pair(tmem_base, kK2TmemCols);
     }
 }
 
