@@ -135,15 +135,21 @@ class ClockSampler:
 
 
 # ----------------------------------------------------------------------------- CPU baseline
+def blas_all_cores():
+    """torchrun exports OMP_NUM_THREADS=1; the CPU legs must use every host core they can."""
+    try:
+        from threadpoolctl import threadpool_info, threadpool_limits
+        threadpool_limits(limits=os.cpu_count() or 1)
+        return max([i.get("num_threads", 1) for i in threadpool_info()] or [1])
+    except Exception:
+        return 1
+
+
 def cpu_baseline(sample32: np.ndarray, n_rows_full: int, dim: int, batch: int, k: int, budget_s: float = 20.0):
     """The oracle's vectorised form (numpy fp32 = the reference CPU path restated) on a row
     sample, scaled linearly in rows to the full corpus."""
     import oracle
-    try:
-        from threadpoolctl import threadpool_info
-        threads = max([i.get("num_threads", 1) for i in threadpool_info()] or [1])
-    except Exception:
-        threads = os.cpu_count() or 1
+    threads = blas_all_cores()
     q = host_queries(max(batch, 1), dim, 0)
     oracle.query_vectorised(q[0], sample32[: 1 << 16], k)     # warm numpy/BLAS
     done, t0 = 0, time.perf_counter()
@@ -169,6 +175,7 @@ def run_reference(args):
     n_sample = min(CPU_SAMPLE_ROWS if args.steps <= 200 else CPU_SAMPLE_ROWS // 4, N_ROWS)
     sample32 = host_sample_rows(n_sample, DIM)
     import oracle
+    threads = blas_all_cores()
     q = host_queries(args.batch, DIM, 0)
     for w in range(args.warmup):
         oracle.query_vectorised(q[w % len(q)], sample32[: 1 << 17], TOPK)
@@ -182,11 +189,6 @@ def run_reference(args):
     el = time.perf_counter() - t0
     scale = n_sample / N_ROWS
     value = n_q / el * scale
-    try:
-        from threadpoolctl import threadpool_info
-        threads = max([i.get("num_threads", 1) for i in threadpool_info()] or [1])
-    except Exception:
-        threads = os.cpu_count() or 1
     sample = (f"first {n_sample:,} of {N_ROWS:,} rows x {DIM}, {n_q} single-query searches in {el:.1f}s, "
               f"scaled x{scale:.4g} (linear in rows); host cores {os.cpu_count()}, BLAS threads {threads}")
     line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
@@ -207,6 +209,14 @@ def workload_config(args, world):
 
 
 # ----------------------------------------------------------------------------- our arm
+def profile_traffic(kernel: str):
+    """DRAM bytes per launch from the committed ncu --set full capture (profiles/traffic.json)."""
+    p = ROOT / "profiles" / "traffic.json"
+    if p.exists():
+        return json.loads(p.read_text()).get(kernel)
+    return None
+
+
 def run_ours(args):
     import torch
     import torch.distributed as dist
@@ -223,110 +233,129 @@ def run_ours(args):
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     lo, hi = shard_range(N_ROWS, world, rank)
+    n_local = hi - lo
     rows = device_corpus(torch, lo, hi, DIM, dev)
     shard = DeviceShard.from_device(rows, None, row_offset=lo)
     torch.cuda.synchronize()
-
-    B, k = args.batch, TOPK
-    q_host = [torch.from_numpy(host_queries(B, DIM, i)).pin_memory() for i in range(N_QUERY_SETS)]
-    q_dev = [q.to(dev) for q in q_host]
     searcher = cuda_searcher(shard) if world > 1 else None
-    out = (torch.empty((B, k), dtype=torch.float32, device=dev), torch.empty((B, k), dtype=torch.int64, device=dev),
-           torch.empty((B,), dtype=torch.int32, device=dev))
-    ws = shard.new_workspace(B, k, 0)
-
-    def step_device(i):
-        q = q_dev[i % N_QUERY_SETS]
-        if world > 1:
-            return searcher.search(q, k)
-        return shard.search_device(q, k, out=out, workspace=ws)
+    k = TOPK
+    pk = peaks()
 
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
 
-    # ---- device-resident timing (value) ----
-    for i in range(args.warmup):
-        step_device(i)
-    barrier()
-    sampler = ClockSampler(local_rank)
-    if rank == 0:
-        sampler.start()
-    launches0 = _native.launch_count()
-    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    barrier()
-    ev0.record()
-    for i in range(args.steps):
-        res = step_device(i)
-    ev1.record()
-    barrier()
-    ms = ev0.elapsed_time(ev1)
-    launches = _native.launch_count() - launches0
-    clocks = sampler.stop() if rank == 0 else None
-    t = torch.tensor([ms], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms = float(t.item())
-    value = B * args.steps / (ms * 1e-3)
+    def max_over_ranks(x: float) -> float:
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
 
-    # ---- end to end through the host-buffer API (e2e) ----
-    res_host = [torch.empty((B, k), dtype=torch.float32).pin_memory(), torch.empty((B, k), dtype=torch.int64).pin_memory(),
-                torch.empty((B,), dtype=torch.int32).pin_memory()]
-    q_stage = torch.empty((B, DIM), dtype=torch.float32, device=dev)
+    def measure(B: int, steps: int, warmup: int, sample_clocks: bool):
+        q_host = [torch.from_numpy(host_queries(B, DIM, i)).pin_memory() for i in range(N_QUERY_SETS)]
+        q_dev = [q.to(dev) for q in q_host]
+        out = (torch.empty((B, k), dtype=torch.float32, device=dev), torch.empty((B, k), dtype=torch.int64, device=dev),
+               torch.empty((B,), dtype=torch.int32, device=dev))
+        ws = shard.new_workspace(B, k, 0)
 
-    def step_e2e(i):
-        if world == 1:
-            return shard.search_host(q_host[i % N_QUERY_SETS].numpy(), k)
-        # serving flow: rank 0 holds the request in pinned memory, everyone searches, rank 0 reads back
-        if rank == 0:
-            q_stage.copy_(q_host[i % N_QUERY_SETS], non_blocking=True)
-        s, r, v, _ = searcher.search(q_stage, k, broadcast=True)
-        if rank == 0:
-            res_host[0].copy_(s, non_blocking=True); res_host[1].copy_(r, non_blocking=True); res_host[2].copy_(v, non_blocking=True)
-        torch.cuda.current_stream().synchronize()
-        return res_host
+        def step_device(i):
+            q = q_dev[i % N_QUERY_SETS]
+            if world > 1:
+                return searcher.search(q, k)
+            return shard.search_device(q, k, out=out, workspace=ws)
 
-    e2e_steps = max(3, min(args.steps, 200))
-    for i in range(min(args.warmup, 5)):
-        step_e2e(i)
-    barrier()
-    t0 = time.perf_counter()
-    for i in range(e2e_steps):
-        step_e2e(i)
-    barrier()
-    e2e_s = time.perf_counter() - t0
-    t = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    e2e_value = B * e2e_steps / float(t.item())
+        # ---- device-resident timing (value) ----
+        for i in range(warmup):
+            step_device(i)
+        barrier()
+        sampler = ClockSampler(local_rank)
+        if rank == 0 and sample_clocks:
+            sampler.start()
+        launches0 = _native.launch_count()
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        barrier()
+        ev0.record()
+        for i in range(steps):
+            step_device(i)
+        ev1.record()
+        barrier()
+        ms = max_over_ranks(ev0.elapsed_time(ev1))
+        launches = _native.launch_count() - launches0
+        clocks = sampler.stop() if (rank == 0 and sample_clocks) else None
 
-    if rank == 0:
-        pk = peaks()
-        n_local = hi - lo
-        if args.batch <= 16:
+        # ---- end to end through the host-buffer API (e2e) ----
+        res_host = [torch.empty((B, k), dtype=torch.float32).pin_memory(), torch.empty((B, k), dtype=torch.int64).pin_memory(),
+                    torch.empty((B,), dtype=torch.int32).pin_memory()]
+        q_stage = torch.empty((B, DIM), dtype=torch.float32, device=dev)
+
+        def step_e2e(i):
+            if world == 1:
+                return shard.search_host(q_host[i % N_QUERY_SETS].numpy(), k)
+            # serving flow: rank 0 holds the request in pinned memory, everyone searches, rank 0 reads back
+            if rank == 0:
+                q_stage.copy_(q_host[i % N_QUERY_SETS], non_blocking=True)
+            s_, r_, v_, _ = searcher.search(q_stage, k, broadcast=True)
+            if rank == 0:
+                res_host[0].copy_(s_, non_blocking=True)
+                res_host[1].copy_(r_, non_blocking=True)
+                res_host[2].copy_(v_, non_blocking=True)
+            torch.cuda.current_stream().synchronize()
+            return res_host
+
+        e2e_steps = max(3, min(steps, 200))
+        for i in range(min(warmup, 5)):
+            step_e2e(i)
+        barrier()
+        t0 = time.perf_counter()
+        for i in range(e2e_steps):
+            step_e2e(i)
+        barrier()
+        e2e_s = max_over_ranks(time.perf_counter() - t0)
+
+        per_step_s = ms / steps * 1e-3
+        if B <= 4:
+            kern = "k1_stream_kernel"
             bytes_per_launch = n_local * DIM * 2          # algorithmic: fp16 shard read once per batch
-            achieved = bytes_per_launch / (ms / args.steps * 1e-3) / 1e9
-            roof = {"bound": "hbm", "kernel": "k1_stream_kernel", "achieved": achieved, "peak": pk["hbm_gbs"], "unit": "GB/s",
-                    "frac": achieved / pk["hbm_gbs"], "traffic": None, "peak_source": pk["source"],
+            achieved = bytes_per_launch / per_step_s / 1e9
+            roof = {"bound": "hbm", "kernel": kern, "achieved": achieved, "peak": pk["hbm_gbs"], "unit": "GB/s",
+                    "frac": achieved / pk["hbm_gbs"], "traffic": profile_traffic(kern) if world == 1 else None, "peak_source": pk["source"],
                     "algorithmic_bytes_per_launch": bytes_per_launch,
-                    "note": "step == one K1 launch per rank (merge fused in its last CTA); duration = CUDA-event step time"}
+                    "note": "a step is ONE K1 launch per rank (merge fused in its last CTA); duration = CUDA-event step time"}
         else:
+            kern = "k2_gemm_topk_pair_kernel" if B > 128 else "k2_gemm_topk_kernel"
             flops = 2.0 * B * n_local * DIM
-            achieved = flops / (ms / args.steps * 1e-3) / 1e12
-            peak = pk["bf16_tflops_sustained"]
-            roof = {"bound": "tensor", "kernel": "k2_gemm_topk_kernel", "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
-                    "frac": achieved / peak, "traffic": None, "peak_source": pk["source"] + " (sustained)",
-                    "algorithmic_flops_per_launch": flops}
+            achieved = flops / per_step_s / 1e12
+            roof = {"bound": "tensor", "kernel": kern, "achieved": achieved, "peak": pk["bf16_tflops_sustained"],
+                    "unit": "TFLOP/s", "frac": achieved / pk["bf16_tflops_sustained"],
+                    "frac_of_burst_peak": achieved / pk["bf16_tflops"], "traffic": profile_traffic(kern) if world == 1 else None,
+                    "peak_source": pk["source"] + " (sustained cuBLAS bf16; burst also given)",
+                    "algorithmic_flops_per_launch": flops,
+                    "note": "duration = CUDA-event step time (prep + K2 + K5 rescore; K2 is >98 % of it per the ncu launch list)"}
+        return {"value": B * steps / (ms * 1e-3), "ms_per_step": ms / steps, "steps": steps, "warmup": warmup,
+                "e2e": {"value": B * e2e_steps / e2e_s, "unit": UNIT, "h2d_bytes_per_step": B * DIM * 4,
+                        "d2h_bytes_per_step": B * k * 12 + B * 4, "steps": e2e_steps},
+                "gpu_launches": int(launches), "clocks": clocks, "roofline": roof}
+
+    main_m = measure(args.batch, args.steps, args.warmup, True)
+    second = None
+    if args.batch == 1 and not args.no_secondary:
+        second = measure(1024, max(5, min(40, args.steps // 10)), 3, True)
+
+    if rank == 0:
         n_sample = min(CPU_SAMPLE_ROWS, n_local)
         sample32 = rows[:n_sample].to(torch.float32).cpu().numpy()
-        base = cpu_baseline(sample32, N_ROWS, DIM, B, k, budget_s=args.cpu_budget)
-        line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-                "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
-                "dtype": "f16", "data": "synthetic", "config": workload_config(args, world),
-                "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": B * DIM * 4,
-                        "d2h_bytes_per_step": B * k * 12 + B * 4, "steps": e2e_steps},
-                "gpu_launches": int(launches), "clocks": clocks, "roofline": roof, "cpu_baseline": base}
+        base = cpu_baseline(sample32, N_ROWS, DIM, args.batch, k, budget_s=args.cpu_budget)
+        line = {"metric": METRIC, "value": main_m["value"], "unit": UNIT, "n_gpus": world, "steps": args.steps,
+                "warmup": args.warmup, "ms_per_step": main_m["ms_per_step"], "higher_is_better": True,
+                "scaling": "strong", "vs_baseline": None, "dtype": "f16", "data": "synthetic",
+                "config": workload_config(args, world), "e2e": main_m["e2e"], "gpu_launches": main_m["gpu_launches"],
+                "clocks": main_m["clocks"], "roofline": main_m["roofline"], "cpu_baseline": base}
+        if second is not None:
+            line["batch1024"] = {"workload": f"{N_ROWS // 1_000_000}Mx{DIM}_fp16_k{TOPK}_b1024", "value": second["value"],
+                                 "unit": UNIT, "ms_per_step": second["ms_per_step"], "steps": second["steps"],
+                                 "e2e": second["e2e"], "gpu_launches": second["gpu_launches"], "clocks": second["clocks"],
+                                 "roofline": second["roofline"]}
         print(json.dumps(line), flush=True)
     barrier()
     shard.close()
@@ -343,6 +372,7 @@ def main():
     ap.add_argument("--batch", type=int, default=1)
     ap.add_argument("--impl", choices=("ours", "reference"), default="ours")
     ap.add_argument("--cpu-budget", type=float, default=15.0)
+    ap.add_argument("--no-secondary", action="store_true", help="skip the batch-1024 (tensor-core) secondary measurement")
     args = ap.parse_args()
     if args.warmup < 3:
         args.warmup = 3

@@ -139,7 +139,7 @@ static int64_t mask_stride_of(const crb_index* ix) { return round_up((std::max<i
 struct WsLayout {
     size_t cand = kWsHeaderBytes;
     size_t k2 = 0;          // K2 region start
-    size_t q16 = 0, invq = 0, eps = 0, qmap = 0, flagged = 0, nflag = 0, cand2 = 0;   // inside the K2 region
+    size_t q16 = 0, invq = 0, eps = 0, qmap = 0, flagged = 0, nflag = 0, progress = 0, cand2 = 0;   // inside the K2 region
     size_t filt = 0;        // survivor lists start; masks follow the lists
     size_t per_filter = 0;  // bytes one more filter costs
 };
@@ -154,6 +154,7 @@ static WsLayout ws_layout(const crb_index* ix, int batch, int k) {
     L.qmap = o;    o += round_up(nmax * 4, 256);
     L.flagged = o; o += round_up(nmax * 4, 256);
     L.nflag = o;   o += 256;
+    L.progress = o; o += 4096;     // [slots, m_pairs] lock-step counters of the pair kernel (<= 1024 ints)
     L.cand2 = o;   o += round_up(std::min<size_t>(nmax, kK2BlockM) * ix->sm_count * k2_kprime(k) * 8 + nmax * k2_kprime(k) * 8, 1024);
     L.filt = o;
     L.per_filter = size_t(list_stride_of(ix)) * 4 + size_t(mask_stride_of(ix)) * 4;
@@ -367,6 +368,12 @@ static int launch_k2(crb_index* ix, const float* d_queries, int batch, int k, in
             kp.slots = std::max(1, (ix->sm_count / 2) / kp.m_tiles);
             kp.slots = static_cast<int>(std::min<int64_t>(kp.slots, std::max<int64_t>(n_tiles, 1)));
             kp.stages = stages2;
+            kp.drift = env_int("CODERAG_B200_K2_DRIFT", 0);
+            kp.progress = nullptr;
+            if (kp.drift > 0 && kp.m_tiles > 1 && kp.m_tiles * kp.slots <= 1024) {
+                kp.progress = reinterpret_cast<int32_t*>(ws + L.progress);
+                CRB_CUDA(cudaMemsetAsync(kp.progress, 0, 4096, stream));
+            }
             const size_t smem = 1024 + size_t(stages2) * kK2PairStageBytes + list_bytes + tail_bytes;
             k2_gemm_topk_pair_kernel<<<2 * kp.m_tiles * kp.slots, kK2Threads, smem, stream>>>(map_q, ix->map_rows_half, kp);
         } else {

@@ -49,6 +49,8 @@ struct K2Params {
     int32_t stages;
     int32_t prefetch;           // L2-prefetch the next corpus tile
     int32_t debug;              // timing experiments only: 1 = no TMA after the first fill, 2 = no epilogue math
+    int32_t* progress;          // [slots, m_tiles] tiles started per pair (pair kernel lock-step), zero on entry
+    int32_t drift;              // a pair may run at most this many corpus tiles ahead of the slowest pair of its slot
 };
 
 // ---- PTX wrappers ------------------------------------------------------------------------------
@@ -522,7 +524,31 @@ k2_gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap map_q, const __grid
         if (lane == 0) {
             int st = 0;
             uint32_t ph = 0;
-            for (int64_t t = slot; t < n_tiles; t += p.slots) {
+            int32_t it = 0;
+            for (int64_t t = slot; t < n_tiles; t += p.slots, ++it) {
+                // Lock-step: the pairs of one slot read the same corpus tiles; keeping them within
+                // `drift` tiles of each other makes all but the first read of a tile an L2 hit (HBM
+                // then sees the corpus once).  The leader's producer publishes / polls; its peer
+                // follows through the shared pipeline.  Bounded spin: never a deadlock.
+                if (leader && p.progress && p.m_tiles > 1) {
+                    volatile int32_t* prog = p.progress + static_cast<int64_t>(slot) * p.m_tiles;
+                    prog[m_pair] = it + 1;
+                    const int32_t need = it + 1 - p.drift;
+                    if (need > 0) {
+                        for (int spin = 0; spin < (1 << 22); ++spin) {
+                            int32_t lo = prog[0];
+                            for (int m = 1; m < p.m_tiles; ++m) { const int32_t v = prog[m]; lo = v < lo ? v : lo; }
+                            if (lo >= need) break;
+                        }
+                    }
+                }
+                // Pull this CTA's half of a FUTURE corpus tile into L2 (p.prefetch tiles ahead) so the
+                // demand loads below hit L2 even when this pair is the first of its slot to get there.
+                if (p.prefetch > 0 && t + static_cast<int64_t>(p.prefetch) * p.slots < n_tiles) {
+                    const int32_t r0 = static_cast<int32_t>((t + static_cast<int64_t>(p.prefetch) * p.slots) * kK2BlockN +
+                                                            rank * (kK2BlockN / 2));
+                    for (int kb = 0; kb < k_blocks; ++kb) tma_prefetch_l2_2d(&map_c, kb * kK2BlockK, r0);
+                }
                 for (int kb = 0; kb < k_blocks; ++kb) {
                     mbar_wait(&empty_bar[st], ph ^ 1u);
                     uint8_t* a = stage_base + static_cast<size_t>(st) * kK2PairStageBytes;

@@ -27,6 +27,8 @@ def run(n, d, b, k, steps=8, algo=2):
 if __name__ == "__main__":
     import os
     shapes = [(10_000_000, 768, 1024, 10), (10_000_000, 768, 128, 10), (10_000_000, 768, 8, 10)]
+    if os.environ.get("PROBE_B"):
+        shapes = [(10_000_000, 768, int(b), 10) for b in os.environ["PROBE_B"].split(",")]
     if os.environ.get("PROBE_FULL"):
         shapes = [(65536, 768, 1024, 10), (1_000_000, 768, 1024, 10), (10_000_000, 768, 1024, 10),
                   (10_000_000, 768, 128, 10), (10_000_000, 768, 8, 10), (10_000_000, 768, 256, 10),
