@@ -9,6 +9,7 @@
 #include <cstdarg>
 #include <cstdio>
 #include <cstdlib>
+#include <cmath>
 #include <cstring>
 #include <map>
 #include <mutex>
@@ -196,25 +197,39 @@ static int make_map_f16(CUtensorMap* map, const void* base, int64_t rows, int di
 // ---------------------------------------------------------------------------------------------
 typedef void (*K1Fn)(const K1Params);
 
-template <int NQ, int CH, int R>
+// Instantiated (NQ, CH, R) combinations.  R = rows in flight per warp: small rows need more of them
+// to keep enough bytes in flight (Little's law: ~35 KB per SM at HBM speed); MINB = 2 caps registers
+// at 128 so two CTAs stay resident when the per-lane footprint (NQ*CH query chunks + R*CH loads) is large.
+template <int NQ, int CH, int R, int MINB>
 static K1Fn k1_pick_kpl(int k) {
-    if (k <= 32) return k1_stream_kernel<NQ, CH, R, 1>;
-    return k1_stream_kernel<NQ, CH, R, 4>;
+    if (k <= 32) return k1_stream_kernel<NQ, CH, R, 1, MINB>;
+    return k1_stream_kernel<NQ, CH, R, 4, MINB>;
 }
-template <int NQ, int R>
-static K1Fn k1_pick_ch(int ch, int k) {
-    switch (ch) {
-        case 1: return k1_pick_kpl<NQ, 1, R>(k);
-        case 2: return k1_pick_kpl<NQ, 2, R>(k);
-        case 3: if constexpr (NQ <= 2) return k1_pick_kpl<NQ, 3, R>(k); else return nullptr;
-        case 4: if constexpr (NQ <= 2) return k1_pick_kpl<NQ, 4, R>(k); else return nullptr;
-    }
+static K1Fn k1_pick(int nq, int ch, int r, int k) {
+#define CRB_K1_CASE(NQ_, CH_, R_, MINB_) if (nq == NQ_ && ch == CH_ && r == R_) return k1_pick_kpl<NQ_, CH_, R_, MINB_>(k);
+    CRB_K1_CASE(1, 1, 4, 2) CRB_K1_CASE(1, 1, 8, 2)
+    CRB_K1_CASE(1, 2, 4, 2) CRB_K1_CASE(1, 2, 6, 2)
+    CRB_K1_CASE(1, 3, 2, 2) CRB_K1_CASE(1, 3, 4, 2)
+    CRB_K1_CASE(1, 4, 2, 2) CRB_K1_CASE(1, 4, 3, 2)
+    CRB_K1_CASE(2, 1, 4, 2)
+    CRB_K1_CASE(2, 2, 2, 2) CRB_K1_CASE(2, 2, 4, 2)
+    CRB_K1_CASE(2, 3, 2, 2)
+    CRB_K1_CASE(2, 4, 2, 1)
+    CRB_K1_CASE(4, 1, 2, 2) CRB_K1_CASE(4, 1, 4, 2)
+    CRB_K1_CASE(4, 2, 2, 1)
+#undef CRB_K1_CASE
     return nullptr;
 }
-static K1Fn k1_pick(int nq, int ch, int r1, int k) {
-    if (nq == 1) return r1 == 2 ? k1_pick_ch<1, 2>(ch, k) : k1_pick_ch<1, 4>(ch, k);
-    if (nq == 2) return k1_pick_ch<2, 2>(ch, k);
-    return k1_pick_ch<4, 2>(ch, k);
+// default rows-in-flight per (NQ, CH); CODERAG_B200_K1_ROWS overrides for NQ == 1 (tuning sweeps)
+static int k1_default_rows(int nq, int ch) {
+    if (nq == 1) {
+        const int def[5] = {0, 8, 6, 4, 3};
+        const int env = env_int("CODERAG_B200_K1_ROWS", 0);
+        if (env > 0 && k1_pick(1, ch, env, 10)) return env;
+        return def[ch];
+    }
+    if (nq == 2) return ch == 1 ? 4 : (ch == 2 ? 4 : 2);
+    return ch == 1 ? 4 : 2;
 }
 static K1Fn k1_pick_generic(int k) {
     if (k <= 32) return k1_stream_generic_kernel<2, 1>;
@@ -249,11 +264,11 @@ static int launch_k1(const crb_index* ix, const float* d_queries, int k, int met
     const int chunks = ix->dim / 8;
     const int ch = (chunks + 31) / 32;
     const bool generic = ch > 4;
-    const int r1 = env_int("CODERAG_B200_K1_ROWS", 4) == 2 ? 2 : 4;
+    const int r1 = generic ? 2 : k1_default_rows(nq, ch);
     K1Fn fn = generic ? k1_pick_generic(k) : k1_pick(nq, ch, r1, k);
     if (!fn) return fail("internal: no K1 instantiation for nq=%d ch=%d", nq, ch);
     const size_t dyn = generic ? size_t(ix->dim) * sizeof(float) : 0;
-    const int rows_per_warp_iter = generic ? 2 : (nq == 1 ? r1 : 2);
+    const int rows_per_warp_iter = r1;
     const int resident = k1_occupancy(fn, dyn) * ix->sm_count;
 
     for (size_t g0 = 0; g0 < groups.size(); g0 += kMaxGroups) {
@@ -310,12 +325,7 @@ static int launch_k2(crb_index* ix, const float* d_queries, int batch, int k, in
                      float* d_scores, int64_t* d_rows, int32_t* d_n_valid, uint64_t* d_keys,
                      std::vector<int>* unproven, cudaStream_t stream) {
     const int kprime = k2_kprime(k);
-    const size_t list_bytes = size_t(kprime) * 128 * 8;
     const size_t tail_bytes = 2 * kK2BlockN * 4 + 256;
-    const size_t smem_room = size_t(227) * 1024 - 1024 - list_bytes - tail_bytes;
-    const int stages1 = static_cast<int>(std::min<size_t>(smem_room / kK2StageBytes, 4));
-    const int stages2 = static_cast<int>(std::min<size_t>(smem_room / kK2PairStageBytes, 8));
-    if (stages1 < 2) return fail("internal: K2 does not fit shared memory for k'=%d", kprime);
     static std::once_flag attr_once;
     static cudaError_t attr_err = cudaSuccess;
     std::call_once(attr_once, [] {
@@ -360,6 +370,13 @@ static int launch_k2(crb_index* ix, const float* d_queries, int batch, int k, in
         kp.kprime = kprime;
         kp.metric = metric;
         const int64_t n_tiles = (ix->n_rows + kK2BlockN - 1) / kK2BlockN;
+        // only query rows that exist own a candidate list: small batches leave room for more stages
+        kp.lstride = n >= kK2BlockM ? kK2BlockM : static_cast<int>(round_up(n, 32));
+        const size_t list_bytes = size_t(kprime) * kp.lstride * 8;
+        const size_t smem_room = size_t(227) * 1024 - 1024 - list_bytes - tail_bytes;
+        const int stages1 = static_cast<int>(std::min<size_t>(smem_room / kK2StageBytes, 4));
+        const int stages2 = static_cast<int>(std::min<size_t>(smem_room / kK2PairStageBytes, 8));
+        if (stages1 < 2) return fail("internal: K2 does not fit shared memory for k'=%d", kprime);
         const bool use_pair = pair_env >= 0 ? (pair_env != 0) : (n > kK2BlockM);
         kp.prefetch = env_int("CODERAG_B200_K2_PREFETCH", 0);
         kp.debug = env_int("CODERAG_B200_K2_DEBUG", 0);
@@ -524,6 +541,26 @@ static int search_impl(crb_index* ix, const float* d_queries, int batch, int k, 
             if (blocks > 0) {
                 k3_filter_kernel<<<blocks, kK3Threads, 0, stream>>>(kp);
                 CRB_LAUNCH_CHECK();
+            }
+        }
+
+        // A filtered row set is worth the tensor-core kernel (which scans the whole shard under a
+        // pass-bit mask) only if that beats gathering the survivors once per nq_cap queries.  The
+        // survivor counts are on the device: read them back (one small synchronising copy; the
+        // K2 path synchronises for its proof flags anyway).
+        if (any_k2_filtered && algo == 0) {
+            uint32_t h_counts[kMaxFilters];
+            CRB_CUDA(cudaMemcpyAsync(h_counts, ws + kWsCountsOffset, sizeof h_counts, cudaMemcpyDeviceToHost, stream));
+            CRB_CUDA(cudaStreamSynchronize(stream));
+            for (auto& kv : by_filter) {
+                if (kv.first < 0 || !use_k2[kv.first]) continue;
+                const double nq_set = static_cast<double>(kv.second.size());
+                const double surv = static_cast<double>(h_counts[slot_of_filter[kv.first]]);
+                const double row_bytes = double(ix->dim) * 2.0;
+                const double t_k1 = std::ceil(nq_set / nq_cap) * (surv * row_bytes / 5.0e12 + 10e-6);
+                const double t_k2 = std::max(double(ix->n_rows) * row_bytes / 3.0e12,
+                                             2.0 * nq_set * double(ix->n_rows) * ix->dim / 9.0e14) + 0.3e-3;
+                if (t_k1 <= t_k2) use_k2[kv.first] = false;
             }
         }
 
@@ -932,10 +969,11 @@ extern "C" int crb_search_noalloc(crb_index* ix, const float* d_queries, int32_t
     const int ng = (batch + nq_cap - 1) / nq_cap;
     const int widest = std::min<int>(batch, nq_cap);
     const int nq = widest <= 1 ? 1 : (widest <= 2 ? 2 : 4);
-    K1Fn fn = generic ? k1_pick_generic(k) : k1_pick(nq, ch, 4, k);
+    const int r1 = generic ? 2 : k1_default_rows(nq, ch);
+    K1Fn fn = generic ? k1_pick_generic(k) : k1_pick(nq, ch, r1, k);
     if (!fn) return fail("internal: no K1 instantiation for nq=%d ch=%d", nq, ch);
     const size_t dyn = generic ? size_t(ix->dim) * sizeof(float) : 0;
-    const int rows_per_warp_iter = generic ? 2 : (nq == 1 ? 4 : 2);
+    const int rows_per_warp_iter = r1;
     int per_sm = 0;
     if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fn, kK1Threads, dyn) != cudaSuccess || per_sm < 1) per_sm = 1;
     const int resident = per_sm * ix->sm_count;

@@ -48,8 +48,8 @@ struct K1Params {
     K1Group groups[kMaxGroups];
 };
 
-template <int NQ, int CH, int R, int KPL>
-__global__ void __launch_bounds__(kK1Threads)
+template <int NQ, int CH, int R, int KPL, int MINB = 1>
+__global__ void __launch_bounds__(kK1Threads, MINB)
 k1_stream_kernel(const __grid_constant__ K1Params p) {
     __shared__ uint64_t xchg[2][32];
     __shared__ float s_invq;

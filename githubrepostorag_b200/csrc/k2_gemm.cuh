@@ -49,6 +49,7 @@ struct K2Params {
     int32_t stages;
     int32_t prefetch;           // L2-prefetch the next corpus tile
     int32_t debug;              // timing experiments only: 1 = no TMA after the first fill, 2 = no epilogue math
+    int32_t lstride;            // candidate-list stride = query rows that own a list (<= 128)
     int32_t* progress;          // [slots, m_tiles] tiles started per pair (pair kernel lock-step), zero on entry
     int32_t drift;              // a pair may run at most this many corpus tiles ahead of the slowest pair of its slot
 };
@@ -134,32 +135,32 @@ constexpr uint32_t kK2IDesc = (1u << 4) | ((kK2BlockN >> 3) << 17) | ((kK2BlockM
 // binary MIN-heap when it reaches k' entries, and from then on an admitted key replaces the root
 // and sifts down (O(log k')).  Kept out of line: the epilogue has 32 call sites per chunk and the
 // call is rare after warm-up.
-CRB_DEVINL void k2_sift_down(uint64_t* list, int i, int n, uint64_t key) {
+CRB_DEVINL void k2_sift_down(uint64_t* list, int ls, int i, int n, uint64_t key) {
     for (;;) {
         int c = 2 * i + 1;
         if (c >= n) break;
-        uint64_t cv = list[c * 128];
+        uint64_t cv = list[c * ls];
         if (c + 1 < n) {
-            const uint64_t rv = list[(c + 1) * 128];
+            const uint64_t rv = list[(c + 1) * ls];
             if (rv < cv) { cv = rv; ++c; }
         }
         if (cv >= key) break;
-        list[i * 128] = cv;
+        list[i * ls] = cv;
         i = c;
     }
-    list[i * 128] = key;
+    list[i * ls] = key;
 }
-__device__ __noinline__ uint2 k2_list_insert(uint64_t* list, uint64_t key, uint32_t state, float thr, int kprime) {
+__device__ __noinline__ uint2 k2_list_insert(uint64_t* list, uint64_t key, uint32_t state, float thr, int kprime, int ls) {
     int count = static_cast<int>(state);
     if (count < kprime) {
-        list[count * 128] = key;
+        list[count * ls] = key;
         ++count;
         if (count == kprime) {
-            for (int i = kprime / 2 - 1; i >= 0; --i) k2_sift_down(list, i, kprime, list[i * 128]);
+            for (int i = kprime / 2 - 1; i >= 0; --i) k2_sift_down(list, ls, i, kprime, list[i * ls]);
             thr = key_score(list[0]);
         }
     } else {
-        k2_sift_down(list, 0, kprime, key);
+        k2_sift_down(list, ls, 0, kprime, key);
         thr = key_score(list[0]);
     }
     return make_uint2(__float_as_uint(thr), static_cast<uint32_t>(count));
@@ -174,7 +175,7 @@ CRB_DEVINL float4 lds_f4(uint32_t saddr) {
 // Examine one 32-column chunk of this thread's accumulator row: scale, and admit columns that
 // beat the thread's threshold.  `inv_saddr` is the shared-window address of the chunk's scales.
 CRB_DEVINL float k2_scan_chunk(const uint32_t (&v)[32], uint32_t inv_saddr, float thr, uint32_t& state,
-                               uint64_t* my_list, int64_t n_first, int kprime) {
+                               uint64_t* my_list, int64_t n_first, int kprime, int ls) {
     float s[32];
 #pragma unroll
     for (int g = 0; g < 8; ++g) {
@@ -192,7 +193,7 @@ CRB_DEVINL float k2_scan_chunk(const uint32_t (&v)[32], uint32_t inv_saddr, floa
 #pragma unroll
         for (int j = 0; j < 32; ++j) {
             if (s[j] > thr) {
-                const uint2 r = k2_list_insert(my_list, make_key(s[j], static_cast<uint32_t>(n_first + j)), state, thr, kprime);
+                const uint2 r = k2_list_insert(my_list, make_key(s[j], static_cast<uint32_t>(n_first + j)), state, thr, kprime, ls);
                 thr = __uint_as_float(r.x);
                 state = r.y;
             }
@@ -249,7 +250,7 @@ k2_gemm_topk_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_cons
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     uint8_t* stage_base = smem;
     uint64_t* lists = reinterpret_cast<uint64_t*>(smem + static_cast<size_t>(p.stages) * kK2StageBytes);
-    float* s_inv = reinterpret_cast<float*>(lists + static_cast<size_t>(p.kprime) * 128);
+    float* s_inv = reinterpret_cast<float*>(lists + static_cast<size_t>(p.kprime) * p.lstride);
     uint64_t* bars = reinterpret_cast<uint64_t*>(s_inv + 2 * kK2BlockN);
     uint64_t* full_bar = bars;                       // [stages]
     uint64_t* empty_bar = bars + p.stages;           // [stages]
@@ -343,9 +344,9 @@ k2_gemm_topk_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_cons
         const int row = quarter * 32 + lane;          // query row inside the tile
         const int et = row;                           // list column of this thread
         const int tid_e = threadIdx.x - 64;           // 0..127 (staging role only)
-        const bool q_valid = (m_tile * kK2BlockM + row) < p.batch;
+        const bool q_valid = (m_tile * kK2BlockM + row) < p.batch && row < p.lstride;
         const bool cosine = (p.metric == 0);
-        uint64_t* my_list = lists + et;               // entry i at my_list[i * 128]
+        uint64_t* my_list = lists + et;               // entry i at my_list[i * lstride]
         uint32_t state = 0;                           // entries in the list
         float thr = q_valid ? __uint_as_float(0xff800000u) : __uint_as_float(0x7f800000u);  // -inf / +inf
         const float qnan = __uint_as_float(0x7fc00000u);
@@ -392,10 +393,10 @@ k2_gemm_topk_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_cons
 #pragma unroll 1
             for (int c = 0; c < n_chunks; c += 2) {
                 tmem_ld32(t_row + (c + 1) * 32, vb);
-                thr = k2_scan_chunk(va, inv_s + c * 128, thr, state, my_list, n0 + c * 32, p.kprime);
+                thr = k2_scan_chunk(va, inv_s + c * 128, thr, state, my_list, n0 + c * 32, p.kprime, p.lstride);
                 tmem_ld_wait();
                 if (c + 2 < n_chunks) tmem_ld32(t_row + (c + 2) * 32, va);
-                thr = k2_scan_chunk(vb, inv_s + (c + 1) * 128, thr, state, my_list, n0 + (c + 1) * 32, p.kprime);
+                thr = k2_scan_chunk(vb, inv_s + (c + 1) * 128, thr, state, my_list, n0 + (c + 1) * 32, p.kprime, p.lstride);
                 tmem_ld_wait();
             }
             tc_fence_before();
@@ -405,7 +406,7 @@ k2_gemm_topk_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_cons
         if (q_valid) {
             uint64_t* out = p.cand + (static_cast<int64_t>(m_tile * kK2BlockM + row) * p.slots + slot) * p.kprime;
             const int count = static_cast<int>(state);
-            for (int i = 0; i < p.kprime; ++i) out[i] = i < count ? my_list[i * 128] : 0ull;
+            for (int i = 0; i < p.kprime; ++i) out[i] = i < count ? my_list[i * p.lstride] : 0ull;
         }
     }
 
@@ -483,7 +484,7 @@ k2_gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap map_q, const __grid
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     uint8_t* stage_base = smem;
     uint64_t* lists = reinterpret_cast<uint64_t*>(smem + static_cast<size_t>(p.stages) * kK2PairStageBytes);
-    float* s_inv = reinterpret_cast<float*>(lists + static_cast<size_t>(p.kprime) * 128);
+    float* s_inv = reinterpret_cast<float*>(lists + static_cast<size_t>(p.kprime) * p.lstride);
     uint64_t* bars = reinterpret_cast<uint64_t*>(s_inv + 2 * kK2BlockN);
     uint64_t* full_bar = bars;
     uint64_t* empty_bar = bars + p.stages;
@@ -597,7 +598,7 @@ k2_gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap map_q, const __grid
         const int quarter = warp & 3;
         const int row = quarter * 32 + lane;
         const int tid_e = threadIdx.x - 64;
-        const bool q_valid = (m_row0 + row) < p.batch;
+        const bool q_valid = (m_row0 + row) < p.batch && row < p.lstride;
         const bool cosine = (p.metric == 0);
         uint64_t* my_list = lists + row;
         uint32_t state = 0;
@@ -640,10 +641,10 @@ k2_gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap map_q, const __grid
 #pragma unroll 1
             for (int c = 0; c < n_chunks; c += 2) {
                 tmem_ld32(t_row + (c + 1) * 32, vb);
-                thr = k2_scan_chunk(va, inv_s + c * 128, thr, state, my_list, n0 + c * 32, p.kprime);
+                thr = k2_scan_chunk(va, inv_s + c * 128, thr, state, my_list, n0 + c * 32, p.kprime, p.lstride);
                 tmem_ld_wait();
                 if (c + 2 < n_chunks) tmem_ld32(t_row + (c + 2) * 32, va);
-                thr = k2_scan_chunk(vb, inv_s + (c + 1) * 128, thr, state, my_list, n0 + (c + 1) * 32, p.kprime);
+                thr = k2_scan_chunk(vb, inv_s + (c + 1) * 128, thr, state, my_list, n0 + (c + 1) * 32, p.kprime, p.lstride);
                 tmem_ld_wait();
             }
             tc_fence_before();
@@ -652,7 +653,7 @@ k2_gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap map_q, const __grid
         if (q_valid) {
             uint64_t* out = p.cand + (static_cast<int64_t>(m_row0 + row) * p.slots + slot) * p.kprime;
             const int count = static_cast<int>(state);
-            for (int i = 0; i < p.kprime; ++i) out[i] = i < count ? my_list[i * 128] : 0ull;
+            for (int i = 0; i < p.kprime; ++i) out[i] = i < count ? my_list[i * p.lstride] : 0ull;
         }
     }
 
