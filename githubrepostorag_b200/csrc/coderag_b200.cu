@@ -323,8 +323,41 @@ static int launch_k1(const crb_index* ix, const float* d_queries, int k, int met
 static int launch_k2(crb_index* ix, const float* d_queries, int batch, int k, int metric,
                      const std::vector<int>& queries, const uint32_t* mask, uint8_t* ws, const WsLayout& L,
                      float* d_scores, int64_t* d_rows, int32_t* d_n_valid, uint64_t* d_keys,
-                     std::vector<int>* unproven, cudaStream_t stream) {
+                     std::vector<int>* unproven, cudaStream_t stream,
+                     const uint32_t* surv_list = nullptr, const uint32_t* surv_count = nullptr,
+                     int64_t n_surv = -1, uint8_t* compact_buf = nullptr, size_t compact_cap = 0) {
     const int kprime = k2_kprime(k);
+
+    // Filtered set with a known, small survivor count: gather the survivors into a dense buffer and
+    // run the GEMM on those rows only (flops and bytes scale with selectivity, not with the shard).
+    const __half* k2_rows = ix->rows;
+    const float* k2_inv = ix->inv_norm;
+    int64_t k2_n = ix->n_rows;
+    const CUtensorMap* map_full = &ix->map_rows;
+    const CUtensorMap* map_half = &ix->map_rows_half;
+    CUtensorMap cmap_full, cmap_half;
+    const uint32_t* remap = nullptr;
+    if (mask && surv_list && n_surv >= 0 && compact_buf) {
+        const size_t row_bytes = size_t(ix->dim) * 2;
+        const size_t inv_off = round_up(size_t(std::max<int64_t>(n_surv, 1)) * row_bytes, 1024);
+        if (inv_off + size_t(std::max<int64_t>(n_surv, 1)) * 4 <= compact_cap && n_surv * 4 <= ix->n_rows) {
+            __half* c_rows = reinterpret_cast<__half*>(compact_buf);
+            float* c_inv = reinterpret_cast<float*>(compact_buf + inv_off);
+            if (n_surv > 0) {
+                const unsigned blocks = static_cast<unsigned>(std::min<int64_t>((n_surv + 7) / 8, int64_t(ix->sm_count) * 16));
+                compact_rows_kernel<<<blocks, 256, 0, stream>>>(ix->rows, ix->inv_norm, surv_list, surv_count, n_surv,
+                                                               ix->dim, c_rows, c_inv);
+                CRB_LAUNCH_CHECK();
+            }
+            if (int rc = make_map_f16(&cmap_full, c_rows, n_surv, ix->dim, kK2BlockN)) return rc;
+            if (int rc = make_map_f16(&cmap_half, c_rows, n_surv, ix->dim, kK2BlockN / 2)) return rc;
+            k2_rows = c_rows; k2_inv = c_inv; k2_n = n_surv;
+            map_full = &cmap_full; map_half = &cmap_half;
+            remap = surv_list;
+            mask = nullptr;
+        }
+    }
+    (void)k2_rows;
     const size_t tail_bytes = 2 * kK2BlockN * 4 + 256;
     static std::once_flag attr_once;
     static cudaError_t attr_err = cudaSuccess;
@@ -361,15 +394,15 @@ static int launch_k2(crb_index* ix, const float* d_queries, int batch, int k, in
         if (int rc = make_map_f16(&map_q, q16, n, ix->dim, kK2BlockM)) return rc;
         K2Params kp;
         memset(&kp, 0, sizeof kp);
-        kp.inv_norm = ix->inv_norm;
+        kp.inv_norm = k2_inv;
         kp.mask = mask;
         kp.cand = cand2;
-        kp.n_rows = ix->n_rows;
+        kp.n_rows = k2_n;
         kp.batch = n;
         kp.dim = ix->dim;
         kp.kprime = kprime;
         kp.metric = metric;
-        const int64_t n_tiles = (ix->n_rows + kK2BlockN - 1) / kK2BlockN;
+        const int64_t n_tiles = (k2_n + kK2BlockN - 1) / kK2BlockN;
         // only query rows that exist own a candidate list: small batches leave room for more stages
         kp.lstride = n >= kK2BlockM ? kK2BlockM : static_cast<int>(round_up(n, 32));
         const size_t list_bytes = size_t(kprime) * kp.lstride * 8;
@@ -392,14 +425,14 @@ static int launch_k2(crb_index* ix, const float* d_queries, int batch, int k, in
                 CRB_CUDA(cudaMemsetAsync(kp.progress, 0, 4096, stream));
             }
             const size_t smem = 1024 + size_t(stages2) * kK2PairStageBytes + list_bytes + tail_bytes;
-            k2_gemm_topk_pair_kernel<<<2 * kp.m_tiles * kp.slots, kK2Threads, smem, stream>>>(map_q, ix->map_rows_half, kp);
+            k2_gemm_topk_pair_kernel<<<2 * kp.m_tiles * kp.slots, kK2Threads, smem, stream>>>(map_q, *map_half, kp);
         } else {
             kp.m_tiles = (n + kK2BlockM - 1) / kK2BlockM;
             kp.slots = std::max(1, ix->sm_count / kp.m_tiles);
             kp.slots = static_cast<int>(std::min<int64_t>(kp.slots, std::max<int64_t>(n_tiles, 1)));
             kp.stages = stages1;
             const size_t smem = 1024 + size_t(stages1) * kK2StageBytes + list_bytes + tail_bytes;
-            k2_gemm_topk_kernel<<<kp.m_tiles * kp.slots, kK2Threads, smem, stream>>>(map_q, ix->map_rows, kp);
+            k2_gemm_topk_kernel<<<kp.m_tiles * kp.slots, kK2Threads, smem, stream>>>(map_q, *map_full, kp);
         }
         CRB_LAUNCH_CHECK();
 
@@ -410,6 +443,7 @@ static int launch_k2(crb_index* ix, const float* d_queries, int batch, int k, in
         rp.inv_norm = ix->inv_norm;
         rp.queries = d_queries;
         rp.q_map = d_qmap;
+        rp.remap = remap;
         rp.cand = cand2;
         rp.invq = invq;
         rp.eps = eps;
@@ -485,6 +519,11 @@ static int search_impl(crb_index* ix, const float* d_queries, int batch, int k, 
     int lists_fit = static_cast<int>(std::min<size_t>((workspace_bytes - L.filt) / L.per_filter, kMaxFilters));
     if (F > 0 && lists_fit < 1)
         return fail("workspace too small for one survivor list: need %zu bytes", L.filt + L.per_filter);
+    lists_fit = std::min(lists_fit, std::max(F, 1));
+    // whatever lies beyond the lists and masks holds compacted survivors for filtered K2 batches
+    const size_t compact_off = round_up(L.filt + size_t(lists_fit) * L.per_filter, 1024);
+    uint8_t* compact_buf = workspace_bytes > compact_off ? ws + compact_off : nullptr;
+    const size_t compact_cap = workspace_bytes > compact_off ? workspace_bytes - compact_off : 0;
     uint32_t* lists = reinterpret_cast<uint32_t*>(ws + L.filt);
     uint32_t* masks = reinterpret_cast<uint32_t*>(ws + L.filt + size_t(std::max(lists_fit, 0)) * size_t(stride) * 4);
 
@@ -548,18 +587,20 @@ static int search_impl(crb_index* ix, const float* d_queries, int batch, int k, 
         // pass-bit mask) only if that beats gathering the survivors once per nq_cap queries.  The
         // survivor counts are on the device: read them back (one small synchronising copy; the
         // K2 path synchronises for its proof flags anyway).
-        if (any_k2_filtered && algo == 0) {
-            uint32_t h_counts[kMaxFilters];
+        uint32_t h_counts[kMaxFilters] = {0};
+        if (any_k2_filtered) {
             CRB_CUDA(cudaMemcpyAsync(h_counts, ws + kWsCountsOffset, sizeof h_counts, cudaMemcpyDeviceToHost, stream));
             CRB_CUDA(cudaStreamSynchronize(stream));
             for (auto& kv : by_filter) {
-                if (kv.first < 0 || !use_k2[kv.first]) continue;
+                if (kv.first < 0 || !use_k2[kv.first] || algo != 0) continue;
                 const double nq_set = static_cast<double>(kv.second.size());
                 const double surv = static_cast<double>(h_counts[slot_of_filter[kv.first]]);
                 const double row_bytes = double(ix->dim) * 2.0;
+                const bool can_compact = surv * (row_bytes + 4.0) + 2048.0 <= double(compact_cap) && surv * 4.0 <= double(ix->n_rows);
+                const double scan_rows = can_compact ? surv : double(ix->n_rows);
                 const double t_k1 = std::ceil(nq_set / nq_cap) * (surv * row_bytes / 5.0e12 + 10e-6);
-                const double t_k2 = std::max(double(ix->n_rows) * row_bytes / 3.0e12,
-                                             2.0 * nq_set * double(ix->n_rows) * ix->dim / 9.0e14) + 0.3e-3;
+                const double t_k2 = std::max(scan_rows * row_bytes / 3.0e12, 2.0 * nq_set * scan_rows * ix->dim / 9.0e14) +
+                                    (can_compact ? 2.0 * surv * row_bytes / 5.0e12 : 0.0) + 0.3e-3;
                 if (t_k1 <= t_k2) use_k2[kv.first] = false;
             }
         }
@@ -570,9 +611,19 @@ static int search_impl(crb_index* ix, const float* d_queries, int batch, int k, 
             if (!use_k2[kv.first]) { k1_sets[kv.first] = kv.second; continue; }
             const uint32_t* mask = kv.first < 0 ? nullptr : masks + size_t(slot_of_filter[kv.first]) * size_t(mstride);
             std::vector<int> unproven;
-            if (int rc = launch_k2(ix, d_queries, batch, k, metric, kv.second, mask, ws, L, d_scores, d_rows,
-                                   d_n_valid, d_keys, &unproven, stream))
-                return rc;
+            int rc;
+            if (kv.first < 0) {
+                rc = launch_k2(ix, d_queries, batch, k, metric, kv.second, mask, ws, L, d_scores, d_rows, d_n_valid,
+                               d_keys, &unproven, stream);
+            } else {
+                const int slot_f = slot_of_filter[kv.first];
+                rc = launch_k2(ix, d_queries, batch, k, metric, kv.second, mask, ws, L, d_scores, d_rows, d_n_valid,
+                               d_keys, &unproven, stream, lists + size_t(slot_f) * size_t(stride),
+                               reinterpret_cast<const uint32_t*>(ws + kWsCountsOffset) + slot_f,
+                               static_cast<int64_t>(std::min<uint64_t>(h_counts[slot_f], uint64_t(ix->n_rows))),
+                               compact_buf, compact_cap);
+            }
+            if (rc) return rc;
             if (!unproven.empty()) k1_sets[kv.first] = unproven;
         }
 
@@ -810,7 +861,15 @@ extern "C" size_t crb_workspace_bytes(const crb_index* ix, int32_t batch, int32_
     if (!ix) return 0;
     const int lists = std::min<int>(std::max<int>(n_filters, 0), kMaxFilters);
     const WsLayout L = ws_layout(ix, std::max(batch, 1), std::min(std::max(k, 1), CRB_MAX_TOPK));
-    return L.filt + size_t(lists) * L.per_filter;
+    size_t total = L.filt + size_t(lists) * L.per_filter;
+    if (lists > 0 && batch > 1) {
+        // room to compact the survivors of a filtered tensor-core batch (up to a quarter of the shard,
+        // capped by CODERAG_B200_COMPACT_MB, default 1024)
+        const size_t cap = size_t(std::max(env_int("CODERAG_B200_COMPACT_MB", 1024), 0)) << 20;
+        const size_t quarter = size_t(ix->n_rows / 4 + 1) * (size_t(ix->dim) * 2 + 4) + 4096;
+        total = round_up(total, 1024) + std::min(cap, quarter);
+    }
+    return total;
 }
 
 extern "C" int crb_search(crb_index* ix, const float* d_queries, int32_t batch, int32_t k,

@@ -671,6 +671,7 @@ struct K5Params {
     const float* inv_norm;
     const float* queries;       // [*, dim] fp32 originals
     const int32_t* q_map;       // slot -> query index in the caller's batch (or nullptr = identity)
+    const uint32_t* remap;      // candidate row -> shard row when K2 ran on compacted survivors (or nullptr)
     const uint64_t* cand;       // [n, slots, kprime]
     const float* invq;          // [n]
     const float* eps;           // [n]
@@ -728,7 +729,7 @@ __global__ void __launch_bounds__(256) k5_rescore_kernel(const __grid_constant__
     for (int c = warp; c < n_cand; c += 8) {
         const uint64_t e = cand[c];
         if (e == 0ull) continue;                       // warp-uniform
-        const uint32_t row = key_row(e);
+        const uint32_t row = p.remap ? p.remap[key_row(e)] : key_row(e);
         const __half* rp = p.rows + static_cast<int64_t>(row) * p.dim;
         float acc = 0.f;
         for (int ch = lane; ch < chunks; ch += 32) {
@@ -780,6 +781,28 @@ __global__ void __launch_bounds__(256) k5_rescore_kernel(const __grid_constant__
             const int at = atomicAdd(p.n_flagged, 1);
             p.flagged[at] = slot_q;
         }
+    }
+}
+
+// Survivor compaction for filtered tensor-core batches: copy the surviving rows (and their inverse
+// norms) of one filter into a dense buffer so K2 spends flops only on survivors.  One warp per row.
+__global__ void __launch_bounds__(256) compact_rows_kernel(const __half* __restrict__ rows,
+                                                           const float* __restrict__ inv_norm,
+                                                           const uint32_t* __restrict__ list,
+                                                           const uint32_t* __restrict__ count_ptr, int64_t cap,
+                                                           int dim, __half* __restrict__ out_rows,
+                                                           float* __restrict__ out_inv) {
+    const int lane = threadIdx.x & 31;
+    const int64_t gw = (static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
+    const int64_t nw = (static_cast<int64_t>(gridDim.x) * blockDim.x) >> 5;
+    const int64_t cnt = static_cast<int64_t>(*count_ptr);
+    const int64_t n = cnt < cap ? cnt : cap;
+    const int chunks = dim >> 3;
+    for (int64_t i = gw; i < n; i += nw) {
+        const int64_t src = static_cast<int64_t>(list[i]);
+        for (int ch = lane; ch < chunks; ch += 32)
+            *reinterpret_cast<uint4*>(out_rows + i * dim + ch * 8) = ld_stream_16(rows + src * dim + ch * 8);
+        if (lane == 0) out_inv[i] = inv_norm[src];
     }
 }
 
