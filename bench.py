@@ -205,7 +205,7 @@ def workload_config(args, world):
     return {"workload": f"{N_ROWS // 1_000_000}Mx{DIM}_fp16_k{TOPK}_b{args.batch}", "n_rows": N_ROWS, "dim": DIM, "k": TOPK,
             "batch": args.batch, "metric": "cosine", "sharding": f"rows/{world}",
             "l2": "inputs larger than L2 (corpus shard >= 1.9 GB vs 126 MB L2); query batches rotate",
-            "query_sets": N_QUERY_SETS}
+            "query_sets": N_QUERY_SETS, "exchange": getattr(args, "exchange_used", "none")}
 
 
 # ----------------------------------------------------------------------------- our arm
@@ -237,7 +237,20 @@ def run_ours(args):
     rows = device_corpus(torch, lo, hi, DIM, dev)
     shard = DeviceShard.from_device(rows, None, row_offset=lo)
     torch.cuda.synchronize()
-    searcher = cuda_searcher(shard) if world > 1 else None
+    searcher, exchange = None, "none"
+    if world > 1:
+        exchange = args.exchange
+        if exchange == "fused":
+            try:
+                from githubrepostorag_b200.sharded import FusedExchangeSearcher
+                searcher = FusedExchangeSearcher(shard, cap_keys=1 << 15)
+            except Exception as e:  # noqa: BLE001 - symmetric memory unavailable: NCCL all-gather instead
+                if rank == 0:
+                    print(f"fused exchange unavailable ({e!r}); using the NCCL all-gather", file=sys.stderr)
+                exchange = "nccl"
+        if searcher is None:
+            searcher = cuda_searcher(shard)
+    args.exchange_used = exchange
     k = TOPK
     pk = peaks()
 
@@ -372,6 +385,8 @@ def main():
     ap.add_argument("--batch", type=int, default=1)
     ap.add_argument("--impl", choices=("ours", "reference"), default="ours")
     ap.add_argument("--cpu-budget", type=float, default=15.0)
+    ap.add_argument("--exchange", choices=("fused", "nccl"), default="fused",
+                    help="N>1: fused NVLink peer-memory exchange (crb_search_exchange) or NCCL all-gather + merge")
     ap.add_argument("--no-secondary", action="store_true", help="skip the batch-1024 (tensor-core) secondary measurement")
     args = ap.parse_args()
     if args.warmup < 3:

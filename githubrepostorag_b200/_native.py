@@ -26,6 +26,13 @@ MAX_KEYS = 8
 MAX_TOPK = 128
 MAX_DIM = 4096
 NOALLOC_MAX_BATCH = 4
+MAX_PEERS = 8
+
+
+class Exchange(C.Structure):
+    """``crb_exchange`` of include/coderag_b200.h."""
+    _fields_ = [("rank", C.c_int32), ("world", C.c_int32), ("cap_keys", C.c_uint64),
+                ("peer_keys", C.c_void_p * MAX_PEERS), ("peer_counters", C.c_void_p * MAX_PEERS)]
 
 # every symbol include/coderag_b200.h declares: name -> (restype, argtypes)
 _vp, _i32, _i64, _sz = C.c_void_p, C.c_int32, C.c_int64, C.c_size_t
@@ -40,6 +47,8 @@ PROTOTYPES = {
     "crb_search": (C.c_int, [_vp, _vp, _i32, _i32, _i32, _vp, _vp, _vp, _vp, _vp, _vp, _sz, _i32, _vp]),
     "crb_search_host": (C.c_int, [_vp, _vp, _i32, _i32, _i32, _vp, _vp, _vp, _vp, _i32]),
     "crb_merge_keys": (C.c_int, [_vp, _i32, _i32, _i32, _i32, _vp, _i32, _vp, _vp, _vp, _vp, _i32, _vp]),
+    "crb_search_exchange": (C.c_int, [_vp, _vp, _i32, _i32, _i32, _vp, _vp, _vp, _vp, _vp, _vp, _sz, _i32, _vp,
+                                       _vp, C.c_uint32, C.c_uint32]),
     "crb_fetch_rows_host": (C.c_int, [_vp, _vp, _i32, _vp]),
     "crb_search_noalloc": (C.c_int, [_vp, _vp, _i32, _i32, _i32, _vp, _vp, _vp, _vp]),
     "crb_launch_count": (_i64, []),

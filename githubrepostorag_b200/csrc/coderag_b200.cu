@@ -260,7 +260,7 @@ struct QueryGroup {
 static int launch_k1(const crb_index* ix, const float* d_queries, int k, int metric,
                      const std::vector<QueryGroup>& groups, const std::vector<int>& slot_of_filter,
                      int nq, uint8_t* ws, const uint32_t* lists, float* d_scores, int64_t* d_rows,
-                     int32_t* d_n_valid, uint64_t* d_keys, cudaStream_t stream) {
+                     int32_t* d_n_valid, uint64_t* d_keys, cudaStream_t stream, const ExchangeDev* ex = nullptr) {
     const int chunks = ix->dim / 8;
     const int ch = (chunks + 31) / 32;
     const bool generic = ch > 4;
@@ -292,6 +292,7 @@ static int launch_k1(const crb_index* ix, const float* d_queries, int k, int met
         p.dim = ix->dim;
         p.k = k;
         p.metric = metric;
+        if (ex) p.ex = *ex;
         for (int g = 0; g < ng; ++g) {
             const QueryGroup& qg = groups[g0 + g];
             for (int q = 0; q < kK1MaxQ; ++q)
@@ -325,7 +326,8 @@ static int launch_k2(crb_index* ix, const float* d_queries, int batch, int k, in
                      float* d_scores, int64_t* d_rows, int32_t* d_n_valid, uint64_t* d_keys,
                      std::vector<int>* unproven, cudaStream_t stream,
                      const uint32_t* surv_list = nullptr, const uint32_t* surv_count = nullptr,
-                     int64_t n_surv = -1, uint8_t* compact_buf = nullptr, size_t compact_cap = 0) {
+                     int64_t n_surv = -1, uint8_t* compact_buf = nullptr, size_t compact_cap = 0,
+                     const ExchangeDev* ex = nullptr) {
     const int kprime = k2_kprime(k);
 
     // Filtered set with a known, small survivor count: gather the survivors into a dense buffer and
@@ -460,6 +462,7 @@ static int launch_k2(crb_index* ix, const float* d_queries, int batch, int k, in
         rp.kprime = kprime;
         rp.slots = kp.slots;
         rp.metric = metric;
+        if (ex) rp.ex = *ex;
         const size_t dyn = size_t(ix->dim) * sizeof(float);
         if (k <= 32) k5_rescore_kernel<1><<<n, 256, dyn, stream>>>(rp);
         else k5_rescore_kernel<4><<<n, 256, dyn, stream>>>(rp);
@@ -485,7 +488,7 @@ static int launch_k2(crb_index* ix, const float* d_queries, int batch, int k, in
 static int search_impl(crb_index* ix, const float* d_queries, int batch, int k, int metric,
                        const int32_t* h_filt, float* d_scores, int64_t* d_rows,
                        int32_t* d_n_valid, uint64_t* d_keys, void* d_workspace,
-                       size_t workspace_bytes, int algo, cudaStream_t stream) {
+                       size_t workspace_bytes, int algo, cudaStream_t stream, const ExchangeDev* ex = nullptr) {
     uint8_t* ws = static_cast<uint8_t*>(d_workspace);
     const int M = ix->n_keys;
     if (algo < 0 || algo > 2) return fail("algo must be 0 (auto), 1 (streaming) or 2 (tensor core)");
@@ -614,14 +617,14 @@ static int search_impl(crb_index* ix, const float* d_queries, int batch, int k, 
             int rc;
             if (kv.first < 0) {
                 rc = launch_k2(ix, d_queries, batch, k, metric, kv.second, mask, ws, L, d_scores, d_rows, d_n_valid,
-                               d_keys, &unproven, stream);
+                               d_keys, &unproven, stream, nullptr, nullptr, -1, nullptr, 0, ex);
             } else {
                 const int slot_f = slot_of_filter[kv.first];
                 rc = launch_k2(ix, d_queries, batch, k, metric, kv.second, mask, ws, L, d_scores, d_rows, d_n_valid,
                                d_keys, &unproven, stream, lists + size_t(slot_f) * size_t(stride),
                                reinterpret_cast<const uint32_t*>(ws + kWsCountsOffset) + slot_f,
                                static_cast<int64_t>(std::min<uint64_t>(h_counts[slot_f], uint64_t(ix->n_rows))),
-                               compact_buf, compact_cap);
+                               compact_buf, compact_cap, ex);
             }
             if (rc) return rc;
             if (!unproven.empty()) k1_sets[kv.first] = unproven;
@@ -642,7 +645,7 @@ static int search_impl(crb_index* ix, const float* d_queries, int batch, int k, 
         if (!groups.empty()) {
             const int nq = max_group <= 1 ? 1 : (max_group <= 2 ? 2 : 4);
             int rc = launch_k1(ix, d_queries, k, metric, groups, slot_of_filter, nq, ws, lists, d_scores,
-                               d_rows, d_n_valid, d_keys, stream);
+                               d_rows, d_n_valid, d_keys, stream, ex);
             if (rc) return rc;
         }
         first = false;
@@ -676,6 +679,53 @@ __global__ void __launch_bounds__(256) merge_keys_kernel(const uint64_t* __restr
     sink.scale = s_invq;
     block_merge_sorted_lists<4>(keys_in + static_cast<int64_t>(b) * k, n_lists, k,
                                 static_cast<int64_t>(batch) * k, sink, xchg, lane, warp, 8);
+}
+
+// Exchange epilogue: wait until every source rank has published `expected` queries into THIS rank's
+// gather buffer (the sinks of the peers' search kernels do the publishing), then merge.  Runs on
+// every GPU of the box at the same time; the spin is bounded so a lost peer cannot hang the GPU
+// (n_valid = -2 marks a timed-out query).
+__global__ void __launch_bounds__(256) merge_wait_kernel(const uint64_t* __restrict__ gather, uint64_t cap,
+                                                         const uint32_t* counters, uint32_t expected,
+                                                         int world, int batch, int k, int metric,
+                                                         const float* __restrict__ queries, int dim,
+                                                         float* scores, int64_t* rows, int32_t* n_valid,
+                                                         uint64_t* keys_out) {
+    __shared__ uint64_t xchg[2][32];
+    __shared__ float s_invq;
+    __shared__ int s_ok;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int b = blockIdx.x;
+    if (threadIdx.x == 0) {
+        const volatile uint32_t* c = counters;
+        int ok = 1;
+        for (int r = 0; r < world; ++r) {
+            long long spins = 0;
+            while (static_cast<int32_t>(c[r] - expected) < 0) {
+                if (++spins > (1ll << 27)) { ok = 0; break; }
+                __nanosleep(64);
+            }
+        }
+        __threadfence_system();
+        s_ok = ok;
+    }
+    if (warp == 1) {
+        const float iq = (metric == 0) ? warp_inv_qnorm(queries + static_cast<int64_t>(b) * dim, dim, lane) : 1.0f;
+        if (lane == 0) s_invq = iq;
+    }
+    __syncthreads();
+    if (!s_ok) {
+        if (threadIdx.x == 0) n_valid[b] = -2;
+        return;
+    }
+    TopKSink sink;
+    sink.scores = scores + static_cast<int64_t>(b) * k;
+    sink.rows = rows + static_cast<int64_t>(b) * k;
+    sink.n_valid = n_valid + b;
+    sink.keys = keys_out ? keys_out + static_cast<int64_t>(b) * k : nullptr;
+    sink.scale = s_invq;
+    block_merge_sorted_lists<1>(gather + static_cast<int64_t>(b) * k, world, k, static_cast<int64_t>(cap), sink, xchg,
+                                lane, warp, 8);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -938,6 +988,45 @@ extern "C" int crb_merge_keys(const uint64_t* d_keys_in, int32_t n_lists, int32_
     CRB_CUDA(guard.status);
     merge_keys_kernel<<<batch, 256, 0, static_cast<cudaStream_t>(stream)>>>(
         d_keys_in, n_lists, batch, k, metric, d_queries, dim, d_scores, d_rows, d_n_valid, d_keys_out);
+    CRB_LAUNCH_CHECK();
+    return 0;
+}
+
+extern "C" int crb_search_exchange(crb_index* ix, const float* d_queries, int32_t batch, int32_t k,
+                                   int32_t metric, const int32_t* h_filt, float* d_scores, int64_t* d_rows,
+                                   int32_t* d_n_valid, uint64_t* d_keys, void* d_workspace,
+                                   size_t workspace_bytes, int32_t algo, void* stream_,
+                                   const crb_exchange* exch, uint32_t call_index, uint32_t expected_total) {
+    if (int rc = validate_search(ix, batch, k, metric)) return rc;
+    if (!d_queries || !d_scores || !d_rows || !d_n_valid || !d_workspace)
+        return fail("NULL device pointer passed to crb_search_exchange");
+    if (!exch) return fail("exchange descriptor is NULL");
+    if (exch->world < 1 || exch->world > CRB_MAX_PEERS || exch->rank < 0 || exch->rank >= exch->world)
+        return fail("exchange: world must be in [1, %d] and rank in [0, world)", CRB_MAX_PEERS);
+    if (uint64_t(batch) * uint64_t(k) > exch->cap_keys)
+        return fail("exchange: batch*k = %lld exceeds the gather slot capacity %llu", (long long)batch * k,
+                    (unsigned long long)exch->cap_keys);
+    ExchangeDev ex;
+    memset(&ex, 0, sizeof ex);
+    ex.world = exch->world;
+    ex.rank = exch->rank;
+    ex.parity = static_cast<int32_t>(call_index & 1u);
+    ex.cap = exch->cap_keys;
+    for (int p = 0; p < exch->world; ++p) {
+        if (!exch->peer_keys[p] || !exch->peer_counters[p]) return fail("exchange: peer %d pointers are NULL", p);
+        ex.keys[p] = exch->peer_keys[p];
+        ex.counters[p] = exch->peer_counters[p];
+    }
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    DeviceGuard guard(ix->device);
+    CRB_CUDA(guard.status);
+    if (int rc = search_impl(ix, d_queries, batch, k, metric, h_filt, d_scores, d_rows, d_n_valid, nullptr,
+                             d_workspace, workspace_bytes, algo, stream, &ex))
+        return rc;
+    const uint64_t* my_gather = exch->peer_keys[exch->rank] + uint64_t(ex.parity) * uint64_t(ex.world) * ex.cap;
+    merge_wait_kernel<<<batch, 256, 0, stream>>>(my_gather, ex.cap, exch->peer_counters[exch->rank], expected_total,
+                                                 ex.world, batch, k, metric, d_queries, ix->dim, d_scores, d_rows,
+                                                 d_n_valid, d_keys);
     CRB_LAUNCH_CHECK();
     return 0;
 }

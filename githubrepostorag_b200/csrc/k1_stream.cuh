@@ -45,6 +45,7 @@ struct K1Params {
     int32_t dim;
     int32_t k;
     int32_t metric;
+    ExchangeDev ex;                // ex.world == 0: local search only
     K1Group groups[kMaxGroups];
 };
 
@@ -193,6 +194,9 @@ k1_stream_kernel(const __grid_constant__ K1Params p) {
         sink.n_valid = p.out_nvalid + qi;
         sink.keys = p.out_keys ? p.out_keys + static_cast<int64_t>(qi) * p.k : nullptr;
         sink.scale = s_invq;
+        sink.ex = p.ex.world > 0 ? &p.ex : nullptr;
+        sink.qi = qi;
+        sink.k = p.k;
         const uint64_t* lists = p.cand + (static_cast<int64_t>(blockIdx.y) * NQ + q) * gridDim.x * p.k;
         block_merge_sorted_lists<kK1MergeLPT>(lists, gridDim.x, p.k, p.k, sink, xchg, lane, warp, kK1Warps);
     }
@@ -290,6 +294,9 @@ k1_stream_generic_kernel(const __grid_constant__ K1Params p) {
     sink.n_valid = p.out_nvalid + qi;
     sink.keys = p.out_keys ? p.out_keys + static_cast<int64_t>(qi) * p.k : nullptr;
     sink.scale = s_invq;
+    sink.ex = p.ex.world > 0 ? &p.ex : nullptr;
+    sink.qi = qi;
+    sink.k = p.k;
     const uint64_t* lists = p.cand + static_cast<int64_t>(blockIdx.y) * gridDim.x * p.k;
     block_merge_sorted_lists<kK1MergeLPT>(lists, gridDim.x, p.k, p.k, sink, xchg, lane, warp, kK1Warps);
     if (threadIdx.x == 0) p.counters[blockIdx.y] = 0u;

@@ -688,6 +688,7 @@ struct K5Params {
     int32_t kprime;
     int32_t slots;
     int32_t metric;
+    ExchangeDev ex;             // ex.world == 0: local search only
 };
 
 template <int KPL>
@@ -760,12 +761,10 @@ __global__ void __launch_bounds__(256) k5_rescore_kernel(const __grid_constant__
         sink.n_valid = p.out_nvalid + qi;
         sink.keys = p.out_keys ? p.out_keys + static_cast<int64_t>(qi) * p.k : nullptr;
         sink.scale = cosine ? iq : 1.0f;
+        sink.qi = qi;
+        sink.k = p.k;
         int nv = 0;
-        for (int r = 0; r < p.k; ++r) {
-            sink.emit(r, s_out[r]);
-            nv += (s_out[r] != 0ull);
-        }
-        *sink.n_valid = nv;
+        for (int r = 0; r < p.k; ++r) nv += (s_out[r] != 0ull);
         // proof: every non-candidate row has exact (normalised) score <= tau_max + margin
         bool proven;
         if (tau_max == __uint_as_float(0xff800000u)) {
@@ -777,6 +776,11 @@ __global__ void __launch_bounds__(256) k5_rescore_kernel(const __grid_constant__
             const float kth = key_score(s_out[p.k - 1]) * iq;   // same units as the approximate scores
             proven = kth > tau_max + margin;
         }
+        // an unproven query is re-run by the streaming kernel, which then publishes it to the peers
+        sink.ex = (proven && p.ex.world > 0) ? &p.ex : nullptr;
+        for (int r = 0; r < p.k; ++r) sink.emit(r, s_out[r]);
+        *sink.n_valid = nv;
+        sink.finish();
         if (!proven) {
             const int at = atomicAdd(p.n_flagged, 1);
             p.flagged[at] = slot_q;

@@ -83,6 +83,21 @@ CRB_DEVINL void block_extract_topk(WarpTopK<KPL>& w, int k, uint64_t* __restrict
     __syncthreads();
 }
 
+// Peer-memory exchange of a row-sharded search (crb_search_exchange): every finished query's k
+// keys are stored straight into EVERY rank's gather buffer over NVLink, then a per-source arrival
+// counter on each rank is bumped (system-scope release), so no collective launch sits between
+// the shard searches and the cross-shard merge.
+constexpr int kMaxPeers = 8;
+struct ExchangeDev {
+    int32_t world;          // 0 = no exchange
+    int32_t rank;
+    int32_t parity;         // gather buffers are double-buffered by call parity
+    int32_t pad;
+    uint64_t cap;           // keys per (parity, source) slot
+    uint64_t* keys[kMaxPeers];      // peer p's gather buffer: [2][world][cap]
+    uint32_t* counters[kMaxPeers];  // peer p's arrival counters: [world], monotonic
+};
+
 // Output of one finished query: scores (times inv_qnorm), global rows, n_valid, keys.
 struct TopKSink {
     float* scores;      // [k]
@@ -90,6 +105,9 @@ struct TopKSink {
     int32_t* n_valid;   // [1]
     uint64_t* keys;     // [k] or nullptr
     float scale;        // 1/||q|| for cosine, 1 for inner product
+    const ExchangeDev* ex = nullptr;   // publish to peers when set
+    int32_t qi = 0;     // query index in the batch
+    int32_t k = 0;
     CRB_DEVINL void emit(int r, uint64_t key) const {
         if (key != 0ull) {
             scores[r] = key_score(key) * scale;
@@ -99,6 +117,18 @@ struct TopKSink {
             rows[r] = -1;
         }
         if (keys) keys[r] = key;
+        if (ex) {
+            const uint64_t off = (static_cast<uint64_t>(ex->parity) * ex->world + ex->rank) * ex->cap +
+                                 static_cast<uint64_t>(qi) * k + r;
+            for (int p = 0; p < ex->world; ++p) ex->keys[p][off] = key;
+        }
+    }
+    // called once by the emitting thread after the k-th emit
+    CRB_DEVINL void finish() const {
+        if (ex) {
+            __threadfence_system();
+            for (int p = 0; p < ex->world; ++p) atomicAdd_system(ex->counters[p] + ex->rank, 1u);
+        }
     }
 };
 
@@ -144,6 +174,7 @@ CRB_DEVINL void block_merge_sorted_lists(const uint64_t* __restrict__ lists, int
     if (threadIdx.x == 0) {
         *sink.n_valid = r;
         for (; r < k; ++r) sink.emit(r, 0ull);
+        sink.finish();
     }
     __syncthreads();
 }

@@ -125,6 +125,33 @@ int crb_merge_keys(const uint64_t *d_keys_in, int32_t n_lists, int32_t batch, in
                    int64_t *d_rows, int32_t *d_n_valid, uint64_t *d_keys_out, int32_t device,
                    void *stream);
 
+/* Row-sharded search with the cross-shard exchange fused in (no reference counterpart: the
+ * reference runs one replica).  Every rank of one box calls this with the same batch/k; each
+ * rank's search kernels store the k exact keys of every finished query straight into EVERY
+ * rank's gather buffer over NVLink peer memory and bump a per-source arrival counter there
+ * (system-scope release); a final kernel on each rank waits for `expected_total` arrivals from
+ * every source and merges -- no collective launch between search and merge.
+ *   peer_keys[p]     device pointer, valid on this rank, to rank p's gather buffer:
+ *                    uint64 [2 (call parity)][world][cap_keys]   (e.g. torch symmetric memory)
+ *   peer_counters[p] device pointer to rank p's uint32 [world] arrival counters (zeroed once)
+ *   call_index       0, 1, 2, ... (its parity picks the gather half; same on all ranks)
+ *   expected_total   queries every source has published once this call is done: the running sum
+ *                    of `batch` over all calls so far, this one included
+ * Outputs are the merged (global) top-k on every rank.  Other arguments as crb_search. */
+#define CRB_MAX_PEERS 8
+typedef struct crb_exchange {
+    int32_t rank;
+    int32_t world;
+    uint64_t cap_keys;
+    uint64_t *peer_keys[CRB_MAX_PEERS];
+    uint32_t *peer_counters[CRB_MAX_PEERS];
+} crb_exchange;
+int crb_search_exchange(crb_index *index, const float *d_queries, int32_t batch, int32_t k,
+                        int32_t metric, const int32_t *h_filt, float *d_scores, int64_t *d_rows,
+                        int32_t *d_n_valid, uint64_t *d_keys, void *d_workspace,
+                        size_t workspace_bytes, int32_t algo, void *stream,
+                        const crb_exchange *exchange, uint32_t call_index, uint32_t expected_total);
+
 /* Fetch stored rows as fp32 (the `embedding` member of the (Document, embedding, id) triples
  * LCCassandra returns; graph-retriever re-scores from it).  h_rows_idx are LOCAL row indices. */
 int crb_fetch_rows_host(crb_index *index, const int64_t *h_rows_idx, int32_t n, float *h_out);
