@@ -150,7 +150,7 @@ CRB_DEVINL void k2_sift_down(uint64_t* list, int ls, int i, int n, uint64_t key)
     }
     list[i * ls] = key;
 }
-__device__ __noinline__ uint2 k2_list_insert(uint64_t* list, uint64_t key, uint32_t state, float thr, int kprime, int ls) {
+CRB_DEVINL uint2 k2_list_insert(uint64_t* list, uint64_t key, uint32_t state, float thr, int kprime, int ls) {
     int count = static_cast<int>(state);
     if (count < kprime) {
         list[count * ls] = key;
@@ -172,8 +172,24 @@ CRB_DEVINL float4 lds_f4(uint32_t saddr) {
     return r;
 }
 
+// s[j] for a run-time j without spilling the array: a 5-level select tree (31 selects).
+CRB_DEVINL float k2_pick(const float (&s)[32], int j) {
+    float a[16], b[8], c[4], d[2];
+#pragma unroll
+    for (int i = 0; i < 16; ++i) a[i] = (j & 16) ? s[i + 16] : s[i];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) b[i] = (j & 8) ? a[i + 8] : a[i];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) c[i] = (j & 4) ? b[i + 4] : b[i];
+#pragma unroll
+    for (int i = 0; i < 2; ++i) d[i] = (j & 2) ? c[i + 2] : c[i];
+    return (j & 1) ? d[1] : d[0];
+}
+
 // Examine one 32-column chunk of this thread's accumulator row: scale, and admit columns that
 // beat the thread's threshold.  `inv_saddr` is the shared-window address of the chunk's scales.
+// Admissions run in warp-lockstep rounds (every lane that still has a pending column inserts one
+// per round), so the heap updates of different lanes overlap instead of serialising.
 CRB_DEVINL float k2_scan_chunk(const uint32_t (&v)[32], uint32_t inv_saddr, float thr, uint32_t& state,
                                uint64_t* my_list, int64_t n_first, int kprime, int ls) {
     float s[32];
@@ -189,13 +205,20 @@ CRB_DEVINL float k2_scan_chunk(const uint32_t (&v)[32], uint32_t inv_saddr, floa
     float best = s[0];
 #pragma unroll
     for (int j = 1; j < 32; ++j) best = fmaxf(best, s[j]);
-    if (best > thr) {
+    if (__any_sync(CRB_FULL_MASK, best > thr)) {
+        uint32_t hit = 0u;
 #pragma unroll
-        for (int j = 0; j < 32; ++j) {
-            if (s[j] > thr) {
-                const uint2 r = k2_list_insert(my_list, make_key(s[j], static_cast<uint32_t>(n_first + j)), state, thr, kprime, ls);
-                thr = __uint_as_float(r.x);
-                state = r.y;
+        for (int j = 0; j < 32; ++j) hit |= (s[j] > thr) ? (1u << j) : 0u;
+        while (__any_sync(CRB_FULL_MASK, hit != 0u)) {
+            if (hit != 0u) {
+                const int j = __ffs(hit) - 1;
+                hit &= hit - 1u;
+                const float sj = k2_pick(s, j);
+                if (sj > thr) {     // the threshold may have risen since the mask was built
+                    const uint2 r = k2_list_insert(my_list, make_key(sj, static_cast<uint32_t>(n_first + j)), state, thr, kprime, ls);
+                    thr = __uint_as_float(r.x);
+                    state = r.y;
+                }
             }
         }
     }
@@ -724,12 +747,35 @@ __global__ void __launch_bounds__(256) k5_rescore_kernel(const __grid_constant__
     for (int o = 16; o > 0; o >>= 1) tau = fmaxf(tau, __shfl_xor_sync(CRB_FULL_MASK, tau, o));
     if (lane == 0) s_tau[warp] = tau;
 
-    // exact canonical score of every candidate (warp per candidate)
+    // Prune before the expensive part: find the k-th best APPROXIMATE score a_k among the candidates.
+    // A candidate with approx < a_k - 2*margin has exact < a_k - margin <= the exact score of each of
+    // the k best approximate candidates, so it cannot be in the exact top-k and is not re-scored.
+    const float margin = p.eps[slot_q] * (cosine ? 1.0f : p.max_norm);
+    float cut = __uint_as_float(0xff800000u);
+    {
+        WarpTopK<KPL> atop;
+        atop.init(p.k, lane);
+        for (int c0 = warp * 32; c0 < n_cand; c0 += 8 * 32) {
+            const int c = c0 + lane;
+            const uint64_t e = c < n_cand ? cand[c] : 0ull;
+#pragma unroll 1
+            for (int l = 0; l < 32; ++l) {
+                const uint64_t el = __shfl_sync(CRB_FULL_MASK, e, l);
+                if (el > atop.thr) atop.insert(el, lane);      // warp-uniform
+            }
+        }
+        block_extract_topk<KPL>(atop, p.k, s_out, xchg, lane, warp, 8);
+        const uint64_t kth = s_out[p.k - 1];
+        if (kth != 0ull) cut = key_score(kth) - 2.0f * margin;
+        __syncthreads();
+    }
+
+    // exact canonical score of every surviving candidate (warp per candidate)
     WarpTopK<KPL> top;
     top.init(p.k, lane);
     for (int c = warp; c < n_cand; c += 8) {
         const uint64_t e = cand[c];
-        if (e == 0ull) continue;                       // warp-uniform
+        if (e == 0ull || key_score(e) < cut) continue;   // warp-uniform
         const uint32_t row = p.remap ? p.remap[key_row(e)] : key_row(e);
         const __half* rp = p.rows + static_cast<int64_t>(row) * p.dim;
         float acc = 0.f;
@@ -772,7 +818,6 @@ __global__ void __launch_bounds__(256) k5_rescore_kernel(const __grid_constant__
         } else if (nv < p.k) {
             proven = false;
         } else {
-            const float margin = p.eps[slot_q] * (cosine ? 1.0f : p.max_norm);
             const float kth = key_score(s_out[p.k - 1]) * iq;   // same units as the approximate scores
             proven = kth > tau_max + margin;
         }
