@@ -41,6 +41,8 @@ PROTOTYPES = {
     "crb_last_error": (C.c_char_p, []),
     "crb_index_create": (C.c_int, [C.POINTER(_vp), _vp, _vp, _vp, _i64, _i32, _i32, _i64, _i32]),
     "crb_index_destroy": (C.c_int, [_vp]),
+    "crb_index_rebind": (C.c_int, [_vp, _vp, _vp, _vp, _i64, _i64]),
+    "crb_tombstone_rows": (C.c_int, [_vp, _vp, _i32]),
     "crb_encode_rows": (C.c_int, [_vp, _vp, _vp, _i64, _i32, _i32, _vp]),
     "crb_row_inv_norms": (C.c_int, [_vp, _vp, _i64, _i32, _i32, _vp]),
     "crb_workspace_bytes": (_sz, [_vp, _i32, _i32, _i32]),

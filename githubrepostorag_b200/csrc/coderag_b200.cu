@@ -116,6 +116,7 @@ struct crb_index {
     const __half* rows = nullptr;
     const float* inv_norm = nullptr;
     const int32_t* codes = nullptr;
+    int64_t code_stride = 0;       // elements between key columns of `codes`
     int64_t n_rows = 0;
     int32_t dim = 0;
     int32_t n_keys = 0;
@@ -567,6 +568,7 @@ static int search_impl(crb_index* ix, const float* d_queries, int batch, int k, 
             kp.masks = any_k2_filtered ? masks : nullptr;
             kp.mask_stride = mstride;
             kp.n_rows = ix->n_rows;
+            kp.code_stride = ix->code_stride;
             kp.list_stride = stride;
             kp.n_keys = M;
             kp.n_filters = f_hi - f_lo;
@@ -799,6 +801,41 @@ static int validate_search(const crb_index* ix, int batch, int k, int metric) {
 
 }  // namespace crb
 
+namespace crb {
+// (Re)bind the corpus buffers of an index: pointers, row count, corpus tensor maps, largest norm.
+static int bind_buffers(crb_index* ix, const void* d_rows_f16, const float* d_inv_norm, const int32_t* d_codes,
+                        int64_t n_rows, int64_t code_stride) {
+    ix->rows = static_cast<const __half*>(d_rows_f16);
+    ix->inv_norm = d_inv_norm;
+    ix->codes = d_codes;
+    ix->code_stride = code_stride;
+    ix->n_rows = n_rows;
+    ix->k2_ok = false;
+    ix->max_norm = 0.f;
+    // tensor-core path set-up: corpus tensor maps and the largest row norm
+    if (n_rows > 0 && make_map_f16(&ix->map_rows, d_rows_f16, n_rows, ix->dim, kK2BlockN) == 0 &&
+        make_map_f16(&ix->map_rows_half, d_rows_f16, n_rows, ix->dim, kK2BlockN / 2) == 0) {
+        unsigned* d_bits = nullptr;
+        const unsigned inf_bits = 0x7f800000u;
+        unsigned h_bits = inf_bits;
+        cudaError_t e = cudaMalloc(&d_bits, sizeof(unsigned));
+        if (e == cudaSuccess) e = cudaMemcpy(d_bits, &inf_bits, sizeof(unsigned), cudaMemcpyHostToDevice);
+        if (e == cudaSuccess) {
+            min_pos_inv_norm_kernel<<<static_cast<unsigned>(std::min<int64_t>((n_rows + 255) / 256, 148 * 8)), 256>>>(d_inv_norm, n_rows, d_bits);
+            g_launches.fetch_add(1, std::memory_order_relaxed);
+            e = cudaMemcpy(&h_bits, d_bits, sizeof(unsigned), cudaMemcpyDeviceToHost);
+        }
+        if (d_bits) cudaFree(d_bits);
+        if (e != cudaSuccess) return fail("index set-up failed: %s", cudaGetErrorString(e));
+        float min_inv;
+        memcpy(&min_inv, &h_bits, 4);
+        ix->max_norm = (h_bits == inf_bits || !(min_inv > 0.f)) ? 0.f : 1.0f / min_inv;
+        ix->k2_ok = true;
+    }
+    return 0;
+}
+}  // namespace crb
+
 // =============================================================================================
 // extern "C"
 // =============================================================================================
@@ -830,40 +867,53 @@ extern "C" int crb_index_create(crb_index** out, const void* d_rows_f16, const f
         return fail("device %d is sm_%d%d; this library is built for sm_100a (B200) only", device,
                     prop.major, prop.minor);
     crb_index* ix = new crb_index();
-    ix->rows = static_cast<const __half*>(d_rows_f16);
-    ix->inv_norm = d_inv_norm;
-    ix->codes = d_codes;
-    ix->n_rows = n_rows;
-    ix->dim = dim;
-    ix->n_keys = n_keys;
-    ix->row_offset = row_offset;
     ix->device = device;
     ix->sm_count = prop.multiProcessorCount;
+    ix->row_offset = row_offset;
+    ix->dim = dim;
+    ix->n_keys = n_keys;
     ix->lanes.resize(std::max(1, env_int("CODERAG_B200_LANES", 4)));
-    // tensor-core path set-up: corpus tensor map and the largest row norm
-    if (n_rows > 0 && make_map_f16(&ix->map_rows, d_rows_f16, n_rows, dim, kK2BlockN) == 0 &&
-        make_map_f16(&ix->map_rows_half, d_rows_f16, n_rows, dim, kK2BlockN / 2) == 0) {
-        unsigned* d_bits = nullptr;
-        const unsigned inf_bits = 0x7f800000u;
-        unsigned h_bits = inf_bits;
-        cudaError_t e = cudaMalloc(&d_bits, sizeof(unsigned));
-        if (e == cudaSuccess) e = cudaMemcpy(d_bits, &inf_bits, sizeof(unsigned), cudaMemcpyHostToDevice);
-        if (e == cudaSuccess) {
-            min_pos_inv_norm_kernel<<<std::min<int64_t>((n_rows + 255) / 256, 148 * 8), 256>>>(d_inv_norm, n_rows, d_bits);
-            g_launches.fetch_add(1, std::memory_order_relaxed);
-            e = cudaMemcpy(&h_bits, d_bits, sizeof(unsigned), cudaMemcpyDeviceToHost);
-        }
-        if (d_bits) cudaFree(d_bits);
-        if (e != cudaSuccess) {
-            delete ix;
-            return fail("index set-up failed: %s", cudaGetErrorString(e));
-        }
-        float min_inv;
-        memcpy(&min_inv, &h_bits, 4);
-        ix->max_norm = (h_bits == inf_bits || !(min_inv > 0.f)) ? 0.f : 1.0f / min_inv;
-        ix->k2_ok = true;
+    if (int rc = bind_buffers(ix, d_rows_f16, d_inv_norm, d_codes, n_rows, n_rows)) {
+        delete ix;
+        return rc;
     }
     *out = ix;
+    return 0;
+}
+
+extern "C" int crb_index_rebind(crb_index* ix, const void* d_rows_f16, const float* d_inv_norm,
+                                const int32_t* d_codes, int64_t n_rows, int64_t code_stride) {
+    if (!ix) return fail("index is NULL");
+    if (n_rows < 0) return fail("n_rows must be >= 0");
+    if (n_rows > 0 && (!d_rows_f16 || !d_inv_norm)) return fail("rows / inv_norm pointers are NULL");
+    if (ix->n_keys > 0 && n_rows > 0 && !d_codes) return fail("codes pointer is NULL with n_keys > 0");
+    if (code_stride < n_rows) return fail("code_stride must be >= n_rows");
+    if (reinterpret_cast<uintptr_t>(d_rows_f16) % 16 != 0) return fail("rows must be 16-byte aligned");
+    if (ix->row_offset + n_rows > int64_t(0xffffffffll)) return fail("row_offset + n_rows must fit in 32 bits");
+    DeviceGuard guard(ix->device);
+    CRB_CUDA(guard.status);
+    return bind_buffers(ix, d_rows_f16, d_inv_norm, d_codes, n_rows, code_stride);
+}
+
+extern "C" int crb_tombstone_rows(crb_index* ix, const int64_t* h_rows_idx, int32_t n) {
+    if (!ix) return fail("index is NULL");
+    if (n <= 0) return 0;
+    if (!h_rows_idx) return fail("NULL pointer passed to crb_tombstone_rows");
+    for (int i = 0; i < n; ++i)
+        if (h_rows_idx[i] < 0 || h_rows_idx[i] >= ix->n_rows)
+            return fail("row index %lld out of range [0, %lld)", (long long)h_rows_idx[i], (long long)ix->n_rows);
+    DeviceGuard guard(ix->device);
+    CRB_CUDA(guard.status);
+    LaneHold hold{ix, checkout_lane(ix)};
+    Lane* l = hold.lane;
+    const size_t bytes = round_up(size_t(n) * sizeof(int64_t), 256);
+    if (int rc = lane_reserve(l, 0, bytes, bytes)) return rc;
+    memcpy(l->h_pin, h_rows_idx, size_t(n) * sizeof(int64_t));
+    CRB_CUDA(cudaMemcpyAsync(l->d_io, l->h_pin, size_t(n) * sizeof(int64_t), cudaMemcpyHostToDevice, l->stream));
+    tombstone_rows_kernel<<<(n + 255) / 256, 256, 0, l->stream>>>(const_cast<float*>(ix->inv_norm),
+                                                                  static_cast<const int64_t*>(l->d_io), n);
+    CRB_LAUNCH_CHECK();
+    CRB_CUDA(cudaStreamSynchronize(l->stream));
     return 0;
 }
 

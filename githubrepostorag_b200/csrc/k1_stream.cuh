@@ -129,7 +129,11 @@ k1_stream_kernel(const __grid_constant__ K1Params p) {
             }
         }
 #pragma unroll
-        for (int j = 0; j < R; ++j) invn[j] = cosine ? __ldg(p.inv_norm + row[j]) : 1.0f;
+        for (int j = 0; j < R; ++j) {
+            // inverse norm; NaN marks a deleted row (the NaN reaches the score and fails `s == s`)
+            const float in = __ldg(p.inv_norm + row[j]);
+            invn[j] = cosine ? in : (in == in ? 1.0f : in);
+        }
 
         float acc[NQ][R];
 #pragma unroll
@@ -261,7 +265,8 @@ k1_stream_generic_kernel(const __grid_constant__ K1Params p) {
         }
 #pragma unroll
         for (int j = 0; j < R; ++j) {
-            const float invn = cosine ? __ldg(p.inv_norm + row[j]) : 1.0f;
+            const float in = __ldg(p.inv_norm + row[j]);
+            const float invn = cosine ? in : (in == in ? 1.0f : in);
             const float s = warp_butterfly_sum(acc[j]) * invn;
             if (ok[j] && !(cosine && invn == 0.f) && s == s) {
                 const uint64_t key = make_key(s, p.row_offset + static_cast<uint32_t>(row[j]));

@@ -376,8 +376,8 @@ k2_gemm_topk_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_cons
         auto column_scale = [&](int64_t n) -> float {
             if (n >= p.n_rows) return qnan;
             if (p.mask && !((p.mask[n >> 5] >> (n & 31)) & 1u)) return qnan;
-            if (!cosine) return 1.0f;
-            const float in = __ldg(p.inv_norm + n);
+            const float in = __ldg(p.inv_norm + n);          // NaN = deleted row
+            if (!cosine) return in == in ? 1.0f : qnan;
             return in > 0.f ? in : qnan;
         };
         float pre[2] = {qnan, qnan};
@@ -630,8 +630,8 @@ k2_gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap map_q, const __grid
         auto column_scale = [&](int64_t n) -> float {
             if (n >= p.n_rows) return qnan;
             if (p.mask && !((p.mask[n >> 5] >> (n & 31)) & 1u)) return qnan;
-            if (!cosine) return 1.0f;
-            const float in = __ldg(p.inv_norm + n);
+            const float in = __ldg(p.inv_norm + n);          // NaN = deleted row
+            if (!cosine) return in == in ? 1.0f : qnan;
             return in > 0.f ? in : qnan;
         };
         float pre[2] = {qnan, qnan};
@@ -788,7 +788,8 @@ __global__ void __launch_bounds__(256) k5_rescore_kernel(const __grid_constant__
             q8[4] = b.x; q8[5] = b.y; q8[6] = b.z; q8[7] = b.w;
             acc = chunk_fma(v, q8, acc);
         }
-        const float invn = cosine ? __ldg(p.inv_norm + row) : 1.0f;
+        const float in = __ldg(p.inv_norm + row);
+        const float invn = cosine ? in : (in == in ? 1.0f : in);
         const float s = warp_butterfly_sum(acc) * invn;
         if (!(cosine && invn == 0.f) && s == s) {
             const uint64_t key = make_key(s, p.row_offset + row);

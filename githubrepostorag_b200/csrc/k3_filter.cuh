@@ -23,6 +23,7 @@ struct K3Params {
     uint32_t* masks;       // [n_filters, mask_stride] one pass bit per row (for K2), or nullptr
     int64_t mask_stride;
     int64_t n_rows;
+    int64_t code_stride;   // elements between consecutive key columns (>= n_rows)
     int64_t list_stride;
     int32_t n_keys;
     int32_t n_filters;
@@ -55,7 +56,7 @@ __global__ void __launch_bounds__(kK3Threads) k3_filter_kernel(const __grid_cons
 #pragma unroll
         for (int j = 0; j < kK3RowsPerThread; ++j) {
             const int64_t row = blk0 + j * kK3Threads + threadIdx.x;
-            code[j] = row < p.n_rows ? __ldg(p.codes + static_cast<int64_t>(m) * p.n_rows + row) : -1;
+            code[j] = row < p.n_rows ? __ldg(p.codes + static_cast<int64_t>(m) * p.code_stride + row) : -1;
         }
         for (int f = 0; f < p.n_filters; ++f) {
             const int32_t w = p.want[f][m];
@@ -155,6 +156,13 @@ __global__ void __launch_bounds__(256) row_inv_norms_kernel(const __half* __rest
         acc = warp_butterfly_sum(acc);
         if (lane == 0) inv_norm[row] = acc > 0.f ? __fdiv_rn(1.0f, __fsqrt_rn(acc)) : 0.f;
     }
+}
+
+// Deleted rows: an inverse norm of NaN marks a row that no search may return (either metric).
+__global__ void __launch_bounds__(256) tombstone_rows_kernel(float* __restrict__ inv_norm,
+                                                             const int64_t* __restrict__ idx, int n) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) inv_norm[idx[i]] = __uint_as_float(0x7fc00000u);
 }
 
 // Stored rows -> fp32 (the `embedding` member of LCCassandra's (Document, embedding, id)).

@@ -94,23 +94,31 @@ class MetadataDictionary:
 
 
 class DeviceShard:
-    """One row-shard of a corpus resident on one GPU."""
+    """One row-shard of a corpus resident on one GPU.
+
+    The buffers may be over-allocated (``capacity >= n_rows``) so rows can be appended without
+    re-uploading the shard (:meth:`append`); deleted rows are tombstoned in place
+    (:meth:`tombstone`, inverse norm := NaN) and never returned.
+    """
 
     def __init__(self, rows: torch.Tensor, inv_norm: torch.Tensor, codes: Optional[torch.Tensor],
-                 row_offset: int = 0):
+                 row_offset: int = 0, n_rows: Optional[int] = None):
         lib = N.load()
         if not rows.is_cuda or rows.dtype != torch.float16 or rows.dim() != 2 or not rows.is_contiguous():
-            raise ValueError("rows must be a contiguous fp16 CUDA tensor [n_rows, dim]")
-        n_rows, dim = rows.shape
-        if inv_norm.dtype != torch.float32 or inv_norm.numel() != n_rows or not inv_norm.is_cuda:
-            raise ValueError("inv_norm must be fp32 CUDA [n_rows]")
+            raise ValueError("rows must be a contiguous fp16 CUDA tensor [capacity, dim]")
+        cap, dim = rows.shape
+        n_rows = cap if n_rows is None else int(n_rows)
+        if not 0 <= n_rows <= cap:
+            raise ValueError("n_rows must be in [0, capacity]")
+        if inv_norm.dtype != torch.float32 or inv_norm.numel() != cap or not inv_norm.is_cuda:
+            raise ValueError("inv_norm must be fp32 CUDA [capacity]")
         n_keys = 0
         if codes is not None:
-            if codes.dtype != torch.int32 or codes.dim() != 2 or codes.shape[1] != n_rows or not codes.is_contiguous():
-                raise ValueError("codes must be a contiguous int32 CUDA tensor [n_keys, n_rows]")
+            if codes.dtype != torch.int32 or codes.dim() != 2 or codes.shape[1] != cap or not codes.is_contiguous():
+                raise ValueError("codes must be a contiguous int32 CUDA tensor [n_keys, capacity]")
             n_keys = codes.shape[0]
-        self.rows, self.inv_norm, self.codes = rows, inv_norm, codes
-        self.n_rows, self.dim, self.n_keys = int(n_rows), int(dim), int(n_keys)
+        self._rows_buf, self._inv_buf, self._codes_buf = rows, inv_norm, codes
+        self.n_rows, self.dim, self.n_keys = n_rows, int(dim), int(n_keys)
         self.row_offset = int(row_offset)
         self.device = rows.device
         handle = C.c_void_p()
@@ -119,43 +127,76 @@ class DeviceShard:
                                      self.device.index or 0))
         self._h = handle
         self._lib = lib
+        if cap != n_rows:
+            N.check(lib.crb_index_rebind(self._h, _ptr(rows), _ptr(inv_norm), _ptr(codes), n_rows, cap))
         self._ws_lock = threading.Lock()
         self._ws: Optional[torch.Tensor] = None
+
+    @property
+    def capacity(self) -> int:
+        return int(self._rows_buf.shape[0])
+
+    @property
+    def rows(self) -> torch.Tensor:
+        return self._rows_buf[:self.n_rows]
+
+    @property
+    def inv_norm(self) -> torch.Tensor:
+        return self._inv_buf[:self.n_rows]
+
+    @property
+    def codes(self) -> Optional[torch.Tensor]:
+        return None if self._codes_buf is None else self._codes_buf[:, :self.n_rows]
 
     # ---- construction ------------------------------------------------------------------
     @classmethod
     def from_host(cls, embeddings: np.ndarray, codes: Optional[np.ndarray] = None, *,
-                  device: int | torch.device = 0, row_offset: int = 0) -> "DeviceShard":
+                  device: int | torch.device = 0, row_offset: int = 0, capacity: Optional[int] = None
+                  ) -> "DeviceShard":
         """Upload host rows.  fp32 input is rounded to fp16 on the device (``crb_encode_rows``);
         fp16 input is copied as is and its inverse norms are computed on the device."""
-        lib = N.load()
         dev = torch.device("cuda", device) if isinstance(device, int) else device
         emb = np.ascontiguousarray(embeddings)
         if emb.ndim != 2:
             raise ValueError("embeddings must be [n_rows, dim]")
         n, d = emb.shape
-        rows = torch.empty((n, d), dtype=torch.float16, device=dev)
-        inv = torch.empty((n,), dtype=torch.float32, device=dev)
+        cap = max(n, int(capacity or 0))
+        rows = torch.empty((cap, d), dtype=torch.float16, device=dev)
+        inv = torch.empty((cap,), dtype=torch.float32, device=dev)
+        codes_t = None
+        if codes is not None and codes.shape[0] > 0:
+            codes_t = torch.full((codes.shape[0], cap), N.CODE_MISSING, dtype=torch.int32, device=dev)
+        cls._upload(rows, inv, codes_t, 0, emb, codes)
+        return cls(rows, inv, codes_t, row_offset, n_rows=n)
+
+    @staticmethod
+    def _upload(rows: torch.Tensor, inv: torch.Tensor, codes_t: Optional[torch.Tensor], at: int,
+                emb: np.ndarray, codes: Optional[np.ndarray]) -> None:
+        """Encode ``emb`` into ``rows[at:at+m]`` / ``inv[at:at+m]`` and copy its code columns."""
+        lib = N.load()
+        dev = rows.device
+        m, d = emb.shape
         stream = torch.cuda.current_stream(dev).cuda_stream
-        for lo in range(0, n, UPLOAD_BLOCK_ROWS):
-            hi = min(n, lo + UPLOAD_BLOCK_ROWS)
+        for lo in range(0, m, UPLOAD_BLOCK_ROWS):
+            hi = min(m, lo + UPLOAD_BLOCK_ROWS)
             blk = torch.from_numpy(emb[lo:hi])
             if emb.dtype == np.float16:
-                rows[lo:hi].copy_(blk, non_blocking=False)
+                rows[at + lo:at + hi].copy_(blk, non_blocking=False)
             elif emb.dtype == np.float32:
                 stage = blk.to(dev)
-                N.check(lib.crb_encode_rows(stage.data_ptr(), rows[lo:hi].data_ptr(), inv[lo:hi].data_ptr(),
-                                            hi - lo, d, dev.index or 0, stream))
+                N.check(lib.crb_encode_rows(stage.data_ptr(), rows[at + lo:at + hi].data_ptr(),
+                                            inv[at + lo:at + hi].data_ptr(), hi - lo, d, dev.index or 0, stream))
                 torch.cuda.current_stream(dev).synchronize()
             else:
                 raise ValueError("embeddings must be float16 or float32")
-        if emb.dtype == np.float16 and n > 0:
-            N.check(lib.crb_row_inv_norms(rows.data_ptr(), inv.data_ptr(), n, d, dev.index or 0, stream))
-        codes_t = None
-        if codes is not None and codes.shape[0] > 0:
-            codes_t = torch.from_numpy(np.ascontiguousarray(codes, dtype=np.int32)).to(dev)
+        if emb.dtype == np.float16 and m > 0:
+            N.check(lib.crb_row_inv_norms(rows[at:at + m].data_ptr(), inv[at:at + m].data_ptr(), m, d,
+                                          dev.index or 0, stream))
+        if codes_t is not None and m > 0:
+            if codes is None or codes.shape != (codes_t.shape[0], m):
+                raise ValueError(f"codes must be [{codes_t.shape[0]}, {m}]")
+            codes_t[:, at:at + m].copy_(torch.from_numpy(np.ascontiguousarray(codes, dtype=np.int32)))
         torch.cuda.current_stream(dev).synchronize()
-        return cls(rows, inv, codes_t, row_offset)
 
     @classmethod
     def from_device(cls, rows: torch.Tensor, codes: Optional[torch.Tensor] = None, *,
@@ -168,6 +209,41 @@ class DeviceShard:
             N.check(lib.crb_row_inv_norms(rows.data_ptr(), inv.data_ptr(), n, d, rows.device.index or 0,
                                           torch.cuda.current_stream(rows.device).cuda_stream))
         return cls(rows, inv, codes, row_offset)
+
+    # ---- write path -----------------------------------------------------
+    def append(self, embeddings: np.ndarray, codes: Optional[np.ndarray] = None) -> int:
+        """Append rows in place (growing the buffers geometrically when full) and re-bind the
+        index.  Returns the local index of the first new row.  No search may be in flight."""
+        emb = np.ascontiguousarray(embeddings)
+        if emb.ndim != 2 or emb.shape[1] != self.dim:
+            raise ValueError(f"embeddings must be [m, {self.dim}]")
+        m = emb.shape[0]
+        first = self.n_rows
+        if m == 0:
+            return first
+        torch.cuda.synchronize(self.device)
+        if first + m > self.capacity:
+            cap = max(first + m, 2 * self.capacity, 1024)
+            rows = torch.empty((cap, self.dim), dtype=torch.float16, device=self.device)
+            inv = torch.empty((cap,), dtype=torch.float32, device=self.device)
+            rows[:first].copy_(self._rows_buf[:first])
+            inv[:first].copy_(self._inv_buf[:first])
+            codes_t = None
+            if self._codes_buf is not None:
+                codes_t = torch.full((self.n_keys, cap), N.CODE_MISSING, dtype=torch.int32, device=self.device)
+                codes_t[:, :first].copy_(self._codes_buf[:, :first])
+            self._rows_buf, self._inv_buf, self._codes_buf = rows, inv, codes_t
+        self._upload(self._rows_buf, self._inv_buf, self._codes_buf, first, emb, codes)
+        self.n_rows = first + m
+        N.check(self._lib.crb_index_rebind(self._h, _ptr(self._rows_buf), _ptr(self._inv_buf), _ptr(self._codes_buf),
+                                           self.n_rows, self.capacity))
+        return first
+
+    def tombstone(self, local_rows: Sequence[int]) -> None:
+        """Delete rows in place: they are never returned again (``crb_tombstone_rows``)."""
+        idx = np.ascontiguousarray(local_rows, dtype=np.int64)
+        if len(idx):
+            N.check(self._lib.crb_tombstone_rows(self._h, _np_ptr(idx), len(idx)))
 
     def close(self) -> None:
         if getattr(self, "_h", None):

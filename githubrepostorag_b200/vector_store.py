@@ -35,21 +35,86 @@ from .types import (Content, Document, FilterCondition, FilterOperator, Metadata
 DEFAULT_FILTER_KEYS = ("namespace", "repo", "module", "file_path", "branch", "component_kind", "scope", "language")
 
 
+class _WriteGate:
+    """Many concurrent searches (the worker's thread pool) or one writer (append / delete /
+    compact re-bind the device buffers, which no search may be using).  Writers have preference:
+    once one is waiting, new readers queue behind it (re-entrant reads of a thread that is already
+    reading pass), so a stream of searches cannot starve an ingest."""
+
+    def __init__(self):
+        self._cv = threading.Condition()
+        self._readers = 0
+        self._writer: Optional[int] = None
+        self._depth = 0
+        self._waiting_writers = 0
+        self._local = threading.local()
+
+    def read(self):
+        gate = self
+
+        class _R:
+            def __enter__(self_inner):
+                me = threading.get_ident()
+                depth = getattr(gate._local, "reads", 0)
+                with gate._cv:
+                    if depth == 0 and gate._writer != me:
+                        while gate._writer is not None or gate._waiting_writers > 0:
+                            gate._cv.wait()
+                    gate._readers += 1
+                gate._local.reads = depth + 1
+
+            def __exit__(self_inner, *exc):
+                gate._local.reads -= 1
+                with gate._cv:
+                    gate._readers -= 1
+                    gate._cv.notify_all()
+        return _R()
+
+    def write(self):
+        gate = self
+
+        class _W:
+            def __enter__(self_inner):
+                me = threading.get_ident()
+                with gate._cv:
+                    if gate._writer == me:
+                        gate._depth += 1
+                        return
+                    if getattr(gate._local, "reads", 0):
+                        raise RuntimeError("internal: write requested while this thread holds a read")
+                    gate._waiting_writers += 1
+                    try:
+                        while gate._writer is not None or gate._readers > 0:
+                            gate._cv.wait()
+                    finally:
+                        gate._waiting_writers -= 1
+                    gate._writer, gate._depth = me, 1
+
+            def __exit__(self_inner, *exc):
+                with gate._cv:
+                    gate._depth -= 1
+                    if gate._depth == 0:
+                        gate._writer = None
+                        gate._cv.notify_all()
+        return _W()
+
+
 class _Rows:
     """Host-side id / text / metadata of the rows, list-backed or synthesised on demand."""
 
     def __init__(self):
-        self.ids: List[str] = []
+        self.ids: List[Optional[str]] = []      # None = deleted row (tombstoned on the device)
         self.texts: List[str] = []
         self.metas: List[Dict[str, Any]] = []
         self.pos: Dict[str, int] = {}
+        self.n_dead = 0
         self.id_fn: Optional[Callable[[int], str]] = None
         self.text_fn: Optional[Callable[[int], str]] = None
         self.meta_fn: Optional[Callable[[int], Dict[str, Any]]] = None
         self.n_lazy = 0
 
     def __len__(self) -> int:
-        return self.n_lazy if self.id_fn else len(self.ids)
+        return self.n_lazy if self.id_fn else len(self.ids) - self.n_dead
 
     def id(self, r: int) -> str:
         return self.id_fn(r) if self.id_fn else self.ids[r]
@@ -63,6 +128,19 @@ class _Rows:
         if self.id_fn:
             return dict(self.meta_fn(r)) if self.meta_fn else {}
         return dict(self.metas[r])
+
+
+def _reading(fn):
+    """Run a read-side face method under the store's read gate, after staged writes are flushed, so
+    the row numbers a search returns stay valid while ids / text / vectors are looked up."""
+    import functools
+
+    @functools.wraps(fn)
+    def wrapped(self, *a, **kw):
+        self._ensure_built()
+        with self._gate.read():
+            return fn(self, *a, **kw)
+    return wrapped
 
 
 class B200VectorStore:
@@ -81,11 +159,12 @@ class B200VectorStore:
         self.dim = dim
         self.dictionary = MetadataDictionary(filter_keys)
         self._rows = _Rows()
-        self._pending: List[np.ndarray] = []
-        self._codes: List[List[int]] = []
         self._shard: Optional[DeviceShard] = None
-        self._dirty = False
-        self._lock = threading.RLock()
+        self._gate = _WriteGate()
+        # writes are staged on the host and reach the device (append / tombstone) at the next read
+        self._pending_emb: List[np.ndarray] = []
+        self._pending_codes: List[np.ndarray] = []
+        self._pending_dead: List[int] = []
 
     # ------------------------------------------------------------------ construction / writes
     @property
@@ -108,45 +187,92 @@ class B200VectorStore:
 
     def _append(self, ids: Sequence[str], embeddings: np.ndarray, texts: Sequence[str],
                 metadatas: Sequence[Mapping[str, Any]]) -> List[str]:
+        """Upsert rows.  New rows are encoded straight into the device shard's spare capacity
+        (``DeviceShard.append`` -- no re-upload of what is already resident); a row whose id
+        exists is tombstoned and its replacement appended, as a CQL INSERT on the primary key
+        overwrites."""
         emb = np.asarray(embeddings, dtype=np.float32)
         if emb.ndim != 2 or len(ids) != emb.shape[0]:
             raise ValueError("embeddings must be [len(ids), dim]")
-        with self._lock:
+        with self._gate.write():
             if self._rows.id_fn:
                 raise RuntimeError("this store was bulk-loaded with from_arrays and is read-only")
             if self.dim is None:
                 self.dim = int(emb.shape[1])
             if emb.shape[1] != self.dim:
                 raise ValueError(f"embedding dimension {emb.shape[1]} != store dimension {self.dim}")
-            fresh_rows = []
-            for i, rid in enumerate(ids):
-                rid = str(rid)
+            last = {str(rid): i for i, rid in enumerate(ids)}          # duplicates inside the batch: last wins
+            order = sorted(last.values())
+            dead, codes = [], []
+            base = len(self._rows.ids)
+            for j, i in enumerate(order):
+                rid = str(ids[i])
                 md = {str(k): v for k, v in dict(metadatas[i] or {}).items() if v is not None}
-                codes = self.dictionary.encode_row(md)
-                if rid in self._rows.pos:      # upsert, as a Cassandra INSERT on the primary key
-                    r = self._rows.pos[rid]
-                    self._rows.texts[r], self._rows.metas[r] = texts[i], md
-                    self._codes[r] = codes
-                    self._overwrite(r, emb[i])
-                else:
-                    self._rows.pos[rid] = len(self._rows.ids)
-                    self._rows.ids.append(rid)
-                    self._rows.texts.append(texts[i])
-                    self._rows.metas.append(md)
-                    self._codes.append(codes)
-                    fresh_rows.append(i)
-            if fresh_rows:
-                self._pending.append(emb[fresh_rows].astype(np.float16))
-            self._dirty = True
+                old = self._rows.pos.get(rid)
+                if old is not None:
+                    dead.append(old)
+                    self._rows.ids[old] = None
+                    self._rows.n_dead += 1
+                self._rows.pos[rid] = base + j
+                self._rows.ids.append(rid)
+                self._rows.texts.append(texts[i])
+                self._rows.metas.append(md)
+                codes.append(self.dictionary.encode_row(md))
+            code_mat = np.asarray(codes, dtype=np.int32).T.copy() if codes else np.empty((self.dictionary.n_keys, 0), np.int32)
+            self._pending_emb.append(emb[order].astype(np.float16))
+            self._pending_codes.append(code_mat)
+            self._pending_dead.extend(dead)
         return [str(i) for i in ids]
 
-    def _overwrite(self, r: int, vec: np.ndarray) -> None:
-        lo = 0
-        for blk in self._pending:
-            if r < lo + len(blk):
-                blk[r - lo] = vec.astype(np.float16)
+    def _flush(self) -> None:
+        """Bring staged writes to the device: append the new rows, tombstone the replaced / deleted."""
+        with self._gate.write():
+            if self._pending_emb:
+                new_emb = np.concatenate(self._pending_emb)
+                code_mat = np.concatenate(self._pending_codes, axis=1)
+                self._pending_emb, self._pending_codes = [], []
+                if self._shard is None:
+                    self._shard = DeviceShard.from_host(new_emb, code_mat, device=self.device,
+                                                        capacity=max(1024, 2 * len(new_emb)))
+                else:
+                    self._shard.append(new_emb, code_mat)
+            if self._pending_dead and self._shard is not None:
+                dead = [r for r in self._pending_dead if r < self._shard.n_rows]
+                self._pending_dead = []
+                if dead:
+                    self._shard.tombstone(dead)
+            self._maybe_compact()
+
+    def _maybe_compact(self) -> None:
+        """Rebuild the shard without its tombstones once they outnumber the live rows."""
+        r = self._rows
+        if r.n_dead > 1024 and r.n_dead > len(r.ids) - r.n_dead:
+            self.compact()
+
+    def compact(self) -> None:
+        """Drop tombstoned rows (device-side gather of the live rows into fresh buffers)."""
+        import torch
+        with self._gate.write():
+            r = self._rows
+            if self._pending_emb or self._pending_dead:
+                self._flush()
+            if r.id_fn or self._shard is None or r.n_dead == 0:
                 return
-            lo += len(blk)
+            live = [i for i, rid in enumerate(r.ids) if rid is not None]
+            idx = torch.as_tensor(live, dtype=torch.int64, device=self._shard.device)
+            old = self._shard
+            rows = old.rows.index_select(0, idx).contiguous()
+            inv = old.inv_norm.index_select(0, idx).contiguous()
+            codes = None if old.codes is None else old.codes.index_select(1, idx).contiguous()
+            if rows.shape[0] == 0:
+                rows = torch.empty((0, old.dim), dtype=torch.float16, device=old.device)
+            self._shard = DeviceShard(rows, inv, codes, old.row_offset)
+            old.close()
+            r.ids = [r.ids[i] for i in live]
+            r.texts = [r.texts[i] for i in live]
+            r.metas = [r.metas[i] for i in live]
+            r.pos = {rid: i for i, rid in enumerate(r.ids)}
+            r.n_dead = 0
 
     def add(self, nodes: Sequence[Any], **kwargs: Any) -> List[str]:
         """LlamaIndex face: nodes carry ``embedding``, ``node_id``, ``metadata``, text."""
@@ -186,43 +312,68 @@ class B200VectorStore:
                               list(ids) if ids else None)
 
     def delete(self, ref_doc_id: str, **kwargs: Any) -> None:
-        with self._lock:
-            r = self._rows.pos.get(str(ref_doc_id))
+        """Tombstone the row on the device (``crb_tombstone_rows``); unknown ids are ignored."""
+        with self._gate.write():
+            r = self._rows.pos.pop(str(ref_doc_id), None)
             if r is None:
                 return
-            emb = np.concatenate(self._pending) if self._pending else np.empty((0, self.dim or 0), np.float16)
-            keep = np.ones(len(emb), dtype=bool)
-            keep[r] = False
-            self._pending = [emb[keep]]
-            for lst in (self._rows.ids, self._rows.texts, self._rows.metas, self._codes):
-                del lst[r]
-            self._rows.pos = {rid: i for i, rid in enumerate(self._rows.ids)}
-            self._dirty = True
+            self._rows.ids[r] = None
+            self._rows.n_dead += 1
+            self._pending_dead.append(r)
 
     def _ensure_built(self) -> DeviceShard:
-        with self._lock:
-            if self._shard is not None and not self._dirty:
-                return self._shard
-            if self._rows.id_fn:
-                return self._shard  # bulk-loaded, never dirty
+        if self._pending_emb or self._pending_dead:
+            self._flush()
+        if self._shard is None:
             if self.dim is None:
                 raise RuntimeError("empty store: dimension unknown (pass dim=...)")
-            emb = np.concatenate(self._pending) if self._pending else np.empty((0, self.dim), np.float16)
-            self._pending = [emb]
-            codes = (np.asarray(self._codes, dtype=np.int32).T.copy() if self._codes
-                     else np.empty((self.dictionary.n_keys, 0), np.int32))
-            if self._shard is not None:
-                self._shard.close()
-            self._shard = DeviceShard.from_host(emb, codes, device=self.device)
-            self._dirty = False
-            return self._shard
+            with self._gate.write():
+                if self._shard is None:
+                    self._shard = DeviceShard.from_host(np.empty((0, self.dim), np.float16),
+                                                        np.empty((self.dictionary.n_keys, 0), np.int32),
+                                                        device=self.device, capacity=1024)
+        return self._shard
 
     def close(self) -> None:
         """Release device resources (mirrors ``GraphRetrieverFactory.close``, ``graph_rag_retrievers.py:136-140``)."""
-        with self._lock:
+        with self._gate.write():
             if self._shard is not None:
                 self._shard.close()
                 self._shard = None
+
+    # ------------------------------------------------------------------ persistence (SURVEY.md §8f-4)
+    def save(self, path: str) -> None:
+        """Checkpoint the store to one ``.npz`` file: the fp16 rows, code columns, dictionary, ids,
+        text and metadata (live rows only).  The reference's equivalent is the Cassandra PVC
+        (``helm/values.yaml:25-28``)."""
+        import json
+        with self._gate.write():
+            if self._rows.id_fn:
+                raise RuntimeError("bulk-loaded (from_arrays) stores keep no ids/text to save")
+            self.compact() if self._rows.n_dead else None
+            sh = self._ensure_built()
+            meta = {"format": 1, "dim": self.dim, "metric": self.metric, "table_name": self.table_name,
+                    "keys": self.dictionary.keys, "values": self.dictionary.values,
+                    "ids": self._rows.ids, "texts": self._rows.texts, "metas": self._rows.metas}
+            blob = np.frombuffer(json.dumps(meta).encode("utf-8"), dtype=np.uint8)
+            codes = sh.codes.cpu().numpy() if sh.codes is not None else np.empty((0, sh.n_rows), np.int32)
+            with open(path, "wb") as f:
+                np.savez(f, rows16=sh.rows.cpu().numpy(), codes=codes, meta=blob)
+
+    @classmethod
+    def load(cls, path: str, *, embedding: Any = None, device: int = 0) -> "B200VectorStore":
+        import json
+        with np.load(path) as z:
+            meta = json.loads(bytes(z["meta"]).decode("utf-8"))
+            rows16, codes = z["rows16"], z["codes"]
+        st = cls(embedding, dim=int(meta["dim"]), filter_keys=meta["keys"], device=device,
+                 table_name=meta.get("table_name", "embeddings"), metric=meta.get("metric", "cosine"))
+        st.dictionary.values = [dict(v) for v in meta["values"]]
+        st._rows.ids, st._rows.texts, st._rows.metas = list(meta["ids"]), list(meta["texts"]), list(meta["metas"])
+        st._rows.pos = {rid: i for i, rid in enumerate(st._rows.ids)}
+        st._shard = DeviceShard.from_host(rows16, codes if codes.shape[0] else None, device=device,
+                                          capacity=max(1024, len(rows16)))
+        return st
 
     def __len__(self) -> int:
         return len(self._rows)
@@ -230,7 +381,6 @@ class B200VectorStore:
     # ------------------------------------------------------------------ the hot path
     def _search(self, queries: np.ndarray, k: int, filters: Sequence[Optional[Mapping[str, Any]]],
                 algo: int = 0) -> Tuple[np.ndarray, np.ndarray, np.ndarray]:
-        shard = self._ensure_built()
         k = int(k)
         if k < 1:
             raise ValueError("k must be >= 1")
@@ -239,7 +389,8 @@ class B200VectorStore:
         filt = None
         if any(f for f in filters):
             filt = np.stack([self.dictionary.encode_filter(f) for f in filters])
-        return shard.search_host(queries, k, metric=self.metric, filt=filt, algo=algo)
+        with self._gate.read():
+            return self._shard.search_host(queries, k, metric=self.metric, filt=filt, algo=algo)
 
     def _embed_query(self, text: str) -> List[float]:
         if self.embeddings is None:
@@ -274,9 +425,12 @@ class B200VectorStore:
             raise NotImplementedError("node_ids restriction is not supported")
         if query.query_embedding is None:
             raise ValueError("query_embedding is required (is_embedding_query=True)")
-        q = np.asarray(query.query_embedding, dtype=np.float32)[None, :]
         flt = self._filters_to_dict(getattr(query, "filters", None))
-        scores, rows, n_valid = self._search(q, query.similarity_top_k, [flt])
+        return self._query(np.asarray(query.query_embedding, dtype=np.float32)[None, :], int(query.similarity_top_k), flt)
+
+    @_reading
+    def _query(self, q: np.ndarray, k: int, flt: Optional[Dict[str, Any]]) -> VectorStoreQueryResult:
+        scores, rows, n_valid = self._search(q, k, [flt])
         nodes, sims, ids = [], [], []
         for j in range(int(n_valid[0])):
             r = int(rows[0, j])
@@ -304,15 +458,17 @@ class B200VectorStore:
         scores, rows, n_valid = self._search(q, k, [dict(filter) if filter else None])
         return [(int(rows[0, j]), float(scores[0, j])) for j in range(int(n_valid[0]))]
 
+    @_reading
     def similarity_search_with_embedding_id_by_vector(
             self, embedding: List[float], k: int = 4, filter: Optional[Dict[str, str]] = None,
             body_search: Any = None) -> List[Tuple[Document, List[float], str]]:
         if body_search:
             raise NotImplementedError("body_search is not supported")
         hits = self._hits(embedding, k, filter)
-        vecs = self._ensure_built().fetch_rows([r for r, _ in hits])
+        vecs = self._shard.fetch_rows([r for r, _ in hits])
         return [(self._doc(r, s), vecs[i].tolist(), self._rows.id(r)) for i, (r, s) in enumerate(hits)]
 
+    @_reading
     def similarity_search_with_score_id_by_vector(
             self, embedding: List[float], k: int = 4, filter: Optional[Dict[str, str]] = None,
             body_search: Any = None) -> List[Tuple[Document, float, str]]:
@@ -358,11 +514,13 @@ class B200VectorStore:
         qvec = self._embed_query(query)
         return qvec, self.search(qvec, k=k, filter=filter)
 
+    @_reading
     def search(self, embedding: Sequence[float], k: int = 4, filter: Optional[Dict[str, Any]] = None, **kw) -> List[Content]:
         hits = self._hits(embedding, k, filter)
-        vecs = self._ensure_built().fetch_rows([r for r, _ in hits])
+        vecs = self._shard.fetch_rows([r for r, _ in hits])
         return [self._content(r, vecs[i]) for i, (r, _) in enumerate(hits)]
 
+    @_reading
     def get(self, ids: Sequence[str], filter: Optional[Dict[str, Any]] = None, **kw) -> List[Content]:
         rows = []
         for rid in dict.fromkeys(ids):
@@ -372,9 +530,10 @@ class B200VectorStore:
             if filter and any(str(self._rows.meta(r).get(k)) != str(v) for k, v in filter.items()):
                 continue
             rows.append(r)
-        vecs = self._ensure_built().fetch_rows(rows)
+        vecs = self._shard.fetch_rows(rows)
         return [self._content(r, vecs[i]) for i, r in enumerate(rows)]
 
+    @_reading
     def adjacent(self, edges: Iterable[Any], query_embedding: Sequence[float], k: int,
                  filter: Optional[Dict[str, Any]] = None, **kw) -> List[Content]:
         """All rows adjacent through ``edges`` -- one filtered top-k per distinct
@@ -410,7 +569,7 @@ class B200VectorStore:
                 if r not in best or s > best[r]:
                     best[r] = s
         top = sorted(best.items(), key=lambda t: (-t[1], -t[0]))[:k]
-        vecs = self._ensure_built().fetch_rows([r for r, _ in top])
+        vecs = self._shard.fetch_rows([r for r, _ in top])
         return [self._content(r, vecs[i]) for i, (r, _) in enumerate(top)]
 
 

@@ -67,6 +67,17 @@ int crb_index_create(crb_index **out, const void *d_rows_f16, const float *d_inv
                      int64_t row_offset, int32_t device);
 int crb_index_destroy(crb_index *index);
 
+/* Write path (stands for LCCassandra.add_documents / CQL INSERT and DELETE on the embeddings
+ * tables: ingest/src/app/services/vector_write_service.py:136-159).  The store appends rows to
+ * buffers it grows geometrically and then re-binds the index to them: new pointers / row count,
+ * `code_stride` = elements between consecutive key columns of `codes` (>= n_rows, so columns can
+ * be over-allocated).  No search may be in flight on the index during the call. */
+int crb_index_rebind(crb_index *index, const void *d_rows_f16, const float *d_inv_norm,
+                     const int32_t *d_codes, int64_t n_rows, int64_t code_stride);
+/* Delete rows (LOCAL indices): their inverse norm becomes NaN, which no search returns under
+ * either metric.  Returns when the device has been updated. */
+int crb_tombstone_rows(crb_index *index, const int64_t *h_rows_idx, int32_t n);
+
 /* Ingest-side conversion (stands for the embedding column write of
  * ingest/src/app/services/vector_write_service.py:158-159): fp32 rows -> fp16 rows and their
  * inverse norms (norm taken of the fp16-rounded row, which is the corpus searched). */
