@@ -47,6 +47,7 @@ PROTOTYPES = {
     "crb_row_inv_norms": (C.c_int, [_vp, _vp, _i64, _i32, _i32, _vp]),
     "crb_workspace_bytes": (_sz, [_vp, _i32, _i32, _i32]),
     "crb_search": (C.c_int, [_vp, _vp, _i32, _i32, _i32, _vp, _vp, _vp, _vp, _vp, _vp, _sz, _i32, _vp]),
+    "crb_search_masked": (C.c_int, [_vp, _vp, _i32, _i32, _i32, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _sz, _i32, _vp]),
     "crb_search_host": (C.c_int, [_vp, _vp, _i32, _i32, _i32, _vp, _vp, _vp, _vp, _i32]),
     "crb_merge_keys": (C.c_int, [_vp, _i32, _i32, _i32, _i32, _vp, _i32, _vp, _vp, _vp, _vp, _i32, _vp]),
     "crb_search_exchange": (C.c_int, [_vp, _vp, _i32, _i32, _i32, _vp, _vp, _vp, _vp, _vp, _vp, _sz, _i32, _vp,

@@ -489,29 +489,32 @@ static int launch_k2(crb_index* ix, const float* d_queries, int batch, int k, in
 static int search_impl(crb_index* ix, const float* d_queries, int batch, int k, int metric,
                        const int32_t* h_filt, float* d_scores, int64_t* d_rows,
                        int32_t* d_n_valid, uint64_t* d_keys, void* d_workspace,
-                       size_t workspace_bytes, int algo, cudaStream_t stream, const ExchangeDev* ex = nullptr) {
+                       size_t workspace_bytes, int algo, cudaStream_t stream, const ExchangeDev* ex = nullptr,
+                       const uint32_t* const* h_mask_ptrs = nullptr) {
     uint8_t* ws = static_cast<uint8_t*>(d_workspace);
     const int M = ix->n_keys;
     if (algo < 0 || algo > 2) return fail("algo must be 0 (auto), 1 (streaming) or 2 (tensor core)");
 
     // distinct filters of the batch
     std::vector<std::array<int32_t, kMaxKeys>> filters;
+    std::vector<const uint32_t*> filter_masks;       // caller-built row mask of each distinct filter (or nullptr)
     std::vector<int> fid(batch, -1);
-    if (h_filt && M > 0) {
+    if ((h_filt && M > 0) || h_mask_ptrs) {
         for (int b = 0; b < batch; ++b) {
             std::array<int32_t, kMaxKeys> f;
             f.fill(CRB_FILT_ANY);
             bool any = false;
-            for (int m = 0; m < M; ++m) {
+            for (int m = 0; m < M && h_filt; ++m) {
                 f[m] = h_filt[size_t(b) * M + m];
                 if (f[m] < CRB_FILT_IMPOSSIBLE) return fail("filter code %d out of range", f[m]);
                 any |= (f[m] != CRB_FILT_ANY);
             }
-            if (!any) continue;
+            const uint32_t* rm = h_mask_ptrs ? h_mask_ptrs[b] : nullptr;
+            if (!any && !rm) continue;
             int id = -1;
             for (size_t i = 0; i < filters.size(); ++i)
-                if (filters[i] == f) { id = static_cast<int>(i); break; }
-            if (id < 0) { id = static_cast<int>(filters.size()); filters.push_back(f); }
+                if (filters[i] == f && filter_masks[i] == rm) { id = static_cast<int>(i); break; }
+            if (id < 0) { id = static_cast<int>(filters.size()); filters.push_back(f); filter_masks.push_back(rm); }
             fid[b] = id;
         }
     }
@@ -574,6 +577,7 @@ static int search_impl(crb_index* ix, const float* d_queries, int batch, int k, 
             kp.n_filters = f_hi - f_lo;
             for (int f = f_lo; f < f_hi; ++f) {
                 slot_of_filter[f] = f - f_lo;
+                kp.extra[f - f_lo] = filter_masks[f];
                 for (int m = 0; m < kMaxKeys; ++m) {
                     kp.want[f - f_lo][m] = m < M ? filters[f][m] : CRB_FILT_ANY;
                     if (m < M && filters[f][m] != CRB_FILT_ANY) kp.used_keys |= (1u << m);
@@ -983,6 +987,20 @@ extern "C" int crb_search(crb_index* ix, const float* d_queries, int32_t batch, 
     CRB_CUDA(guard.status);
     return search_impl(ix, d_queries, batch, k, metric, h_filt, d_scores, d_rows, d_n_valid, d_keys,
                        d_workspace, workspace_bytes, algo, static_cast<cudaStream_t>(stream));
+}
+
+extern "C" int crb_search_masked(crb_index* ix, const float* d_queries, int32_t batch, int32_t k,
+                                 int32_t metric, const int32_t* h_filt, const uint32_t* const* h_row_mask_ptrs,
+                                 float* d_scores, int64_t* d_rows, int32_t* d_n_valid, uint64_t* d_keys,
+                                 void* d_workspace, size_t workspace_bytes, int32_t algo, void* stream) {
+    if (int rc = validate_search(ix, batch, k, metric)) return rc;
+    if (!d_queries || !d_scores || !d_rows || !d_n_valid || !d_workspace)
+        return fail("NULL device pointer passed to crb_search_masked");
+    DeviceGuard guard(ix->device);
+    CRB_CUDA(guard.status);
+    return search_impl(ix, d_queries, batch, k, metric, h_filt, d_scores, d_rows, d_n_valid, d_keys,
+                       d_workspace, workspace_bytes, algo, static_cast<cudaStream_t>(stream), nullptr,
+                       h_row_mask_ptrs);
 }
 
 extern "C" int crb_search_host(crb_index* ix, const float* h_queries, int32_t batch, int32_t k,

@@ -29,6 +29,7 @@ struct K3Params {
     int32_t n_filters;
     uint32_t used_keys;    // bit m set when any filter constrains key m
     int32_t want[kMaxFilters][kMaxKeys];
+    const uint32_t* extra[kMaxFilters];   // optional caller-built pass-bit mask ANDed into filter f (or nullptr)
 };
 
 __global__ void __launch_bounds__(kK3Threads) k3_filter_kernel(const __grid_constant__ K3Params p) {
@@ -64,6 +65,16 @@ __global__ void __launch_bounds__(kK3Threads) k3_filter_kernel(const __grid_cons
 #pragma unroll
             for (int j = 0; j < kK3RowsPerThread; ++j)
                 if (code[j] != w) pass[j] &= ~(1u << f);
+        }
+    }
+    // caller-built row masks (membership in list-valued metadata, IN lists, ...): one bit per row
+    for (int f = 0; f < p.n_filters; ++f) {
+        const uint32_t* ex = p.extra[f];
+        if (!ex) continue;
+#pragma unroll
+        for (int j = 0; j < kK3RowsPerThread; ++j) {
+            const int64_t row = blk0 + j * kK3Threads + threadIdx.x;
+            if (row < p.n_rows && !((__ldg(ex + (row >> 5)) >> (row & 31)) & 1u)) pass[j] &= ~(1u << f);
         }
     }
     __syncthreads();

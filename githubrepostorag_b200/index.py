@@ -304,8 +304,11 @@ class DeviceShard:
                       filt: Optional[np.ndarray] = None, algo: int = 0,
                       out: Optional[Tuple[torch.Tensor, torch.Tensor, torch.Tensor]] = None,
                       keys_out: Optional[torch.Tensor] = None,
-                      workspace: Optional[torch.Tensor] = None):
-        """Device-resident queries and results, asynchronous on torch's current stream."""
+                      workspace: Optional[torch.Tensor] = None,
+                      row_masks: Optional[Sequence[Optional[torch.Tensor]]] = None):
+        """Device-resident queries and results, asynchronous on torch's current stream.
+        ``row_masks[b]`` (optional) is an int32 CUDA tensor of ``ceil(n_rows/32)`` words: one
+        pass-bit per row, ANDed with query b's equality filter (``crb_search_masked``)."""
         if not queries.is_cuda or queries.dtype != torch.float32 or not queries.is_contiguous():
             raise ValueError("queries must be a contiguous fp32 CUDA tensor [batch, dim]")
         b, d = queries.shape
@@ -317,18 +320,48 @@ class DeviceShard:
                    torch.empty((b, k), dtype=torch.int64, device=self.device),
                    torch.empty((b,), dtype=torch.int32, device=self.device))
         scores, rows, n_valid = out
+        mask_ptrs = None
+        if row_masks is not None and any(m is not None for m in row_masks):
+            if len(row_masks) != b:
+                raise ValueError("row_masks must have one entry per query")
+            words = (self.n_rows + 31) // 32
+            arr = (C.c_void_p * b)()
+            for i, m in enumerate(row_masks):
+                if m is None:
+                    continue
+                if not m.is_cuda or m.dtype != torch.int32 or m.numel() < words or not m.is_contiguous():
+                    raise ValueError(f"row mask must be a contiguous int32 CUDA tensor of >= {words} words")
+                arr[i] = m.data_ptr()
+            mask_ptrs = arr
         if workspace is None:
-            nf = 0 if f is None else len({tuple(r) for r in f.tolist() if any(c != N.FILT_ANY for c in r)})
+            rows_f = [tuple(r) for r in f.tolist()] if f is not None else [()] * b
+            ids_m = [0 if (row_masks is None or row_masks[i] is None) else row_masks[i].data_ptr() for i in range(b)]
+            nf = len({(rows_f[i], ids_m[i]) for i in range(b)
+                      if ids_m[i] or any(c != N.FILT_ANY for c in rows_f[i])})
             need = self.workspace_bytes(b, k, nf)
             with self._ws_lock:
                 if self._ws is None or self._ws.numel() < need:
                     self._ws = torch.zeros(need, dtype=torch.uint8, device=self.device)
                 workspace = self._ws
         stream = torch.cuda.current_stream(self.device).cuda_stream
-        N.check(self._lib.crb_search(self._h, queries.data_ptr(), b, k, self._metric(metric), _np_ptr(f),
-                                     scores.data_ptr(), rows.data_ptr(), n_valid.data_ptr(), _ptr(keys_out),
-                                     workspace.data_ptr(), workspace.numel(), algo, stream))
+        if mask_ptrs is None:
+            N.check(self._lib.crb_search(self._h, queries.data_ptr(), b, k, self._metric(metric), _np_ptr(f),
+                                         scores.data_ptr(), rows.data_ptr(), n_valid.data_ptr(), _ptr(keys_out),
+                                         workspace.data_ptr(), workspace.numel(), algo, stream))
+        else:
+            N.check(self._lib.crb_search_masked(self._h, queries.data_ptr(), b, k, self._metric(metric), _np_ptr(f),
+                                                mask_ptrs, scores.data_ptr(), rows.data_ptr(), n_valid.data_ptr(),
+                                                _ptr(keys_out), workspace.data_ptr(), workspace.numel(), algo, stream))
         return scores, rows, n_valid
+
+    def pack_row_mask(self, keep: torch.Tensor) -> torch.Tensor:
+        """bool ``[n_rows]`` on the device -> the int32 pass-bit words ``crb_search_masked`` reads."""
+        n = self.n_rows
+        words = (n + 31) // 32
+        bits = torch.zeros(words * 32, dtype=torch.int64, device=self.device)
+        bits[:n] = keep.to(torch.int64)
+        w = (bits.view(words, 32) << torch.arange(32, device=self.device, dtype=torch.int64)).sum(dim=1)
+        return (w & 0xFFFFFFFF).to(torch.int64).where(w < 2**31, w - 2**32).to(torch.int32).contiguous()
 
     def fetch_rows(self, local_rows: Sequence[int]) -> np.ndarray:
         idx = np.ascontiguousarray(local_rows, dtype=np.int64)

@@ -19,6 +19,8 @@ class VectorStoreQueryMode(str, Enum):
 
 class FilterOperator(str, Enum):
     EQ = "=="
+    IN = "in"
+    CONTAINS = "contains"
 
 
 class FilterCondition(str, Enum):

@@ -33,6 +33,10 @@ from .types import (Content, Document, FilterCondition, FilterOperator, Metadata
 # keys the reference filters or traverses on (agent_graph.py:200-233; graph_rag_retrievers.py:82-100;
 # north star adds branch / component_kind, written at ingest_controller.py:169-173)
 DEFAULT_FILTER_KEYS = ("namespace", "repo", "module", "file_path", "branch", "component_kind", "scope", "language")
+# list-valued metadata the ingest writer shreds into key->value entries for traversal
+# (ingest/src/app/services/vector_write_service.py:28-34,152-154): a filter on one of these keys
+# means MEMBERSHIP ("the row's list contains the value"), served by a per-query row mask.
+DEFAULT_MULTI_VALUED_KEYS = ("topics", "imports", "labels")
 
 
 class _WriteGate:
@@ -150,7 +154,8 @@ class B200VectorStore:
 
     def __init__(self, embedding: Any = None, *, dim: Optional[int] = None,
                  filter_keys: Sequence[str] = DEFAULT_FILTER_KEYS, device: int = 0,
-                 table_name: str = "embeddings", metric: str = "cosine"):
+                 table_name: str = "embeddings", metric: str = "cosine",
+                 multi_valued_keys: Sequence[str] = DEFAULT_MULTI_VALUED_KEYS):
         N.load()  # fail loudly at construction when the CUDA library is missing
         self.embeddings = embedding          # object with embed_query / embed_documents
         self.table_name = table_name
@@ -165,6 +170,10 @@ class B200VectorStore:
         self._pending_emb: List[np.ndarray] = []
         self._pending_codes: List[np.ndarray] = []
         self._pending_dead: List[int] = []
+        # membership postings of list-valued metadata: (key, value) -> host row numbers
+        self.multi_valued_keys = tuple(k for k in multi_valued_keys if k not in self.dictionary.keys)
+        self._postings: Dict[Tuple[str, str], List[int]] = {}
+        self._mask_cache: Dict[Any, Any] = {}
 
     # ------------------------------------------------------------------ construction / writes
     @property
@@ -218,15 +227,29 @@ class B200VectorStore:
                 self._rows.texts.append(texts[i])
                 self._rows.metas.append(md)
                 codes.append(self.dictionary.encode_row(md))
+                self._post(base + j, md)
             code_mat = np.asarray(codes, dtype=np.int32).T.copy() if codes else np.empty((self.dictionary.n_keys, 0), np.int32)
             self._pending_emb.append(emb[order].astype(np.float16))
             self._pending_codes.append(code_mat)
             self._pending_dead.extend(dead)
         return [str(i) for i in ids]
 
+    @staticmethod
+    def _members(v: Any) -> List[str]:
+        if isinstance(v, (list, tuple, set, frozenset)):
+            return [str(x) for x in v]
+        return [str(v)]
+
+    def _post(self, row: int, md: Mapping[str, Any]) -> None:
+        for key in self.multi_valued_keys:
+            if key in md:
+                for val in self._members(md[key]):
+                    self._postings.setdefault((key, val), []).append(row)
+
     def _flush(self) -> None:
         """Bring staged writes to the device: append the new rows, tombstone the replaced / deleted."""
         with self._gate.write():
+            self._mask_cache.clear()
             if self._pending_emb:
                 new_emb = np.concatenate(self._pending_emb)
                 code_mat = np.concatenate(self._pending_codes, axis=1)
@@ -273,6 +296,10 @@ class B200VectorStore:
             r.metas = [r.metas[i] for i in live]
             r.pos = {rid: i for i, rid in enumerate(r.ids)}
             r.n_dead = 0
+            self._postings = {}
+            self._mask_cache.clear()
+            for i, md in enumerate(r.metas):
+                self._post(i, md)
 
     def add(self, nodes: Sequence[Any], **kwargs: Any) -> List[str]:
         """LlamaIndex face: nodes carry ``embedding``, ``node_id``, ``metadata``, text."""
@@ -371,6 +398,8 @@ class B200VectorStore:
         st.dictionary.values = [dict(v) for v in meta["values"]]
         st._rows.ids, st._rows.texts, st._rows.metas = list(meta["ids"]), list(meta["texts"]), list(meta["metas"])
         st._rows.pos = {rid: i for i, rid in enumerate(st._rows.ids)}
+        for i, md in enumerate(st._rows.metas):
+            st._post(i, md)
         st._shard = DeviceShard.from_host(rows16, codes if codes.shape[0] else None, device=device,
                                           capacity=max(1024, len(rows16)))
         return st
@@ -386,11 +415,66 @@ class B200VectorStore:
             raise ValueError("k must be >= 1")
         if k > N.MAX_TOPK:
             raise ValueError(f"k={k} exceeds the supported maximum {N.MAX_TOPK}")
+        split = [self._split_filter(f) for f in filters]
         filt = None
-        if any(f for f in filters):
-            filt = np.stack([self.dictionary.encode_filter(f) for f in filters])
+        if any(eq for eq, _ in split):
+            filt = np.stack([self.dictionary.encode_filter(eq) for eq, _ in split])
         with self._gate.read():
-            return self._shard.search_host(queries, k, metric=self.metric, filt=filt, algo=algo)
+            if not any(extra for _, extra in split):
+                return self._shard.search_host(queries, k, metric=self.metric, filt=filt, algo=algo)
+            # predicates one code per key cannot express ride on a per-query row mask (device path)
+            import torch
+            masks = [self._row_mask(extra) if extra else None for _, extra in split]
+            q = torch.from_numpy(np.ascontiguousarray(queries, dtype=np.float32)).to(self._shard.device)
+            s_, r_, v_ = self._shard.search_device(q, k, metric=self.metric, filt=filt, algo=algo, row_masks=masks)
+            return s_.cpu().numpy(), r_.cpu().numpy(), v_.cpu().numpy()
+
+    def _split_filter(self, flt: Optional[Mapping[str, Any]]):
+        """``{key: value | ("in", [values]) }`` -> (equalities on coded keys, extra predicates).
+        Extra predicates: membership on a list-valued key, IN on a coded key."""
+        if not flt:
+            return None, ()
+        eq: Dict[str, Any] = {}
+        extra = []
+        for key, val in flt.items():
+            if isinstance(val, tuple) and len(val) == 2 and val[0] == "in":
+                extra.append(("in", key, tuple(sorted(str(v) for v in val[1]))))
+            elif key in self.multi_valued_keys:
+                extra.append(("has", key, str(val)))
+            else:
+                eq[key] = val
+        return (eq or None), tuple(sorted(extra))
+
+    def _row_mask(self, extra):
+        """Device pass-bit mask of the rows satisfying every extra predicate (cached until the next write)."""
+        import torch
+        cached = self._mask_cache.get(extra)
+        if cached is not None:
+            return cached
+        sh = self._shard
+        keep = torch.ones(sh.n_rows, dtype=torch.bool, device=sh.device)
+        for kind, key, arg in extra:
+            if kind == "has":
+                rows = [r for r in self._postings.get((key, arg), ()) if r < sh.n_rows]
+                hit = torch.zeros(sh.n_rows, dtype=torch.bool, device=sh.device)
+                if rows:
+                    hit[torch.as_tensor(rows, dtype=torch.int64, device=sh.device)] = True
+                keep &= hit
+            else:   # "in" on a coded key
+                pos = self.dictionary._pos.get(key)
+                if pos is None or sh.codes is None:
+                    keep.zero_()
+                    continue
+                codes = [self.dictionary.values[pos][v] for v in arg if v in self.dictionary.values[pos]]
+                if not codes:
+                    keep.zero_()
+                    continue
+                keep &= torch.isin(sh.codes[pos], torch.as_tensor(codes, dtype=torch.int32, device=sh.device))
+        mask = sh.pack_row_mask(keep)
+        if len(self._mask_cache) > 256:
+            self._mask_cache.clear()
+        self._mask_cache[extra] = mask
+        return mask
 
     def _embed_query(self, text: str) -> List[float]:
         if self.embeddings is None:
@@ -409,11 +493,16 @@ class B200VectorStore:
         out: Dict[str, Any] = {}
         for f in getattr(filters, "filters", []) or []:
             op = getattr(f, "operator", FilterOperator.EQ)
-            if str(getattr(op, "value", op)) != "==":
-                raise NotImplementedError(f"filter operator {op!r} is not supported (EQ only)")
-            if f.key in out and out[f.key] != f.value:
+            name = str(getattr(op, "value", op)).lower()
+            if name in ("==", "contains"):        # CONTAINS on a list-valued key == membership
+                val: Any = f.value
+            elif name == "in":
+                val = ("in", list(f.value))
+            else:
+                raise NotImplementedError(f"filter operator {op!r} is not supported (EQ, IN, CONTAINS)")
+            if f.key in out and out[f.key] != val:
                 return {"__impossible__": "1"}  # k == a AND k == b
-            out[f.key] = f.value
+            out[f.key] = val
         return out
 
     # ------------------------------------------------------------------ face A: LlamaIndex

@@ -119,6 +119,18 @@ int crb_search(crb_index *index, const float *d_queries, int32_t batch, int32_t 
                uint64_t *d_keys, void *d_workspace, size_t workspace_bytes, int32_t algo,
                void *stream);
 
+/* crb_search with one optional caller-built ROW MASK per query, ANDed with the equality filter:
+ * h_row_mask_ptrs is a host array of `batch` DEVICE pointers (NULL entries = no mask; the array
+ * may be NULL), each to ceil(n_rows/32) uint32 words, bit r%32 of word r/32 set when local row r
+ * may be returned.  This carries predicates one code per key cannot express -- membership in
+ * list-valued metadata (`topics`, `imports`, `labels`, which the ingest writer shreds into
+ * key->value entries, ingest/src/app/services/vector_write_service.py:28-34,152-154) and IN
+ * lists.  Queries with the same filter codes AND the same mask pointer share one survivor list. */
+int crb_search_masked(crb_index *index, const float *d_queries, int32_t batch, int32_t k,
+                      int32_t metric, const int32_t *h_filt, const uint32_t *const *h_row_mask_ptrs,
+                      float *d_scores, int64_t *d_rows, int32_t *d_n_valid, uint64_t *d_keys,
+                      void *d_workspace, size_t workspace_bytes, int32_t algo, void *stream);
+
 /* Same search through HOST buffers: copies the queries in, runs, copies the results out and
  * returns when they are in the caller's arrays.  This is the call the Python store makes per
  * retriever.invoke(); it uses an internal pool of streams/staging buffers, one per concurrent

@@ -136,3 +136,49 @@ def test_readers_race_a_writer():
     [t.join() for t in ts]
     assert not errors, errors[:2]
     st.close()
+
+
+def test_list_valued_membership_and_in_filters():
+    """`topics` / `imports` / `labels` are lists; a filter on them means membership.
+    Also the IN operator on a coded key, and membership edges in adjacent()."""
+    from githubrepostorag_b200.types import FilterOperator, MetadataFilter, MetadataFilters, VectorStoreQuery
+    from githubrepostorag_b200.vector_store import B200VectorStore
+    rng = np.random.default_rng(11)
+    n, d, k = 5000, 48, 9
+    emb = rng.standard_normal((n, d), dtype=np.float32).astype(np.float16).astype(np.float32)
+    vocab = ["kafka", "jms", "redis", "grpc", "auth", "sql"]
+    metas = []
+    for i in range(n):
+        t = [vocab[j] for j in range(len(vocab)) if rng.random() < 0.2]
+        md = {"namespace": "default", "repo": f"r{i % 6}", "imports": [f"lib{i % 40}", "os"]}
+        if t:
+            md["topics"] = t
+        metas.append(md)
+    ids = [S.row_id(i) for i in range(n)]
+    st = B200VectorStore(dim=d)
+    st.add_embeddings(ids[:3000], emb[:3000], None, metas[:3000])
+    q = rng.standard_normal(d, dtype=np.float32)
+
+    def expect(pred):
+        keep = np.array([pred(m) for m in metas[:len(st)]])
+        s, r = oracle.query_vectorised(q, emb[:len(st)].astype(np.float16), k, keep=keep)
+        return [ids[int(i)] for i in r]
+
+    assert _query(st, q, k, {"topics": "kafka"}).ids == expect(lambda m: "kafka" in m.get("topics", ()))
+    assert _query(st, q, k, {"topics": "kafka", "repo": "r2"}).ids == \
+        expect(lambda m: "kafka" in m.get("topics", ()) and m["repo"] == "r2")
+    assert _query(st, q, k, {"topics": "grpc", "imports": "lib7"}).ids == \
+        expect(lambda m: "grpc" in m.get("topics", ()) and "lib7" in m["imports"])
+    assert _query(st, q, k, {"topics": "no-such-topic"}).ids == []
+    st.add_embeddings(ids[3000:], emb[3000:], None, metas[3000:])          # masks are rebuilt after a write
+    assert _query(st, q, k, {"topics": "kafka"}).ids == expect(lambda m: "kafka" in m.get("topics", ()))
+    f = MetadataFilters(filters=[MetadataFilter(key="repo", value=["r1", "r4", "zzz"], operator=FilterOperator.IN),
+                                 MetadataFilter(key="topics", value="sql", operator=FilterOperator.CONTAINS)])
+    got = st.query(VectorStoreQuery(query_embedding=q.tolist(), similarity_top_k=k, filters=f))
+    assert got.ids == expect(lambda m: m["repo"] in ("r1", "r4") and "sql" in m.get("topics", ()))
+    assert got.nodes[0].metadata["topics"] == metas[int(got.ids[0][4:])]["topics"]      # lists come back as lists
+    adj = st.adjacent({("topics", "auth"), ("repo", "r5")}, q.tolist(), k=k, filter={"namespace": "default"})
+    assert [c.id for c in adj] == expect(lambda m: "auth" in m.get("topics", ()) or m["repo"] == "r5")
+    st.delete(got.ids[0])
+    assert got.ids[0] not in _query(st, q, k, {"topics": "sql"}).ids
+    st.close()
