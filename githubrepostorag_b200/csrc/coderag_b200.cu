@@ -141,7 +141,7 @@ static int64_t mask_stride_of(const crb_index* ix) { return round_up((std::max<i
 struct WsLayout {
     size_t cand = kWsHeaderBytes;
     size_t k2 = 0;          // K2 region start
-    size_t q16 = 0, invq = 0, eps = 0, qmap = 0, flagged = 0, nflag = 0, progress = 0, cand2 = 0;   // inside the K2 region
+    size_t q16 = 0, invq = 0, eps = 0, qmap = 0, flagged = 0, nflag = 0, cand2 = 0;   // inside the K2 region
     size_t filt = 0;        // survivor lists start; masks follow the lists
     size_t per_filter = 0;  // bytes one more filter costs
 };
@@ -156,8 +156,10 @@ static WsLayout ws_layout(const crb_index* ix, int batch, int k) {
     L.qmap = o;    o += round_up(nmax * 4, 256);
     L.flagged = o; o += round_up(nmax * 4, 256);
     L.nflag = o;   o += 256;
-    L.progress = o; o += 4096;     // [slots, m_pairs] lock-step counters of the pair kernel (<= 1024 ints)
-    L.cand2 = o;   o += round_up(std::min<size_t>(nmax, kK2BlockM) * ix->sm_count * k2_kprime(k) * 8 + nmax * k2_kprime(k) * 8, 1024);
+    // per query: one k'-list per CTA (pair) that served its query tile -- at most sm_count lists when the
+    // batch is one tile, sm_count/2 when CTA pairs serve every query tile of the batch (m-inner)
+    L.cand2 = o;   o += round_up(std::max<size_t>(std::min<size_t>(nmax, kK2BlockM) * ix->sm_count,
+                                                   nmax * size_t(ix->sm_count / 2 + 1)) * k2_kprime(k) * 8 + nmax * k2_kprime(k) * 8, 1024);
     L.filt = o;
     L.per_filter = size_t(list_stride_of(ix)) * 4 + size_t(mask_stride_of(ix)) * 4;
     return L;
@@ -411,23 +413,29 @@ static int launch_k2(crb_index* ix, const float* d_queries, int batch, int k, in
         const size_t list_bytes = size_t(kprime) * kp.lstride * 8;
         const size_t smem_room = size_t(227) * 1024 - 1024 - list_bytes - tail_bytes;
         const int stages1 = static_cast<int>(std::min<size_t>(smem_room / kK2StageBytes, 4));
-        const int stages2 = static_cast<int>(std::min<size_t>(smem_room / kK2PairStageBytes, 8));
         if (stages1 < 2) return fail("internal: K2 does not fit shared memory for k'=%d", kprime);
         const bool use_pair = pair_env >= 0 ? (pair_env != 0) : (n > kK2BlockM);
         kp.prefetch = env_int("CODERAG_B200_K2_PREFETCH", 0);
         kp.debug = env_int("CODERAG_B200_K2_DEBUG", 0);
         if (use_pair) {
-            kp.m_tiles = (n + 255) / 256;                       // query tile PAIRS
+            const int m_pairs = (n + 255) / 256;                // query tile PAIRS
+            // m-inner: one CTA pair serves up to 4 query-tile pairs per corpus tile while their candidate
+            // lists fit next to >= 4 pipeline stages (CODERAG_B200_K2_MINNER=1 restores one group per pair)
+            int mi = std::min(m_pairs, std::max(1, env_int("CODERAG_B200_K2_MINNER", 4)));
+            auto pair_stages = [&](int mi_) {
+                const size_t fixed_b = size_t(mi_) * list_bytes + tail_bytes + size_t(mi_) * 1024;
+                return static_cast<int>(std::min<size_t>((size_t(227) * 1024 - 1024 - fixed_b) / kK2PairStageBytes, 8));
+            };
+            while (mi > 1 && (size_t(mi) * list_bytes + tail_bytes + size_t(mi) * 1024 + 1024 + 4 * size_t(kK2PairStageBytes) >
+                              size_t(227) * 1024))
+                --mi;
+            kp.m_inner = mi;
+            kp.m_tiles = (m_pairs + mi - 1) / mi;               // query groups
             kp.slots = std::max(1, (ix->sm_count / 2) / kp.m_tiles);
             kp.slots = static_cast<int>(std::min<int64_t>(kp.slots, std::max<int64_t>(n_tiles, 1)));
-            kp.stages = stages2;
-            kp.drift = env_int("CODERAG_B200_K2_DRIFT", 0);
-            kp.progress = nullptr;
-            if (kp.drift > 0 && kp.m_tiles > 1 && kp.m_tiles * kp.slots <= 1024) {
-                kp.progress = reinterpret_cast<int32_t*>(ws + L.progress);
-                CRB_CUDA(cudaMemsetAsync(kp.progress, 0, 4096, stream));
-            }
-            const size_t smem = 1024 + size_t(stages2) * kK2PairStageBytes + list_bytes + tail_bytes;
+            kp.stages = pair_stages(mi);
+            const size_t smem = 1024 + size_t(kp.stages) * kK2PairStageBytes + size_t(mi) * list_bytes + tail_bytes +
+                                size_t(mi) * 1024;
             k2_gemm_topk_pair_kernel<<<2 * kp.m_tiles * kp.slots, kK2Threads, smem, stream>>>(map_q, *map_half, kp);
         } else {
             kp.m_tiles = (n + kK2BlockM - 1) / kK2BlockM;

@@ -50,8 +50,7 @@ struct K2Params {
     int32_t prefetch;           // L2-prefetch the next corpus tile
     int32_t debug;              // timing experiments only: 1 = no TMA after the first fill, 2 = no epilogue math
     int32_t lstride;            // candidate-list stride = query rows that own a list (<= 128)
-    int32_t* progress;          // [slots, m_tiles] tiles started per pair (pair kernel lock-step), zero on entry
-    int32_t drift;              // a pair may run at most this many corpus tiles ahead of the slowest pair of its slot
+    int32_t m_inner;            // pair kernel: query-tile pairs served per corpus tile by one CTA pair (>= 1)
 };
 
 // ---- PTX wrappers ------------------------------------------------------------------------------
@@ -498,17 +497,26 @@ CRB_DEVINL void umma_commit_pair(uint64_t* bar) {
                  ::"r"(smem_u32(bar)), "h"(static_cast<uint16_t>(3)) : "memory");
 }
 
-// grid = 2 * m_pairs * slots CTAs in clusters of 2.  Pair P serves query rows
-// [ (P % m_pairs) * 256, +256 ) and corpus tiles  P / m_pairs + i * slots.  (p.m_tiles = m_pairs.)
+// grid = 2 * m_tiles * slots CTAs in clusters of 2.  Pair P = blockIdx.x / 2 belongs to query group
+// P % m_tiles and corpus slot P / m_tiles.  A group is m_inner consecutive query-tile pairs (256
+// queries each); the pair walks corpus tiles  slot + i * slots  and, for EACH tile, runs the MMA once
+// per query-tile pair of its group ("m-inner" order).  With m_inner covering the whole batch every
+// corpus tile is fetched from HBM by exactly one pair and its re-reads for the other query tiles
+// follow within microseconds, i.e. hit L2 (with m_inner = 1, pairs of different query groups share
+// tiles only by luck: ncu showed 3x the corpus in DRAM reads).
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kK2Threads, 1)
 k2_gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant__ CUtensorMap map_c,
                          const __grid_constant__ K2Params p) {
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    const int MI = p.m_inner;
     uint8_t* stage_base = smem;
     uint64_t* lists = reinterpret_cast<uint64_t*>(smem + static_cast<size_t>(p.stages) * kK2PairStageBytes);
-    float* s_inv = reinterpret_cast<float*>(lists + static_cast<size_t>(p.kprime) * p.lstride);
-    uint64_t* bars = reinterpret_cast<uint64_t*>(s_inv + 2 * kK2BlockN);
+    const size_t list_elems = static_cast<size_t>(p.kprime) * p.lstride;        // one query tile's lists
+    float* s_inv = reinterpret_cast<float*>(lists + static_cast<size_t>(MI) * list_elems);
+    float* s_thr = s_inv + 2 * kK2BlockN;                                       // [MI][128]
+    uint32_t* s_state = reinterpret_cast<uint32_t*>(s_thr + MI * 128);          // [MI][128]
+    uint64_t* bars = reinterpret_cast<uint64_t*>(s_state + MI * 128);
     uint64_t* full_bar = bars;
     uint64_t* empty_bar = bars + p.stages;
     uint64_t* tfull_bar = bars + 2 * p.stages;
@@ -520,11 +528,12 @@ k2_gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap map_q, const __grid
     const uint32_t rank = cluster_ctarank();
     const bool leader = (rank == 0);
     const int pair = blockIdx.x >> 1;
-    const int m_pair = pair % p.m_tiles;
+    const int m_group = pair % p.m_tiles;
     const int slot = pair / p.m_tiles;
-    const int m_row0 = m_pair * 256 + static_cast<int>(rank) * kK2BlockM;   // first query row of this CTA
     const int64_t n_tiles = (p.n_rows + kK2BlockN - 1) / kK2BlockN;
     const int k_blocks = (p.dim + kK2BlockK - 1) / kK2BlockK;
+    // first query row of this CTA for inner index j
+    auto m_row0 = [&](int j) { return (m_group * MI + j) * 256 + static_cast<int>(rank) * kK2BlockM; };
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < p.stages; ++s) {
@@ -548,42 +557,21 @@ k2_gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap map_q, const __grid
         if (lane == 0) {
             int st = 0;
             uint32_t ph = 0;
-            int32_t it = 0;
-            for (int64_t t = slot; t < n_tiles; t += p.slots, ++it) {
-                // Lock-step: the pairs of one slot read the same corpus tiles; keeping them within
-                // `drift` tiles of each other makes all but the first read of a tile an L2 hit (HBM
-                // then sees the corpus once).  The leader's producer publishes / polls; its peer
-                // follows through the shared pipeline.  Bounded spin: never a deadlock.
-                if (leader && p.progress && p.m_tiles > 1) {
-                    volatile int32_t* prog = p.progress + static_cast<int64_t>(slot) * p.m_tiles;
-                    prog[m_pair] = it + 1;
-                    const int32_t need = it + 1 - p.drift;
-                    if (need > 0) {
-                        for (int spin = 0; spin < (1 << 22); ++spin) {
-                            int32_t lo = prog[0];
-                            for (int m = 1; m < p.m_tiles; ++m) { const int32_t v = prog[m]; lo = v < lo ? v : lo; }
-                            if (lo >= need) break;
-                        }
+            for (int64_t t = slot; t < n_tiles; t += p.slots) {
+                for (int j = 0; j < MI; ++j) {
+                    const int a_row = m_row0(j);
+                    for (int kb = 0; kb < k_blocks; ++kb) {
+                        mbar_wait(&empty_bar[st], ph ^ 1u);
+                        uint8_t* a = stage_base + static_cast<size_t>(st) * kK2PairStageBytes;
+                        uint8_t* b = a + kK2StageBytesA;
+                        const uint32_t full_leader = mapa_u32(smem_u32(&full_bar[st]), 0);
+                        if (leader) mbar_expect_tx(&full_bar[st], 2 * kK2PairStageBytes);
+                        tma_load_2d_pair(&map_q, a, full_leader, kb * kK2BlockK, a_row);
+                        tma_load_2d_pair(&map_c, b, full_leader, kb * kK2BlockK,
+                                         static_cast<int32_t>(t * kK2BlockN + rank * (kK2BlockN / 2)));
+                        if (!leader) mbar_arrive_cluster(full_leader);
+                        if (++st == p.stages) { st = 0; ph ^= 1u; }
                     }
-                }
-                // Pull this CTA's half of a FUTURE corpus tile into L2 (p.prefetch tiles ahead) so the
-                // demand loads below hit L2 even when this pair is the first of its slot to get there.
-                if (p.prefetch > 0 && t + static_cast<int64_t>(p.prefetch) * p.slots < n_tiles) {
-                    const int32_t r0 = static_cast<int32_t>((t + static_cast<int64_t>(p.prefetch) * p.slots) * kK2BlockN +
-                                                            rank * (kK2BlockN / 2));
-                    for (int kb = 0; kb < k_blocks; ++kb) tma_prefetch_l2_2d(&map_c, kb * kK2BlockK, r0);
-                }
-                for (int kb = 0; kb < k_blocks; ++kb) {
-                    mbar_wait(&empty_bar[st], ph ^ 1u);
-                    uint8_t* a = stage_base + static_cast<size_t>(st) * kK2PairStageBytes;
-                    uint8_t* b = a + kK2StageBytesA;
-                    const uint32_t full_leader = mapa_u32(smem_u32(&full_bar[st]), 0);
-                    if (leader) mbar_expect_tx(&full_bar[st], 2 * kK2PairStageBytes);
-                    tma_load_2d_pair(&map_q, a, full_leader, kb * kK2BlockK, m_row0);
-                    tma_load_2d_pair(&map_c, b, full_leader, kb * kK2BlockK,
-                                     static_cast<int32_t>(t * kK2BlockN + rank * (kK2BlockN / 2)));
-                    if (!leader) mbar_arrive_cluster(full_leader);
-                    if (++st == p.stages) { st = 0; ph ^= 1u; }
                 }
             }
         }
@@ -593,40 +581,43 @@ k2_gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap map_q, const __grid
             int st = 0;
             uint32_t ph = 0;
             int64_t it = 0;
-            for (int64_t t = slot; t < n_tiles; t += p.slots, ++it) {
-                const int buf = static_cast<int>(it & 1);
-                const uint32_t use = static_cast<uint32_t>(it >> 1);
-                mbar_wait(&tempty_bar[buf], (use & 1u) ^ 1u);
-                tc_fence_after();
-                const uint32_t d_tmem = tmem_base + static_cast<uint32_t>(buf * kK2BlockN);
-                for (int kb = 0; kb < k_blocks; ++kb) {
-                    mbar_wait(&full_bar[st], ph);
+            for (int64_t t = slot; t < n_tiles; t += p.slots) {
+                for (int j = 0; j < MI; ++j, ++it) {
+                    const int buf = static_cast<int>(it & 1);
+                    const uint32_t use = static_cast<uint32_t>(it >> 1);
+                    mbar_wait(&tempty_bar[buf], (use & 1u) ^ 1u);
                     tc_fence_after();
-                    const uint32_t a_addr = smem_u32(stage_base + static_cast<size_t>(st) * kK2PairStageBytes);
-                    const uint32_t b_addr = a_addr + kK2StageBytesA;
+                    const uint32_t d_tmem = tmem_base + static_cast<uint32_t>(buf * kK2BlockN);
+                    for (int kb = 0; kb < k_blocks; ++kb) {
+                        mbar_wait(&full_bar[st], ph);
+                        tc_fence_after();
+                        const uint32_t a_addr = smem_u32(stage_base + static_cast<size_t>(st) * kK2PairStageBytes);
+                        const uint32_t b_addr = a_addr + kK2StageBytesA;
 #pragma unroll
-                    for (int k = 0; k < kK2BlockK / kK2UmmaK; ++k) {
-                        const uint64_t da = umma_desc_sw128(a_addr + k * kK2UmmaK * 2);
-                        const uint64_t db = umma_desc_sw128(b_addr + k * kK2UmmaK * 2);
-                        umma_f16_pair(d_tmem, da, db, kK2PairIDesc, (kb | k) != 0 ? 1u : 0u);
+                        for (int k = 0; k < kK2BlockK / kK2UmmaK; ++k) {
+                            const uint64_t da = umma_desc_sw128(a_addr + k * kK2UmmaK * 2);
+                            const uint64_t db = umma_desc_sw128(b_addr + k * kK2UmmaK * 2);
+                            umma_f16_pair(d_tmem, da, db, kK2PairIDesc, (kb | k) != 0 ? 1u : 0u);
+                        }
+                        umma_commit_pair(&empty_bar[st]);
+                        if (++st == p.stages) { st = 0; ph ^= 1u; }
                     }
-                    umma_commit_pair(&empty_bar[st]);
-                    if (++st == p.stages) { st = 0; ph ^= 1u; }
+                    umma_commit_pair(&tfull_bar[buf]);
                 }
-                umma_commit_pair(&tfull_bar[buf]);
             }
         }
     } else {
-        // ===== epilogue: identical to the single-CTA kernel, on this CTA's 128 query rows =====
+        // ===== epilogue: this CTA's 128 query rows of each query tile of the group =====
         const int quarter = warp & 3;
         const int row = quarter * 32 + lane;
         const int tid_e = threadIdx.x - 64;
-        const bool q_valid = (m_row0 + row) < p.batch && row < p.lstride;
         const bool cosine = (p.metric == 0);
-        uint64_t* my_list = lists + row;
-        uint32_t state = 0;
-        float thr = q_valid ? __uint_as_float(0xff800000u) : __uint_as_float(0x7f800000u);
         const float qnan = __uint_as_float(0x7fc00000u);
+        for (int j = 0; j < MI; ++j) {
+            const bool v = (m_row0(j) + row) < p.batch && row < p.lstride;
+            s_thr[j * 128 + row] = v ? __uint_as_float(0xff800000u) : __uint_as_float(0x7f800000u);   // -inf / +inf
+            s_state[j * 128 + row] = 0u;
+        }
         auto column_scale = [&](int64_t n) -> float {
             if (n >= p.n_rows) return qnan;
             if (p.mask && !((p.mask[n >> 5] >> (n & 31)) & 1u)) return qnan;
@@ -636,47 +627,59 @@ k2_gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap map_q, const __grid
         };
         float pre[2] = {qnan, qnan};
         int64_t it = 0;
-        for (int64_t t = slot; t < n_tiles; t += p.slots, ++it) {
-            const int buf = static_cast<int>(it & 1);
-            const uint32_t use = static_cast<uint32_t>(it >> 1);
+        for (int64_t t = slot; t < n_tiles; t += p.slots) {
             const int64_t n0 = t * kK2BlockN;
-            float* inv = s_inv + buf * kK2BlockN;
-            if (it == 0) { pre[0] = column_scale(n0 + tid_e); pre[1] = column_scale(n0 + tid_e + 128); }
-            inv[tid_e] = pre[0];
-            inv[tid_e + 128] = pre[1];
-            if (t + p.slots < n_tiles) {
-                const int64_t nn = (t + p.slots) * kK2BlockN;
-                pre[0] = column_scale(nn + tid_e);
-                pre[1] = column_scale(nn + tid_e + 128);
-            }
-            epi_bar_sync();
-            mbar_wait(&tfull_bar[buf], use & 1u);
-            tc_fence_after();
-            const uint32_t t_row = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) +
-                                   static_cast<uint32_t>(buf * kK2BlockN);
-            const uint32_t inv_s = smem_u32(inv);
-            const int n_chunks = (p.debug & 2) ? 0 : kK2BlockN / 32;
-            uint32_t va[32], vb[32];
-            if (n_chunks > 0) {
-                tmem_ld32(t_row, va);
-                tmem_ld_wait();
-            }
+            for (int j = 0; j < MI; ++j, ++it) {
+                const int buf = static_cast<int>(it & 1);
+                const uint32_t use = static_cast<uint32_t>(it >> 1);
+                float* inv = s_inv + buf * kK2BlockN;
+                if (it == 0) { pre[0] = column_scale(n0 + tid_e); pre[1] = column_scale(n0 + tid_e + 128); }
+                inv[tid_e] = pre[0];
+                inv[tid_e + 128] = pre[1];
+                // scales of the NEXT item's corpus tile (the same tile until j wraps)
+                const int64_t nt = (j + 1 < MI) ? t : t + p.slots;
+                if (nt < n_tiles && nt != t) {
+                    pre[0] = column_scale(nt * kK2BlockN + tid_e);
+                    pre[1] = column_scale(nt * kK2BlockN + tid_e + 128);
+                }
+                uint64_t* my_list = lists + static_cast<size_t>(j) * list_elems + row;
+                float thr = s_thr[j * 128 + row];
+                uint32_t state = s_state[j * 128 + row];
+                epi_bar_sync();
+                mbar_wait(&tfull_bar[buf], use & 1u);
+                tc_fence_after();
+                const uint32_t t_row = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) +
+                                       static_cast<uint32_t>(buf * kK2BlockN);
+                const uint32_t inv_s = smem_u32(inv);
+                const int n_chunks = (p.debug & 2) ? 0 : kK2BlockN / 32;
+                uint32_t va[32], vb[32];
+                if (n_chunks > 0) {
+                    tmem_ld32(t_row, va);
+                    tmem_ld_wait();
+                }
 #pragma unroll 1
-            for (int c = 0; c < n_chunks; c += 2) {
-                tmem_ld32(t_row + (c + 1) * 32, vb);
-                thr = k2_scan_chunk(va, inv_s + c * 128, thr, state, my_list, n0 + c * 32, p.kprime, p.lstride);
-                tmem_ld_wait();
-                if (c + 2 < n_chunks) tmem_ld32(t_row + (c + 2) * 32, va);
-                thr = k2_scan_chunk(vb, inv_s + (c + 1) * 128, thr, state, my_list, n0 + (c + 1) * 32, p.kprime, p.lstride);
-                tmem_ld_wait();
+                for (int c = 0; c < n_chunks; c += 2) {
+                    tmem_ld32(t_row + (c + 1) * 32, vb);
+                    thr = k2_scan_chunk(va, inv_s + c * 128, thr, state, my_list, n0 + c * 32, p.kprime, p.lstride);
+                    tmem_ld_wait();
+                    if (c + 2 < n_chunks) tmem_ld32(t_row + (c + 2) * 32, va);
+                    thr = k2_scan_chunk(vb, inv_s + (c + 1) * 128, thr, state, my_list, n0 + (c + 1) * 32, p.kprime, p.lstride);
+                    tmem_ld_wait();
+                }
+                tc_fence_before();
+                mbar_arrive_cluster(mapa_u32(smem_u32(&tempty_bar[buf]), 0));
+                s_thr[j * 128 + row] = thr;
+                s_state[j * 128 + row] = state;
             }
-            tc_fence_before();
-            mbar_arrive_cluster(mapa_u32(smem_u32(&tempty_bar[buf]), 0));
         }
-        if (q_valid) {
-            uint64_t* out = p.cand + (static_cast<int64_t>(m_row0 + row) * p.slots + slot) * p.kprime;
-            const int count = static_cast<int>(state);
-            for (int i = 0; i < p.kprime; ++i) out[i] = i < count ? my_list[i * p.lstride] : 0ull;
+        for (int j = 0; j < MI; ++j) {
+            const int qrow = m_row0(j) + row;
+            if (qrow < p.batch && row < p.lstride) {
+                uint64_t* out = p.cand + (static_cast<int64_t>(qrow) * p.slots + slot) * p.kprime;
+                const uint64_t* my_list = lists + static_cast<size_t>(j) * list_elems + row;
+                const int count = static_cast<int>(s_state[j * 128 + row]);
+                for (int i = 0; i < p.kprime; ++i) out[i] = i < count ? my_list[i * p.lstride] : 0ull;
+            }
         }
     }
 
