@@ -234,6 +234,17 @@ static int k1_default_rows(int nq, int ch) {
     if (nq == 2) return ch == 1 ? 4 : (ch == 2 ? 4 : 2);
     return ch == 1 ? 4 : 2;
 }
+// half-warp kernels for dim <= 512 (R = row PAIRS in flight per warp)
+template <int NQ, int R>
+static K1Fn k1_half_kpl(int k) {
+    if (k <= 32) return k1_stream_half_kernel<NQ, R, 1>;
+    return k1_stream_half_kernel<NQ, R, 4>;
+}
+static K1Fn k1_pick_half(int nq, int r, int k) {
+    if (nq == 1) return r == 2 ? k1_half_kpl<1, 2>(k) : (r == 3 ? k1_half_kpl<1, 3>(k) : k1_half_kpl<1, 4>(k));
+    if (nq == 2) return k1_half_kpl<2, 2>(k);
+    return k1_half_kpl<4, 1>(k);
+}
 static K1Fn k1_pick_generic(int k) {
     if (k <= 32) return k1_stream_generic_kernel<2, 1>;
     return k1_stream_generic_kernel<2, 4>;
@@ -267,8 +278,14 @@ static int launch_k1(const crb_index* ix, const float* d_queries, int k, int met
     const int chunks = ix->dim / 8;
     const int ch = (chunks + 31) / 32;
     const bool generic = ch > 4;
-    const int r1 = generic ? 2 : k1_default_rows(nq, ch);
+    int r1 = generic ? 2 : k1_default_rows(nq, ch);
     K1Fn fn = generic ? k1_pick_generic(k) : k1_pick(nq, ch, r1, k);
+    if (!generic && ch <= 2 && nq <= 2 && env_int("CODERAG_B200_K1_HALF", 1)) {
+        // short rows: two rows per warp step (bit-identical scores, fewer instructions per row)
+        const int rp = nq == 1 ? std::min(std::max(env_int("CODERAG_B200_K1_HALF_PAIRS", 3), 2), 4) : (nq == 2 ? 2 : 1);
+        fn = k1_pick_half(nq, rp, k);
+        r1 = 2 * rp;
+    }
     if (!fn) return fail("internal: no K1 instantiation for nq=%d ch=%d", nq, ch);
     const size_t dyn = generic ? size_t(ix->dim) * sizeof(float) : 0;
     const int rows_per_warp_iter = r1;

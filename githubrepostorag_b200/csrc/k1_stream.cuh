@@ -207,6 +207,165 @@ k1_stream_kernel(const __grid_constant__ K1Params p) {
     if (threadIdx.x == 0) p.counters[blockIdx.y] = 0u;
 }
 
+// Half-warp variant for short rows (dim <= 512, i.e. <= 64 chunks): two rows per warp step, 16 lanes
+// each, so no lane idles on a 768-byte row and the butterfly needs four shuffle levels instead of
+// five.  Scores are BIT-IDENTICAL to the canonical 32-lane order: half-lane h computes the canonical
+// partials of lanes h (chunks h, h+32) and h+16 (chunks h+16, h+48) in two accumulators, adds them
+// (the canonical xor-16 level, locally), then runs the xor-8/4/2/1 levels inside its half.
+template <int NQ, int R, int KPL>
+__global__ void __launch_bounds__(kK1Threads, 2)
+k1_stream_half_kernel(const __grid_constant__ K1Params p) {
+    __shared__ uint64_t xchg[2][32];
+    __shared__ float s_invq;
+    __shared__ int s_last;
+
+    const int lane = threadIdx.x & 31;
+    const int warp = threadIdx.x >> 5;
+    const int half = lane >> 4;
+    const int hl = lane & 15;
+    const K1Group& G = p.groups[blockIdx.y];
+    const int chunks = p.dim >> 3;
+    const bool cosine = (p.metric == 0);
+
+    float qr[NQ][4][8];
+#pragma unroll
+    for (int q = 0; q < NQ; ++q) {
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+            const int ch = hl + 16 * c;
+            if (G.q_idx[q] >= 0 && ch < chunks) {
+                const float4* src = reinterpret_cast<const float4*>(
+                    p.queries + static_cast<int64_t>(G.q_idx[q]) * p.dim + ch * 8);
+                const float4 a = __ldg(src), b = __ldg(src + 1);
+                qr[q][c][0] = a.x; qr[q][c][1] = a.y; qr[q][c][2] = a.z; qr[q][c][3] = a.w;
+                qr[q][c][4] = b.x; qr[q][c][5] = b.y; qr[q][c][6] = b.z; qr[q][c][7] = b.w;
+            } else {
+#pragma unroll
+                for (int e = 0; e < 8; ++e) qr[q][c][e] = 0.f;
+            }
+        }
+    }
+
+    WarpTopK<KPL> top[NQ];
+#pragma unroll
+    for (int q = 0; q < NQ; ++q) top[q].init(p.k, lane);
+
+    const bool use_list = G.filter >= 0;
+    int64_t n_items = p.n_rows;
+    const uint32_t* list = nullptr;
+    if (use_list) {
+        const int64_t cnt = static_cast<int64_t>(p.list_counts[G.filter]);
+        n_items = cnt < p.n_rows ? cnt : p.n_rows;
+        list = p.lists + static_cast<int64_t>(G.filter) * p.list_stride;
+    }
+    constexpr int RW = 2 * R;   // rows per warp step
+    const int64_t stride = static_cast<int64_t>(gridDim.x) * kK1Warps * RW;
+    int64_t item0 = (static_cast<int64_t>(blockIdx.x) * kK1Warps + warp) * RW;
+
+    uint32_t idx_next = 0u;
+    if (use_list && lane < RW && item0 + lane < n_items) idx_next = list[item0 + lane];
+
+    for (; item0 < n_items; item0 += stride) {
+        const uint32_t idx_cur = idx_next;
+        idx_next = 0u;
+        if (use_list && lane < RW && item0 + stride + lane < n_items) idx_next = list[item0 + stride + lane];
+
+        int64_t row[R];     // this half's row of pair j
+        bool ok[R];
+#pragma unroll
+        for (int j = 0; j < R; ++j) {
+            const int it = 2 * j + half;
+            ok[j] = (item0 + it) < n_items;
+            const uint32_t li = __shfl_sync(CRB_FULL_MASK, idx_cur, it);
+            row[j] = use_list ? static_cast<int64_t>(li) : (item0 + it);
+            if (!ok[j]) row[j] = 0;
+        }
+        uint4 v[R][4];
+        float invn[R];
+#pragma unroll
+        for (int j = 0; j < R; ++j) {
+            const __half* rp = p.rows + row[j] * p.dim;
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+                const int ch = hl + 16 * c;
+                if (ch < chunks) v[j][c] = ld_stream_16(rp + ch * 8);
+            }
+        }
+#pragma unroll
+        for (int j = 0; j < R; ++j) {
+            const float in = __ldg(p.inv_norm + row[j]);
+            invn[j] = cosine ? in : (in == in ? 1.0f : in);
+        }
+#pragma unroll
+        for (int j = 0; j < R; ++j) {
+#pragma unroll
+            for (int q = 0; q < NQ; ++q) {
+                // canonical lane hl: chunks hl, hl+32 ; canonical lane hl+16: chunks hl+16, hl+48
+                float a0 = 0.f, a1 = 0.f;
+                if (hl < chunks) a0 = chunk_fma(v[j][0], qr[q][0], a0);
+                if (hl + 32 < chunks) a0 = chunk_fma(v[j][2], qr[q][2], a0);
+                if (hl + 16 < chunks) a1 = chunk_fma(v[j][1], qr[q][1], a1);
+                if (hl + 48 < chunks) a1 = chunk_fma(v[j][3], qr[q][3], a1);
+                float s = a0 + a1;                                   // canonical xor-16 level
+                s += __shfl_xor_sync(CRB_FULL_MASK, s, 8);
+                s += __shfl_xor_sync(CRB_FULL_MASK, s, 4);
+                s += __shfl_xor_sync(CRB_FULL_MASK, s, 2);
+                s += __shfl_xor_sync(CRB_FULL_MASK, s, 1);
+                s *= invn[j];
+                const bool good = ok[j] && !(cosine && invn[j] == 0.f) && G.q_idx[q] >= 0 && s == s;
+                const uint64_t key = good ? make_key(s, p.row_offset + static_cast<uint32_t>(row[j])) : 0ull;
+                // admit the two rows of the step one after the other (warp-uniform keys)
+#pragma unroll
+                for (int h = 0; h < 2; ++h) {
+                    const uint64_t kh = __shfl_sync(CRB_FULL_MASK, key, h * 16);
+                    if (kh > top[q].thr) top[q].insert(kh, lane);
+                }
+            }
+        }
+    }
+
+#pragma unroll
+    for (int q = 0; q < NQ; ++q) {
+        if (G.q_idx[q] < 0) continue;
+        uint64_t* out = p.cand +
+            ((static_cast<int64_t>(blockIdx.y) * NQ + q) * gridDim.x + blockIdx.x) * p.k;
+        block_extract_topk<KPL>(top[q], p.k, out, xchg, lane, warp, kK1Warps);
+    }
+
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence();
+        const unsigned t = atomicAdd(&p.counters[blockIdx.y], 1u);
+        s_last = (t == gridDim.x - 1) ? 1 : 0;
+    }
+    __syncthreads();
+    if (!s_last) return;
+    __threadfence();
+
+#pragma unroll
+    for (int q = 0; q < NQ; ++q) {
+        const int qi = G.q_idx[q];
+        if (qi < 0) continue;
+        if (warp == 0) {
+            const float iq = cosine ? warp_inv_qnorm(p.queries + static_cast<int64_t>(qi) * p.dim, p.dim, lane) : 1.0f;
+            if (lane == 0) s_invq = iq;
+        }
+        __syncthreads();
+        TopKSink sink;
+        sink.scores = p.out_scores + static_cast<int64_t>(qi) * p.k;
+        sink.rows = p.out_rows + static_cast<int64_t>(qi) * p.k;
+        sink.n_valid = p.out_nvalid + qi;
+        sink.keys = p.out_keys ? p.out_keys + static_cast<int64_t>(qi) * p.k : nullptr;
+        sink.scale = s_invq;
+        sink.ex = p.ex.world > 0 ? &p.ex : nullptr;
+        sink.qi = qi;
+        sink.k = p.k;
+        const uint64_t* lists = p.cand + (static_cast<int64_t>(blockIdx.y) * NQ + q) * gridDim.x * p.k;
+        block_merge_sorted_lists<kK1MergeLPT>(lists, gridDim.x, p.k, p.k, sink, xchg, lane, warp, kK1Warps);
+    }
+    if (threadIdx.x == 0) p.counters[blockIdx.y] = 0u;
+}
+
 // Generic-dimension variant (dim up to CRB_MAX_DIM, one query per group): the query lives in
 // shared memory and chunks are walked with a runtime loop; same canonical summation order.
 template <int R, int KPL>

@@ -565,11 +565,16 @@ k2_gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap map_q, const __grid
                         uint8_t* a = stage_base + static_cast<size_t>(st) * kK2PairStageBytes;
                         uint8_t* b = a + kK2StageBytesA;
                         const uint32_t full_leader = mapa_u32(smem_u32(&full_bar[st]), 0);
-                        if (leader) mbar_expect_tx(&full_bar[st], 2 * kK2PairStageBytes);
-                        tma_load_2d_pair(&map_q, a, full_leader, kb * kK2BlockK, a_row);
-                        tma_load_2d_pair(&map_c, b, full_leader, kb * kK2BlockK,
-                                         static_cast<int32_t>(t * kK2BlockN + rank * (kK2BlockN / 2)));
-                        if (!leader) mbar_arrive_cluster(full_leader);
+                        if ((p.debug & 1) && (t != slot || j != 0 || kb >= p.stages)) {
+                            // timing experiment: no TMA after the first fill (MMA runs on stale tiles)
+                            if (leader) mbar_arrive(&full_bar[st]); else mbar_arrive_cluster(full_leader);
+                        } else {
+                            if (leader) mbar_expect_tx(&full_bar[st], 2 * kK2PairStageBytes);
+                            tma_load_2d_pair(&map_q, a, full_leader, kb * kK2BlockK, a_row);
+                            tma_load_2d_pair(&map_c, b, full_leader, kb * kK2BlockK,
+                                             static_cast<int32_t>(t * kK2BlockN + rank * (kK2BlockN / 2)));
+                            if (!leader) mbar_arrive_cluster(full_leader);
+                        }
                         if (++st == p.stages) { st = 0; ph ^= 1u; }
                     }
                 }
