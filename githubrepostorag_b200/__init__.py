@@ -9,7 +9,8 @@ from . import _native  # noqa: F401
 from .types import (Content, Document, MetadataFilter, MetadataFilters, NodeWithScore, TextNode,  # noqa: F401
                     VectorStoreQuery, VectorStoreQueryResult)
 
-__all__ = ["B200VectorStore", "B200Retriever", "DeviceShard", "MetadataDictionary", "merge_keys"]
+__all__ = ["B200VectorStore", "B200Retriever", "DeviceShard", "MetadataDictionary", "merge_keys",
+           "GraphRetrieverFactory", "EagerGraphRetriever", "Eager", "TableNames", "make_graph_retriever_factory"]
 
 
 def __getattr__(name):  # torch is imported only when the device classes are first used
@@ -19,4 +20,7 @@ def __getattr__(name):  # torch is imported only when the device classes are fir
     if name in ("B200VectorStore", "B200Retriever", "DEFAULT_FILTER_KEYS"):
         from . import vector_store
         return getattr(vector_store, name)
+    if name in ("GraphRetrieverFactory", "EagerGraphRetriever", "Eager", "TableNames", "make_graph_retriever_factory"):
+        from . import retrievers
+        return getattr(retrievers, name)
     raise AttributeError(name)
