@@ -115,3 +115,68 @@ def test_k2_sharded_equals_unsharded(torch_cuda):
     assert torch.equal(r0, r1) and torch.equal(s0.view(torch.int32), s1.view(torch.int32))
     for sh in shards + [whole]:
         sh.close()
+
+
+def test_exchange_entry_point_world_of_one(torch_cuda):
+    """crb_search_exchange with a single rank (its own buffer as the only 'peer'): exercises the
+    publish / wait-and-merge path on one GPU; the 2-GPU version is tests/test_gpu_multi.py."""
+    import ctypes as C
+
+    from githubrepostorag_b200 import _native as N
+    torch = torch_cuda
+    lib = N.load()
+    n, d = 60_000, 384
+    rows16 = S.corpus(99, n, d)
+    sh = _shard(torch, rows16)
+    cap = 4096
+    buf = torch.zeros(2 * cap + 32, dtype=torch.int64, device="cuda")
+    ex = N.Exchange()
+    ex.rank, ex.world, ex.cap_keys = 0, 1, cap
+    ex.peer_keys[0] = buf.data_ptr()
+    ex.peer_counters[0] = buf.data_ptr() + 8 * 2 * cap
+    published = 0
+    for call, (b, k, algo) in enumerate(((1, 10, 0), (5, 7, 0), (150, 10, 2), (2, 100, 1))):
+        q = torch.from_numpy(S.queries(200 + call, b, d)).cuda()
+        want = [t.clone() for t in sh.search_device(q, k, algo=algo)]
+        s = torch.empty((b, k), dtype=torch.float32, device="cuda")
+        r = torch.empty((b, k), dtype=torch.int64, device="cuda")
+        v = torch.empty((b,), dtype=torch.int32, device="cuda")
+        ws = sh.new_workspace(b, k, 0)
+        published += b
+        N.check(lib.crb_search_exchange(sh._h, q.data_ptr(), b, k, 0, None, s.data_ptr(), r.data_ptr(), v.data_ptr(),
+                                        None, ws.data_ptr(), ws.numel(), algo, torch.cuda.current_stream().cuda_stream,
+                                        C.byref(ex), call, published))
+        torch.cuda.synchronize()
+        assert torch.equal(r, want[1]) and torch.equal(v, want[2]) and torch.equal(s.view(torch.int32), want[0].view(torch.int32))
+    sh.close()
+
+
+def test_row_masks_through_the_c_abi(torch_cuda):
+    torch = torch_cuda
+    n, d, k = 50_000, 128, 10
+    rows16 = S.corpus(17, n, d)
+    rng = np.random.default_rng(4)
+    code = rng.integers(0, 5, n).astype(np.int32)
+    sh = _shard(torch, rows16, code[None, :])
+    keep_a = rng.random(n) < 0.03
+    keep_b = rng.random(n) < 0.5
+    ma = sh.pack_row_mask(torch.from_numpy(keep_a).cuda())
+    mb = sh.pack_row_mask(torch.from_numpy(keep_b).cuda())
+    batch = 40
+    q = S.queries(18, batch, d)
+    masks = [ma if i % 3 == 0 else (mb if i % 3 == 1 else None) for i in range(batch)]
+    filt = np.array([[2 if i % 2 else -1] for i in range(batch)], np.int32)
+    for algo in (1, 2, 0):
+        s, r, v = sh.search_device(torch.from_numpy(q).cuda(), k, filt=filt, row_masks=masks, algo=algo)
+        torch.cuda.synchronize()
+        keep = np.ones((batch, n), bool)
+        for i in range(batch):
+            if i % 3 == 0:
+                keep[i] &= keep_a
+            elif i % 3 == 1:
+                keep[i] &= keep_b
+            if i % 2:
+                keep[i] &= code == 2
+        _check(q, rows16, s.cpu().numpy(), r.cpu().numpy(), v.cpu().numpy(), k, oracle.MODE_COSINE, keep=keep,
+               what=f"row masks algo={algo}")
+    sh.close()
