@@ -448,12 +448,48 @@ static int launch_k2(crb_index* ix, const float* d_queries, int batch, int k, in
                 --mi;
             kp.m_inner = mi;
             kp.m_tiles = (m_pairs + mi - 1) / mi;               // query groups
-            kp.slots = std::max(1, (ix->sm_count / 2) / kp.m_tiles);
-            kp.slots = static_cast<int>(std::min<int64_t>(kp.slots, std::max<int64_t>(n_tiles, 1)));
             kp.stages = pair_stages(mi);
             const size_t smem = 1024 + size_t(kp.stages) * kK2PairStageBytes + size_t(mi) * list_bytes + tail_bytes +
                                 size_t(mi) * 1024;
-            k2_gemm_topk_pair_kernel<<<2 * kp.m_tiles * kp.slots, kK2Threads, smem, stream>>>(map_q, *map_half, kp);
+            // 4-CTA clusters (two pairs sharing every query k-block by TMA multicast) when the device can keep
+            // enough of them resident; CODERAG_B200_K2_QUAD=0/1 forces
+            int quad_clusters = 0;
+            const int quad_env = env_int("CODERAG_B200_K2_QUAD", -1);
+            if (quad_env != 0 && n_tiles >= 2) {
+                static std::once_flag quad_once;
+                static cudaError_t quad_err = cudaSuccess;
+                std::call_once(quad_once, [] {
+                    quad_err = cudaFuncSetAttribute(k2_gemm_topk_quad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+                });
+                CRB_CUDA(quad_err);
+                cudaLaunchConfig_t cfg;
+                memset(&cfg, 0, sizeof cfg);
+                cfg.gridDim = dim3(4 * 64);
+                cfg.blockDim = dim3(kK2Threads);
+                cfg.dynamicSmemBytes = smem;
+                cudaLaunchAttribute at;
+                at.id = cudaLaunchAttributeClusterDimension;
+                at.val.clusterDim.x = 4; at.val.clusterDim.y = 1; at.val.clusterDim.z = 1;
+                cfg.attrs = &at; cfg.numAttrs = 1;
+                int max_clusters = 0;
+                if (cudaOccupancyMaxActiveClusters(&max_clusters, k2_gemm_topk_quad_kernel, &cfg) == cudaSuccess)
+                    quad_clusters = max_clusters;
+                (void)cudaGetLastError();
+                // worth it only if (almost) the whole machine fits: 4-CTA clusters can strand SMs in uneven GPCs
+                if (quad_env < 0 && quad_clusters * 4 < (ix->sm_count * 9) / 10) quad_clusters = 0;
+            }
+            if (quad_clusters >= kp.m_tiles) {
+                CUtensorMap map_q64;
+                if (int rc = make_map_f16(&map_q64, q16, n, ix->dim, kK2BlockM / 2)) return rc;
+                int cslots = std::max(1, quad_clusters / kp.m_tiles);
+                cslots = static_cast<int>(std::min<int64_t>(cslots, (n_tiles + 1) / 2));
+                kp.slots = 2 * cslots;
+                k2_gemm_topk_quad_kernel<<<4 * kp.m_tiles * cslots, kK2Threads, smem, stream>>>(map_q64, *map_half, kp);
+            } else {
+                kp.slots = std::max(1, (ix->sm_count / 2) / kp.m_tiles);
+                kp.slots = static_cast<int>(std::min<int64_t>(kp.slots, std::max<int64_t>(n_tiles, 1)));
+                k2_gemm_topk_pair_kernel<<<2 * kp.m_tiles * kp.slots, kK2Threads, smem, stream>>>(map_q, *map_half, kp);
+            }
         } else {
             kp.m_tiles = (n + kK2BlockM - 1) / kK2BlockM;
             kp.slots = std::max(1, ix->sm_count / kp.m_tiles);
