@@ -180,3 +180,42 @@ def test_row_masks_through_the_c_abi(torch_cuda):
         _check(q, rows16, s.cpu().numpy(), r.cpu().numpy(), v.cpu().numpy(), k, oracle.MODE_COSINE, keep=keep,
                what=f"row masks algo={algo}")
     sh.close()
+
+
+def test_k2_large_batches_k_boundary_and_threads(torch_cuda):
+    import threading
+    torch = torch_cuda
+    n, d = 40_000, 128
+    rows16 = S.corpus(123, n, d)
+    sh = _shard(torch, rows16)
+    # a batch larger than one K2 launch serves (2048 queries) is split internally
+    q = S.queries(124, 2500, d)
+    s2, r2, v2 = sh.search_host(q, 10, algo=2)
+    pick = [0, 1, 2047, 2048, 2049, 2499]
+    s1, r1, v1 = sh.search_host(q[pick], 10, algo=1)
+    assert np.array_equal(r2[pick], r1) and np.array_equal(s2[pick], s1)
+    _check(q[pick[:3]], rows16, s2[pick[:3]], r2[pick[:3]], v2[pick[:3]], 10, oracle.MODE_COSINE, what="batch 2500")
+    # largest k the tensor-core path takes (116), and the first it hands to the streaming kernel (117)
+    for k in (116, 117, 128):
+        qa = S.queries(125 + k, 9, d)
+        a = sh.search_host(qa, k, algo=2)
+        b = sh.search_host(qa, k, algo=1)
+        assert np.array_equal(a[1], b[1]) and np.array_equal(a[0], b[0]), k
+    # concurrent tensor-core batches from the worker's thread pool
+    qs = [S.queries(300 + i, 130, d) for i in range(6)]
+    want = [sh.search_host(x, 10, algo=1) for x in qs]
+    errors = []
+
+    def work(i):
+        try:
+            for _ in range(3):
+                got = sh.search_host(qs[i], 10, algo=2)
+                assert np.array_equal(got[1], want[i][1]) and np.array_equal(got[0], want[i][0])
+        except Exception as e:  # noqa: BLE001
+            errors.append(e)
+
+    ts = [threading.Thread(target=work, args=(i,)) for i in range(6)]
+    [t.start() for t in ts]
+    [t.join() for t in ts]
+    assert not errors, errors[:2]
+    sh.close()
