@@ -35,7 +35,7 @@ DIM = 768
 TOPK = 10
 SEED = 1003                       # C3 base seed
 GEN_BLOCK = 1 << 18
-CPU_SAMPLE_ROWS = 1_000_000
+CPU_SAMPLE_ROWS = int(os.environ.get("CODERAG_BENCH_SAMPLE_ROWS", 1_000_000))   # bounded CPU sample (tests shrink it)
 N_QUERY_SETS = 4                  # rotate distinct query batches between timed steps
 
 
