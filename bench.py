@@ -161,7 +161,17 @@ def cpu_baseline(sample32: np.ndarray, n_rows_full: int, dim: int, batch: int, k
             break
     qps_sample = done / el
     scale = len(sample32) / n_rows_full
-    return {"value": qps_sample * scale, "unit": UNIT, "cores": int(threads), "kind": "port",
+    one_thread = None
+    try:  # BASELINE.md reports the all-core and the single-thread figure
+        from threadpoolctl import threadpool_limits
+        with threadpool_limits(limits=1):
+            t1 = time.perf_counter()
+            for i in range(2):
+                oracle.query_vectorised(q[i % len(q)], sample32, k)
+            one_thread = 2 / (time.perf_counter() - t1) * scale
+    except Exception:
+        pass
+    return {"value": qps_sample * scale, "unit": UNIT, "cores": int(threads), "kind": "port", "value_1_thread": one_thread,
             "sample": f"first {len(sample32):,} of {n_rows_full:,} rows x {dim} (fp32 in RAM), {done} single-query "
                       f"searches in {el:.1f}s = {qps_sample:.3f} q/s on the sample, scaled x{scale:.4g} (linear in rows); "
                       f"host cores {os.cpu_count()}, BLAS threads {threads}"}

@@ -39,6 +39,22 @@ DEFAULT_FILTER_KEYS = ("namespace", "repo", "module", "file_path", "branch", "co
 DEFAULT_MULTI_VALUED_KEYS = ("topics", "imports", "labels")
 
 
+def _retrieval_histogram():
+    """``rag_b200_retrieval_seconds``: the search call's latency, next to the worker's own
+    ``rag_worker_retrieval_seconds`` (``rag_worker/src/worker/worker.py:47``).  None when
+    prometheus_client is not installed."""
+    try:
+        from prometheus_client import REGISTRY, Histogram
+        existing = getattr(REGISTRY, "_names_to_collectors", {}).get("rag_b200_retrieval_seconds")
+        if existing is not None:
+            return existing
+        return Histogram("rag_b200_retrieval_seconds", "B200 vector search latency (one store call, all its queries)",
+                         ["table", "kernel_path"],
+                         buckets=(1e-4, 2.5e-4, 5e-4, 1e-3, 2.5e-3, 5e-3, 1e-2, 2.5e-2, 5e-2, 0.1, 0.25, 1.0))
+    except Exception:  # noqa: BLE001
+        return None
+
+
 class _WriteGate:
     """Many concurrent searches (the worker's thread pool) or one writer (append / delete /
     compact re-bind the device buffers, which no search may be using).  Writers have preference:
@@ -174,6 +190,7 @@ class B200VectorStore:
         self.multi_valued_keys = tuple(k for k in multi_valued_keys if k not in self.dictionary.keys)
         self._postings: Dict[Tuple[str, str], List[int]] = {}
         self._mask_cache: Dict[Any, Any] = {}
+        self._hist = _retrieval_histogram()
 
     # ------------------------------------------------------------------ construction / writes
     @property
@@ -419,6 +436,15 @@ class B200VectorStore:
         filt = None
         if any(eq for eq, _ in split):
             filt = np.stack([self.dictionary.encode_filter(eq) for eq, _ in split])
+        import time
+        t0 = time.perf_counter()
+        try:
+            return self._search_locked(queries, k, filt, split, algo)
+        finally:
+            if self._hist is not None:
+                self._hist.labels(self.table_name, "masked" if any(e for _, e in split) else "host").observe(time.perf_counter() - t0)
+
+    def _search_locked(self, queries, k, filt, split, algo):
         with self._gate.read():
             if not any(extra for _, extra in split):
                 return self._shard.search_host(queries, k, metric=self.metric, filt=filt, algo=algo)
