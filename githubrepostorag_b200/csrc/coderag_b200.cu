@@ -127,6 +127,9 @@ struct crb_index {
     bool k2_ok = false;            // corpus tensor map encoded
     CUtensorMap map_rows;          // fp16 [n_rows, dim], box 64 x 256, 128 B swizzle
     CUtensorMap map_rows_half;     // same, box 64 x 128 (one CTA's half tile in the pair kernel)
+    cudaStream_t aux_stream = nullptr;   // side stream for the co-running second K2 kernel
+    cudaEvent_t aux_fork = nullptr, aux_join = nullptr;
+    std::mutex aux_mu;                   // one co-running launch enqueues at a time
     std::mutex mu;
     std::condition_variable cv;
     std::vector<crb::Lane> lanes;
@@ -475,10 +478,43 @@ static int launch_k2(crb_index* ix, const float* d_queries, int batch, int k, in
                 if (cudaOccupancyMaxActiveClusters(&max_clusters, k2_gemm_topk_quad_kernel, &cfg) == cudaSuccess)
                     quad_clusters = max_clusters;
                 (void)cudaGetLastError();
-                // worth it only if (almost) the whole machine fits: 4-CTA clusters can strand SMs in uneven GPCs
-                if (quad_env < 0 && quad_clusters * 4 < (ix->sm_count * 9) / 10) quad_clusters = 0;
             }
-            if (quad_clusters >= kp.m_tiles) {
+            // Co-run: 4-CTA clusters fit only part of the machine (132 of 148 SMs on B200: GPCs whose SM count
+            // is not a multiple of 4 strand a TPC each).  Give the clusters their share of the corpus tiles and
+            // run the CTA-pair kernel on the stranded SMs at the same time, on a side stream.
+            const int corun_env = env_int("CODERAG_B200_K2_CORUN", -1);
+            const int stranded_pairs = (ix->sm_count - quad_clusters * 4) / 2;
+            const bool corun = quad_clusters >= kp.m_tiles && kp.m_tiles == 1 && stranded_pairs >= 1 && n_tiles >= 4096 &&
+                               (corun_env > 0 || (corun_env < 0 && quad_env != 0 && quad_clusters * 4 >= ix->sm_count * 3 / 4));
+            std::unique_lock<std::mutex> aux_lock(ix->aux_mu, std::defer_lock);
+            if (corun && aux_lock.try_lock()) {
+                if (!ix->aux_stream) {
+                    CRB_CUDA(cudaStreamCreateWithFlags(&ix->aux_stream, cudaStreamNonBlocking));
+                    CRB_CUDA(cudaEventCreateWithFlags(&ix->aux_fork, cudaEventDisableTiming));
+                    CRB_CUDA(cudaEventCreateWithFlags(&ix->aux_join, cudaEventDisableTiming));
+                }
+                CUtensorMap map_q64;
+                if (int rc = make_map_f16(&map_q64, q16, n, ix->dim, kK2BlockM / 2)) return rc;
+                const int cslots = quad_clusters;
+                // per-SM the clusters are ~1.14x faster (a quarter less L2->SM traffic)
+                const double w_quad = cslots * 4 * (env_int("CODERAG_B200_K2_CORUN_W", 114) / 100.0), w_pair = stranded_pairs * 2.0;
+                int64_t split = static_cast<int64_t>(double(n_tiles) * w_quad / (w_quad + w_pair));
+                split -= split % 2;
+                K2Params kq = kp, kr = kp;
+                kq.slots = 2 * cslots; kq.slots_total = 2 * cslots + stranded_pairs; kq.slot_base = 0;
+                kq.tile_lo = 0; kq.tile_hi = split;
+                kr.slots = stranded_pairs; kr.slots_total = kq.slots_total; kr.slot_base = 2 * cslots;
+                kr.tile_lo = split; kr.tile_hi = n_tiles;
+                kp.slots = kq.slots_total;                       // what K5 walks per query
+                CRB_CUDA(cudaEventRecord(ix->aux_fork, stream));
+                CRB_CUDA(cudaStreamWaitEvent(ix->aux_stream, ix->aux_fork, 0));
+                k2_gemm_topk_quad_kernel<<<4 * cslots, kK2Threads, smem, stream>>>(map_q64, *map_half, kq);
+                CRB_LAUNCH_CHECK();
+                k2_gemm_topk_pair_kernel<<<2 * stranded_pairs, kK2Threads, smem, ix->aux_stream>>>(map_q, *map_half, kr);
+                CRB_LAUNCH_CHECK();
+                CRB_CUDA(cudaEventRecord(ix->aux_join, ix->aux_stream));
+                CRB_CUDA(cudaStreamWaitEvent(stream, ix->aux_join, 0));
+            } else if (quad_clusters >= kp.m_tiles && (quad_env > 0 || quad_clusters * 4 >= (ix->sm_count * 9) / 10)) {
                 CUtensorMap map_q64;
                 if (int rc = make_map_f16(&map_q64, q16, n, ix->dim, kK2BlockM / 2)) return rc;
                 int cslots = std::max(1, quad_clusters / kp.m_tiles);
@@ -985,6 +1021,9 @@ extern "C" int crb_tombstone_rows(crb_index* ix, const int64_t* h_rows_idx, int3
 extern "C" int crb_index_destroy(crb_index* ix) {
     if (!ix) return 0;
     DeviceGuard guard(ix->device);
+    if (ix->aux_stream) { cudaStreamSynchronize(ix->aux_stream); cudaStreamDestroy(ix->aux_stream); }
+    if (ix->aux_fork) cudaEventDestroy(ix->aux_fork);
+    if (ix->aux_join) cudaEventDestroy(ix->aux_join);
     for (auto& l : ix->lanes) {
         if (l.stream) cudaStreamSynchronize(l.stream);
         if (l.d_ws) cudaFree(l.d_ws);

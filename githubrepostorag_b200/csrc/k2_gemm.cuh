@@ -51,6 +51,12 @@ struct K2Params {
     int32_t debug;              // timing experiments only: 1 = no TMA after the first fill, 2 = no epilogue math
     int32_t lstride;            // candidate-list stride = query rows that own a list (<= 128)
     int32_t m_inner;            // pair kernel: query-tile pairs served per corpus tile by one CTA pair (>= 1)
+    // A launch may cover only corpus tiles [tile_lo, tile_hi) and write its candidate lists at
+    // slot_base.. of slots_total per query (two kernels splitting one shard run side by side).
+    int64_t tile_lo;
+    int64_t tile_hi;            // 0 = all tiles
+    int32_t slot_base;
+    int32_t slots_total;        // 0 = slots
 };
 
 // ---- PTX wrappers ------------------------------------------------------------------------------
@@ -530,7 +536,9 @@ k2_gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap map_q, const __grid
     const int pair = blockIdx.x >> 1;
     const int m_group = pair % p.m_tiles;
     const int slot = pair / p.m_tiles;
-    const int64_t n_tiles = (p.n_rows + kK2BlockN - 1) / kK2BlockN;
+    const int64_t all_tiles = (p.n_rows + kK2BlockN - 1) / kK2BlockN;
+    const int64_t n_tiles = p.tile_hi > 0 ? (p.tile_hi < all_tiles ? p.tile_hi : all_tiles) : all_tiles;
+    const int slots_total = p.slots_total > 0 ? p.slots_total : p.slots;
     const int k_blocks = (p.dim + kK2BlockK - 1) / kK2BlockK;
     // first query row of this CTA for inner index j
     auto m_row0 = [&](int j) { return (m_group * MI + j) * 256 + static_cast<int>(rank) * kK2BlockM; };
@@ -557,7 +565,7 @@ k2_gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap map_q, const __grid
         if (lane == 0) {
             int st = 0;
             uint32_t ph = 0;
-            for (int64_t t = slot; t < n_tiles; t += p.slots) {
+            for (int64_t t = p.tile_lo + slot; t < n_tiles; t += p.slots) {
                 for (int j = 0; j < MI; ++j) {
                     const int a_row = m_row0(j);
                     for (int kb = 0; kb < k_blocks; ++kb) {
@@ -586,7 +594,7 @@ k2_gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap map_q, const __grid
             int st = 0;
             uint32_t ph = 0;
             int64_t it = 0;
-            for (int64_t t = slot; t < n_tiles; t += p.slots) {
+            for (int64_t t = p.tile_lo + slot; t < n_tiles; t += p.slots) {
                 for (int j = 0; j < MI; ++j, ++it) {
                     const int buf = static_cast<int>(it & 1);
                     const uint32_t use = static_cast<uint32_t>(it >> 1);
@@ -632,7 +640,7 @@ k2_gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap map_q, const __grid
         };
         float pre[2] = {qnan, qnan};
         int64_t it = 0;
-        for (int64_t t = slot; t < n_tiles; t += p.slots) {
+        for (int64_t t = p.tile_lo + slot; t < n_tiles; t += p.slots) {
             const int64_t n0 = t * kK2BlockN;
             for (int j = 0; j < MI; ++j, ++it) {
                 const int buf = static_cast<int>(it & 1);
@@ -680,7 +688,7 @@ k2_gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap map_q, const __grid
         for (int j = 0; j < MI; ++j) {
             const int qrow = m_row0(j) + row;
             if (qrow < p.batch && row < p.lstride) {
-                uint64_t* out = p.cand + (static_cast<int64_t>(qrow) * p.slots + slot) * p.kprime;
+                uint64_t* out = p.cand + (static_cast<int64_t>(qrow) * slots_total + p.slot_base + slot) * p.kprime;
                 const uint64_t* my_list = lists + static_cast<size_t>(j) * list_elems + row;
                 const int count = static_cast<int>(s_state[j * 128 + row]);
                 for (int i = 0; i < p.kprime; ++i) out[i] = i < count ? my_list[i * p.lstride] : 0ull;
@@ -746,8 +754,10 @@ k2_gemm_topk_quad_kernel(const __grid_constant__ CUtensorMap map_q64, const __gr
     const int cslot = cid / p.m_tiles;
     const int cslots = p.slots >> 1;                 // clusters per query group; p.slots = candidate lists per query
     const int slot = cslot * 2 + static_cast<int>(pr);
-    const int64_t n_tiles = (p.n_rows + kK2BlockN - 1) / kK2BlockN;
-    const int64_t n_tile_pairs = (n_tiles + 1) / 2;  // both pairs run every iteration (a missing tile reads as zeros)
+    const int64_t all_tiles = (p.n_rows + kK2BlockN - 1) / kK2BlockN;
+    const int64_t n_tiles = p.tile_hi > 0 ? (p.tile_hi < all_tiles ? p.tile_hi : all_tiles) : all_tiles;
+    const int slots_total = p.slots_total > 0 ? p.slots_total : p.slots;
+    const int64_t n_tile_pairs = (n_tiles - p.tile_lo + 1) / 2;  // both pairs run every iteration (a missing tile reads as zeros)
     const int k_blocks = (p.dim + kK2BlockK - 1) / kK2BlockK;
     // first query row of this CTA for inner index j
     auto m_row0 = [&](int j) { return (m_group * MI + j) * 256 + static_cast<int>(rank) * kK2BlockM; };
@@ -775,7 +785,7 @@ k2_gemm_topk_quad_kernel(const __grid_constant__ CUtensorMap map_q64, const __gr
             int st = 0;
             uint32_t ph = 0;
             for (int64_t u = cslot; u < n_tile_pairs; u += cslots) {
-                const int64_t t = 2 * u + pr;
+                const int64_t t = p.tile_lo + 2 * u + pr;
                 for (int j = 0; j < MI; ++j) {
                     const int a_row = m_row0(j);
                     for (int kb = 0; kb < k_blocks; ++kb) {
@@ -805,7 +815,7 @@ k2_gemm_topk_quad_kernel(const __grid_constant__ CUtensorMap map_q64, const __gr
             uint32_t ph = 0;
             int64_t it = 0;
             for (int64_t u = cslot; u < n_tile_pairs; u += cslots) {
-                const int64_t t = 2 * u + pr;
+                const int64_t t = p.tile_lo + 2 * u + pr;
                 for (int j = 0; j < MI; ++j, ++it) {
                     const int buf = static_cast<int>(it & 1);
                     const uint32_t use = static_cast<uint32_t>(it >> 1);
@@ -843,7 +853,7 @@ k2_gemm_topk_quad_kernel(const __grid_constant__ CUtensorMap map_q64, const __gr
             s_state[j * 128 + row] = 0u;
         }
         auto column_scale = [&](int64_t n) -> float {
-            if (n >= p.n_rows) return qnan;
+            if (n >= p.n_rows || n >= n_tiles * kK2BlockN) return qnan;   // also: a pair's dummy tile past this launch's range
             if (p.mask && !((p.mask[n >> 5] >> (n & 31)) & 1u)) return qnan;
             const float in = __ldg(p.inv_norm + n);          // NaN = deleted row
             if (!cosine) return in == in ? 1.0f : qnan;
@@ -852,7 +862,7 @@ k2_gemm_topk_quad_kernel(const __grid_constant__ CUtensorMap map_q64, const __gr
         float pre[2] = {qnan, qnan};
         int64_t it = 0;
         for (int64_t u = cslot; u < n_tile_pairs; u += cslots) {
-                const int64_t t = 2 * u + pr;
+                const int64_t t = p.tile_lo + 2 * u + pr;
             const int64_t n0 = t * kK2BlockN;
             for (int j = 0; j < MI; ++j, ++it) {
                 const int buf = static_cast<int>(it & 1);
@@ -900,7 +910,7 @@ k2_gemm_topk_quad_kernel(const __grid_constant__ CUtensorMap map_q64, const __gr
         for (int j = 0; j < MI; ++j) {
             const int qrow = m_row0(j) + row;
             if (qrow < p.batch && row < p.lstride) {
-                uint64_t* out = p.cand + (static_cast<int64_t>(qrow) * p.slots + slot) * p.kprime;
+                uint64_t* out = p.cand + (static_cast<int64_t>(qrow) * slots_total + p.slot_base + slot) * p.kprime;
                 const uint64_t* my_list = lists + static_cast<size_t>(j) * list_elems + row;
                 const int count = static_cast<int>(s_state[j * 128 + row]);
                 for (int i = 0; i < p.kprime; ++i) out[i] = i < count ? my_list[i * p.lstride] : 0ull;
