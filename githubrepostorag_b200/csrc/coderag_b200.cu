@@ -1012,6 +1012,7 @@ extern "C" int crb_tombstone_rows(crb_index* ix, const int64_t* h_rows_idx, int3
     memcpy(l->h_pin, h_rows_idx, size_t(n) * sizeof(int64_t));
     CRB_CUDA(cudaMemcpyAsync(l->d_io, l->h_pin, size_t(n) * sizeof(int64_t), cudaMemcpyHostToDevice, l->stream));
     tombstone_rows_kernel<<<(n + 255) / 256, 256, 0, l->stream>>>(const_cast<float*>(ix->inv_norm),
+                                                                  const_cast<__half*>(ix->rows), ix->dim,
                                                                   static_cast<const int64_t*>(l->d_io), n);
     CRB_LAUNCH_CHECK();
     CRB_CUDA(cudaStreamSynchronize(l->stream));

@@ -49,6 +49,31 @@ struct K1Params {
     K1Group groups[kMaxGroups];
 };
 
+// Last-CTA work for one finished query: merge the per-CTA lists, emit (and publish to peers).  Kept out
+// of line so its registers and code stay out of the streaming loop's allocation (inlined, it pushed
+// the d=768 kernel against its 128-register cap and cost 7 % of the bandwidth).
+__device__ __noinline__ void k1_merge_query(const K1Params& p, int qi, int64_t list_slot, const float* q_ptr,
+                                            uint64_t (*xchg)[32], float* s_invq) {
+    const int lane = threadIdx.x & 31;
+    const int warp = threadIdx.x >> 5;
+    if (warp == 0) {
+        const float iq = (p.metric == 0) ? warp_inv_qnorm(q_ptr, p.dim, lane) : 1.0f;
+        if (lane == 0) *s_invq = iq;
+    }
+    __syncthreads();
+    TopKSink sink;
+    sink.scores = p.out_scores + static_cast<int64_t>(qi) * p.k;
+    sink.rows = p.out_rows + static_cast<int64_t>(qi) * p.k;
+    sink.n_valid = p.out_nvalid + qi;
+    sink.keys = p.out_keys ? p.out_keys + static_cast<int64_t>(qi) * p.k : nullptr;
+    sink.scale = *s_invq;
+    sink.ex = p.ex.world > 0 ? &p.ex : nullptr;
+    sink.qi = qi;
+    sink.k = p.k;
+    const uint64_t* lists = p.cand + list_slot * gridDim.x * p.k;
+    block_merge_sorted_lists<kK1MergeLPT>(lists, gridDim.x, p.k, p.k, sink, xchg, lane, warp, kK1Warps);
+}
+
 template <int NQ, int CH, int R, int KPL, int MINB = 1>
 __global__ void __launch_bounds__(kK1Threads, MINB)
 k1_stream_kernel(const __grid_constant__ K1Params p) {
@@ -129,11 +154,10 @@ k1_stream_kernel(const __grid_constant__ K1Params p) {
             }
         }
 #pragma unroll
-        for (int j = 0; j < R; ++j) {
-            // inverse norm; NaN marks a deleted row (the NaN reaches the score and fails `s == s`)
-            const float in = __ldg(p.inv_norm + row[j]);
-            invn[j] = cosine ? in : (in == in ? 1.0f : in);
-        }
+        // (keep this load predicated on the metric: the d=768 instantiation sits at 125 of the 128 registers
+        //  that two resident CTAs allow; an unconditional load + select tipped ptxas into re-materialising
+        //  row pointers between the 12 LDG.128s and cost 7 % of the bandwidth -- profiles/_ab/k1_ab.py)
+        for (int j = 0; j < R; ++j) invn[j] = cosine ? __ldg(p.inv_norm + row[j]) : 1.0f;
 
         float acc[NQ][R];
 #pragma unroll
@@ -187,22 +211,8 @@ k1_stream_kernel(const __grid_constant__ K1Params p) {
     for (int q = 0; q < NQ; ++q) {
         const int qi = G.q_idx[q];
         if (qi < 0) continue;
-        if (warp == 0) {
-            const float iq = cosine ? warp_inv_qnorm(p.queries + static_cast<int64_t>(qi) * p.dim, p.dim, lane) : 1.0f;
-            if (lane == 0) s_invq = iq;
-        }
-        __syncthreads();
-        TopKSink sink;
-        sink.scores = p.out_scores + static_cast<int64_t>(qi) * p.k;
-        sink.rows = p.out_rows + static_cast<int64_t>(qi) * p.k;
-        sink.n_valid = p.out_nvalid + qi;
-        sink.keys = p.out_keys ? p.out_keys + static_cast<int64_t>(qi) * p.k : nullptr;
-        sink.scale = s_invq;
-        sink.ex = p.ex.world > 0 ? &p.ex : nullptr;
-        sink.qi = qi;
-        sink.k = p.k;
-        const uint64_t* lists = p.cand + (static_cast<int64_t>(blockIdx.y) * NQ + q) * gridDim.x * p.k;
-        block_merge_sorted_lists<kK1MergeLPT>(lists, gridDim.x, p.k, p.k, sink, xchg, lane, warp, kK1Warps);
+        k1_merge_query(p, qi, static_cast<int64_t>(blockIdx.y) * NQ + q,
+                       p.queries + static_cast<int64_t>(qi) * p.dim, xchg, &s_invq);
     }
     if (threadIdx.x == 0) p.counters[blockIdx.y] = 0u;
 }
@@ -292,10 +302,7 @@ k1_stream_half_kernel(const __grid_constant__ K1Params p) {
             }
         }
 #pragma unroll
-        for (int j = 0; j < R; ++j) {
-            const float in = __ldg(p.inv_norm + row[j]);
-            invn[j] = cosine ? in : (in == in ? 1.0f : in);
-        }
+        for (int j = 0; j < R; ++j) invn[j] = cosine ? __ldg(p.inv_norm + row[j]) : 1.0f;
 #pragma unroll
         for (int j = 0; j < R; ++j) {
 #pragma unroll
@@ -346,22 +353,8 @@ k1_stream_half_kernel(const __grid_constant__ K1Params p) {
     for (int q = 0; q < NQ; ++q) {
         const int qi = G.q_idx[q];
         if (qi < 0) continue;
-        if (warp == 0) {
-            const float iq = cosine ? warp_inv_qnorm(p.queries + static_cast<int64_t>(qi) * p.dim, p.dim, lane) : 1.0f;
-            if (lane == 0) s_invq = iq;
-        }
-        __syncthreads();
-        TopKSink sink;
-        sink.scores = p.out_scores + static_cast<int64_t>(qi) * p.k;
-        sink.rows = p.out_rows + static_cast<int64_t>(qi) * p.k;
-        sink.n_valid = p.out_nvalid + qi;
-        sink.keys = p.out_keys ? p.out_keys + static_cast<int64_t>(qi) * p.k : nullptr;
-        sink.scale = s_invq;
-        sink.ex = p.ex.world > 0 ? &p.ex : nullptr;
-        sink.qi = qi;
-        sink.k = p.k;
-        const uint64_t* lists = p.cand + (static_cast<int64_t>(blockIdx.y) * NQ + q) * gridDim.x * p.k;
-        block_merge_sorted_lists<kK1MergeLPT>(lists, gridDim.x, p.k, p.k, sink, xchg, lane, warp, kK1Warps);
+        k1_merge_query(p, qi, static_cast<int64_t>(blockIdx.y) * NQ + q,
+                       p.queries + static_cast<int64_t>(qi) * p.dim, xchg, &s_invq);
     }
     if (threadIdx.x == 0) p.counters[blockIdx.y] = 0u;
 }
@@ -424,8 +417,7 @@ k1_stream_generic_kernel(const __grid_constant__ K1Params p) {
         }
 #pragma unroll
         for (int j = 0; j < R; ++j) {
-            const float in = __ldg(p.inv_norm + row[j]);
-            const float invn = cosine ? in : (in == in ? 1.0f : in);
+            const float invn = cosine ? __ldg(p.inv_norm + row[j]) : 1.0f;
             const float s = warp_butterfly_sum(acc[j]) * invn;
             if (ok[j] && !(cosine && invn == 0.f) && s == s) {
                 const uint64_t key = make_key(s, p.row_offset + static_cast<uint32_t>(row[j]));
@@ -447,22 +439,7 @@ k1_stream_generic_kernel(const __grid_constant__ K1Params p) {
     if (!s_last) return;
     __threadfence();
 
-    if (warp == 0) {
-        const float iq = cosine ? warp_inv_qnorm(s_q, p.dim, lane) : 1.0f;
-        if (lane == 0) s_invq = iq;
-    }
-    __syncthreads();
-    TopKSink sink;
-    sink.scores = p.out_scores + static_cast<int64_t>(qi) * p.k;
-    sink.rows = p.out_rows + static_cast<int64_t>(qi) * p.k;
-    sink.n_valid = p.out_nvalid + qi;
-    sink.keys = p.out_keys ? p.out_keys + static_cast<int64_t>(qi) * p.k : nullptr;
-    sink.scale = s_invq;
-    sink.ex = p.ex.world > 0 ? &p.ex : nullptr;
-    sink.qi = qi;
-    sink.k = p.k;
-    const uint64_t* lists = p.cand + static_cast<int64_t>(blockIdx.y) * gridDim.x * p.k;
-    block_merge_sorted_lists<kK1MergeLPT>(lists, gridDim.x, p.k, p.k, sink, xchg, lane, warp, kK1Warps);
+    k1_merge_query(p, qi, static_cast<int64_t>(blockIdx.y), s_q, xchg, &s_invq);
     if (threadIdx.x == 0) p.counters[blockIdx.y] = 0u;
 }
 

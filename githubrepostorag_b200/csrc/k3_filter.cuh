@@ -169,11 +169,16 @@ __global__ void __launch_bounds__(256) row_inv_norms_kernel(const __half* __rest
     }
 }
 
-// Deleted rows: an inverse norm of NaN marks a row that no search may return (either metric).
-__global__ void __launch_bounds__(256) tombstone_rows_kernel(float* __restrict__ inv_norm,
-                                                             const int64_t* __restrict__ idx, int n) {
+// Deleted rows: the inverse norm becomes NaN and so does the first 16-byte chunk of the row itself, so
+// every score of the row is NaN under either metric (cosine: NaN scale; inner product: NaN dot) and
+// fails the `s == s` / `s > threshold` admission tests of every kernel at no cost to the scan loops.
+__global__ void __launch_bounds__(256) tombstone_rows_kernel(float* __restrict__ inv_norm, __half* __restrict__ rows,
+                                                             int dim, const int64_t* __restrict__ idx, int n) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < n) inv_norm[idx[i]] = __uint_as_float(0x7fc00000u);
+    if (i < n) {
+        inv_norm[idx[i]] = __uint_as_float(0x7fc00000u);
+        *reinterpret_cast<uint4*>(rows + idx[i] * dim) = make_uint4(0x7e007e00u, 0x7e007e00u, 0x7e007e00u, 0x7e007e00u);
+    }
 }
 
 // Stored rows -> fp32 (the `embedding` member of LCCassandra's (Document, embedding, id)).

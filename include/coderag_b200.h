@@ -74,8 +74,8 @@ int crb_index_destroy(crb_index *index);
  * be over-allocated).  No search may be in flight on the index during the call. */
 int crb_index_rebind(crb_index *index, const void *d_rows_f16, const float *d_inv_norm,
                      const int32_t *d_codes, int64_t n_rows, int64_t code_stride);
-/* Delete rows (LOCAL indices): their inverse norm becomes NaN, which no search returns under
- * either metric.  Returns when the device has been updated. */
+/* Delete rows (LOCAL indices): their inverse norm and the first 16 bytes of the row become NaN, so
+ * no search returns them under either metric.  Returns when the device has been updated. */
 int crb_tombstone_rows(crb_index *index, const int64_t *h_rows_idx, int32_t n);
 
 /* Ingest-side conversion (stands for the embedding column write of
