@@ -118,3 +118,26 @@ def test_synthetic_generator_is_block_stable():
     assert set(flt) == {"namespace", "component_kind"} and 0.0 < sel < 0.5
     md = S.metadata_dicts({k: v[:3] for k, v in c_full.items()})
     assert all(isinstance(v, str) for row in md for v in row.values())
+
+
+def test_k1_d768_hot_loop_keeps_its_loads_together(lib):
+    """Build-time guard (no GPU needed): the d=768 streaming kernel must keep its 12 row loads in one tight
+    group.  When register pressure crosses the 128-register line that two resident CTAs allow, ptxas
+    re-materialises row pointers between the loads and the kernel loses 7 % of HBM bandwidth
+    (seen once; profiles/_ab/k1_ab.py measures it on a GPU)."""
+    import shutil
+    import subprocess
+    from githubrepostorag_b200 import _native
+    if not shutil.which("cuobjdump"):
+        pytest.skip("cuobjdump not on PATH")
+    sass = subprocess.run(["cuobjdump", "-sass", str(_native.lib_path())], capture_output=True, text=True).stdout
+    take, lines = False, []
+    for ln in sass.splitlines():
+        if "Function :" in ln:
+            take = "k1_stream_kernelILi1ELi3ELi4ELi1ELi2E" in ln
+        elif take and "/*" in ln and ";" in ln:
+            lines.append(ln)
+    loads = [i for i, ln in enumerate(lines) if "LDG.E" in ln and ".128" in ln]
+    assert len(loads) >= 12, "d=768 kernel not found or has no 128-bit loads"
+    first12 = loads[:12]
+    assert first12[-1] - first12[0] <= 64, f"row loads are spread over {first12[-1] - first12[0]} instructions"
