@@ -137,7 +137,7 @@ def test_k1_d768_hot_loop_keeps_its_loads_together(lib):
             take = "k1_stream_kernelILi1ELi3ELi4ELi1ELi2E" in ln
         elif take and "/*" in ln and ";" in ln:
             lines.append(ln)
-    loads = [i for i, ln in enumerate(lines) if "LDG.E" in ln and ".128" in ln]
+    loads = [i for i, ln in enumerate(lines) if "LDG.E.NA.128" in ln]      # the streaming (no-allocate) row loads
     assert len(loads) >= 12, "d=768 kernel not found or has no 128-bit loads"
     first12 = loads[:12]
     assert first12[-1] - first12[0] <= 64, f"row loads are spread over {first12[-1] - first12[0]} instructions"
