@@ -94,10 +94,10 @@ constexpr int64_t kK2MinRows = 16384;                   // below this K1 is alwa
 // (shared memory holds k' x 128 keys next to >= 2 pipeline stages, which caps k' at 120)
 constexpr int kK2MaxKPrime = 120;
 static inline int k2_kprime(int k) {
-    if (k <= 10) return 16;
+    if (k <= 10) return std::max(k + 2, getenv("CODERAG_B200_K2_KPRIME") ? atoi(getenv("CODERAG_B200_K2_KPRIME")) : 16);
     return std::min<int>(kK2MaxKPrime, static_cast<int>(round_up(k + k / 2, 8)));
 }
-static inline bool k2_supports_k(int k) { return k2_kprime(k) >= k + 4; }
+static inline bool k2_supports_k(int k) { return k2_kprime(k) >= k + 2; }
 
 struct Lane {
     cudaStream_t stream = nullptr;
@@ -441,7 +441,9 @@ static int launch_k2(crb_index* ix, const float* d_queries, int batch, int k, in
             const int m_pairs = (n + 255) / 256;                // query tile PAIRS
             // m-inner: one CTA pair serves up to 4 query-tile pairs per corpus tile while their candidate
             // lists fit next to >= 4 pipeline stages (CODERAG_B200_K2_MINNER=1 restores one group per pair)
-            int mi = std::min(m_pairs, std::max(1, env_int("CODERAG_B200_K2_MINNER", 4)));
+            // (measured: 5 pipeline stages with 2 query-tile pairs per corpus tile beat 4 stages with 4 pairs
+            //  up to 4 pairs -- 12.4 vs 13.0 ms at B=1024; beyond that fewer HBM re-reads win)
+            int mi = std::min(m_pairs, std::max(1, env_int("CODERAG_B200_K2_MINNER", m_pairs <= 4 ? 2 : 4)));
             auto pair_stages = [&](int mi_) {
                 const size_t fixed_b = size_t(mi_) * list_bytes + tail_bytes + size_t(mi_) * 1024;
                 return static_cast<int>(std::min<size_t>((size_t(227) * 1024 - 1024 - fixed_b) / kK2PairStageBytes, 8));
