@@ -384,14 +384,19 @@ static int launch_k2(crb_index* ix, const float* d_queries, int batch, int k, in
     }
     (void)k2_rows;
     const size_t tail_bytes = 2 * kK2BlockN * 4 + 256;
-    static std::once_flag attr_once;
-    static cudaError_t attr_err = cudaSuccess;
-    std::call_once(attr_once, [] {
-        attr_err = cudaFuncSetAttribute(k2_gemm_topk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
-        if (attr_err == cudaSuccess)
-            attr_err = cudaFuncSetAttribute(k2_gemm_topk_pair_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
-    });
-    CRB_CUDA(attr_err);
+    // opt in to 227 KB of dynamic shared memory: a per-device attribute, set once per device ordinal
+    {
+        static std::mutex attr_mu;
+        static bool attr_done[64] = {};
+        std::lock_guard<std::mutex> lk(attr_mu);
+        const int dv = ix->device & 63;
+        if (!attr_done[dv]) {
+            CRB_CUDA(cudaFuncSetAttribute(k2_gemm_topk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+            CRB_CUDA(cudaFuncSetAttribute(k2_gemm_topk_pair_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+            CRB_CUDA(cudaFuncSetAttribute(k2_gemm_topk_quad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+            attr_done[dv] = true;
+        }
+    }
     // CTA pairs (cta_group::2) pay off once there are >= 2 query tiles; CODERAG_B200_K2_PAIR=0/1 forces.
     const int pair_env = env_int("CODERAG_B200_K2_PAIR", -1);
 
@@ -461,12 +466,6 @@ static int launch_k2(crb_index* ix, const float* d_queries, int batch, int k, in
             int quad_clusters = 0;
             const int quad_env = env_int("CODERAG_B200_K2_QUAD", -1);
             if (quad_env != 0 && n_tiles >= 2) {
-                static std::once_flag quad_once;
-                static cudaError_t quad_err = cudaSuccess;
-                std::call_once(quad_once, [] {
-                    quad_err = cudaFuncSetAttribute(k2_gemm_topk_quad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
-                });
-                CRB_CUDA(quad_err);
                 cudaLaunchConfig_t cfg;
                 memset(&cfg, 0, sizeof cfg);
                 cfg.gridDim = dim3(4 * 64);
