@@ -144,7 +144,7 @@ static int64_t mask_stride_of(const crb_index* ix) { return round_up((std::max<i
 struct WsLayout {
     size_t cand = kWsHeaderBytes;
     size_t k2 = 0;          // K2 region start
-    size_t q16 = 0, invq = 0, eps = 0, qmap = 0, flagged = 0, nflag = 0, cand2 = 0;   // inside the K2 region
+    size_t q16 = 0, invq = 0, eps = 0, qmap = 0, flagged = 0, nflag = 0, fbcnt = 0, cand2 = 0;   // inside the K2 region
     size_t filt = 0;        // survivor lists start; masks follow the lists
     size_t per_filter = 0;  // bytes one more filter costs
 };
@@ -159,6 +159,7 @@ static WsLayout ws_layout(const crb_index* ix, int batch, int k) {
     L.qmap = o;    o += round_up(nmax * 4, 256);
     L.flagged = o; o += round_up(nmax * 4, 256);
     L.nflag = o;   o += 256;
+    L.fbcnt = o;   o += round_up(nmax * 4, 256);   // fallback arrival counters, cleared with nflag
     // per query: one k'-list per CTA (pair) that served its query tile -- at most sm_count lists when the
     // batch is one tile, sm_count/2 when CTA pairs serve every query tile of the batch (m-inner)
     L.cand2 = o;   o += round_up(std::max<size_t>(std::min<size_t>(nmax, kK2BlockM) * ix->sm_count,
@@ -342,12 +343,12 @@ static int launch_k1(const crb_index* ix, const float* d_queries, int k, int met
 // K2 launch: tensor-core candidates + K5 exact rescore for one set of queries sharing a row set
 // ---------------------------------------------------------------------------------------------
 // `queries` are indices into the caller's batch; `mask` is the pass-bit array of their common
-// filter (nullptr = whole shard).  Queries K5 cannot prove exact are appended to `unproven`
-// (the caller re-runs them through K1).  Synchronises the stream once to read the flag count.
+// filter (nullptr = whole shard).  Queries K5 cannot prove exact are flagged on the device and re-run
+// by k1_fallback_kernel, launched right behind K5: nothing here waits for the stream.
 static int launch_k2(crb_index* ix, const float* d_queries, int batch, int k, int metric,
                      const std::vector<int>& queries, const uint32_t* mask, uint8_t* ws, const WsLayout& L,
                      float* d_scores, int64_t* d_rows, int32_t* d_n_valid, uint64_t* d_keys,
-                     std::vector<int>* unproven, cudaStream_t stream,
+                     cudaStream_t stream,
                      const uint32_t* surv_list = nullptr, const uint32_t* surv_count = nullptr,
                      int64_t n_surv = -1, uint8_t* compact_buf = nullptr, size_t compact_cap = 0,
                      const ExchangeDev* ex = nullptr) {
@@ -537,7 +538,7 @@ static int launch_k2(crb_index* ix, const float* d_queries, int batch, int k, in
         }
         CRB_LAUNCH_CHECK();
 
-        CRB_CUDA(cudaMemsetAsync(nflag, 0, 4, stream));
+        CRB_CUDA(cudaMemsetAsync(nflag, 0, (L.fbcnt - L.nflag) + size_t(n) * 4, stream));
         K5Params rp;
         memset(&rp, 0, sizeof rp);
         rp.rows = ix->rows;
@@ -567,15 +568,36 @@ static int launch_k2(crb_index* ix, const float* d_queries, int batch, int k, in
         else k5_rescore_kernel<4><<<n, 256, dyn, stream>>>(rp);
         CRB_LAUNCH_CHECK();
 
-        int32_t h_nflag = 0;
-        CRB_CUDA(cudaMemcpyAsync(&h_nflag, nflag, 4, cudaMemcpyDeviceToHost, stream));
-        CRB_CUDA(cudaStreamSynchronize(stream));
-        if (h_nflag > 0) {
-            std::vector<int32_t> h_flag(h_nflag);
-            CRB_CUDA(cudaMemcpyAsync(h_flag.data(), flagged, size_t(h_nflag) * 4, cudaMemcpyDeviceToHost, stream));
-            CRB_CUDA(cudaStreamSynchronize(stream));
-            for (int32_t slot_q : h_flag) unproven->push_back(queries[c0 + slot_q]);
-        }
+        // the queries K5 flagged, through the streaming scan (a one-word read per CTA when there are none)
+        FbParams fp;
+        memset(&fp, 0, sizeof fp);
+        fp.rows = ix->rows;
+        fp.inv_norm = ix->inv_norm;
+        fp.queries = d_queries;
+        fp.q_map = d_qmap;
+        fp.flagged = flagged;
+        fp.n_flagged = nflag;
+        fp.list = surv_list;
+        fp.list_count = surv_count;
+        fp.cand = reinterpret_cast<uint64_t*>(ws + kWsHeaderBytes);
+        fp.counters = reinterpret_cast<unsigned*>(ws + L.fbcnt);
+        fp.out_scores = d_scores;
+        fp.out_rows = d_rows;
+        fp.out_nvalid = d_n_valid;
+        fp.out_keys = d_keys;
+        fp.n_rows = ix->n_rows;
+        fp.cand_lists = int64_t(kWsCandBytes) / (int64_t(k) * 8);
+        fp.row_offset = static_cast<uint32_t>(ix->row_offset);
+        fp.dim = ix->dim;
+        fp.k = k;
+        fp.metric = metric;
+        if (ex) fp.ex = *ex;
+        typedef void (*FbFn)(const FbParams);
+        const FbFn fb = k <= 32 ? static_cast<FbFn>(k1_fallback_kernel<4, 1>) : static_cast<FbFn>(k1_fallback_kernel<4, 4>);
+        int fb_occ = 0;
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&fb_occ, fb, kK1Threads, dyn) != cudaSuccess || fb_occ < 1) fb_occ = 1;
+        fb<<<static_cast<unsigned>(fb_occ * ix->sm_count), kK1Threads, dyn, stream>>>(fp);
+        CRB_LAUNCH_CHECK();
     }
     (void)batch;
     return 0;
@@ -692,8 +714,8 @@ static int search_impl(crb_index* ix, const float* d_queries, int batch, int k, 
 
         // A filtered row set is worth the tensor-core kernel (which scans the whole shard under a
         // pass-bit mask) only if that beats gathering the survivors once per nq_cap queries.  The
-        // survivor counts are on the device: read them back (one small synchronising copy; the
-        // K2 path synchronises for its proof flags anyway).
+        // survivor counts are on the device: read them back (one small synchronising copy -- the only
+        // point where a search waits for its stream, and only for filtered tensor-core row sets).
         uint32_t h_counts[kMaxFilters] = {0};
         if (any_k2_filtered) {
             CRB_CUDA(cudaMemcpyAsync(h_counts, ws + kWsCountsOffset, sizeof h_counts, cudaMemcpyDeviceToHost, stream));
@@ -712,26 +734,24 @@ static int search_impl(crb_index* ix, const float* d_queries, int batch, int k, 
             }
         }
 
-        // tensor-core row sets first; what K5 cannot prove joins the streaming groups
+        // tensor-core row sets first (what K5 cannot prove is re-run on the device, inside launch_k2)
         std::map<int, std::vector<int>> k1_sets;
         for (auto& kv : by_filter) {
             if (!use_k2[kv.first]) { k1_sets[kv.first] = kv.second; continue; }
             const uint32_t* mask = kv.first < 0 ? nullptr : masks + size_t(slot_of_filter[kv.first]) * size_t(mstride);
-            std::vector<int> unproven;
             int rc;
             if (kv.first < 0) {
                 rc = launch_k2(ix, d_queries, batch, k, metric, kv.second, mask, ws, L, d_scores, d_rows, d_n_valid,
-                               d_keys, &unproven, stream, nullptr, nullptr, -1, nullptr, 0, ex);
+                               d_keys, stream, nullptr, nullptr, -1, nullptr, 0, ex);
             } else {
                 const int slot_f = slot_of_filter[kv.first];
                 rc = launch_k2(ix, d_queries, batch, k, metric, kv.second, mask, ws, L, d_scores, d_rows, d_n_valid,
-                               d_keys, &unproven, stream, lists + size_t(slot_f) * size_t(stride),
+                               d_keys, stream, lists + size_t(slot_f) * size_t(stride),
                                reinterpret_cast<const uint32_t*>(ws + kWsCountsOffset) + slot_f,
                                static_cast<int64_t>(std::min<uint64_t>(h_counts[slot_f], uint64_t(ix->n_rows))),
                                compact_buf, compact_cap, ex);
             }
             if (rc) return rc;
-            if (!unproven.empty()) k1_sets[kv.first] = unproven;
         }
 
         std::vector<QueryGroup> groups;

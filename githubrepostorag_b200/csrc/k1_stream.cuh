@@ -443,4 +443,151 @@ k1_stream_generic_kernel(const __grid_constant__ K1Params p) {
     if (threadIdx.x == 0) p.counters[blockIdx.y] = 0u;
 }
 
+// ---------------------------------------------------------------------------------------------
+// Device-side fallback for tensor-core batches: K5 appends the queries it could not prove exact to
+// `flagged`; this kernel, launched unconditionally right behind K5, re-runs exactly those through
+// the streaming scan -- no host round trip, so the tensor-core path stays asynchronous on its stream.
+// The grid is fixed (about one wave of the machine); the CTAs split themselves over however many
+// queries were flagged: cpq = CTAs per query (all of them for one query, one each for many), query
+// f is served by CTA columns f, f + n_cols, ...  Zero flagged queries: every CTA reads one word and exits.
+// Same canonical summation order as every other scoring kernel, so the result is bit-identical to K1's.
+struct FbParams {
+    const __half* rows;
+    const float* inv_norm;
+    const float* queries;        // [batch, dim] fp32
+    const int32_t* q_map;        // chunk slot -> query index in the caller's batch (nullptr = identity)
+    const int32_t* flagged;      // [n_flagged] chunk slots
+    const int32_t* n_flagged;
+    const uint32_t* list;        // survivors of the set's filter (nullptr = whole shard)
+    const uint32_t* list_count;
+    uint64_t* cand;              // [flagged query][cpq][k] scratch
+    unsigned* counters;          // [chunk] arrival counters, zero before the launch
+    float* out_scores;
+    int64_t* out_rows;
+    int32_t* out_nvalid;
+    uint64_t* out_keys;
+    int64_t n_rows;
+    int64_t cand_lists;          // lists of k keys that fit in `cand`
+    uint32_t row_offset;
+    int32_t dim;
+    int32_t k;
+    int32_t metric;
+    ExchangeDev ex;
+};
+
+__device__ __noinline__ void fb_merge_query(const FbParams& p, int qi, const uint64_t* lists, int n_lists,
+                                            const float* s_q, uint64_t (*xchg)[32], float* s_invq) {
+    const int lane = threadIdx.x & 31;
+    const int warp = threadIdx.x >> 5;
+    if (warp == 0) {
+        const float iq = (p.metric == 0) ? warp_inv_qnorm(s_q, p.dim, lane) : 1.0f;
+        if (lane == 0) *s_invq = iq;
+    }
+    __syncthreads();
+    TopKSink sink;
+    sink.scores = p.out_scores + static_cast<int64_t>(qi) * p.k;
+    sink.rows = p.out_rows + static_cast<int64_t>(qi) * p.k;
+    sink.n_valid = p.out_nvalid + qi;
+    sink.keys = p.out_keys ? p.out_keys + static_cast<int64_t>(qi) * p.k : nullptr;
+    sink.scale = *s_invq;
+    sink.ex = p.ex.world > 0 ? &p.ex : nullptr;
+    sink.qi = qi;
+    sink.k = p.k;
+    block_merge_sorted_lists<kK1MergeLPT>(lists, n_lists, p.k, p.k, sink, xchg, lane, warp, kK1Warps);
+}
+
+template <int R, int KPL>
+__global__ void __launch_bounds__(kK1Threads)
+k1_fallback_kernel(const __grid_constant__ FbParams p) {
+    extern __shared__ float s_q[];  // [dim]
+    __shared__ uint64_t xchg[2][32];
+    __shared__ float s_invq;
+    __shared__ int s_last;
+
+    const int nf = *p.n_flagged;
+    if (nf <= 0) return;
+    const int lane = threadIdx.x & 31;
+    const int warp = threadIdx.x >> 5;
+    const int chunks = p.dim >> 3;
+    const bool cosine = (p.metric == 0);
+
+    // CTAs per query: the whole grid for one query, never more lists than the scratch or the merge hold
+    int64_t cpq = static_cast<int64_t>(gridDim.x) / nf;
+    const int64_t fit = p.cand_lists / nf;
+    if (cpq > fit) cpq = fit;
+    if (cpq > kK1MaxGridX) cpq = kK1MaxGridX;
+    if (cpq < 1) cpq = 1;
+    const int n_cols = static_cast<int>(gridDim.x / cpq);
+    const int col = static_cast<int>(blockIdx.x / cpq);
+    const int x = static_cast<int>(blockIdx.x % cpq);
+    if (col >= n_cols) return;
+
+    int64_t n_items = p.n_rows;
+    if (p.list) {
+        const int64_t cnt = static_cast<int64_t>(*p.list_count);
+        n_items = cnt < p.n_rows ? cnt : p.n_rows;
+    }
+    const int64_t stride = cpq * kK1Warps * R;
+
+    for (int f = col; f < nf; f += n_cols) {
+        const int slot_q = p.flagged[f];
+        const int qi = p.q_map ? p.q_map[slot_q] : slot_q;
+        __syncthreads();   // the previous query's merge is done with s_q
+        for (int i = threadIdx.x; i < p.dim; i += kK1Threads)
+            s_q[i] = p.queries[static_cast<int64_t>(qi) * p.dim + i];
+        __syncthreads();
+
+        WarpTopK<KPL> top;
+        top.init(p.k, lane);
+        for (int64_t item0 = (static_cast<int64_t>(x) * kK1Warps + warp) * R; item0 < n_items; item0 += stride) {
+            int64_t row[R];
+            bool ok[R];
+            float acc[R];
+#pragma unroll
+            for (int j = 0; j < R; ++j) {
+                ok[j] = (item0 + j) < n_items;
+                row[j] = ok[j] ? (p.list ? static_cast<int64_t>(p.list[item0 + j]) : item0 + j) : 0;
+                acc[j] = 0.f;
+            }
+            for (int ch = lane; ch < chunks; ch += 32) {
+                uint4 v[R];
+#pragma unroll
+                for (int j = 0; j < R; ++j) v[j] = ld_stream_16(p.rows + row[j] * p.dim + ch * 8);
+                float q8[8];
+                const float4 a = *reinterpret_cast<const float4*>(s_q + ch * 8);
+                const float4 b = *reinterpret_cast<const float4*>(s_q + ch * 8 + 4);
+                q8[0] = a.x; q8[1] = a.y; q8[2] = a.z; q8[3] = a.w;
+                q8[4] = b.x; q8[5] = b.y; q8[6] = b.z; q8[7] = b.w;
+#pragma unroll
+                for (int j = 0; j < R; ++j) acc[j] = chunk_fma(v[j], q8, acc[j]);
+            }
+#pragma unroll
+            for (int j = 0; j < R; ++j) {
+                const float invn = cosine ? __ldg(p.inv_norm + row[j]) : 1.0f;
+                const float s = warp_butterfly_sum(acc[j]) * invn;
+                if (ok[j] && !(cosine && invn == 0.f) && s == s) {
+                    const uint64_t key = make_key(s, p.row_offset + static_cast<uint32_t>(row[j]));
+                    if (key > top.thr) top.insert(key, lane);
+                }
+            }
+        }
+
+        uint64_t* lists = p.cand + static_cast<int64_t>(f) * cpq * p.k;
+        block_extract_topk<KPL>(top, p.k, lists + static_cast<int64_t>(x) * p.k, xchg, lane, warp, kK1Warps);
+
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            __threadfence();
+            const unsigned t = atomicAdd(&p.counters[f], 1u);
+            s_last = (t == static_cast<unsigned>(cpq) - 1u) ? 1 : 0;
+        }
+        __syncthreads();
+        if (s_last) {
+            __threadfence();
+            fb_merge_query(p, qi, lists, static_cast<int>(cpq), s_q, xchg, &s_invq);
+        }
+    }
+}
+
+
 }  // namespace crb

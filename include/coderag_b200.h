@@ -97,7 +97,9 @@ int crb_row_inv_norms(const void *d_rows_f16, float *d_inv_norm, int64_t n_rows,
  * non-trivial filters. */
 size_t crb_workspace_bytes(const crb_index *index, int32_t batch, int32_t k, int32_t n_filters);
 
-/* Top-k search, queries and results resident on the device; asynchronous on `stream`.
+/* Top-k search, queries and results resident on the device; asynchronous on `stream` (one
+ * exception: a FILTERED row set that qualifies for the tensor-core kernel reads its survivor
+ * count back once, a small synchronising copy, to pick its plan).
  *   d_queries  fp32 [batch, dim]
  *   h_filt     int32 [batch, n_keys] on the HOST (NULL = no filter): AND of equalities, one
  *              code per key (CRB_FILT_ANY / CRB_FILT_IMPOSSIBLE as above).  Rows with the same

@@ -94,6 +94,38 @@ def test_k2_unprovable_queries_fall_back_to_streaming(torch_cuda):
     sh.close()
 
 
+def test_k2_device_side_fallback_many_queries_filters_and_large_k(torch_cuda):
+    """A corpus of duplicated rows leaves MOST queries unprovable; the device-side fallback must serve
+    one, a few and hundreds of flagged queries, under a filter (non-identity query map, survivor list)
+    and at both k widths -- bit-identical to the streaming kernel every time."""
+    torch = torch_cuda
+    n, d = 60_000, 256
+    rng = np.random.default_rng(23)
+    base = rng.standard_normal((200, d), dtype=np.float32).astype(np.float16)
+    rows16 = base[rng.integers(0, 200, size=n)]            # every row has ~300 bit-identical twins
+    rows16[:5000] = rng.standard_normal((5000, d), dtype=np.float32).astype(np.float16)
+    code_mat = np.stack([np.arange(n, dtype=np.int32) % 3] + [np.zeros(n, np.int32)] * 3)
+    sh = _shard(torch, rows16, code_mat)
+    for batch, k in ((1, 10), (7, 10), (300, 10), (40, 100)):
+        q = base[rng.integers(0, 200, size=batch)].astype(np.float32) + 0.01 * rng.standard_normal((batch, d), dtype=np.float32)
+        filt = np.full((batch, 4), -1, np.int32)
+        filt[batch // 3:, 0] = 1                           # the later two thirds share one filter
+        for f in (None, filt):
+            (s1, r1, v1), (s2, r2, v2) = _both(sh, torch, q, k, oracle.MODE_COSINE, filt=f)
+            assert torch.equal(r1, r2), f"rows differ B={batch} k={k} filtered={f is not None}"
+            assert torch.equal(v1, v2) and torch.equal(s1.view(torch.int32), s2.view(torch.int32))
+    # keys output of the fallback feeds the cross-shard merge
+    q = base[:9].astype(np.float32)
+    qd = torch.from_numpy(q).cuda()
+    keys = torch.empty((9, 10), dtype=torch.int64, device="cuda")
+    s2, r2, v2 = [t.clone() for t in sh.search_device(qd, 10, keys_out=keys, algo=2)]
+    keys1 = torch.empty_like(keys)
+    sh.search_device(qd, 10, keys_out=keys1, algo=1)
+    torch.cuda.synchronize()
+    assert torch.equal(keys, keys1)
+    sh.close()
+
+
 def test_k2_sharded_equals_unsharded(torch_cuda):
     torch = torch_cuda
     from githubrepostorag_b200.index import merge_keys
