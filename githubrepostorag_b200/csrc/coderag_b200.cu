@@ -98,6 +98,8 @@ static inline int k2_kprime(int k) {
     return std::min<int>(kK2MaxKPrime, static_cast<int>(round_up(k + k / 2, 8)));
 }
 static inline bool k2_supports_k(int k) { return k2_kprime(k) >= k + 2; }
+// classes of the shared admission threshold: a power of two >= k (see k2_gemm.cuh)
+static inline int k2_gthr_groups(int k) { int g = 16; while (g < k + k / 4 + 1 && g < 128) g *= 2; return g; }
 
 struct Lane {
     cudaStream_t stream = nullptr;
@@ -144,7 +146,7 @@ static int64_t mask_stride_of(const crb_index* ix) { return round_up((std::max<i
 struct WsLayout {
     size_t cand = kWsHeaderBytes;
     size_t k2 = 0;          // K2 region start
-    size_t q16 = 0, invq = 0, eps = 0, qmap = 0, flagged = 0, nflag = 0, fbcnt = 0, cand2 = 0;   // inside the K2 region
+    size_t q16 = 0, invq = 0, eps = 0, qmap = 0, flagged = 0, nflag = 0, fbcnt = 0, gthr = 0, cand2 = 0;   // inside the K2 region
     size_t filt = 0;        // survivor lists start; masks follow the lists
     size_t per_filter = 0;  // bytes one more filter costs
 };
@@ -160,6 +162,7 @@ static WsLayout ws_layout(const crb_index* ix, int batch, int k) {
     L.flagged = o; o += round_up(nmax * 4, 256);
     L.nflag = o;   o += 256;
     L.fbcnt = o;   o += round_up(nmax * 4, 256);   // fallback arrival counters, cleared with nflag
+    L.gthr = o;    o += round_up(nmax * size_t(k2_gthr_groups(k)) * 4, 256);   // K2's shared threshold classes, cleared with nflag
     // per query: one k'-list per CTA (pair) that served its query tile -- at most sm_count lists when the
     // batch is one tile, sm_count/2 when CTA pairs serve every query tile of the batch (m-inner)
     L.cand2 = o;   o += round_up(std::max<size_t>(std::min<size_t>(nmax, kK2BlockM) * ix->sm_count,
@@ -421,10 +424,18 @@ static int launch_k2(crb_index* ix, const float* d_queries, int batch, int k, in
         k2_prep_queries_kernel<<<n, 128, 0, stream>>>(d_queries, d_qmap, n, ix->dim, q16, invq, eps);
         CRB_LAUNCH_CHECK();
 
+        // one clear for the flag count, the fallback's arrival counters and the shared thresholds
+        const int groups = k2_gthr_groups(k);
+        CRB_CUDA(cudaMemsetAsync(nflag, 0, (L.gthr - L.nflag) + size_t(n) * groups * 4, stream));
+
         CUtensorMap map_q;
         if (int rc = make_map_f16(&map_q, q16, n, ix->dim, kK2BlockM)) return rc;
         K2Params kp;
         memset(&kp, 0, sizeof kp);
+        kp.gthr = env_int("CODERAG_B200_K2_GTHR", 1) ? reinterpret_cast<uint32_t*>(ws + L.gthr) : nullptr;
+        kp.gthr_groups = groups;
+        kp.gthr_every = std::max(1, env_int("CODERAG_B200_K2_GTHR_EVERY", groups / 16));   // ~4 vector loads per tile
+        kp.gthr_prepass = env_int("CODERAG_B200_K2_PREPASS", 1);
         kp.inv_norm = k2_inv;
         kp.mask = mask;
         kp.cand = cand2;
@@ -476,10 +487,20 @@ static int launch_k2(crb_index* ix, const float* d_queries, int batch, int k, in
                 at.id = cudaLaunchAttributeClusterDimension;
                 at.val.clusterDim.x = 4; at.val.clusterDim.y = 1; at.val.clusterDim.z = 1;
                 cfg.attrs = &at; cfg.numAttrs = 1;
-                int max_clusters = 0;
-                if (cudaOccupancyMaxActiveClusters(&max_clusters, k2_gemm_topk_quad_kernel, &cfg) == cudaSuccess)
-                    quad_clusters = max_clusters;
-                (void)cudaGetLastError();
+                // the answer depends on the device and the shared-memory size only: ask once
+                static std::mutex occ_mu;
+                static std::map<std::pair<int, size_t>, int> occ_cache;
+                std::lock_guard<std::mutex> lk(occ_mu);
+                auto okey = std::make_pair(ix->device, smem);
+                auto oit = occ_cache.find(okey);
+                if (oit == occ_cache.end()) {
+                    int max_clusters = 0;
+                    if (cudaOccupancyMaxActiveClusters(&max_clusters, k2_gemm_topk_quad_kernel, &cfg) != cudaSuccess)
+                        max_clusters = 0;
+                    (void)cudaGetLastError();
+                    oit = occ_cache.emplace(okey, max_clusters).first;
+                }
+                quad_clusters = oit->second;
             }
             // Co-run: 4-CTA clusters fit only part of the machine (132 of 148 SMs on B200: GPCs whose SM count
             // is not a multiple of 4 strand a TPC each).  Give the clusters their share of the corpus tiles and
@@ -538,7 +559,6 @@ static int launch_k2(crb_index* ix, const float* d_queries, int batch, int k, in
         }
         CRB_LAUNCH_CHECK();
 
-        CRB_CUDA(cudaMemsetAsync(nflag, 0, (L.fbcnt - L.nflag) + size_t(n) * 4, stream));
         K5Params rp;
         memset(&rp, 0, sizeof rp);
         rp.rows = ix->rows;
@@ -553,6 +573,8 @@ static int launch_k2(crb_index* ix, const float* d_queries, int batch, int k, in
         rp.out_rows = d_rows;
         rp.out_nvalid = d_n_valid;
         rp.out_keys = d_keys;
+        rp.gthr = kp.gthr;
+        rp.gthr_groups = groups;
         rp.flagged = flagged;
         rp.n_flagged = nflag;
         rp.max_norm = ix->max_norm;
@@ -594,8 +616,20 @@ static int launch_k2(crb_index* ix, const float* d_queries, int batch, int k, in
         if (ex) fp.ex = *ex;
         typedef void (*FbFn)(const FbParams);
         const FbFn fb = k <= 32 ? static_cast<FbFn>(k1_fallback_kernel<4, 1>) : static_cast<FbFn>(k1_fallback_kernel<4, 4>);
+        static std::mutex fb_mu;
+        static std::map<std::pair<const void*, size_t>, int> fb_cache;
         int fb_occ = 0;
-        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&fb_occ, fb, kK1Threads, dyn) != cudaSuccess || fb_occ < 1) fb_occ = 1;
+        {
+            std::lock_guard<std::mutex> lk(fb_mu);
+            auto fkey = std::make_pair(reinterpret_cast<const void*>(fb), dyn);
+            auto fit = fb_cache.find(fkey);
+            if (fit == fb_cache.end()) {
+                int occ = 0;
+                if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, fb, kK1Threads, dyn) != cudaSuccess || occ < 1) occ = 1;
+                fit = fb_cache.emplace(fkey, occ).first;
+            }
+            fb_occ = fit->second;
+        }
         fb<<<static_cast<unsigned>(fb_occ * ix->sm_count), kK1Threads, dyn, stream>>>(fp);
         CRB_LAUNCH_CHECK();
     }

@@ -39,6 +39,10 @@ struct K2Params {
     const float* inv_norm;      // [n_rows]
     const uint32_t* mask;       // [ceil(n_rows/32)] pass bits or nullptr
     uint64_t* cand;             // [batch, slots, kprime] approximate keys (local row in low 32 bits)
+    uint32_t* gthr;             // [batch, gthr_groups] shared threshold classes per query (ord(score), 0 = none yet) or nullptr
+    int32_t gthr_groups;        // power of two in [16, 128], >= k
+    int32_t gthr_every;         // a list re-reads its query's classes every this many corpus tiles
+    int32_t gthr_prepass;       // read the first accumulator tile of a list twice (see k2_first_visit)
     int64_t n_rows;
     int32_t batch;
     int32_t dim;
@@ -196,7 +200,7 @@ CRB_DEVINL float k2_pick(const float (&s)[32], int j) {
 // Admissions run in warp-lockstep rounds (every lane that still has a pending column inserts one
 // per round), so the heap updates of different lanes overlap instead of serialising.
 CRB_DEVINL float k2_scan_chunk(const uint32_t (&v)[32], uint32_t inv_saddr, float thr, uint32_t& state,
-                               uint64_t* my_list, int64_t n_first, int kprime, int ls) {
+                               uint64_t* my_list, int64_t n_first, int kprime, int ls, float& item_best) {
     float s[32];
 #pragma unroll
     for (int g = 0; g < 8; ++g) {
@@ -210,6 +214,7 @@ CRB_DEVINL float k2_scan_chunk(const uint32_t (&v)[32], uint32_t inv_saddr, floa
     float best = s[0];
 #pragma unroll
     for (int j = 1; j < 32; ++j) best = fmaxf(best, s[j]);
+    item_best = fmaxf(item_best, best);
     if (__any_sync(CRB_FULL_MASK, best > thr)) {
         uint32_t hit = 0u;
 #pragma unroll
@@ -221,13 +226,68 @@ CRB_DEVINL float k2_scan_chunk(const uint32_t (&v)[32], uint32_t inv_saddr, floa
                 const float sj = k2_pick(s, j);
                 if (sj > thr) {     // the threshold may have risen since the mask was built
                     const uint2 r = k2_list_insert(my_list, make_key(sj, static_cast<uint32_t>(n_first + j)), state, thr, kprime, ls);
-                    thr = __uint_as_float(r.x);
+                    thr = fmaxf(__uint_as_float(r.x), thr);   // never below the shared threshold folded in earlier
                     state = r.y;
                 }
             }
         }
     }
     return thr;
+}
+
+// Shared admission threshold.  Every CTA (pair) that serves a query keeps its own k'-list, so on its own
+// each list would admit ~k'(1 + ln(rows seen / k')) columns, and every admission costs its whole warp a
+// round -- at B = 1024 that was a quarter of the kernel on a 1.25M-row shard.  The lists of one query
+// therefore share a lower bound of the query's k-th best score: corpus tile t belongs to class t mod G
+// (G >= k classes), each thread raises its tile's class to the tile's best score with a fire-and-forget
+// atomic max, and the bound is the MINIMUM over the classes -- G distinct rows (one per class, tiles are
+// disjoint) score at least that much, so the k-th best does too.  A thread re-reads the G words of its
+// query when it starts a tile (the loads fly during the wait for the accumulator) and drops every column
+// at or below the bound without touching its list.  K5 folds the final bound into tau_max, so the proof
+// of exactness covers these drops exactly like the drops of a full list.
+CRB_DEVINL float k2_gthr_float(uint32_t o) { return o ? ord_to_f32(o) : __uint_as_float(0xff800000u); }
+CRB_DEVINL uint32_t k2_gthr_min(const uint32_t* g, int groups) {
+    uint32_t m = 0xffffffffu;
+    for (int i = 0; i < groups; i += 4) {
+        uint32_t a, b, c, d;
+        asm volatile("ld.global.cg.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(a), "=r"(b), "=r"(c), "=r"(d) : "l"(g + i));
+        m = min(min(m, a), min(b, min(c, d)));
+    }
+    return m;
+}
+CRB_DEVINL void k2_gthr_publish(uint32_t* g, int groups, int64_t tile, float item_best) {
+    atomicMax(g + (tile & (groups - 1)), f32_to_ord(item_best));
+}
+
+// First visit of a list: every CTA starts with an empty list and no bound, and filling a list from
+// arbitrary columns costs ~k'(1 + ln(256/k')) admissions per thread that are almost all evicted later.
+// So the first accumulator tile is read twice: a max-only pass publishes the tile's best score, a short
+// bounded poll lets the other CTAs' first tiles land (they start together; slots >= classes fills every
+// class), and the normal pass then runs under a bound that only a handful of columns clear.
+CRB_DEVINL float k2_first_visit(uint32_t t_row, uint32_t inv_s, int n_chunks, bool g_live, uint32_t* my_g, int groups,
+                                int64_t tile, float thr) {
+    float pb = __uint_as_float(0xff800000u);
+    uint32_t v[32];
+#pragma unroll 1
+    for (int c = 0; c < n_chunks; ++c) {
+        tmem_ld32(t_row + c * 32, v);
+        tmem_ld_wait();
+#pragma unroll
+        for (int g = 0; g < 8; ++g) {
+            const float4 w = lds_f4(inv_s + c * 128 + g * 16);
+            pb = fmaxf(pb, fmaxf(fmaxf(__uint_as_float(v[4 * g + 0]) * w.x, __uint_as_float(v[4 * g + 1]) * w.y),
+                                 fmaxf(__uint_as_float(v[4 * g + 2]) * w.z, __uint_as_float(v[4 * g + 3]) * w.w)));
+        }
+    }
+    if (g_live && pb > __uint_as_float(0xff800000u)) k2_gthr_publish(my_g, groups, tile, pb);
+    uint32_t gm = 0u;
+#pragma unroll 1
+    for (int tries = 0; tries < 8; ++tries) {
+        gm = g_live ? k2_gthr_min(my_g, groups) : 1u;
+        if (__all_sync(CRB_FULL_MASK, gm != 0u)) break;
+        __nanosleep(256);
+    }
+    return g_live ? fmaxf(thr, k2_gthr_float(gm)) : thr;
 }
 
 // ---- query preparation -------------------------------------------------------------------------
@@ -403,9 +463,14 @@ k2_gemm_topk_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_cons
                 pre[0] = column_scale(nn + tid_e);
                 pre[1] = column_scale(nn + tid_e + 128);
             }
+            uint32_t* my_g = p.gthr + static_cast<int64_t>(m_tile * kK2BlockM + row) * p.gthr_groups;
+            const bool g_live = p.gthr && q_valid;
+            const uint32_t g_ord = (g_live && (it % p.gthr_every) == 0) ? k2_gthr_min(my_g, p.gthr_groups) : 0u;
             epi_bar_sync();
             mbar_wait(&tfull_bar[buf], use & 1u);
             tc_fence_after();
+            thr = fmaxf(thr, k2_gthr_float(g_ord));
+            float item_best = __uint_as_float(0xff800000u);
             const uint32_t t_row = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) +
                                    static_cast<uint32_t>(buf * kK2BlockN);
             // TMEM -> registers one 32-column chunk ahead of the chunk being examined.  The common
@@ -413,6 +478,9 @@ k2_gemm_topk_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_cons
             // ONE branch; only a chunk that holds a new candidate walks its 32 columns.
             const uint32_t inv_s = smem_u32(inv);
             const int n_chunks = (p.debug & 2) ? 0 : kK2BlockN / 32;
+            if (p.gthr && p.gthr_prepass && it == 0)
+                thr = k2_first_visit(t_row, inv_s, n_chunks, g_live, my_g, p.gthr_groups, t, thr);
+            const float thr0 = thr;
             uint32_t va[32], vb[32];
             if (n_chunks > 0) {
                 tmem_ld32(t_row, va);
@@ -421,14 +489,15 @@ k2_gemm_topk_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_cons
 #pragma unroll 1
             for (int c = 0; c < n_chunks; c += 2) {
                 tmem_ld32(t_row + (c + 1) * 32, vb);
-                thr = k2_scan_chunk(va, inv_s + c * 128, thr, state, my_list, n0 + c * 32, p.kprime, p.lstride);
+                thr = k2_scan_chunk(va, inv_s + c * 128, thr, state, my_list, n0 + c * 32, p.kprime, p.lstride, item_best);
                 tmem_ld_wait();
                 if (c + 2 < n_chunks) tmem_ld32(t_row + (c + 2) * 32, va);
-                thr = k2_scan_chunk(vb, inv_s + (c + 1) * 128, thr, state, my_list, n0 + (c + 1) * 32, p.kprime, p.lstride);
+                thr = k2_scan_chunk(vb, inv_s + (c + 1) * 128, thr, state, my_list, n0 + (c + 1) * 32, p.kprime, p.lstride, item_best);
                 tmem_ld_wait();
             }
             tc_fence_before();
             mbar_arrive(&tempty_bar[buf]);
+            if (g_live && item_best > thr0) k2_gthr_publish(my_g, p.gthr_groups, t, item_best);
         }
         // flush this CTA's list for the query
         if (q_valid) {
@@ -658,13 +727,22 @@ k2_gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap map_q, const __grid
                 uint64_t* my_list = lists + static_cast<size_t>(j) * list_elems + row;
                 float thr = s_thr[j * 128 + row];
                 uint32_t state = s_state[j * 128 + row];
+                const int qrow_g = m_row0(j) + row;
+                const bool g_live = p.gthr && qrow_g < p.batch && row < p.lstride;
+                uint32_t* my_g = p.gthr + static_cast<int64_t>(qrow_g) * p.gthr_groups;
+                const uint32_t g_ord = (g_live && ((it / MI) % p.gthr_every) == 0) ? k2_gthr_min(my_g, p.gthr_groups) : 0u;
                 epi_bar_sync();
                 mbar_wait(&tfull_bar[buf], use & 1u);
                 tc_fence_after();
+                thr = fmaxf(thr, k2_gthr_float(g_ord));
+                float item_best = __uint_as_float(0xff800000u);
                 const uint32_t t_row = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) +
                                        static_cast<uint32_t>(buf * kK2BlockN);
                 const uint32_t inv_s = smem_u32(inv);
                 const int n_chunks = (p.debug & 2) ? 0 : kK2BlockN / 32;
+                if (p.gthr && p.gthr_prepass && it < MI)
+                    thr = k2_first_visit(t_row, inv_s, n_chunks, g_live, my_g, p.gthr_groups, t, thr);
+                const float thr0 = thr;
                 uint32_t va[32], vb[32];
                 if (n_chunks > 0) {
                     tmem_ld32(t_row, va);
@@ -673,16 +751,17 @@ k2_gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap map_q, const __grid
 #pragma unroll 1
                 for (int c = 0; c < n_chunks; c += 2) {
                     tmem_ld32(t_row + (c + 1) * 32, vb);
-                    thr = k2_scan_chunk(va, inv_s + c * 128, thr, state, my_list, n0 + c * 32, p.kprime, p.lstride);
+                    thr = k2_scan_chunk(va, inv_s + c * 128, thr, state, my_list, n0 + c * 32, p.kprime, p.lstride, item_best);
                     tmem_ld_wait();
                     if (c + 2 < n_chunks) tmem_ld32(t_row + (c + 2) * 32, va);
-                    thr = k2_scan_chunk(vb, inv_s + (c + 1) * 128, thr, state, my_list, n0 + (c + 1) * 32, p.kprime, p.lstride);
+                    thr = k2_scan_chunk(vb, inv_s + (c + 1) * 128, thr, state, my_list, n0 + (c + 1) * 32, p.kprime, p.lstride, item_best);
                     tmem_ld_wait();
                 }
                 tc_fence_before();
                 mbar_arrive_cluster(mapa_u32(smem_u32(&tempty_bar[buf]), 0));
                 s_thr[j * 128 + row] = thr;
                 s_state[j * 128 + row] = state;
+                if (g_live && item_best > thr0) k2_gthr_publish(my_g, p.gthr_groups, t, item_best);
             }
         }
         for (int j = 0; j < MI; ++j) {
@@ -880,13 +959,22 @@ k2_gemm_topk_quad_kernel(const __grid_constant__ CUtensorMap map_q64, const __gr
                 uint64_t* my_list = lists + static_cast<size_t>(j) * list_elems + row;
                 float thr = s_thr[j * 128 + row];
                 uint32_t state = s_state[j * 128 + row];
+                const int qrow_g = m_row0(j) + row;
+                const bool g_live = p.gthr && qrow_g < p.batch && row < p.lstride;
+                uint32_t* my_g = p.gthr + static_cast<int64_t>(qrow_g) * p.gthr_groups;
+                const uint32_t g_ord = (g_live && ((it / MI) % p.gthr_every) == 0) ? k2_gthr_min(my_g, p.gthr_groups) : 0u;
                 epi_bar_sync();
                 mbar_wait(&tfull_bar[buf], use & 1u);
                 tc_fence_after();
+                thr = fmaxf(thr, k2_gthr_float(g_ord));
+                float item_best = __uint_as_float(0xff800000u);
                 const uint32_t t_row = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) +
                                        static_cast<uint32_t>(buf * kK2BlockN);
                 const uint32_t inv_s = smem_u32(inv);
                 const int n_chunks = (p.debug & 2) ? 0 : kK2BlockN / 32;
+                if (p.gthr && p.gthr_prepass && it < MI)
+                    thr = k2_first_visit(t_row, inv_s, n_chunks, g_live, my_g, p.gthr_groups, t, thr);
+                const float thr0 = thr;
                 uint32_t va[32], vb[32];
                 if (n_chunks > 0) {
                     tmem_ld32(t_row, va);
@@ -895,16 +983,17 @@ k2_gemm_topk_quad_kernel(const __grid_constant__ CUtensorMap map_q64, const __gr
 #pragma unroll 1
                 for (int c = 0; c < n_chunks; c += 2) {
                     tmem_ld32(t_row + (c + 1) * 32, vb);
-                    thr = k2_scan_chunk(va, inv_s + c * 128, thr, state, my_list, n0 + c * 32, p.kprime, p.lstride);
+                    thr = k2_scan_chunk(va, inv_s + c * 128, thr, state, my_list, n0 + c * 32, p.kprime, p.lstride, item_best);
                     tmem_ld_wait();
                     if (c + 2 < n_chunks) tmem_ld32(t_row + (c + 2) * 32, va);
-                    thr = k2_scan_chunk(vb, inv_s + (c + 1) * 128, thr, state, my_list, n0 + (c + 1) * 32, p.kprime, p.lstride);
+                    thr = k2_scan_chunk(vb, inv_s + (c + 1) * 128, thr, state, my_list, n0 + (c + 1) * 32, p.kprime, p.lstride, item_best);
                     tmem_ld_wait();
                 }
                 tc_fence_before();
                 mbar_arrive_cluster(mapa_u32(smem_u32(&tempty_bar[buf]), lead_rank));
                 s_thr[j * 128 + row] = thr;
                 s_state[j * 128 + row] = state;
+                if (g_live && item_best > thr0) k2_gthr_publish(my_g, p.gthr_groups, t, item_best);
             }
         }
         for (int j = 0; j < MI; ++j) {
@@ -940,6 +1029,8 @@ struct K5Params {
     int64_t* out_rows;
     int32_t* out_nvalid;
     uint64_t* out_keys;
+    const uint32_t* gthr;       // [n, gthr_groups] K2's shared threshold classes (nullptr = not used)
+    int32_t gthr_groups;
     int32_t* flagged;           // [n] slots whose result is not proven
     int32_t* n_flagged;
     float max_norm;             // largest row norm (inner-product margin)
@@ -1039,6 +1130,8 @@ __global__ void __launch_bounds__(256) k5_rescore_kernel(const __grid_constant__
     if (threadIdx.x == 0) {
         float tau_max = s_tau[0];
         for (int w = 1; w < 8; ++w) tau_max = fmaxf(tau_max, s_tau[w]);
+        // columns K2 dropped against the shared bound scored at most its final value
+        if (p.gthr) tau_max = fmaxf(tau_max, k2_gthr_float(k2_gthr_min(p.gthr + static_cast<int64_t>(slot_q) * p.gthr_groups, p.gthr_groups)));
         const float iq = p.invq[slot_q];
         TopKSink sink;
         sink.scores = p.out_scores + static_cast<int64_t>(qi) * p.k;
