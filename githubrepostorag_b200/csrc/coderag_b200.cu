@@ -434,7 +434,7 @@ static int launch_k2(crb_index* ix, const float* d_queries, int batch, int k, in
         memset(&kp, 0, sizeof kp);
         kp.gthr = env_int("CODERAG_B200_K2_GTHR", 1) ? reinterpret_cast<uint32_t*>(ws + L.gthr) : nullptr;
         kp.gthr_groups = groups;
-        kp.gthr_every = std::max(1, env_int("CODERAG_B200_K2_GTHR_EVERY", groups / 16));   // ~4 vector loads per tile
+        kp.gthr_every = std::max(0, env_int("CODERAG_B200_K2_GTHR_EVERY", 0));   // 0 = dense first, then four reads per octave
         kp.gthr_prepass = env_int("CODERAG_B200_K2_PREPASS", 1);
         kp.inv_norm = k2_inv;
         kp.mask = mask;

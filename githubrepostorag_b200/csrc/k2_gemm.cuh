@@ -41,7 +41,7 @@ struct K2Params {
     uint64_t* cand;             // [batch, slots, kprime] approximate keys (local row in low 32 bits)
     uint32_t* gthr;             // [batch, gthr_groups] shared threshold classes per query (ord(score), 0 = none yet) or nullptr
     int32_t gthr_groups;        // power of two in [16, 128], >= k
-    int32_t gthr_every;         // a list re-reads its query's classes every this many corpus tiles
+    int32_t gthr_every;         // a list re-reads its query's classes every this many corpus tiles (0 = k2_gthr_due's schedule)
     int32_t gthr_prepass;       // read the first accumulator tile of a list twice (see k2_first_visit)
     int64_t n_rows;
     int32_t batch;
@@ -255,6 +255,31 @@ CRB_DEVINL uint32_t k2_gthr_min(const uint32_t* g, int groups) {
     }
     return m;
 }
+// The first 16 classes are fetched into registers BEFORE the thread waits for its accumulator and folded
+// after, so the L2 round trip overlaps the wait (exposed, it cost 10 % of an HBM-bound B = 64 search);
+// classes beyond 16 (k > 12) are read in place, every groups/16-th tile only.
+CRB_DEVINL void k2_gthr_issue16(const uint32_t* g, uint32_t (&r)[16]) {
+#pragma unroll
+    for (int i = 0; i < 16; i += 4)
+        asm volatile("ld.global.cg.v4.u32 {%0, %1, %2, %3}, [%4];"
+                     : "=r"(r[i]), "=r"(r[i + 1]), "=r"(r[i + 2]), "=r"(r[i + 3]) : "l"(g + i));
+}
+CRB_DEVINL uint32_t k2_gthr_fold16(const uint32_t (&r)[16]) {
+    uint32_t m = r[0];
+#pragma unroll
+    for (int i = 1; i < 16; ++i) m = min(m, r[i]);
+    return m;
+}
+// When a list re-reads the bound.  The bound moves like an order statistic -- fast over the first tiles,
+// then logarithmically -- so visits are dense at first and then four per octave (8, 10, 12, 14, 16, 20, ...):
+// ~4 log2(tiles) reads instead of one per tile (per-tile reads of lines all CTAs share cost an HBM-bound
+// B = 64 search 10 %, a fixed every-8th cadence cost a B = 1024 search of a 1.25M-row shard 10 %).
+CRB_DEVINL bool k2_gthr_due(int visit, int every) {
+    if (every > 0) return (visit % every) == 0;
+    if (visit < 8) return true;
+    const int hb = 31 - __clz(visit);
+    return (visit & ((1 << (hb - 2)) - 1)) == 0;
+}
 CRB_DEVINL void k2_gthr_publish(uint32_t* g, int groups, int64_t tile, float item_best) {
     atomicMax(g + (tile & (groups - 1)), f32_to_ord(item_best));
 }
@@ -465,10 +490,16 @@ k2_gemm_topk_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_cons
             }
             uint32_t* my_g = p.gthr + static_cast<int64_t>(m_tile * kK2BlockM + row) * p.gthr_groups;
             const bool g_live = p.gthr && q_valid;
-            const uint32_t g_ord = (g_live && (it % p.gthr_every) == 0) ? k2_gthr_min(my_g, p.gthr_groups) : 0u;
+            const bool g_read = g_live && k2_gthr_due(static_cast<int>(it), p.gthr_every);
+            uint32_t gr[16];
+#pragma unroll
+            for (int i = 0; i < 16; ++i) gr[i] = 0u;
+            if (g_read) k2_gthr_issue16(my_g, gr);
             epi_bar_sync();
             mbar_wait(&tfull_bar[buf], use & 1u);
             tc_fence_after();
+            uint32_t g_ord = k2_gthr_fold16(gr);
+            if (g_read && p.gthr_groups > 16) g_ord = min(g_ord, k2_gthr_min(my_g + 16, p.gthr_groups - 16));
             thr = fmaxf(thr, k2_gthr_float(g_ord));
             float item_best = __uint_as_float(0xff800000u);
             const uint32_t t_row = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) +
@@ -730,10 +761,16 @@ k2_gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap map_q, const __grid
                 const int qrow_g = m_row0(j) + row;
                 const bool g_live = p.gthr && qrow_g < p.batch && row < p.lstride;
                 uint32_t* my_g = p.gthr + static_cast<int64_t>(qrow_g) * p.gthr_groups;
-                const uint32_t g_ord = (g_live && ((it / MI) % p.gthr_every) == 0) ? k2_gthr_min(my_g, p.gthr_groups) : 0u;
+                const bool g_read = g_live && k2_gthr_due(static_cast<int>(it / MI), p.gthr_every);
+                uint32_t gr[16];
+#pragma unroll
+                for (int i = 0; i < 16; ++i) gr[i] = 0u;
+                if (g_read) k2_gthr_issue16(my_g, gr);
                 epi_bar_sync();
                 mbar_wait(&tfull_bar[buf], use & 1u);
                 tc_fence_after();
+                uint32_t g_ord = k2_gthr_fold16(gr);
+                if (g_read && p.gthr_groups > 16) g_ord = min(g_ord, k2_gthr_min(my_g + 16, p.gthr_groups - 16));
                 thr = fmaxf(thr, k2_gthr_float(g_ord));
                 float item_best = __uint_as_float(0xff800000u);
                 const uint32_t t_row = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) +
@@ -962,10 +999,16 @@ k2_gemm_topk_quad_kernel(const __grid_constant__ CUtensorMap map_q64, const __gr
                 const int qrow_g = m_row0(j) + row;
                 const bool g_live = p.gthr && qrow_g < p.batch && row < p.lstride;
                 uint32_t* my_g = p.gthr + static_cast<int64_t>(qrow_g) * p.gthr_groups;
-                const uint32_t g_ord = (g_live && ((it / MI) % p.gthr_every) == 0) ? k2_gthr_min(my_g, p.gthr_groups) : 0u;
+                const bool g_read = g_live && k2_gthr_due(static_cast<int>(it / MI), p.gthr_every);
+                uint32_t gr[16];
+#pragma unroll
+                for (int i = 0; i < 16; ++i) gr[i] = 0u;
+                if (g_read) k2_gthr_issue16(my_g, gr);
                 epi_bar_sync();
                 mbar_wait(&tfull_bar[buf], use & 1u);
                 tc_fence_after();
+                uint32_t g_ord = k2_gthr_fold16(gr);
+                if (g_read && p.gthr_groups > 16) g_ord = min(g_ord, k2_gthr_min(my_g + 16, p.gthr_groups - 16));
                 thr = fmaxf(thr, k2_gthr_float(g_ord));
                 float item_best = __uint_as_float(0xff800000u);
                 const uint32_t t_row = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) +
@@ -1087,8 +1130,11 @@ __global__ void __launch_bounds__(256) k5_rescore_kernel(const __grid_constant__
         for (int c0 = warp * 32; c0 < n_cand; c0 += 8 * 32) {
             const int c = c0 + lane;
             const uint64_t e = c < n_cand ? cand[c] : 0ull;
-#pragma unroll 1
-            for (int l = 0; l < 32; ++l) {
+            // only lanes whose candidate beats the running k-th best are visited (the bound only rises)
+            unsigned hit = __ballot_sync(CRB_FULL_MASK, e > atop.thr);
+            while (hit) {
+                const int l = __ffs(hit) - 1;
+                hit &= hit - 1u;
                 const uint64_t el = __shfl_sync(CRB_FULL_MASK, e, l);
                 if (el > atop.thr) atop.insert(el, lane);      // warp-uniform
             }
@@ -1102,9 +1148,14 @@ __global__ void __launch_bounds__(256) k5_rescore_kernel(const __grid_constant__
     // exact canonical score of every surviving candidate (warp per candidate)
     WarpTopK<KPL> top;
     top.init(p.k, lane);
-    for (int c = warp; c < n_cand; c += 8) {
-        const uint64_t e = cand[c];
-        if (e == 0ull || key_score(e) < cut) continue;   // warp-uniform
+    for (int c0 = warp * 32; c0 < n_cand; c0 += 8 * 32) {
+      const int cl = c0 + lane;
+      const uint64_t el = cl < n_cand ? cand[cl] : 0ull;
+      unsigned live = __ballot_sync(CRB_FULL_MASK, el != 0ull && !(key_score(el) < cut));
+      while (live) {
+        const int src = __ffs(live) - 1;
+        live &= live - 1u;
+        const uint64_t e = __shfl_sync(CRB_FULL_MASK, el, src);
         const uint32_t row = p.remap ? p.remap[key_row(e)] : key_row(e);
         const __half* rp = p.rows + static_cast<int64_t>(row) * p.dim;
         float acc = 0.f;
@@ -1124,6 +1175,7 @@ __global__ void __launch_bounds__(256) k5_rescore_kernel(const __grid_constant__
             const uint64_t key = make_key(s, p.row_offset + row);
             if (key > top.thr) top.insert(key, lane);
         }
+      }
     }
     block_extract_topk<KPL>(top, p.k, s_out, xchg, lane, warp, 8);
 
