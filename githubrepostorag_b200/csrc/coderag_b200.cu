@@ -146,7 +146,7 @@ static int64_t mask_stride_of(const crb_index* ix) { return round_up((std::max<i
 struct WsLayout {
     size_t cand = kWsHeaderBytes;
     size_t k2 = 0;          // K2 region start
-    size_t q16 = 0, invq = 0, eps = 0, qmap = 0, flagged = 0, nflag = 0, fbcnt = 0, gthr = 0, cand2 = 0;   // inside the K2 region
+    size_t q16 = 0, invq = 0, eps = 0, qmap = 0, flagged = 0, nflag = 0, fbcnt = 0, gthr = 0, tau = 0, cand2 = 0;   // inside the K2 region
     size_t filt = 0;        // survivor lists start; masks follow the lists
     size_t per_filter = 0;  // bytes one more filter costs
 };
@@ -165,8 +165,9 @@ static WsLayout ws_layout(const crb_index* ix, int batch, int k) {
     L.gthr = o;    o += round_up(nmax * size_t(k2_gthr_groups(k)) * 4, 256);   // K2's shared threshold classes, cleared with nflag
     // per query: one k'-list per CTA (pair) that served its query tile -- at most sm_count lists when the
     // batch is one tile, sm_count/2 when CTA pairs serve every query tile of the batch (m-inner)
-    L.cand2 = o;   o += round_up(std::max<size_t>(std::min<size_t>(nmax, kK2BlockM) * ix->sm_count,
-                                                   nmax * size_t(ix->sm_count / 2 + 1)) * k2_kprime(k) * 8 + nmax * k2_kprime(k) * 8, 1024);
+    const size_t n_lists = std::max<size_t>(std::min<size_t>(nmax, kK2BlockM) * ix->sm_count, nmax * size_t(ix->sm_count / 2 + 1)) + nmax;
+    L.tau = o;     o += round_up(n_lists * 4, 256);     // one float per list
+    L.cand2 = o;   o += round_up(n_lists * k2_kprime(k) * 8, 1024);
     L.filt = o;
     L.per_filter = size_t(list_stride_of(ix)) * 4 + size_t(mask_stride_of(ix)) * 4;
     return L;
@@ -439,6 +440,7 @@ static int launch_k2(crb_index* ix, const float* d_queries, int batch, int k, in
         kp.inv_norm = k2_inv;
         kp.mask = mask;
         kp.cand = cand2;
+        kp.tau = reinterpret_cast<float*>(ws + L.tau);
         kp.n_rows = k2_n;
         kp.batch = n;
         kp.dim = ix->dim;
@@ -567,6 +569,7 @@ static int launch_k2(crb_index* ix, const float* d_queries, int batch, int k, in
         rp.q_map = d_qmap;
         rp.remap = remap;
         rp.cand = cand2;
+        rp.tau = kp.tau;
         rp.invq = invq;
         rp.eps = eps;
         rp.out_scores = d_scores;

@@ -39,6 +39,7 @@ struct K2Params {
     const float* inv_norm;      // [n_rows]
     const uint32_t* mask;       // [ceil(n_rows/32)] pass bits or nullptr
     uint64_t* cand;             // [batch, slots, kprime] approximate keys (local row in low 32 bits)
+    float* tau;                 // [batch, slots] smallest key score of each list that filled up (-inf otherwise)
     uint32_t* gthr;             // [batch, gthr_groups] shared threshold classes per query (ord(score), 0 = none yet) or nullptr
     int32_t gthr_groups;        // power of two in [16, 128], >= k
     int32_t gthr_every;         // a list re-reads its query's classes every this many corpus tiles (0 = k2_gthr_due's schedule)
@@ -535,6 +536,9 @@ k2_gemm_topk_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_cons
             uint64_t* out = p.cand + (static_cast<int64_t>(m_tile * kK2BlockM + row) * p.slots + slot) * p.kprime;
             const int count = static_cast<int>(state);
             for (int i = 0; i < p.kprime; ++i) out[i] = i < count ? my_list[i * p.lstride] : 0ull;
+            // a full list is a min-heap: its root is the best score it may have dropped
+            p.tau[static_cast<int64_t>(m_tile * kK2BlockM + row) * p.slots + slot] =
+                count == p.kprime ? key_score(my_list[0]) : __uint_as_float(0xff800000u);
         }
     }
 
@@ -808,6 +812,8 @@ k2_gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap map_q, const __grid
                 const uint64_t* my_list = lists + static_cast<size_t>(j) * list_elems + row;
                 const int count = static_cast<int>(s_state[j * 128 + row]);
                 for (int i = 0; i < p.kprime; ++i) out[i] = i < count ? my_list[i * p.lstride] : 0ull;
+                p.tau[static_cast<int64_t>(qrow) * slots_total + p.slot_base + slot] =
+                    count == p.kprime ? key_score(my_list[0]) : __uint_as_float(0xff800000u);
             }
         }
     }
@@ -1046,6 +1052,8 @@ k2_gemm_topk_quad_kernel(const __grid_constant__ CUtensorMap map_q64, const __gr
                 const uint64_t* my_list = lists + static_cast<size_t>(j) * list_elems + row;
                 const int count = static_cast<int>(s_state[j * 128 + row]);
                 for (int i = 0; i < p.kprime; ++i) out[i] = i < count ? my_list[i * p.lstride] : 0ull;
+                p.tau[static_cast<int64_t>(qrow) * slots_total + p.slot_base + slot] =
+                    count == p.kprime ? key_score(my_list[0]) : __uint_as_float(0xff800000u);
             }
         }
     }
@@ -1066,6 +1074,7 @@ struct K5Params {
     const int32_t* q_map;       // slot -> query index in the caller's batch (or nullptr = identity)
     const uint32_t* remap;      // candidate row -> shard row when K2 ran on compacted survivors (or nullptr)
     const uint64_t* cand;       // [n, slots, kprime]
+    const float* tau;           // [n, slots] from K2: what each full list may have dropped
     const float* invq;          // [n]
     const float* eps;           // [n]
     float* out_scores;
@@ -1086,12 +1095,55 @@ struct K5Params {
     ExchangeDev ex;             // ex.world == 0: local search only
 };
 
+constexpr int kK5Gather = 2048;   // candidates K5 can gather into shared memory
+
+// Block-wide bitonic sort of n (a power of two >= 32) keys in shared memory, descending; 256 threads.
+CRB_DEVINL void block_bitonic_desc(uint64_t* a, int n) {
+    for (int size = 2; size <= n; size <<= 1) {
+        for (int stride = size >> 1; stride > 0; stride >>= 1) {
+            __syncthreads();
+            for (int t = threadIdx.x; t < (n >> 1); t += 256) {
+                const int i = 2 * t - (t & (stride - 1));
+                const int j = i + stride;
+                const bool desc = (i & size) == 0;
+                const uint64_t x = a[i], y = a[j];
+                if ((x < y) == desc) { a[i] = y; a[j] = x; }
+            }
+        }
+    }
+    __syncthreads();
+}
+
+// Exact canonical score of one approximate candidate -> its exact key (0 = not a hit).  One warp.
+CRB_DEVINL uint64_t k5_exact_key(const K5Params& p, uint64_t e, const float* s_q, int chunks, bool cosine, int lane) {
+    if (e == 0ull) return 0ull;
+    const uint32_t row = p.remap ? p.remap[key_row(e)] : key_row(e);
+    const __half* rp = p.rows + static_cast<int64_t>(row) * p.dim;
+    float acc = 0.f;
+    for (int ch = lane; ch < chunks; ch += 32) {
+        const uint4 v = ld_stream_16(rp + ch * 8);
+        float q8[8];
+        const float4 a = *reinterpret_cast<const float4*>(s_q + ch * 8);
+        const float4 b = *reinterpret_cast<const float4*>(s_q + ch * 8 + 4);
+        q8[0] = a.x; q8[1] = a.y; q8[2] = a.z; q8[3] = a.w;
+        q8[4] = b.x; q8[5] = b.y; q8[6] = b.z; q8[7] = b.w;
+        acc = chunk_fma(v, q8, acc);
+    }
+    const float in = __ldg(p.inv_norm + row);
+    const float invn = cosine ? in : (in == in ? 1.0f : in);
+    const float s = warp_butterfly_sum(acc) * invn;
+    if ((cosine && invn == 0.f) || !(s == s)) return 0ull;
+    return make_key(s, p.row_offset + row);
+}
+
 template <int KPL>
 __global__ void __launch_bounds__(256) k5_rescore_kernel(const __grid_constant__ K5Params p) {
     extern __shared__ float s_q[];   // [dim]
     __shared__ uint64_t xchg[2][32];
     __shared__ uint64_t s_out[kMaxTopK];
+    __shared__ uint64_t s_c[kK5Gather];
     __shared__ float s_tau[8];
+    __shared__ int s_n;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int slot_q = blockIdx.x;
     const int qi = p.q_map ? p.q_map[slot_q] : slot_q;
@@ -1100,104 +1152,120 @@ __global__ void __launch_bounds__(256) k5_rescore_kernel(const __grid_constant__
     for (int i = threadIdx.x; i < p.dim; i += 256) s_q[i] = p.queries[static_cast<int64_t>(qi) * p.dim + i];
     __syncthreads();
 
-    const uint64_t* cand = p.cand + static_cast<int64_t>(slot_q) * p.slots * p.kprime;
-    const int n_cand = p.slots * p.kprime;
+    const uint64_t* cand_all = p.cand + static_cast<int64_t>(slot_q) * p.slots * p.kprime;
+    const int n_all = p.slots * p.kprime;
+    const float margin = p.eps[slot_q] * (cosine ? 1.0f : p.max_norm);
+    const float ninf = __uint_as_float(0xff800000u);
 
-    // tau_max: the best "k'-th approximate score" among FULL slot lists
-    float tau = __uint_as_float(0xff800000u);
-    for (int s = threadIdx.x; s < p.slots; s += 256) {
-        bool full = true;
-        uint64_t m = ~0ull;
-        for (int i = 0; i < p.kprime; ++i) {
-            const uint64_t e = cand[s * p.kprime + i];
-            full &= (e != 0ull);
-            m = e < m ? e : m;
-        }
-        if (full) tau = fmaxf(tau, key_score(m));
-    }
+    // tau_max: the best score any FULL slot list may have dropped, and K2's shared bound (columns dropped
+    // against the bound scored at most its final value)
+    float tau = ninf;
+    for (int s = threadIdx.x; s < p.slots; s += 256) tau = fmaxf(tau, p.tau[static_cast<int64_t>(slot_q) * p.slots + s]);
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) tau = fmaxf(tau, __shfl_xor_sync(CRB_FULL_MASK, tau, o));
     if (lane == 0) s_tau[warp] = tau;
+    const float gbound = p.gthr ? k2_gthr_float(k2_gthr_min(p.gthr + static_cast<int64_t>(slot_q) * p.gthr_groups, p.gthr_groups)) : ninf;
+
+    // Stage 0: the bound is at most the k-th best approximate score a_k, so only candidates within
+    // 2*margin of it can matter (see below); they are a few dozen of the slots*k' entries.  Gather them
+    // into shared memory and run the rest on that short list (all candidates when it would not fit).
+    if (threadIdx.x == 0) s_n = 0;
+    __syncthreads();
+    const float gcut = gbound - 2.0f * margin;          // -inf when there is no bound
+    for (int c = threadIdx.x; c < n_all; c += 256) {
+        const uint64_t e = cand_all[c];
+        if (e != 0ull && !(key_score(e) < gcut)) {
+            const int at = atomicAdd(&s_n, 1);
+            if (at < kK5Gather) s_c[at] = e;
+        }
+    }
+    __syncthreads();
+    const bool gathered = s_n <= kK5Gather;
+    const uint64_t* cand = gathered ? s_c : cand_all;
+    const int n_cand = gathered ? s_n : n_all;
 
     // Prune before the expensive part: find the k-th best APPROXIMATE score a_k among the candidates.
     // A candidate with approx < a_k - 2*margin has exact < a_k - margin <= the exact score of each of
     // the k best approximate candidates, so it cannot be in the exact top-k and is not re-scored.
-    const float margin = p.eps[slot_q] * (cosine ? 1.0f : p.max_norm);
-    float cut = __uint_as_float(0xff800000u);
-    {
-        WarpTopK<KPL> atop;
-        atop.init(p.k, lane);
+    float cut = ninf;
+    if (gathered) {
+        // ---- short list in shared memory: sort it, re-score the prefix that can matter in place, sort again ----
+        int np = 32;
+        while (np < n_cand) np <<= 1;
+        for (int i = n_cand + threadIdx.x; i < np; i += 256) s_c[i] = 0ull;
+        block_bitonic_desc(s_c, np);
+        const uint64_t kth = p.k <= n_cand ? s_c[p.k - 1] : 0ull;
+        if (kth != 0ull) cut = key_score(kth) - 2.0f * margin;
+        if (threadIdx.x == 0) s_n = 0;
+        __syncthreads();
+        {   // sorted descending, so the candidates that can matter are a prefix; count it
+            int mine = 0;
+            for (int i = threadIdx.x; i < n_cand; i += 256) mine += !(key_score(s_c[i]) < cut);
+            mine = __reduce_add_sync(CRB_FULL_MASK, mine);
+            if (lane == 0 && mine) atomicAdd(&s_n, mine);
+        }
+        __syncthreads();
+        const int m = s_n;
+        for (int c = warp; c < m; c += 8) {
+            const uint64_t e = s_c[c];
+            const uint64_t key = k5_exact_key(p, e, s_q, chunks, cosine, lane);
+            if (lane == 0) s_c[c] = key;
+        }
+        int mp = 32;
+        while (mp < m) mp <<= 1;
+        for (int i = m + threadIdx.x; i < mp; i += 256) s_c[i] = 0ull;
+        block_bitonic_desc(s_c, mp);                     // exact keys, best first (0 = dropped / padding)
+        if (threadIdx.x < p.k) s_out[threadIdx.x] = threadIdx.x < mp ? s_c[threadIdx.x] : 0ull;
+        __syncthreads();
+    } else {
+        {
+            WarpTopK<KPL> atop;
+            atop.init(p.k, lane);
+            for (int c0 = warp * 32; c0 < n_cand; c0 += 8 * 32) {
+                const int c = c0 + lane;
+                const uint64_t e = c < n_cand ? cand[c] : 0ull;
+                // only lanes whose candidate beats the running k-th best are visited (the bound only rises)
+                unsigned hit = __ballot_sync(CRB_FULL_MASK, e > atop.thr);
+                while (hit) {
+                    const int l = __ffs(hit) - 1;
+                    hit &= hit - 1u;
+                    const uint64_t el = __shfl_sync(CRB_FULL_MASK, e, l);
+                    if (el > atop.thr) atop.insert(el, lane);      // warp-uniform
+                }
+            }
+            block_extract_topk<KPL>(atop, p.k, s_out, xchg, lane, warp, 8);
+            const uint64_t kth = s_out[p.k - 1];
+            if (kth != 0ull) cut = key_score(kth) - 2.0f * margin;
+            __syncthreads();
+        }
+        // exact canonical score of every surviving candidate (warp per candidate)
+        WarpTopK<KPL> top;
+        top.init(p.k, lane);
         for (int c0 = warp * 32; c0 < n_cand; c0 += 8 * 32) {
-            const int c = c0 + lane;
-            const uint64_t e = c < n_cand ? cand[c] : 0ull;
-            // only lanes whose candidate beats the running k-th best are visited (the bound only rises)
-            unsigned hit = __ballot_sync(CRB_FULL_MASK, e > atop.thr);
-            while (hit) {
-                const int l = __ffs(hit) - 1;
-                hit &= hit - 1u;
-                const uint64_t el = __shfl_sync(CRB_FULL_MASK, e, l);
-                if (el > atop.thr) atop.insert(el, lane);      // warp-uniform
+            const int cl = c0 + lane;
+            const uint64_t el = cl < n_cand ? cand[cl] : 0ull;
+            unsigned live = __ballot_sync(CRB_FULL_MASK, el != 0ull && !(key_score(el) < cut));
+            while (live) {
+                const int src = __ffs(live) - 1;
+                live &= live - 1u;
+                const uint64_t key = k5_exact_key(p, __shfl_sync(CRB_FULL_MASK, el, src), s_q, chunks, cosine, lane);
+                if (key > top.thr) top.insert(key, lane);
             }
         }
-        block_extract_topk<KPL>(atop, p.k, s_out, xchg, lane, warp, 8);
-        const uint64_t kth = s_out[p.k - 1];
-        if (kth != 0ull) cut = key_score(kth) - 2.0f * margin;
-        __syncthreads();
+        block_extract_topk<KPL>(top, p.k, s_out, xchg, lane, warp, 8);
     }
 
-    // exact canonical score of every surviving candidate (warp per candidate)
-    WarpTopK<KPL> top;
-    top.init(p.k, lane);
-    for (int c0 = warp * 32; c0 < n_cand; c0 += 8 * 32) {
-      const int cl = c0 + lane;
-      const uint64_t el = cl < n_cand ? cand[cl] : 0ull;
-      unsigned live = __ballot_sync(CRB_FULL_MASK, el != 0ull && !(key_score(el) < cut));
-      while (live) {
-        const int src = __ffs(live) - 1;
-        live &= live - 1u;
-        const uint64_t e = __shfl_sync(CRB_FULL_MASK, el, src);
-        const uint32_t row = p.remap ? p.remap[key_row(e)] : key_row(e);
-        const __half* rp = p.rows + static_cast<int64_t>(row) * p.dim;
-        float acc = 0.f;
-        for (int ch = lane; ch < chunks; ch += 32) {
-            const uint4 v = ld_stream_16(rp + ch * 8);
-            float q8[8];
-            const float4 a = *reinterpret_cast<const float4*>(s_q + ch * 8);
-            const float4 b = *reinterpret_cast<const float4*>(s_q + ch * 8 + 4);
-            q8[0] = a.x; q8[1] = a.y; q8[2] = a.z; q8[3] = a.w;
-            q8[4] = b.x; q8[5] = b.y; q8[6] = b.z; q8[7] = b.w;
-            acc = chunk_fma(v, q8, acc);
-        }
-        const float in = __ldg(p.inv_norm + row);
-        const float invn = cosine ? in : (in == in ? 1.0f : in);
-        const float s = warp_butterfly_sum(acc) * invn;
-        if (!(cosine && invn == 0.f) && s == s) {
-            const uint64_t key = make_key(s, p.row_offset + row);
-            if (key > top.thr) top.insert(key, lane);
-        }
-      }
-    }
-    block_extract_topk<KPL>(top, p.k, s_out, xchg, lane, warp, 8);
-
+    // ---- proof, then every rank of the result is written by its own thread ----
+    const float iq = p.invq[slot_q];
     if (threadIdx.x == 0) {
         float tau_max = s_tau[0];
         for (int w = 1; w < 8; ++w) tau_max = fmaxf(tau_max, s_tau[w]);
-        // columns K2 dropped against the shared bound scored at most its final value
-        if (p.gthr) tau_max = fmaxf(tau_max, k2_gthr_float(k2_gthr_min(p.gthr + static_cast<int64_t>(slot_q) * p.gthr_groups, p.gthr_groups)));
-        const float iq = p.invq[slot_q];
-        TopKSink sink;
-        sink.scores = p.out_scores + static_cast<int64_t>(qi) * p.k;
-        sink.rows = p.out_rows + static_cast<int64_t>(qi) * p.k;
-        sink.n_valid = p.out_nvalid + qi;
-        sink.keys = p.out_keys ? p.out_keys + static_cast<int64_t>(qi) * p.k : nullptr;
-        sink.scale = cosine ? iq : 1.0f;
-        sink.qi = qi;
-        sink.k = p.k;
+        tau_max = fmaxf(tau_max, gbound);
         int nv = 0;
         for (int r = 0; r < p.k; ++r) nv += (s_out[r] != 0ull);
         // proof: every non-candidate row has exact (normalised) score <= tau_max + margin
         bool proven;
-        if (tau_max == __uint_as_float(0xff800000u)) {
+        if (tau_max == ninf) {
             proven = true;                              // no slot list overflowed: nothing was dropped
         } else if (nv < p.k) {
             proven = false;
@@ -1205,9 +1273,27 @@ __global__ void __launch_bounds__(256) k5_rescore_kernel(const __grid_constant__
             const float kth = key_score(s_out[p.k - 1]) * iq;   // same units as the approximate scores
             proven = kth > tau_max + margin;
         }
-        // an unproven query is re-run by the streaming kernel, which then publishes it to the peers
-        sink.ex = (proven && p.ex.world > 0) ? &p.ex : nullptr;
-        for (int r = 0; r < p.k; ++r) sink.emit(r, s_out[r]);
+        s_n = proven ? nv : -1 - nv;
+    }
+    __syncthreads();
+    const bool proven = s_n >= 0;
+    const int nv = proven ? s_n : -1 - s_n;
+    TopKSink sink;
+    sink.scores = p.out_scores + static_cast<int64_t>(qi) * p.k;
+    sink.rows = p.out_rows + static_cast<int64_t>(qi) * p.k;
+    sink.n_valid = p.out_nvalid + qi;
+    sink.keys = p.out_keys ? p.out_keys + static_cast<int64_t>(qi) * p.k : nullptr;
+    sink.scale = cosine ? iq : 1.0f;
+    sink.qi = qi;
+    sink.k = p.k;
+    // an unproven query is re-run by the fallback kernel, which then publishes it to the peers
+    sink.ex = (proven && p.ex.world > 0) ? &p.ex : nullptr;
+    if (threadIdx.x < p.k) {
+        sink.emit(threadIdx.x, s_out[threadIdx.x]);
+        if (sink.ex) __threadfence_system();
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
         *sink.n_valid = nv;
         sink.finish();
         if (!proven) {
