@@ -207,7 +207,7 @@ def run_reference(args):
             "config": workload_config(args, world),
             "cpu_baseline": {"value": value, "unit": UNIT, "cores": int(threads), "kind": "port", "sample": sample},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-    print(json.dumps(line), flush=True)
+    emit_line(line)
     return 0
 
 
@@ -379,12 +379,21 @@ def run_ours(args):
                                  "unit": UNIT, "ms_per_step": second["ms_per_step"], "steps": second["steps"],
                                  "e2e": second["e2e"], "gpu_launches": second["gpu_launches"], "clocks": second["clocks"],
                                  "roofline": second["roofline"]}
-        print(json.dumps(line), flush=True)
+        emit_line(line)
     barrier()
     shard.close()
     if world > 1:
         dist.destroy_process_group()
     return 0
+
+
+_JSON_OUT = None
+
+
+def emit_line(line):
+    out = _JSON_OUT or sys.stdout
+    out.write(json.dumps(line) + "\n")
+    out.flush()
 
 
 def main():
@@ -401,6 +410,12 @@ def main():
     args = ap.parse_args()
     if args.warmup < 3:
         args.warmup = 3
+    # stdout carries the ONE JSON line and nothing else: libraries that print there (NCCL's version banner does,
+    # from C, when NCCL_DEBUG is set) are pointed at stderr for the whole run
+    global _JSON_OUT
+    sys.stdout.flush()
+    _JSON_OUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
     return run_reference(args) if args.impl == "reference" else run_ours(args)
 
 
