@@ -343,6 +343,76 @@ static int launch_k1(const crb_index* ix, const float* d_queries, int k, int met
     return 0;
 }
 
+// Single-query groups with unequal row sets (one query vector, many filters): the balanced kernel.
+static int launch_k1_balanced(const crb_index* ix, const float* d_queries, int k, int metric,
+                              const std::vector<QueryGroup>& groups, const std::vector<int>& slot_of_filter,
+                              uint8_t* ws, const uint32_t* lists, float* d_scores, int64_t* d_rows,
+                              int32_t* d_n_valid, uint64_t* d_keys, cudaStream_t stream, const ExchangeDev* ex) {
+    typedef void (*BalFn)(const BalParams);
+    const int ch = (ix->dim / 8 + 31) / 32;     // 16-byte chunks per lane
+    BalFn fn;
+#define CRB_BAL(CH_, R_) (k <= 32 ? static_cast<BalFn>(k1_balanced_kernel<CH_, R_, 1>) : static_cast<BalFn>(k1_balanced_kernel<CH_, R_, 4>))
+    switch (ch) {
+        case 1: fn = CRB_BAL(1, 8); break;
+        case 2: fn = CRB_BAL(2, 6); break;
+        case 3: fn = CRB_BAL(3, 4); break;
+        case 4: fn = CRB_BAL(4, 3); break;
+        default: fn = CRB_BAL(0, 2); break;
+    }
+#undef CRB_BAL
+    const size_t dyn = size_t(ix->dim) * sizeof(float);
+    static std::mutex mu;
+    static std::map<std::pair<const void*, size_t>, int> cache;
+    int occ = 0;
+    {
+        std::lock_guard<std::mutex> lk(mu);
+        auto key = std::make_pair(reinterpret_cast<const void*>(fn), dyn);
+        auto it = cache.find(key);
+        if (it == cache.end()) {
+            int n = 0;
+            if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, fn, kK1Threads, dyn) != cudaSuccess || n < 1) n = 1;
+            it = cache.emplace(key, n).first;
+        }
+        occ = it->second;
+    }
+    for (size_t g0 = 0; g0 < groups.size(); g0 += kMaxGroups) {
+        const int ng = static_cast<int>(std::min<size_t>(kMaxGroups, groups.size() - g0));
+        BalParams p;
+        memset(&p, 0, sizeof p);
+        p.rows = ix->rows;
+        p.inv_norm = ix->inv_norm;
+        p.queries = d_queries;
+        p.lists = lists;
+        p.list_counts = reinterpret_cast<const uint32_t*>(ws + kWsCountsOffset);
+        p.cand = reinterpret_cast<uint64_t*>(ws + kWsHeaderBytes);
+        p.counters = reinterpret_cast<unsigned*>(ws);
+        p.out_scores = d_scores;
+        p.out_rows = d_rows;
+        p.out_nvalid = d_n_valid;
+        p.out_keys = d_keys;
+        p.n_rows = ix->n_rows;
+        p.list_stride = list_stride_of(ix);
+        p.row_offset = static_cast<uint32_t>(ix->row_offset);
+        p.dim = ix->dim;
+        p.k = k;
+        p.metric = metric;
+        p.n_groups = ng;
+        if (ex) p.ex = *ex;
+        for (int g = 0; g < ng; ++g) {
+            const QueryGroup& qg = groups[g0 + g];
+            p.q_idx[g] = qg.queries[0];
+            p.filter[g] = qg.filter < 0 ? -1 : slot_of_filter[qg.filter];
+        }
+        // one wave, but never more lists than the scratch region or the merge can hold
+        int64_t grid = int64_t(occ) * ix->sm_count;
+        grid = std::min<int64_t>(grid, kK1MaxGridX);
+        grid = std::min<int64_t>(grid, int64_t(kWsCandBytes) / (int64_t(k) * 8) - 2 * kMaxGroups);
+        fn<<<static_cast<unsigned>(std::max<int64_t>(grid, 1)), kK1Threads, dyn, stream>>>(p);
+        CRB_LAUNCH_CHECK();
+    }
+    return 0;
+}
+
 // ---------------------------------------------------------------------------------------------
 // K2 launch: tensor-core candidates + K5 exact rescore for one set of queries sharing a row set
 // ---------------------------------------------------------------------------------------------
@@ -805,8 +875,14 @@ static int search_impl(crb_index* ix, const float* d_queries, int batch, int k, 
         }
         if (!groups.empty()) {
             const int nq = max_group <= 1 ? 1 : (max_group <= 2 ? 2 : 4);
-            int rc = launch_k1(ix, d_queries, k, metric, groups, slot_of_filter, nq, ws, lists, d_scores,
-                               d_rows, d_n_valid, d_keys, stream, ex);
+            // single-query groups over different row sets (the adjacent() fan-out): split the grid by rows, not by group
+            bool any_filtered = false;
+            for (const QueryGroup& g : groups) any_filtered |= (g.filter >= 0);
+            const bool balanced = max_group == 1 && groups.size() >= 2 && any_filtered && env_int("CODERAG_B200_K1_BALANCED", 1);
+            int rc = balanced ? launch_k1_balanced(ix, d_queries, k, metric, groups, slot_of_filter, ws, lists, d_scores,
+                                                   d_rows, d_n_valid, d_keys, stream, ex)
+                              : launch_k1(ix, d_queries, k, metric, groups, slot_of_filter, nq, ws, lists, d_scores,
+                                          d_rows, d_n_valid, d_keys, stream, ex);
             if (rc) return rc;
         }
         first = false;

@@ -590,4 +590,199 @@ k1_fallback_kernel(const __grid_constant__ FbParams p) {
 }
 
 
+// ---------------------------------------------------------------------------------------------
+// Balanced multi-group variant: "one query vector, many filters" (the graph retriever's adjacent()
+// fan-out) produces single-query groups whose row sets differ by orders of magnitude -- a file's 20
+// rows next to a repository's 500 000.  k1_stream_kernel gives every group the same share of the
+// grid, so the big group crawls on 1/groups of the machine.  Here the groups' row sets are laid end to
+// end in units of one CTA step (kK1Warps * R rows) and the 1-D grid cuts that line into equal pieces:
+// CTA c owns units [c*T/C, (c+1)*T/C), which may span several groups (it then serves them one after
+// the other) or be one of many pieces of a big group.  The CTAs first(g)..last(g) that touch group g
+// each write one sorted list (list index c + g is collision-free) and the last to arrive merges them.
+// Survivor counts are read on the device, so nothing here waits for the host.
+struct BalParams {
+    const __half* rows;
+    const float* inv_norm;
+    const float* queries;          // [batch, dim] fp32
+    const uint32_t* lists;         // [n_filters, list_stride]
+    const uint32_t* list_counts;   // [n_filters]
+    uint64_t* cand;                // [(grid + 2 * groups), k] scratch
+    unsigned* counters;            // [groups] arrival counters, zero between launches
+    float* out_scores;
+    int64_t* out_rows;
+    int32_t* out_nvalid;
+    uint64_t* out_keys;
+    int64_t n_rows;
+    int64_t list_stride;
+    uint32_t row_offset;
+    int32_t dim;
+    int32_t k;
+    int32_t metric;
+    int32_t n_groups;
+    ExchangeDev ex;
+    int32_t q_idx[kMaxGroups];     // one query per group
+    int32_t filter[kMaxGroups];    // -1 = whole shard, else survivor list slot
+};
+
+__device__ __noinline__ void bal_merge_query(const BalParams& p, int qi, const uint64_t* lists, int n_lists,
+                                             const float* s_q, uint64_t (*xchg)[32], float* s_invq) {
+    const int lane = threadIdx.x & 31;
+    const int warp = threadIdx.x >> 5;
+    if (warp == 0) {
+        const float iq = (p.metric == 0) ? warp_inv_qnorm(s_q, p.dim, lane) : 1.0f;
+        if (lane == 0) *s_invq = iq;
+    }
+    __syncthreads();
+    TopKSink sink;
+    sink.scores = p.out_scores + static_cast<int64_t>(qi) * p.k;
+    sink.rows = p.out_rows + static_cast<int64_t>(qi) * p.k;
+    sink.n_valid = p.out_nvalid + qi;
+    sink.keys = p.out_keys ? p.out_keys + static_cast<int64_t>(qi) * p.k : nullptr;
+    sink.scale = *s_invq;
+    sink.ex = p.ex.world > 0 ? &p.ex : nullptr;
+    sink.qi = qi;
+    sink.k = p.k;
+    block_merge_sorted_lists<kK1MergeLPT>(lists, n_lists, p.k, p.k, sink, xchg, lane, warp, kK1Warps);
+}
+
+// CH = 16-byte chunks per lane (dim <= 256 * CH), all loads of a step issued before the first FMA;
+// CH = 0 walks any dimension with a run-time loop.
+template <int CH, int R, int KPL>
+__global__ void __launch_bounds__(kK1Threads, CH == 0 ? 1 : 2)
+k1_balanced_kernel(const __grid_constant__ BalParams p) {
+    extern __shared__ float s_q[];  // [dim]
+    __shared__ uint64_t xchg[2][32];
+    __shared__ int64_t s_upref[kMaxGroups + 1];   // units before group g
+    __shared__ int64_t s_items[kMaxGroups];
+    __shared__ float s_invq;
+    __shared__ int s_last;
+
+    const int lane = threadIdx.x & 31;
+    const int warp = threadIdx.x >> 5;
+    const int chunks = p.dim >> 3;
+    const bool cosine = (p.metric == 0);
+    constexpr int64_t U = static_cast<int64_t>(kK1Warps) * R;   // rows per CTA step
+
+    if (threadIdx.x == 0) {
+        int64_t acc = 0;
+        for (int g = 0; g < p.n_groups; ++g) {
+            int64_t n = p.n_rows;
+            if (p.filter[g] >= 0) {
+                const int64_t cnt = static_cast<int64_t>(p.list_counts[p.filter[g]]);
+                n = cnt < p.n_rows ? cnt : p.n_rows;
+            }
+            s_items[g] = n;
+            s_upref[g] = acc;
+            acc += (n + U - 1) / U;
+        }
+        s_upref[p.n_groups] = acc;
+    }
+    __syncthreads();
+    const int64_t T = s_upref[p.n_groups];
+    const int64_t C = gridDim.x;
+    const int64_t c = blockIdx.x;
+    const int64_t my_lo = (c * T) / C, my_hi = ((c + 1) * T) / C;
+
+    int loaded_q = -1;
+    for (int g = 0; g < p.n_groups; ++g) {
+        const int64_t u0 = s_upref[g], u1 = s_upref[g + 1];
+        // CTAs that own a list of this group (every CTA evaluates this identically)
+        int64_t first = 0, last = 0;
+        if (u1 > u0) {
+            first = ((u0 + 1) * C + T - 1) / T - 1;
+            last = (u1 * C + T - 1) / T - 1;
+        }
+        const bool empty = (u1 == u0);           // no rows: CTA 0 emits "no hits" from a list of its own
+        if (c < first || c > last) continue;     // uniform per CTA
+        const int qi = p.q_idx[g];
+        if (qi != loaded_q) {
+            __syncthreads();
+            for (int i = threadIdx.x; i < p.dim; i += kK1Threads)
+                s_q[i] = p.queries[static_cast<int64_t>(qi) * p.dim + i];
+            loaded_q = qi;
+        }
+        __syncthreads();
+
+        const int64_t n_items = s_items[g];
+        const uint32_t* list = p.filter[g] >= 0 ? p.lists + static_cast<int64_t>(p.filter[g]) * p.list_stride : nullptr;
+        const int64_t lo = (my_lo > u0 ? my_lo : u0) - u0, hi = (my_hi < u1 ? my_hi : u1) - u0;   // units inside the group
+
+        WarpTopK<KPL> top;
+        top.init(p.k, lane);
+        for (int64_t u = lo; u < hi; ++u) {
+            const int64_t item0 = u * U + static_cast<int64_t>(warp) * R;
+            int64_t row[R];
+            bool ok[R];
+            float acc[R];
+#pragma unroll
+            for (int j = 0; j < R; ++j) {
+                ok[j] = (item0 + j) < n_items;
+                row[j] = ok[j] ? (list ? static_cast<int64_t>(list[item0 + j]) : item0 + j) : 0;
+                acc[j] = 0.f;
+            }
+            if constexpr (CH > 0) {
+                uint4 v[R][CH];
+#pragma unroll
+                for (int j = 0; j < R; ++j) {
+                    const __half* rp = p.rows + row[j] * p.dim;
+#pragma unroll
+                    for (int cc = 0; cc < CH; ++cc)
+                        if (lane + 32 * cc < chunks) v[j][cc] = ld_stream_16(rp + (lane + 32 * cc) * 8);
+                }
+#pragma unroll
+                for (int cc = 0; cc < CH; ++cc) {
+                    const int ch = lane + 32 * cc;
+                    if (ch < chunks) {
+                        float q8[8];
+                        const float4 a = *reinterpret_cast<const float4*>(s_q + ch * 8);
+                        const float4 b = *reinterpret_cast<const float4*>(s_q + ch * 8 + 4);
+                        q8[0] = a.x; q8[1] = a.y; q8[2] = a.z; q8[3] = a.w;
+                        q8[4] = b.x; q8[5] = b.y; q8[6] = b.z; q8[7] = b.w;
+#pragma unroll
+                        for (int j = 0; j < R; ++j) acc[j] = chunk_fma(v[j][cc], q8, acc[j]);
+                    }
+                }
+            } else {
+                for (int ch = lane; ch < chunks; ch += 32) {
+                    uint4 v[R];
+#pragma unroll
+                    for (int j = 0; j < R; ++j) v[j] = ld_stream_16(p.rows + row[j] * p.dim + ch * 8);
+                    float q8[8];
+                    const float4 a = *reinterpret_cast<const float4*>(s_q + ch * 8);
+                    const float4 b = *reinterpret_cast<const float4*>(s_q + ch * 8 + 4);
+                    q8[0] = a.x; q8[1] = a.y; q8[2] = a.z; q8[3] = a.w;
+                    q8[4] = b.x; q8[5] = b.y; q8[6] = b.z; q8[7] = b.w;
+#pragma unroll
+                    for (int j = 0; j < R; ++j) acc[j] = chunk_fma(v[j], q8, acc[j]);
+                }
+            }
+#pragma unroll
+            for (int j = 0; j < R; ++j) {
+                const float invn = cosine ? __ldg(p.inv_norm + row[j]) : 1.0f;
+                const float s = warp_butterfly_sum(acc[j]) * invn;
+                if (ok[j] && !(cosine && invn == 0.f) && s == s) {
+                    const uint64_t key = make_key(s, p.row_offset + static_cast<uint32_t>(row[j]));
+                    if (key > top.thr) top.insert(key, lane);
+                }
+            }
+        }
+
+        uint64_t* lists_g = p.cand + (empty ? C + p.n_groups + g : first + g) * p.k;
+        block_extract_topk<KPL>(top, p.k, lists_g + (c - first) * p.k, xchg, lane, warp, kK1Warps);
+
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            __threadfence();
+            const unsigned t = atomicAdd(&p.counters[g], 1u);
+            s_last = (t == static_cast<unsigned>(last - first)) ? 1 : 0;
+        }
+        __syncthreads();
+        if (s_last) {
+            __threadfence();
+            bal_merge_query(p, qi, lists_g, static_cast<int>(last - first + 1), s_q, xchg, &s_invq);
+            if (threadIdx.x == 0) p.counters[g] = 0u;
+        }
+    }
+}
+
 }  // namespace crb

@@ -674,6 +674,9 @@ class B200VectorStore:
                 flts.append({"__impossible__": "1"})
             else:
                 flts.append({**base, fld: val})
+        # edges that resolve to the same filter (an edge on a key the caller's filter already pins) are one search:
+        # the results are merged by row below, and single-query groups keep the fan-out on the balanced kernel
+        flts = list({tuple(sorted((str(a), str(b)) for a, b in f.items())): f for f in flts}.values())
         q = np.repeat(np.asarray(query_embedding, dtype=np.float32)[None, :], len(flts), axis=0)
         scores, rows, n_valid = self._search(q, k, flts)
         best: Dict[int, float] = {}

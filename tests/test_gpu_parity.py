@@ -196,6 +196,55 @@ def test_many_filters_one_query_vector(torch_cuda):
     sh.close()
 
 
+@pytest.mark.parametrize("d,k", [(384, 8), (768, 40), (1536, 5)])
+def test_skewed_fan_out_balanced_kernel(torch_cuda, d, k):
+    """adjacent() fan-out with row sets from a handful of rows to the whole table: the balanced kernel
+    (grid split by rows, not by group) must return exactly what the per-group kernel returns, and both
+    must match the oracle -- including a filter nothing passes and an impossible one."""
+    import os
+    torch = torch_cuda
+    n = 120_000
+    rng = np.random.default_rng(100 + d)
+    rows16 = rng.standard_normal((n, d), dtype=np.float32).astype(np.float16)
+    repo = (rng.zipf(1.4, n) % 300).astype(np.int32)            # repo 1 holds a large share, most are tiny
+    fpath = rng.integers(0, 20_000, n).astype(np.int32)         # ~6 rows per file
+    code_mat = np.stack([np.zeros(n, np.int32), repo, fpath])
+    sh = _shard(torch, rows16, code_mat)
+    qv = rng.standard_normal(d, dtype=np.float32)
+    wants = [[0, -1, -1], [-1, 1, -1], [-1, 2, -1], [-1, 250, -1], [0, 1, 77], [-1, -1, 123], [-1, -1, 19_999],
+             [-1, 299, 5], [-1, 999, -1], [-2, -1, -1], [-1, 7, -1], [-1, 3, -1]]
+    q = np.tile(qv, (len(wants), 1))
+    filt = np.asarray(wants, np.int32)
+    qd = torch.from_numpy(q).cuda()
+    keys_a = torch.empty((len(wants), k), dtype=torch.int64, device="cuda")
+    keys_b = torch.empty_like(keys_a)
+    os.environ["CODERAG_B200_K1_BALANCED"] = "1"
+    try:
+        sa, ra, va = [t.clone() for t in sh.search_device(qd, k, filt=filt, keys_out=keys_a)]
+        os.environ["CODERAG_B200_K1_BALANCED"] = "0"
+        sb, rb, vb = [t.clone() for t in sh.search_device(qd, k, filt=filt, keys_out=keys_b)]
+    finally:
+        os.environ.pop("CODERAG_B200_K1_BALANCED", None)
+    torch.cuda.synchronize()
+    assert torch.equal(ra, rb) and torch.equal(va, vb) and torch.equal(sa.view(torch.int32), sb.view(torch.int32))
+    assert torch.equal(keys_a, keys_b)
+    keep = np.ones((len(wants), n), dtype=bool)
+    for i, w in enumerate(wants):
+        for m in range(3):
+            if w[m] == -2:
+                keep[i] = False
+            elif w[m] >= 0:
+                keep[i] &= code_mat[m] == w[m]
+    assert va.cpu().numpy()[8] == 0 and va.cpu().numpy()[9] == 0
+    _check(q, rows16, sa.cpu().numpy(), ra.cpu().numpy(), va.cpu().numpy(), k, oracle.MODE_COSINE, keep=keep,
+           what=f"skewed fan-out d={d}")
+    # twice in a row on the same workspace-less path: arrival counters must have reset themselves
+    s2, r2, v2 = sh.search_device(qd, k, filt=filt)
+    torch.cuda.synchronize()
+    assert torch.equal(r2, ra) and torch.equal(s2.view(torch.int32), sa.view(torch.int32))
+    sh.close()
+
+
 def test_store_adjacent_and_retriever_faces(torch_cuda):
     from githubrepostorag_b200.vector_store import B200VectorStore
     rng = np.random.default_rng(3)
