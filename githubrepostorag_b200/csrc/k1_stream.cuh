@@ -709,15 +709,23 @@ k1_balanced_kernel(const __grid_constant__ BalParams p) {
 
         WarpTopK<KPL> top;
         top.init(p.k, lane);
+        // survivor indices of the NEXT step are fetched (lane j holds row j's) while this step's rows stream
+        uint32_t idx_next = 0u;
+        if (list && lane < R && lo < hi && lo * U + static_cast<int64_t>(warp) * R + lane < n_items)
+            idx_next = list[lo * U + static_cast<int64_t>(warp) * R + lane];
         for (int64_t u = lo; u < hi; ++u) {
             const int64_t item0 = u * U + static_cast<int64_t>(warp) * R;
+            const uint32_t idx_cur = idx_next;
+            idx_next = 0u;
+            if (list && lane < R && u + 1 < hi && item0 + U + lane < n_items) idx_next = list[item0 + U + lane];
             int64_t row[R];
             bool ok[R];
             float acc[R];
 #pragma unroll
             for (int j = 0; j < R; ++j) {
                 ok[j] = (item0 + j) < n_items;
-                row[j] = ok[j] ? (list ? static_cast<int64_t>(list[item0 + j]) : item0 + j) : 0;
+                const uint32_t li = __shfl_sync(CRB_FULL_MASK, idx_cur, j);
+                row[j] = ok[j] ? (list ? static_cast<int64_t>(li) : item0 + j) : 0;
                 acc[j] = 0.f;
             }
             if constexpr (CH > 0) {

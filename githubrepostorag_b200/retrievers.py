@@ -103,9 +103,16 @@ class EagerGraphRetriever:
                     seen[c.id] = (c, depth)
                     frontier.append(c)
         docs = []
+        # one matrix product for all selected rows (graph-retriever scores each node from its embedding)
+        sims = {}
+        if selected:
+            E = np.asarray([seen[rid][0].embedding for rid in selected], dtype=np.float32)
+            den = np.linalg.norm(q) * np.linalg.norm(E, axis=1)
+            dots = E @ q
+            sims = {rid: (float(dots[i] / den[i]) if den[i] > 0 else 0.0) for i, rid in enumerate(selected)}
         for rid in selected:
             c, d = seen[rid]
-            sim = self._cos(q, c.embedding)
+            sim = sims[rid]
             md = dict(c.metadata)
             md.update({"_depth": d, "_similarity_score": sim, "score": sim})
             docs.append(Document(page_content=c.content, metadata=md, id=c.id))
