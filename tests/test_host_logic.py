@@ -141,3 +141,39 @@ def test_k1_d768_hot_loop_keeps_its_loads_together(lib):
     assert len(loads) >= 12, "d=768 kernel not found or has no 128-bit loads"
     first12 = loads[:12]
     assert first12[-1] - first12[0] <= 64, f"row loads are spread over {first12[-1] - first12[0]} instructions"
+
+
+def test_tensor_core_kernels_are_tcgen05_tma_tmem_without_spills(lib):
+    """Build-time evidence (no GPU needed): the K2 kernels issue tcgen05 MMAs fed by TMA and read their
+    accumulators from TMEM -- not mma.sync / wmma -- and neither they nor the d=768 streaming kernel spill."""
+    import re
+    import shutil
+    import subprocess
+    from githubrepostorag_b200 import _native
+    if not shutil.which("cuobjdump"):
+        pytest.skip("cuobjdump not on PATH")
+    sass = subprocess.run(["cuobjdump", "-sass", str(_native.lib_path())], capture_output=True, text=True).stdout
+    per_fn, cur = {}, None
+    for ln in sass.splitlines():
+        if "Function :" in ln:
+            cur = ln.split("Function :")[1].strip()
+            per_fn[cur] = []
+        elif cur is not None:
+            per_fn[cur].append(ln)
+    for tag in ("k2_gemm_topk_kernel", "k2_gemm_topk_pair_kernel", "k2_gemm_topk_quad_kernel"):
+        names = [n for n in per_fn if tag in n]
+        assert names, f"{tag} not in the library"
+        body = "\n".join(per_fn[names[0]])
+        assert "UTCHMMA" in body, f"{tag}: no tcgen05.mma (UTCHMMA)"
+        assert "UTMALDG" in body, f"{tag}: no TMA tensor load (UTMALDG)"
+        assert "LDTM" in body, f"{tag}: no TMEM load (LDTM)"
+        assert not re.search(r"\bHMMA\b", body), f"{tag}: legacy mma.sync found"
+    res = subprocess.run(["cuobjdump", "-res-usage", str(_native.lib_path())], capture_output=True, text=True).stdout
+    fn = None
+    for ln in res.splitlines():
+        if "Function" in ln:
+            fn = ln
+        elif "REG:" in ln and fn and any(t in fn for t in ("k2_gemm_topk", "k1_stream_kernelILi1ELi3ELi4ELi1ELi2E")):
+            assert "LOCAL:0" in ln, f"local memory in {fn}: {ln}"
+            stack = int(re.search(r"STACK:(\d+)", ln).group(1))
+            assert stack == 0, f"spill stack in {fn}: {ln}"
