@@ -155,7 +155,7 @@ static WsLayout ws_layout(const crb_index* ix, int batch, int k) {
     L.k2 = kWsHeaderBytes + kWsCandBytes;
     const size_t nmax = static_cast<size_t>(std::min(batch, kK2MaxChunk));
     size_t o = L.k2;
-    L.q16 = o;     o += round_up(nmax * ix->dim * 2, 1024);
+    L.q16 = o;     o += round_up(round_up(nmax, 256) * ix->dim * 2, 1024);   // padded to whole query tile pairs
     L.invq = o;    o += round_up(nmax * 4, 256);
     L.eps = o;     o += round_up(nmax * 4, 256);
     L.qmap = o;    o += round_up(nmax * 4, 256);
@@ -492,7 +492,8 @@ static int launch_k2(crb_index* ix, const float* d_queries, int batch, int k, in
             CRB_CUDA(cudaMemcpyAsync(qmap, queries.data() + c0, size_t(n) * 4, cudaMemcpyHostToDevice, stream));
             d_qmap = qmap;
         }
-        k2_prep_queries_kernel<<<n, 128, 0, stream>>>(d_queries, d_qmap, n, ix->dim, q16, invq, eps);
+        const int n_pad = static_cast<int>(round_up(n, 256));   // zero rows up to a whole tile pair: no TMA out-of-bounds fill
+        k2_prep_queries_kernel<<<n_pad, 128, 0, stream>>>(d_queries, d_qmap, n, ix->dim, q16, invq, eps);
         CRB_LAUNCH_CHECK();
 
         // one clear for the flag count, the fallback's arrival counters and the shared thresholds
@@ -500,7 +501,7 @@ static int launch_k2(crb_index* ix, const float* d_queries, int batch, int k, in
         CRB_CUDA(cudaMemsetAsync(nflag, 0, (L.gthr - L.nflag) + size_t(n) * groups * 4, stream));
 
         CUtensorMap map_q;
-        if (int rc = make_map_f16(&map_q, q16, n, ix->dim, kK2BlockM)) return rc;
+        if (int rc = make_map_f16(&map_q, q16, n_pad, ix->dim, kK2BlockM)) return rc;
         K2Params kp;
         memset(&kp, 0, sizeof kp);
         kp.gthr = env_int("CODERAG_B200_K2_GTHR", 1) ? reinterpret_cast<uint32_t*>(ws + L.gthr) : nullptr;
@@ -589,7 +590,7 @@ static int launch_k2(crb_index* ix, const float* d_queries, int batch, int k, in
                     CRB_CUDA(cudaEventCreateWithFlags(&ix->aux_join, cudaEventDisableTiming));
                 }
                 CUtensorMap map_q64;
-                if (int rc = make_map_f16(&map_q64, q16, n, ix->dim, kK2BlockM / 2)) return rc;
+                if (int rc = make_map_f16(&map_q64, q16, n_pad, ix->dim, kK2BlockM / 2)) return rc;
                 const int cslots = quad_clusters;
                 // per-SM the clusters are ~1.14x faster (a quarter less L2->SM traffic)
                 const double w_quad = cslots * 4 * (env_int("CODERAG_B200_K2_CORUN_W", 114) / 100.0), w_pair = stranded_pairs * 2.0;
@@ -611,7 +612,7 @@ static int launch_k2(crb_index* ix, const float* d_queries, int batch, int k, in
                 CRB_CUDA(cudaStreamWaitEvent(stream, ix->aux_join, 0));
             } else if (quad_clusters >= kp.m_tiles && (quad_env > 0 || quad_clusters * 4 >= (ix->sm_count * 9) / 10)) {
                 CUtensorMap map_q64;
-                if (int rc = make_map_f16(&map_q64, q16, n, ix->dim, kK2BlockM / 2)) return rc;
+                if (int rc = make_map_f16(&map_q64, q16, n_pad, ix->dim, kK2BlockM / 2)) return rc;
                 int cslots = std::max(1, quad_clusters / kp.m_tiles);
                 cslots = static_cast<int>(std::min<int64_t>(cslots, (n_tiles + 1) / 2));
                 kp.slots = 2 * cslots;

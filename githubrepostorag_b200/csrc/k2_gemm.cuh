@@ -326,7 +326,12 @@ __global__ void __launch_bounds__(128) k2_prep_queries_kernel(const float* __res
     __shared__ float s_iq;
     __shared__ float s_part[4];
     const int slot = blockIdx.x;
-    if (slot >= n) return;
+    if (slot >= n) {
+        // padding rows up to a whole query tile: zeros in memory, so the TMA never has to synthesise
+        // out-of-bounds rows (a B = 8 search spent 25 % longer per corpus tile filling 120 of them)
+        for (int i = threadIdx.x; i < dim; i += blockDim.x) q16[static_cast<int64_t>(slot) * dim + i] = __float2half_rn(0.f);
+        return;
+    }
     const float* q = queries + static_cast<int64_t>(q_map ? q_map[slot] : slot) * dim;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     if (warp == 0) {
