@@ -310,6 +310,7 @@ def run_ours(args):
         # ---- end to end through the host-buffer API (e2e) ----
         res_host = [torch.empty((B, k), dtype=torch.float32).pin_memory(), torch.empty((B, k), dtype=torch.int64).pin_memory(),
                     torch.empty((B,), dtype=torch.int32).pin_memory()]
+        res_packed = torch.empty((B * k * 12 + B * 4,), dtype=torch.uint8).pin_memory()
         q_stage = torch.empty((B, DIM), dtype=torch.float32, device=dev)
 
         def step_e2e(i):
@@ -320,9 +321,13 @@ def run_ours(args):
                 q_stage.copy_(q_host[i % N_QUERY_SETS], non_blocking=True)
             s_, r_, v_, _ = searcher.search(q_stage, k, broadcast=True)
             if rank == 0:
-                res_host[0].copy_(s_, non_blocking=True)
-                res_host[1].copy_(r_, non_blocking=True)
-                res_host[2].copy_(v_, non_blocking=True)
+                packed = getattr(searcher, "last_packed", None)
+                if packed is not None:                       # scores, rows and n_valid in ONE device-to-host copy
+                    res_packed.copy_(packed, non_blocking=True)
+                else:
+                    res_host[0].copy_(s_, non_blocking=True)
+                    res_host[1].copy_(r_, non_blocking=True)
+                    res_host[2].copy_(v_, non_blocking=True)
             torch.cuda.current_stream().synchronize()
             return res_host
 

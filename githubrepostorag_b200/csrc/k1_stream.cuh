@@ -793,4 +793,215 @@ k1_balanced_kernel(const __grid_constant__ BalParams p) {
     }
 }
 
+// ---------------------------------------------------------------------------------------------
+// Fused filter + score: ONE query under ONE filter -- what every retriever.invoke(q, filter={namespace,
+// repo, ...}) starts with (agent_graph.py:249) -- in a single pass and a single launch.  K3 + K1 read the
+// code columns, write a survivor list, launch again, read the list and gather; here a warp reads the
+// code columns of a 128-row stripe (one 16-byte load per key per lane), evaluates the AND of equalities
+// (and the caller's row mask), queues the survivors' row numbers in shared memory and scores them R at
+// a time with the canonical summation order as soon as R are waiting.  No list, no counters, no second
+// launch: algorithmic bytes = n_rows * used_keys * 4 + survivors * dim * 2, all in one HBM stream.
+struct FusedParams {
+    const __half* rows;
+    const float* inv_norm;
+    const float* query;            // [dim] fp32
+    const int32_t* codes;          // [n_keys, code_stride]
+    const uint32_t* row_mask;      // optional caller pass bits (or nullptr)
+    uint64_t* cand;                // [grid, k] scratch
+    unsigned* counter;             // arrival counter, zero between launches
+    float* out_scores;             // [k] of this query
+    int64_t* out_rows;
+    int32_t* out_nvalid;
+    uint64_t* out_keys;            // or nullptr
+    int64_t n_rows;
+    int64_t code_stride;
+    uint32_t row_offset;
+    int32_t dim;
+    int32_t k;
+    int32_t metric;
+    int32_t qi;                    // query index in the batch (exchange slot)
+    int32_t n_keys;
+    int32_t want[kMaxKeys];        // -1 = any
+    int32_t vec_ok;                // code columns are 16-byte aligned: vector loads
+    ExchangeDev ex;
+};
+
+constexpr int kFusedStripe = 1024;  // rows per warp step of the scan
+
+template <int CH, int R, int KPL>
+__global__ void __launch_bounds__(kK1Threads, 2)
+k1_fused_filter_kernel(const __grid_constant__ FusedParams p) {
+    __shared__ uint64_t xchg[2][32];
+    __shared__ uint32_t s_queue[kK1Warps][128 + 8];
+    __shared__ float s_invq;
+    __shared__ int s_last;
+
+    const int lane = threadIdx.x & 31;
+    const int warp = threadIdx.x >> 5;
+    const int chunks = p.dim >> 3;
+    const bool cosine = (p.metric == 0);
+    const uint32_t lt = (1u << lane) - 1u;
+
+    float qr[CH][8];
+#pragma unroll
+    for (int c = 0; c < CH; ++c) {
+        const int ch = lane + 32 * c;
+        if (ch < chunks) {
+            const float4* src = reinterpret_cast<const float4*>(p.query + ch * 8);
+            const float4 a = __ldg(src), b = __ldg(src + 1);
+            qr[c][0] = a.x; qr[c][1] = a.y; qr[c][2] = a.z; qr[c][3] = a.w;
+            qr[c][4] = b.x; qr[c][5] = b.y; qr[c][6] = b.z; qr[c][7] = b.w;
+        } else {
+#pragma unroll
+            for (int e = 0; e < 8; ++e) qr[c][e] = 0.f;
+        }
+    }
+
+    WarpTopK<KPL> top;
+    top.init(p.k, lane);
+    uint32_t* queue = s_queue[warp];
+    int queued = 0;                                   // warp-uniform
+
+    auto score_batch = [&](int first, int n_take) {   // rows queue[first .. first + n_take), n_take <= R
+        int64_t row[R];
+        bool ok[R];
+#pragma unroll
+        for (int j = 0; j < R; ++j) {
+            ok[j] = j < n_take;
+            row[j] = ok[j] ? static_cast<int64_t>(queue[first + j]) : 0;
+        }
+        uint4 v[R][CH];
+#pragma unroll
+        for (int j = 0; j < R; ++j) {
+            const __half* rp = p.rows + row[j] * p.dim;
+#pragma unroll
+            for (int c = 0; c < CH; ++c)
+                if (lane + 32 * c < chunks) v[j][c] = ld_stream_16(rp + (lane + 32 * c) * 8);
+        }
+        float invn[R];
+#pragma unroll
+        for (int j = 0; j < R; ++j) invn[j] = cosine ? __ldg(p.inv_norm + row[j]) : 1.0f;
+        float acc[R];
+#pragma unroll
+        for (int j = 0; j < R; ++j) acc[j] = 0.f;
+#pragma unroll
+        for (int c = 0; c < CH; ++c) {
+            if (lane + 32 * c < chunks) {
+#pragma unroll
+                for (int j = 0; j < R; ++j) acc[j] = chunk_fma(v[j][c], qr[c], acc[j]);
+            }
+        }
+#pragma unroll
+        for (int j = 0; j < R; ++j) {
+            const float s = warp_butterfly_sum(acc[j]) * invn[j];
+            if (ok[j] && !(cosine && invn[j] == 0.f) && s == s) {
+                const uint64_t key = make_key(s, p.row_offset + static_cast<uint32_t>(row[j]));
+                if (key > top.thr) top.insert(key, lane);
+            }
+        }
+    };
+
+    // A warp scans 1024 rows per step: per key, eight 16-byte loads per lane in flight (4 KB per warp), folded
+    // into one 32-bit pass word before the next key's loads reuse the registers -- with one 128-row stripe per
+    // step the scan was latency-bound (24 KB in flight per SM) and slower than the two-kernel path.
+    const int64_t n_stripes = (p.n_rows + kFusedStripe - 1) / kFusedStripe;
+    const int64_t step = static_cast<int64_t>(gridDim.x) * kK1Warps;
+    for (int64_t st = static_cast<int64_t>(blockIdx.x) * kK1Warps + warp; st < n_stripes; st += step) {
+        const int64_t base = st * kFusedStripe;
+        const int64_t r0 = base + 4 * lane;                       // sub-stripe i holds rows r0 + 128 i .. + 3
+        const bool whole = base + kFusedStripe <= p.n_rows;       // warp-uniform
+        uint32_t pass = 0xffffffffu;                              // bit 4 i + j <-> row r0 + 128 i + j
+        if (!whole) {
+            pass = 0u;
+#pragma unroll
+            for (int i = 0; i < 8; ++i)
+#pragma unroll
+                for (int j = 0; j < 4; ++j)
+                    if (r0 + 128 * i + j < p.n_rows) pass |= 1u << (4 * i + j);
+        }
+        for (int m = 0; m < p.n_keys; ++m) {
+            const int32_t w = p.want[m];
+            if (w == -1) continue;
+            const int32_t* col = p.codes + static_cast<int64_t>(m) * p.code_stride + r0;
+            if (whole && p.vec_ok) {
+                int4 c[8];
+#pragma unroll
+                for (int i = 0; i < 8; ++i) c[i] = __ldg(reinterpret_cast<const int4*>(col + 128 * i));
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    uint32_t bad = (c[i].x != w ? 1u : 0u) | (c[i].y != w ? 2u : 0u) | (c[i].z != w ? 4u : 0u) | (c[i].w != w ? 8u : 0u);
+                    pass &= ~(bad << (4 * i));
+                }
+            } else {
+#pragma unroll
+                for (int i = 0; i < 8; ++i)
+#pragma unroll
+                    for (int j = 0; j < 4; ++j)
+                        if (((pass >> (4 * i + j)) & 1u) && __ldg(col + 128 * i + j) != w) pass &= ~(1u << (4 * i + j));
+            }
+        }
+        if (p.row_mask) {
+            // rows r0 + 128 i .. + 3 sit in one mask word (r0 is a multiple of 4)
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                if ((pass >> (4 * i)) & 0xfu) {
+                    const int64_t r = r0 + 128 * i;
+                    const uint32_t word = __ldg(p.row_mask + (r >> 5));
+                    pass &= ~(0xfu << (4 * i)) | (((word >> (r & 31)) & 0xfu) << (4 * i));
+                }
+            }
+        }
+        // queue the survivors (order is irrelevant: keys carry the row), scoring whenever R are waiting
+        if (__ballot_sync(CRB_FULL_MASK, pass != 0u) == 0u) continue;
+#pragma unroll 1
+        for (int i = 0; i < 8; ++i) {
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const uint32_t bit = (pass >> (4 * i + j)) & 1u;
+                const uint32_t b = __ballot_sync(CRB_FULL_MASK, bit);
+                if (bit) queue[queued + __popc(b & lt)] = static_cast<uint32_t>(r0 + 128 * i + j);
+                queued += __popc(b);
+            }
+            __syncwarp();
+            while (queued >= R) {          // at most 128 pushed since the last drain: the queue cannot overflow
+                queued -= R;
+                score_batch(queued, R);
+            }
+            __syncwarp();
+        }
+    }
+    __syncwarp();
+    if (queued > 0) score_batch(0, queued);
+
+    uint64_t* out = p.cand + static_cast<int64_t>(blockIdx.x) * p.k;
+    block_extract_topk<KPL>(top, p.k, out, xchg, lane, warp, kK1Warps);
+
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence();
+        const unsigned t = atomicAdd(p.counter, 1u);
+        s_last = (t == gridDim.x - 1) ? 1 : 0;
+    }
+    __syncthreads();
+    if (!s_last) return;
+    __threadfence();
+
+    if (warp == 0) {
+        const float iq = cosine ? warp_inv_qnorm(p.query, p.dim, lane) : 1.0f;
+        if (lane == 0) s_invq = iq;
+    }
+    __syncthreads();
+    TopKSink sink;
+    sink.scores = p.out_scores;
+    sink.rows = p.out_rows;
+    sink.n_valid = p.out_nvalid;
+    sink.keys = p.out_keys;
+    sink.scale = s_invq;
+    sink.ex = p.ex.world > 0 ? &p.ex : nullptr;
+    sink.qi = p.qi;
+    sink.k = p.k;
+    block_merge_sorted_lists<kK1MergeLPT>(p.cand, gridDim.x, p.k, p.k, sink, xchg, lane, warp, kK1Warps);
+    if (threadIdx.x == 0) *p.counter = 0u;
+}
+
 }  // namespace crb

@@ -145,9 +145,13 @@ class FusedExchangeSearcher:
         if b * k > self.cap_keys:
             raise ValueError(f"batch*k = {b * k} exceeds cap_keys = {self.cap_keys}")
         dev = self.shard.device
-        scores = torch.empty((b, k), dtype=torch.float32, device=dev)
-        rows = torch.empty((b, k), dtype=torch.int64, device=dev)
-        n_valid = torch.empty((b,), dtype=torch.int32, device=dev)
+        # one allocation for the three results (rows first: 8-byte aligned), so a caller that wants them on the
+        # host moves ``last_packed`` with a single copy
+        packed = torch.empty((b * k * 12 + b * 4,), dtype=torch.uint8, device=dev)
+        rows = packed[: b * k * 8].view(torch.int64).view(b, k)
+        scores = packed[b * k * 8: b * k * 12].view(torch.float32).view(b, k)
+        n_valid = packed[b * k * 12:].view(torch.int32)
+        self.last_packed = packed
         f = self.shard._filt(filt, b)
         nf = 0 if f is None else len({tuple(r) for r in f.tolist() if any(c != N.FILT_ANY for c in r)})
         need = self.shard.workspace_bytes(b, k, nf)

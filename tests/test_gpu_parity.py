@@ -245,6 +245,56 @@ def test_skewed_fan_out_balanced_kernel(torch_cuda, d, k):
     sh.close()
 
 
+@pytest.mark.parametrize("n,d,k", [(100_000, 384, 10), (77_777, 768, 40), (50_001, 1024, 20), (3_000, 64, 5)])
+def test_fused_filter_and_score_single_query(torch_cuda, n, d, k):
+    """One query under one filter runs the fused filter+score kernel: same rows and score bits as the
+    K3 + K1 pair it replaces, and the oracle's answer -- across selectivities from nothing to everything,
+    odd row counts (unaligned code columns -> scalar loads), a caller row mask, and the keys output."""
+    import os
+    torch = torch_cuda
+    rng = np.random.default_rng(n + d)
+    rows16 = rng.standard_normal((n, d), dtype=np.float32).astype(np.float16)
+    code_mat = np.stack([rng.integers(0, 2, n), (rng.zipf(1.5, n) % 40), rng.integers(0, 1000, n)]).astype(np.int32)
+    sh = _shard(torch, rows16, code_mat)
+    q = rng.standard_normal((1, d), dtype=np.float32)
+    qd = torch.from_numpy(q).cuda()
+    extra = rng.random(n) < 0.3
+    mask_dev = sh.pack_row_mask(torch.from_numpy(extra).cuda())
+    cases = [([0, -1, -1], None), ([-1, 1, -1], None), ([1, 3, -1], None), ([-1, -1, 7], None), ([1, 39, 999], None),
+             ([-1, 55, -1], None), ([0, 1, -1], mask_dev), ([-1, -1, -1], mask_dev)]
+    for want, mask in cases:
+        filt = np.asarray([want], np.int32)
+        out = {}
+        for fused in ("1", "0"):
+            os.environ["CODERAG_B200_K1_FUSED"] = fused
+            try:
+                keys = torch.empty((1, k), dtype=torch.int64, device="cuda")
+                s_, r_, v_ = sh.search_device(qd, k, filt=filt, keys_out=keys, row_masks=None if mask is None else [mask])
+                torch.cuda.synchronize()
+                out[fused] = (s_.clone(), r_.clone(), v_.clone(), keys.clone())
+            finally:
+                os.environ.pop("CODERAG_B200_K1_FUSED", None)
+        a, b = out["1"], out["0"]
+        assert torch.equal(a[1], b[1]) and torch.equal(a[2], b[2]), f"rows differ for {want}"
+        assert torch.equal(a[0].view(torch.int32), b[0].view(torch.int32)) and torch.equal(a[3], b[3])
+        keep = np.ones(n, dtype=bool)
+        for m in range(3):
+            if want[m] >= 0:
+                keep &= code_mat[m] == want[m]
+        if mask is not None:
+            keep &= extra
+        _check(q, rows16, a[0].cpu().numpy(), a[1].cpu().numpy(), a[2].cpu().numpy(), k, oracle.MODE_COSINE, keep=keep,
+               what=f"fused n={n} d={d} want={want} mask={mask is not None}")
+    # inner product, and twice in a row (the arrival counter resets itself)
+    filt = np.asarray([[1, -1, -1]], np.int32)
+    keep = code_mat[0] == 1
+    for _ in range(2):
+        s_, r_, v_ = sh.search_device(qd, k, filt=filt, metric="ip")
+        torch.cuda.synchronize()
+        _check(q, rows16, s_.cpu().numpy(), r_.cpu().numpy(), v_.cpu().numpy(), k, oracle.MODE_DOT, keep=keep, what="fused ip")
+    sh.close()
+
+
 def test_store_adjacent_and_retriever_faces(torch_cuda):
     from githubrepostorag_b200.vector_store import B200VectorStore
     rng = np.random.default_rng(3)
