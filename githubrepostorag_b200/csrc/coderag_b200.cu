@@ -89,6 +89,7 @@ static inline int64_t round_up(int64_t v, int64_t m) { return (v + m - 1) / m * 
 
 constexpr int kK2MaxChunk = kK2MaxMTiles * kK2BlockM;   // queries per K2 launch
 constexpr int64_t kK2MinRows = 16384;                   // below this K1 is always used
+constexpr int64_t kK2SmallBatchRows = 131072;           // from here on even a 2-query unfiltered batch takes K2
 
 // k' (candidates kept per query per CTA) for a requested k
 // (shared memory holds k' x 128 keys next to >= 2 pipeline stages, which caps k' at 120)
@@ -860,7 +861,14 @@ static int search_impl(crb_index* ix, const float* d_queries, int batch, int k, 
         std::map<int, bool> use_k2;
         bool any_k2_filtered = false;
         for (auto& kv : by_filter) {
-            const bool big = static_cast<int>(kv.second.size()) > nq_cap;
+            // The streaming kernel is instruction-bound, so a second query in a group costs almost a second
+            // pass (10M x 768: B=1 2.29 ms, B=2 3.93 ms, B=4 6.9 ms) while the tensor-core kernel serves any
+            // B <= 128 in one HBM pass (2.2 ms): an unfiltered row set with two or more queries goes there as
+            // soon as the shard is big enough to hide its fixed cost (200k x 384, B=2: 0.056 vs 0.076 ms).
+            // A filtered set still needs more queries than one streaming pass serves, because choosing costs
+            // a survivor-count read-back.
+            const int sz = static_cast<int>(kv.second.size());
+            const bool big = kv.first < 0 ? (sz > nq_cap || (sz >= 2 && ix->n_rows >= kK2SmallBatchRows)) : sz > nq_cap;
             use_k2[kv.first] = k2_possible && (algo == 2 || big);
             any_k2_filtered |= (use_k2[kv.first] && kv.first >= 0);
         }
@@ -910,7 +918,8 @@ static int search_impl(crb_index* ix, const float* d_queries, int batch, int k, 
                 const double row_bytes = double(ix->dim) * 2.0;
                 const bool can_compact = surv * (row_bytes + 4.0) + 2048.0 <= double(compact_cap) && surv * 4.0 <= double(ix->n_rows);
                 const double scan_rows = can_compact ? surv : double(ix->n_rows);
-                const double t_k1 = std::ceil(nq_set / nq_cap) * (surv * row_bytes / 5.0e12 + 10e-6);
+                // (a group of nq_cap queries shares the row reads but not the arithmetic: charge every query its bytes)
+                const double t_k1 = nq_set * (surv * row_bytes / 5.0e12) + std::ceil(nq_set / nq_cap) * 10e-6;
                 const double t_k2 = std::max(scan_rows * row_bytes / 3.0e12, 2.0 * nq_set * scan_rows * ix->dim / 9.0e14) +
                                     (can_compact ? 2.0 * surv * row_bytes / 5.0e12 : 0.0) + 0.3e-3;
                 if (t_k1 <= t_k2) use_k2[kv.first] = false;
