@@ -597,7 +597,11 @@ static int launch_k2(crb_index* ix, const float* d_queries, int batch, int k, in
             // lists fit next to >= 4 pipeline stages (CODERAG_B200_K2_MINNER=1 restores one group per pair)
             // (measured: 5 pipeline stages with 2 query-tile pairs per corpus tile beat 4 stages with 4 pairs
             //  up to 4 pairs -- 12.4 vs 13.0 ms at B=1024; beyond that fewer HBM re-reads win)
-            int mi = std::min(m_pairs, std::max(1, env_int("CODERAG_B200_K2_MINNER", m_pairs <= 4 ? 2 : 4)));
+            // (after the shared admission bound made the epilogue cheap the two are equal at 10M rows -- 12.89 vs 12.90 ms,
+            //  interleaved A/B -- and 4 pairs read the corpus from HBM once instead of 1.4 times (ncu: 15.4 vs 21.6 GB);
+            //  2 pairs stay 4 % ahead on shards of a few million rows, where HBM is idle anyway)
+            const int mi_default = m_pairs <= 4 ? (n_tiles >= 20000 ? 4 : 2) : 4;
+            int mi = std::min(m_pairs, std::max(1, env_int("CODERAG_B200_K2_MINNER", mi_default)));
             auto pair_stages = [&](int mi_) {
                 const size_t fixed_b = size_t(mi_) * list_bytes + tail_bytes + size_t(mi_) * 1024;
                 return static_cast<int>(std::min<size_t>((size_t(227) * 1024 - 1024 - fixed_b) / kK2PairStageBytes, 8));
@@ -645,7 +649,7 @@ static int launch_k2(crb_index* ix, const float* d_queries, int batch, int k, in
             const int corun_env = env_int("CODERAG_B200_K2_CORUN", -1);
             const int stranded_pairs = (ix->sm_count - quad_clusters * 4) / 2;
             const bool corun = quad_clusters >= kp.m_tiles && kp.m_tiles == 1 && stranded_pairs >= 1 && n_tiles >= 4096 &&
-                               (corun_env > 0 || (corun_env < 0 && quad_env != 0 && quad_clusters * 4 >= ix->sm_count * 3 / 4));
+                               corun_env > 0;   // opt-in: interleaved A/B shows no gain at B=1024 (12.17 / 11.95 vs 11.48 / 12.14 ms)
             std::unique_lock<std::mutex> aux_lock(ix->aux_mu, std::defer_lock);
             if (corun && aux_lock.try_lock()) {
                 if (!ix->aux_stream) {
