@@ -126,6 +126,29 @@ def test_k2_device_side_fallback_many_queries_filters_and_large_k(torch_cuda):
     sh.close()
 
 
+@pytest.mark.parametrize("d", [384, 768])
+def test_default_plan_for_tiny_batches_equals_streaming_kernel(torch_cuda, d):
+    """Unfiltered batches of 2-4 queries take the tensor-core kernel by default on shards >= 128k rows
+    (the streaming kernel pays almost one pass per query); the answer must not depend on the plan."""
+    torch = torch_cuda
+    n, k = 140_000, 10
+    rows16 = S.corpus(500 + d, n, d)
+    sh = _shard(torch, rows16)
+    launches = __import__("githubrepostorag_b200._native", fromlist=["launch_count"]).launch_count
+    for batch in (1, 2, 3, 4, 9):
+        q = S.queries(2000 + batch, batch, d)
+        qd = torch.from_numpy(q).cuda()
+        l0 = launches()
+        s0, r0, v0 = [t.clone() for t in sh.search_device(qd, k)]
+        n_default = launches() - l0
+        s1, r1, v1 = [t.clone() for t in sh.search_device(qd, k, algo=1)]
+        torch.cuda.synchronize()
+        assert torch.equal(r0, r1) and torch.equal(v0, v1) and torch.equal(s0.view(torch.int32), s1.view(torch.int32))
+        # one streaming launch for a single query; prep + K2 + K5 + fallback for two or more
+        assert n_default == (1 if batch == 1 else 4), f"B={batch}: {n_default} launches"
+    sh.close()
+
+
 def test_k2_sharded_equals_unsharded(torch_cuda):
     torch = torch_cuda
     from githubrepostorag_b200.index import merge_keys
