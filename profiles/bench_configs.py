@@ -57,7 +57,20 @@ def case(name, n, d, b, k, steps, codes=None, filt=None, alg_bytes=None, algo=0)
 
 
 if __name__ == "__main__":
-    which = sys.argv[1:] or ["C2", "C4", "C5"]
+    which = sys.argv[1:] or ["C1", "C2", "C4", "C5"]
+    if "C1" in which:
+        # the reference's own CPU-runnable case: the whole table (7.7 MB) sits in L2, the call is launch latency
+        case("C1 10kx384 b1 k5", 10_000, 384, 1, 5, 1000, alg_bytes=10_000 * 384 * 2)
+        import time
+        rows = device_rows(10_000, 384, 7)
+        sh = DeviceShard.from_device(rows)
+        qh = np.random.default_rng(0).standard_normal((1, 384), dtype=np.float32)
+        for _ in range(50): sh.search_host(qh, 5)
+        t0 = time.perf_counter()
+        for _ in range(1000): sh.search_host(qh, 5)
+        print(json.dumps({"case": "C1 10kx384 b1 k5 through crb_search_host (host buffers in and out)",
+                          "ms_per_call": round((time.perf_counter() - t0), 4)}), flush=True)
+        sh.close()
     if "C2" in which:
         case("C2 1Mx768 b1 k10", 1_000_000, 768, 1, 10, 400, alg_bytes=1_000_000 * 768 * 2)
     if "C4" in which:
