@@ -832,7 +832,12 @@ static int search_impl(crb_index* ix, const float* d_queries, int batch, int k, 
 
     const int chunks = ix->dim / 8;
     const int ch = (chunks + 31) / 32;
-    const int nq_cap = ch > 4 ? 1 : (ch <= 2 ? 4 : 2);
+    const int nq_cap = ch > 4 ? 1 : (ch <= 2 ? 4 : 2);     // queries a filtered row set needs to exceed before K2 is considered
+    // queries per streaming group: two share their row reads; four in a group are slower than two groups of two
+    // everywhere (1M x 384, 10 % filter, B=4: 0.132 ms vs 0.089 ms; unfiltered 12.5M x 384: 10.3 ms vs 2 x 3.9 ms),
+    // because the streaming kernel is instruction-bound and the four-query variant fits one CTA per SM only
+    // (profiles/group_width_probe.py, small_batch_dispatch.py).
+    const int nq_group = std::max(1, std::min(nq_cap, env_int("CODERAG_B200_K1_GROUP", ch > 4 ? 1 : 2)));
 
     // one query under one satisfiable filter: filter and score in one pass, no survivor list.  OPT-IN
     // (CODERAG_B200_K1_FUSED=1): measured 6 % faster than K3 + K1 at 1 % selectivity (10M x 1024: 84.8 vs 89.9 us)
@@ -923,7 +928,7 @@ static int search_impl(crb_index* ix, const float* d_queries, int batch, int k, 
                 const bool can_compact = surv * (row_bytes + 4.0) + 2048.0 <= double(compact_cap) && surv * 4.0 <= double(ix->n_rows);
                 const double scan_rows = can_compact ? surv : double(ix->n_rows);
                 // (a group of nq_cap queries shares the row reads but not the arithmetic: charge every query its bytes)
-                const double t_k1 = nq_set * (surv * row_bytes / 5.0e12) + std::ceil(nq_set / nq_cap) * 10e-6;
+                const double t_k1 = nq_set * (surv * row_bytes / 5.0e12) + std::ceil(nq_set / nq_group) * 10e-6;
                 const double t_k2 = std::max(scan_rows * row_bytes / 3.0e12, 2.0 * nq_set * scan_rows * ix->dim / 9.0e14) +
                                     (can_compact ? 2.0 * surv * row_bytes / 5.0e12 : 0.0) + 0.3e-3;
                 if (t_k1 <= t_k2) use_k2[kv.first] = false;
@@ -954,10 +959,10 @@ static int search_impl(crb_index* ix, const float* d_queries, int batch, int k, 
         int max_group = 1;
         for (auto& kv : k1_sets) {
             const std::vector<int>& qs = kv.second;
-            for (size_t i = 0; i < qs.size(); i += nq_cap) {
+            for (size_t i = 0; i < qs.size(); i += nq_group) {
                 QueryGroup g;
                 g.filter = kv.first;
-                g.queries.assign(qs.begin() + i, qs.begin() + std::min(qs.size(), i + nq_cap));
+                g.queries.assign(qs.begin() + i, qs.begin() + std::min(qs.size(), i + nq_group));
                 max_group = std::max<int>(max_group, static_cast<int>(g.queries.size()));
                 groups.push_back(std::move(g));
             }
