@@ -149,6 +149,39 @@ def test_default_plan_for_tiny_batches_equals_streaming_kernel(torch_cuda, d):
     sh.close()
 
 
+def test_unfiltered_search_can_be_captured_in_a_cuda_graph(torch_cuda):
+    """Nothing on the unfiltered path waits for the host any more (the tensor-core path re-runs unprovable
+    queries on the device), so a caller can capture crb_search in a CUDA graph and replay it on new
+    queries written into the captured buffer -- streaming (B=1) and tensor-core (B=8) plans alike."""
+    torch = torch_cuda
+    n, d, k = 150_000, 256, 10
+    rows16 = S.corpus(901, n, d)
+    sh = _shard(torch, rows16)
+    for b in (1, 8):
+        q = torch.from_numpy(S.queries(3000 + b, b, d)).cuda()
+        ws = sh.new_workspace(b, k, 0)
+        for _ in range(2):
+            sh.search_device(q, k, workspace=ws)         # first calls set function attributes / caches
+        torch.cuda.synchronize()
+        g = torch.cuda.CUDAGraph()
+        side = torch.cuda.Stream()
+        with torch.cuda.stream(side):
+            with torch.cuda.graph(g, stream=side):
+                res = sh.search_device(q, k, workspace=ws)
+        for seed in (1, 2):
+            q2 = torch.from_numpy(S.queries(4000 + 10 * b + seed, b, d)).cuda()
+            q.copy_(q2)
+            g.replay()
+            torch.cuda.synchronize()
+            got = [t.clone() for t in res]
+            want = sh.search_device(q2, k)
+            torch.cuda.synchronize()
+            assert torch.equal(got[1], want[1]) and torch.equal(got[2], want[2])
+            assert torch.equal(got[0].view(torch.int32), want[0].view(torch.int32))
+        del g
+    sh.close()
+
+
 def test_k2_sharded_equals_unsharded(torch_cuda):
     torch = torch_cuda
     from githubrepostorag_b200.index import merge_keys
