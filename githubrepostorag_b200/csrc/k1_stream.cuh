@@ -74,7 +74,8 @@ __device__ __noinline__ void k1_merge_query(const K1Params& p, int qi, int64_t l
     block_merge_sorted_lists<kK1MergeLPT>(lists, gridDim.x, p.k, p.k, sink, xchg, lane, warp, kK1Warps);
 }
 
-template <int NQ, int CH, int R, int KPL, int MINB = 1>
+// EX: the row has exactly 32 * CH chunks (dim = 256 * CH, e.g. 768 and 1024): no per-chunk range tests in the loop.
+template <int NQ, int CH, int R, int KPL, int MINB = 1, bool EX = false>
 __global__ void __launch_bounds__(kK1Threads, MINB)
 k1_stream_kernel(const __grid_constant__ K1Params p) {
     __shared__ uint64_t xchg[2][32];
@@ -150,7 +151,7 @@ k1_stream_kernel(const __grid_constant__ K1Params p) {
 #pragma unroll
             for (int c = 0; c < CH; ++c) {
                 const int ch = lane + 32 * c;
-                if (ch < chunks) v[j][c] = ld_stream_16(rp + ch * 8);
+                if (EX || ch < chunks) v[j][c] = ld_stream_16(rp + ch * 8);
             }
         }
 #pragma unroll
@@ -166,7 +167,7 @@ k1_stream_kernel(const __grid_constant__ K1Params p) {
             for (int j = 0; j < R; ++j) acc[q][j] = 0.f;
 #pragma unroll
         for (int c = 0; c < CH; ++c) {
-            if (lane + 32 * c < chunks) {
+            if (EX || lane + 32 * c < chunks) {
 #pragma unroll
                 for (int j = 0; j < R; ++j)
 #pragma unroll
@@ -222,7 +223,9 @@ k1_stream_kernel(const __grid_constant__ K1Params p) {
 // five.  Scores are BIT-IDENTICAL to the canonical 32-lane order: half-lane h computes the canonical
 // partials of lanes h (chunks h, h+32) and h+16 (chunks h+16, h+48) in two accumulators, adds them
 // (the canonical xor-16 level, locally), then runs the xor-8/4/2/1 levels inside its half.
-template <int NQ, int R, int KPL>
+// E3: the row has exactly 48 chunks (dim = 384, the reference's embedding width): every half-lane owns exactly
+// three chunks, so the per-chunk range tests and the fourth chunk slot disappear from the loop.
+template <int NQ, int R, int KPL, bool E3 = false>
 __global__ void __launch_bounds__(kK1Threads, 2)
 k1_stream_half_kernel(const __grid_constant__ K1Params p) {
     __shared__ uint64_t xchg[2][32];
@@ -237,11 +240,12 @@ k1_stream_half_kernel(const __grid_constant__ K1Params p) {
     const int chunks = p.dim >> 3;
     const bool cosine = (p.metric == 0);
 
-    float qr[NQ][4][8];
+    constexpr int NC = E3 ? 3 : 4;      // chunk slots per half-lane
+    float qr[NQ][NC][8];
 #pragma unroll
     for (int q = 0; q < NQ; ++q) {
 #pragma unroll
-        for (int c = 0; c < 4; ++c) {
+        for (int c = 0; c < NC; ++c) {
             const int ch = hl + 16 * c;
             if (G.q_idx[q] >= 0 && ch < chunks) {
                 const float4* src = reinterpret_cast<const float4*>(
@@ -290,15 +294,15 @@ k1_stream_half_kernel(const __grid_constant__ K1Params p) {
             row[j] = use_list ? static_cast<int64_t>(li) : (item0 + it);
             if (!ok[j]) row[j] = 0;
         }
-        uint4 v[R][4];
+        uint4 v[R][NC];
         float invn[R];
 #pragma unroll
         for (int j = 0; j < R; ++j) {
             const __half* rp = p.rows + row[j] * p.dim;
 #pragma unroll
-            for (int c = 0; c < 4; ++c) {
+            for (int c = 0; c < NC; ++c) {
                 const int ch = hl + 16 * c;
-                if (ch < chunks) v[j][c] = ld_stream_16(rp + ch * 8);
+                if (E3 || ch < chunks) v[j][c] = ld_stream_16(rp + ch * 8);
             }
         }
 #pragma unroll
@@ -309,10 +313,16 @@ k1_stream_half_kernel(const __grid_constant__ K1Params p) {
             for (int q = 0; q < NQ; ++q) {
                 // canonical lane hl: chunks hl, hl+32 ; canonical lane hl+16: chunks hl+16, hl+48
                 float a0 = 0.f, a1 = 0.f;
-                if (hl < chunks) a0 = chunk_fma(v[j][0], qr[q][0], a0);
-                if (hl + 32 < chunks) a0 = chunk_fma(v[j][2], qr[q][2], a0);
-                if (hl + 16 < chunks) a1 = chunk_fma(v[j][1], qr[q][1], a1);
-                if (hl + 48 < chunks) a1 = chunk_fma(v[j][3], qr[q][3], a1);
+                if constexpr (E3) {
+                    a0 = chunk_fma(v[j][0], qr[q][0], a0);
+                    a0 = chunk_fma(v[j][2], qr[q][2], a0);
+                    a1 = chunk_fma(v[j][1], qr[q][1], a1);
+                } else {
+                    if (hl < chunks) a0 = chunk_fma(v[j][0], qr[q][0], a0);
+                    if (hl + 32 < chunks) a0 = chunk_fma(v[j][2], qr[q][2], a0);
+                    if (hl + 16 < chunks) a1 = chunk_fma(v[j][1], qr[q][1], a1);
+                    if (hl + 48 < chunks) a1 = chunk_fma(v[j][NC - 1], qr[q][NC - 1], a1);
+                }
                 float s = a0 + a1;                                   // canonical xor-16 level
                 s += __shfl_xor_sync(CRB_FULL_MASK, s, 8);
                 s += __shfl_xor_sync(CRB_FULL_MASK, s, 4);
@@ -321,11 +331,14 @@ k1_stream_half_kernel(const __grid_constant__ K1Params p) {
                 s *= invn[j];
                 const bool good = ok[j] && !(cosine && invn[j] == 0.f) && G.q_idx[q] >= 0 && s == s;
                 const uint64_t key = good ? make_key(s, p.row_offset + static_cast<uint32_t>(row[j])) : 0ull;
-                // admit the two rows of the step one after the other (warp-uniform keys)
+                // one vote per row pair; only a pair that holds a candidate is broadcast and admitted,
+                // one row after the other (warp-uniform keys)
+                if (__any_sync(CRB_FULL_MASK, key > top[q].thr)) {
 #pragma unroll
-                for (int h = 0; h < 2; ++h) {
-                    const uint64_t kh = __shfl_sync(CRB_FULL_MASK, key, h * 16);
-                    if (kh > top[q].thr) top[q].insert(kh, lane);
+                    for (int h = 0; h < 2; ++h) {
+                        const uint64_t kh = __shfl_sync(CRB_FULL_MASK, key, h * 16);
+                        if (kh > top[q].thr) top[q].insert(kh, lane);
+                    }
                 }
             }
         }

@@ -7,8 +7,8 @@ rows = torch.randn((n, d), device="cuda").to(torch.float16)
 sh = DeviceShard.from_device(rows)
 q = torch.randn((1, d), device="cuda")
 ws = sh.new_workspace(1, 10, 0)
-for knobs in ({}, {"CODERAG_B200_K1_HALF": "0"}, {"CODERAG_B200_K1_HALF_PAIRS": "2"}, {"CODERAG_B200_K1_HALF_PAIRS": "4"},
-              {"CODERAG_B200_K1_HALF": "0", "CODERAG_B200_K1_ROWS": "4"}, {}):
+for knobs in ({}, {"CODERAG_B200_K1_E3": "0"}, {"CODERAG_B200_K1_HALF_PAIRS": "2"}, {"CODERAG_B200_K1_HALF_PAIRS": "4"},
+              {"CODERAG_B200_K1_E3": "0", "CODERAG_B200_K1_HALF_PAIRS": "4"}, {"CODERAG_B200_K1_HALF": "0"}, {}):
     for k_, v in knobs.items(): os.environ[k_] = v
     for _ in range(5): sh.search_device(q, 10, workspace=ws, algo=1)
     torch.cuda.synchronize()

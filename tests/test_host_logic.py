@@ -134,7 +134,7 @@ def test_k1_d768_hot_loop_keeps_its_loads_together(lib):
     take, lines = False, []
     for ln in sass.splitlines():
         if "Function :" in ln:
-            take = "k1_stream_kernelILi1ELi3ELi4ELi1ELi2E" in ln
+            take = "k1_stream_kernelILi1ELi3ELi4ELi1ELi2ELb1E" in ln      # the exact-width (dim = 768) instantiation the plan dispatches
         elif take and "/*" in ln and ";" in ln:
             lines.append(ln)
     loads = [i for i, ln in enumerate(lines) if "LDG.E.NA.128" in ln]      # the streaming (no-allocate) row loads
