@@ -295,6 +295,33 @@ def test_fused_filter_and_score_single_query(torch_cuda, n, d, k):
     sh.close()
 
 
+@pytest.mark.parametrize("d,knob", [(384, "CODERAG_B200_K1_E3"), (768, "CODERAG_B200_K1_EX")])
+def test_exact_width_instantiations_return_the_same_bits(torch_cuda, d, knob):
+    """dim 384 and dim 768 run streaming-kernel instantiations without per-chunk range tests; they must return
+    exactly what the generic instantiation returns (same canonical summation order), filtered or not, both k widths."""
+    import os
+    torch = torch_cuda
+    n = 90_001
+    rng = np.random.default_rng(d)
+    rows16 = rng.standard_normal((n, d), dtype=np.float32).astype(np.float16)
+    code_mat = (np.arange(n) % 7).astype(np.int32)[None, :].copy()
+    sh = _shard(torch, rows16, code_mat)
+    qd = torch.from_numpy(rng.standard_normal((1, d), dtype=np.float32)).cuda()
+    for k in (10, 64):
+        for filt in (None, np.asarray([[3]], np.int32)):
+            out = {}
+            for v in ("1", "0"):
+                os.environ[knob] = v
+                try:
+                    out[v] = [t.clone() for t in sh.search_device(qd, k, filt=filt, algo=1)]
+                    torch.cuda.synchronize()
+                finally:
+                    os.environ.pop(knob, None)
+            a, b = out["1"], out["0"]
+            assert torch.equal(a[1], b[1]) and torch.equal(a[2], b[2]) and torch.equal(a[0].view(torch.int32), b[0].view(torch.int32))
+    sh.close()
+
+
 def test_store_adjacent_and_retriever_faces(torch_cuda):
     from githubrepostorag_b200.vector_store import B200VectorStore
     rng = np.random.default_rng(3)
