@@ -442,6 +442,13 @@ static int launch_k1_balanced(const crb_index* ix, const float* d_queries, int k
         default: fn = CRB_BAL(0, 2); break;
     }
 #undef CRB_BAL
+    // dim <= 512: the half-warp layout (two rows per warp step); dim = 384 has the exact three-slot instantiation
+    if (ch <= 2 && env_int("CODERAG_B200_K1_HALF", 1)) {
+        if (ix->dim == 384)
+            fn = k <= 32 ? static_cast<BalFn>(k1_balanced_kernel<2, 3, 1, 3>) : static_cast<BalFn>(k1_balanced_kernel<2, 3, 4, 3>);
+        else
+            fn = k <= 32 ? static_cast<BalFn>(k1_balanced_kernel<2, 3, 1, 4>) : static_cast<BalFn>(k1_balanced_kernel<2, 3, 4, 4>);
+    }
     const size_t dyn = size_t(ix->dim) * sizeof(float);
     static std::mutex mu;
     static std::map<std::pair<const void*, size_t>, int> cache;

@@ -660,7 +660,10 @@ __device__ __noinline__ void bal_merge_query(const BalParams& p, int qi, const u
 
 // CH = 16-byte chunks per lane (dim <= 256 * CH), all loads of a step issued before the first FMA;
 // CH = 0 walks any dimension with a run-time loop.
-template <int CH, int R, int KPL>
+// HC > 0 selects the half-warp layout of k1_stream_half_kernel for dim <= 512 (two rows per warp step, 16 lanes
+// each, HC chunk slots per half-lane; HC = 3 means exactly 48 chunks, i.e. dim = 384, without range tests); R then
+// counts row PAIRS per step and CH is ignored.  Same canonical summation order, so the same score bits.
+template <int CH, int R, int KPL, int HC = 0>
 __global__ void __launch_bounds__(kK1Threads, CH == 0 ? 1 : 2)
 k1_balanced_kernel(const __grid_constant__ BalParams p) {
     extern __shared__ float s_q[];  // [dim]
@@ -674,7 +677,8 @@ k1_balanced_kernel(const __grid_constant__ BalParams p) {
     const int warp = threadIdx.x >> 5;
     const int chunks = p.dim >> 3;
     const bool cosine = (p.metric == 0);
-    constexpr int64_t U = static_cast<int64_t>(kK1Warps) * R;   // rows per CTA step
+    constexpr int RW = HC > 0 ? 2 * R : R;                      // rows per warp step
+    constexpr int64_t U = static_cast<int64_t>(kK1Warps) * RW;  // rows per CTA step
 
     if (threadIdx.x == 0) {
         int64_t acc = 0;
@@ -724,13 +728,77 @@ k1_balanced_kernel(const __grid_constant__ BalParams p) {
         top.init(p.k, lane);
         // survivor indices of the NEXT step are fetched (lane j holds row j's) while this step's rows stream
         uint32_t idx_next = 0u;
-        if (list && lane < R && lo < hi && lo * U + static_cast<int64_t>(warp) * R + lane < n_items)
-            idx_next = list[lo * U + static_cast<int64_t>(warp) * R + lane];
+        if (list && lane < RW && lo < hi && lo * U + static_cast<int64_t>(warp) * RW + lane < n_items)
+            idx_next = list[lo * U + static_cast<int64_t>(warp) * RW + lane];
         for (int64_t u = lo; u < hi; ++u) {
-            const int64_t item0 = u * U + static_cast<int64_t>(warp) * R;
+            const int64_t item0 = u * U + static_cast<int64_t>(warp) * RW;
             const uint32_t idx_cur = idx_next;
             idx_next = 0u;
-            if (list && lane < R && u + 1 < hi && item0 + U + lane < n_items) idx_next = list[item0 + U + lane];
+            if (list && lane < RW && u + 1 < hi && item0 + U + lane < n_items) idx_next = list[item0 + U + lane];
+            if constexpr (HC > 0) {
+                const int half = lane >> 4, hl = lane & 15;
+                int64_t hrow[R];
+                bool hok[R];
+#pragma unroll
+                for (int j = 0; j < R; ++j) {
+                    const int it = 2 * j + half;
+                    hok[j] = (item0 + it) < n_items;
+                    const uint32_t li = __shfl_sync(CRB_FULL_MASK, idx_cur, it);
+                    hrow[j] = hok[j] ? (list ? static_cast<int64_t>(li) : item0 + it) : 0;
+                }
+                uint4 hv[R][HC];
+#pragma unroll
+                for (int j = 0; j < R; ++j) {
+                    const __half* rp = p.rows + hrow[j] * p.dim;
+#pragma unroll
+                    for (int cc = 0; cc < HC; ++cc)
+                        if (HC == 3 || hl + 16 * cc < chunks) hv[j][cc] = ld_stream_16(rp + (hl + 16 * cc) * 8);
+                }
+                float hinv[R];
+#pragma unroll
+                for (int j = 0; j < R; ++j) hinv[j] = cosine ? __ldg(p.inv_norm + hrow[j]) : 1.0f;
+                float a0[R], a1[R];
+#pragma unroll
+                for (int j = 0; j < R; ++j) { a0[j] = 0.f; a1[j] = 0.f; }
+                // canonical lane hl: chunks hl, hl+32 (slots 0, 2); canonical lane hl+16: chunks hl+16, hl+48 (slots 1, 3)
+#pragma unroll
+                for (int cc = 0; cc < HC; ++cc) {
+                    const int slot = cc == 0 ? 0 : (cc == 1 ? 2 : (cc == 2 ? 1 : 3));   // a0's chunks first, in order
+                    if (slot >= HC) continue;
+                    const int ch = hl + 16 * slot;
+                    if (HC == 3 || ch < chunks) {
+                        float q8[8];
+                        const float4 a = *reinterpret_cast<const float4*>(s_q + ch * 8);
+                        const float4 b = *reinterpret_cast<const float4*>(s_q + ch * 8 + 4);
+                        q8[0] = a.x; q8[1] = a.y; q8[2] = a.z; q8[3] = a.w;
+                        q8[4] = b.x; q8[5] = b.y; q8[6] = b.z; q8[7] = b.w;
+#pragma unroll
+                        for (int j = 0; j < R; ++j) {
+                            if (slot == 0 || slot == 2) a0[j] = chunk_fma(hv[j][slot], q8, a0[j]);
+                            else a1[j] = chunk_fma(hv[j][slot], q8, a1[j]);
+                        }
+                    }
+                }
+#pragma unroll
+                for (int j = 0; j < R; ++j) {
+                    float sc = a0[j] + a1[j];                               // canonical xor-16 level
+                    sc += __shfl_xor_sync(CRB_FULL_MASK, sc, 8);
+                    sc += __shfl_xor_sync(CRB_FULL_MASK, sc, 4);
+                    sc += __shfl_xor_sync(CRB_FULL_MASK, sc, 2);
+                    sc += __shfl_xor_sync(CRB_FULL_MASK, sc, 1);
+                    sc *= hinv[j];
+                    const bool good = hok[j] && !(cosine && hinv[j] == 0.f) && sc == sc;
+                    const uint64_t key = good ? make_key(sc, p.row_offset + static_cast<uint32_t>(hrow[j])) : 0ull;
+                    if (__any_sync(CRB_FULL_MASK, key > top.thr)) {
+#pragma unroll
+                        for (int h = 0; h < 2; ++h) {
+                            const uint64_t kh = __shfl_sync(CRB_FULL_MASK, key, h * 16);
+                            if (kh > top.thr) top.insert(kh, lane);
+                        }
+                    }
+                }
+                continue;
+            }
             int64_t row[R];
             bool ok[R];
             float acc[R];

@@ -196,7 +196,7 @@ def test_many_filters_one_query_vector(torch_cuda):
     sh.close()
 
 
-@pytest.mark.parametrize("d,k", [(384, 8), (768, 40), (1536, 5)])
+@pytest.mark.parametrize("d,k", [(384, 8), (768, 40), (1536, 5), (256, 8), (72, 40)])
 def test_skewed_fan_out_balanced_kernel(torch_cuda, d, k):
     """adjacent() fan-out with row sets from a handful of rows to the whole table: the balanced kernel
     (grid split by rows, not by group) must return exactly what the per-group kernel returns, and both
