@@ -177,3 +177,47 @@ def test_tensor_core_kernels_are_tcgen05_tma_tmem_without_spills(lib):
             assert "LOCAL:0" in ln, f"local memory in {fn}: {ln}"
             stack = int(re.search(r"STACK:(\d+)", ln).group(1))
             assert stack == 0, f"spill stack in {fn}: {ln}"
+
+
+def test_adjacent_searches_each_distinct_filter_once(lib, monkeypatch):
+    """Host logic of the graph-retriever fan-out, no GPU: edges that resolve to the same filter (an edge on a key the
+    caller's filter already pins, a repeated edge) become ONE query of the batched search, an edge that contradicts
+    the caller's filter becomes the impossible filter, and the merged result is the best k rows over all edges."""
+    from githubrepostorag_b200.types import TextNode
+    from githubrepostorag_b200.vector_store import B200VectorStore
+    st = B200VectorStore(dim=8)
+    st.add([TextNode(text=f"t{i}", metadata={"namespace": "ns", "repo": "a" if i < 3 else "b"}, id_=f"n{i}",
+                     embedding=[float(i + 1)] * 8) for i in range(6)])
+    seen = {}
+
+    def fake_search(queries, k, filters, algo=0):
+        seen["filters"] = [dict(f) for f in filters]
+        seen["queries"] = np.asarray(queries)
+        b = len(filters)
+        scores = np.full((b, k), -np.inf, np.float32)
+        rows = np.full((b, k), -1, np.int64)
+        nv = np.zeros(b, np.int32)
+        for i, f in enumerate(filters):
+            if "__impossible__" in f:
+                continue
+            hit = [r for r in range(6) if all(str(st._rows.meta(r).get(kk)) == str(v) for kk, v in f.items())][:k]
+            for j, r in enumerate(hit):
+                scores[i, j], rows[i, j] = 1.0 - 0.1 * r, r
+            nv[i] = len(hit)
+        return scores, rows, nv
+
+    class FakeShard:
+        def fetch_rows(self, rows):
+            return np.zeros((len(rows), 8), np.float32)
+
+    monkeypatch.setattr(st, "_ensure_built", lambda: None)
+    monkeypatch.setattr(st, "_search", fake_search)
+    monkeypatch.setattr(st, "_shard", FakeShard(), raising=False)
+    edges = [("namespace", "ns"), ("repo", "a"), ("repo", "a"), ("namespace", "other"), ("repo", "b")]
+    out = st.adjacent(edges, [0.5] * 8, k=4, filter={"namespace": "ns"})
+    flt = seen["filters"]
+    assert len(flt) == 4                                            # 5 edges: one repeated, none merged wrongly
+    assert {"namespace": "ns"} in flt and {"namespace": "ns", "repo": "a"} in flt and {"namespace": "ns", "repo": "b"} in flt
+    assert sum("__impossible__" in f for f in flt) == 1            # namespace=other contradicts the caller's filter
+    assert seen["queries"].shape == (4, 8)
+    assert [c.id for c in out] == ["n0", "n1", "n2", "n3"]          # best four rows over all edges, de-duplicated
