@@ -67,3 +67,55 @@ def test_bound_reread_schedule_is_dense_then_four_per_octave():
     for lo in (16, 64, 1024):
         assert sum(1 for v in due if lo <= v < 2 * lo) == 4
     assert len(due) == 8 + 4 * 9          # 8 dense visits, then four in each of the 9 octaves up to 4096
+
+
+def bitonic_desc(a):
+    """block_bitonic_desc (csrc/k2_gemm.cuh) restated: the compare-exchange schedule K5 sorts its candidates with."""
+    a = list(a)
+    n = len(a)
+    size = 2
+    while size <= n:
+        stride = size >> 1
+        while stride > 0:
+            for t in range(n >> 1):
+                i = 2 * t - (t & (stride - 1))
+                j = i + stride
+                desc = (i & size) == 0
+                if (a[i] < a[j]) == desc:
+                    a[i], a[j] = a[j], a[i]
+            stride >>= 1
+        size <<= 1
+    return a
+
+
+@settings(max_examples=60, deadline=None)
+@given(st.sampled_from([32, 64, 128, 256, 512, 1024, 2048]), st.integers(min_value=0, max_value=2**32 - 1))
+def test_k5_bitonic_schedule_sorts_descending(n, seed):
+    rng = np.random.default_rng(seed)
+    keys = rng.integers(0, 2**63 - 1, size=n, dtype=np.int64).tolist()
+    keys[: n // 4] = [0] * (n // 4)                 # zero padding, as K5 pads its list to a power of two
+    assert bitonic_desc(keys) == sorted(keys, reverse=True)
+
+
+@settings(max_examples=300, deadline=None)
+@given(st.integers(min_value=1, max_value=2048), st.integers(min_value=1, max_value=1200),
+       st.integers(min_value=2048, max_value=120000))
+def test_fallback_kernel_split_serves_every_flagged_query_once(nf, grid, cand_lists):
+    """k1_fallback_kernel (csrc/k1_stream.cuh): `grid` CTAs split themselves over `nf` flagged queries --
+    cpq CTAs per query, query f served by column f mod n_cols; every query gets exactly cpq lists and the
+    lists of different queries never overlap in the scratch region."""
+    cpq = min(grid // nf, cand_lists // nf, 1024)
+    cpq = max(cpq, 1)
+    n_cols = grid // cpq
+    assert n_cols >= 1
+    served = {}
+    for cta in range(grid):
+        col, x = cta // cpq, cta % cpq
+        if col >= n_cols:
+            continue
+        for f in range(col, nf, n_cols):
+            served.setdefault(f, []).append(x)
+    assert sorted(served) == list(range(nf))
+    for f, xs in served.items():
+        assert sorted(xs) == list(range(cpq))        # arrival count the last CTA waits for
+    assert nf * cpq <= cand_lists                    # scratch holds [flagged][cpq][k]; the library's region holds >= 8192 lists, a chunk <= 2048 queries
