@@ -130,9 +130,6 @@ struct crb_index {
     bool k2_ok = false;            // corpus tensor map encoded
     CUtensorMap map_rows;          // fp16 [n_rows, dim], box 64 x 256, 128 B swizzle
     CUtensorMap map_rows_half;     // same, box 64 x 128 (one CTA's half tile in the pair kernel)
-    cudaStream_t aux_stream = nullptr;   // side stream for the co-running second K2 kernel
-    cudaEvent_t aux_fork = nullptr, aux_join = nullptr;
-    std::mutex aux_mu;                   // one co-running launch enqueues at a time
     std::mutex mu;
     std::condition_variable cv;
     std::vector<crb::Lane> lanes;
@@ -557,7 +554,6 @@ static int launch_k2(crb_index* ix, const float* d_queries, int batch, int k, in
         if (!attr_done[dv]) {
             CRB_CUDA(cudaFuncSetAttribute(k2_gemm_topk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
             CRB_CUDA(cudaFuncSetAttribute(k2_gemm_topk_pair_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-            CRB_CUDA(cudaFuncSetAttribute(k2_gemm_topk_quad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
             attr_done[dv] = true;
         }
     }
@@ -639,82 +635,9 @@ static int launch_k2(crb_index* ix, const float* d_queries, int batch, int k, in
             kp.stages = pair_stages(mi);
             const size_t smem = 1024 + size_t(kp.stages) * kK2PairStageBytes + size_t(mi) * list_bytes + tail_bytes +
                                 size_t(mi) * 1024;
-            // 4-CTA clusters (two pairs sharing every query k-block by TMA multicast) when the device can keep
-            // enough of them resident; CODERAG_B200_K2_QUAD=0/1 forces
-            int quad_clusters = 0;
-            const int quad_env = env_int("CODERAG_B200_K2_QUAD", -1);
-            if (quad_env != 0 && n_tiles >= 2) {
-                cudaLaunchConfig_t cfg;
-                memset(&cfg, 0, sizeof cfg);
-                cfg.gridDim = dim3(4 * 64);
-                cfg.blockDim = dim3(kK2Threads);
-                cfg.dynamicSmemBytes = smem;
-                cudaLaunchAttribute at;
-                at.id = cudaLaunchAttributeClusterDimension;
-                at.val.clusterDim.x = 4; at.val.clusterDim.y = 1; at.val.clusterDim.z = 1;
-                cfg.attrs = &at; cfg.numAttrs = 1;
-                // the answer depends on the device and the shared-memory size only: ask once
-                static std::mutex occ_mu;
-                static std::map<std::pair<int, size_t>, int> occ_cache;
-                std::lock_guard<std::mutex> lk(occ_mu);
-                auto okey = std::make_pair(ix->device, smem);
-                auto oit = occ_cache.find(okey);
-                if (oit == occ_cache.end()) {
-                    int max_clusters = 0;
-                    if (cudaOccupancyMaxActiveClusters(&max_clusters, k2_gemm_topk_quad_kernel, &cfg) != cudaSuccess)
-                        max_clusters = 0;
-                    (void)cudaGetLastError();
-                    oit = occ_cache.emplace(okey, max_clusters).first;
-                }
-                quad_clusters = oit->second;
-            }
-            // Co-run: 4-CTA clusters fit only part of the machine (132 of 148 SMs on B200: GPCs whose SM count
-            // is not a multiple of 4 strand a TPC each).  Give the clusters their share of the corpus tiles and
-            // run the CTA-pair kernel on the stranded SMs at the same time, on a side stream.
-            const int corun_env = env_int("CODERAG_B200_K2_CORUN", -1);
-            const int stranded_pairs = (ix->sm_count - quad_clusters * 4) / 2;
-            const bool corun = quad_clusters >= kp.m_tiles && kp.m_tiles == 1 && stranded_pairs >= 1 && n_tiles >= 4096 &&
-                               corun_env > 0;   // opt-in: interleaved A/B shows no gain at B=1024 (12.17 / 11.95 vs 11.48 / 12.14 ms)
-            std::unique_lock<std::mutex> aux_lock(ix->aux_mu, std::defer_lock);
-            if (corun && aux_lock.try_lock()) {
-                if (!ix->aux_stream) {
-                    CRB_CUDA(cudaStreamCreateWithFlags(&ix->aux_stream, cudaStreamNonBlocking));
-                    CRB_CUDA(cudaEventCreateWithFlags(&ix->aux_fork, cudaEventDisableTiming));
-                    CRB_CUDA(cudaEventCreateWithFlags(&ix->aux_join, cudaEventDisableTiming));
-                }
-                CUtensorMap map_q64;
-                if (int rc = make_map_f16(&map_q64, q16, n_pad, ix->dim, kK2BlockM / 2)) return rc;
-                const int cslots = quad_clusters;
-                // per-SM the clusters are ~1.14x faster (a quarter less L2->SM traffic)
-                const double w_quad = cslots * 4 * (env_int("CODERAG_B200_K2_CORUN_W", 114) / 100.0), w_pair = stranded_pairs * 2.0;
-                int64_t split = static_cast<int64_t>(double(n_tiles) * w_quad / (w_quad + w_pair));
-                split -= split % 2;
-                K2Params kq = kp, kr = kp;
-                kq.slots = 2 * cslots; kq.slots_total = 2 * cslots + stranded_pairs; kq.slot_base = 0;
-                kq.tile_lo = 0; kq.tile_hi = split;
-                kr.slots = stranded_pairs; kr.slots_total = kq.slots_total; kr.slot_base = 2 * cslots;
-                kr.tile_lo = split; kr.tile_hi = n_tiles;
-                kp.slots = kq.slots_total;                       // what K5 walks per query
-                CRB_CUDA(cudaEventRecord(ix->aux_fork, stream));
-                CRB_CUDA(cudaStreamWaitEvent(ix->aux_stream, ix->aux_fork, 0));
-                k2_gemm_topk_quad_kernel<<<4 * cslots, kK2Threads, smem, stream>>>(map_q64, *map_half, kq);
-                CRB_LAUNCH_CHECK();
-                k2_gemm_topk_pair_kernel<<<2 * stranded_pairs, kK2Threads, smem, ix->aux_stream>>>(map_q, *map_half, kr);
-                CRB_LAUNCH_CHECK();
-                CRB_CUDA(cudaEventRecord(ix->aux_join, ix->aux_stream));
-                CRB_CUDA(cudaStreamWaitEvent(stream, ix->aux_join, 0));
-            } else if (quad_clusters >= kp.m_tiles && (quad_env > 0 || quad_clusters * 4 >= (ix->sm_count * 9) / 10)) {
-                CUtensorMap map_q64;
-                if (int rc = make_map_f16(&map_q64, q16, n_pad, ix->dim, kK2BlockM / 2)) return rc;
-                int cslots = std::max(1, quad_clusters / kp.m_tiles);
-                cslots = static_cast<int>(std::min<int64_t>(cslots, (n_tiles + 1) / 2));
-                kp.slots = 2 * cslots;
-                k2_gemm_topk_quad_kernel<<<4 * kp.m_tiles * cslots, kK2Threads, smem, stream>>>(map_q64, *map_half, kp);
-            } else {
-                kp.slots = std::max(1, (ix->sm_count / 2) / kp.m_tiles);
-                kp.slots = static_cast<int>(std::min<int64_t>(kp.slots, std::max<int64_t>(n_tiles, 1)));
-                k2_gemm_topk_pair_kernel<<<2 * kp.m_tiles * kp.slots, kK2Threads, smem, stream>>>(map_q, *map_half, kp);
-            }
+            kp.slots = std::max(1, (ix->sm_count / 2) / kp.m_tiles);
+            kp.slots = static_cast<int>(std::min<int64_t>(kp.slots, std::max<int64_t>(n_tiles, 1)));
+            k2_gemm_topk_pair_kernel<<<2 * kp.m_tiles * kp.slots, kK2Threads, smem, stream>>>(map_q, *map_half, kp);
         } else {
             kp.m_tiles = (n + kK2BlockM - 1) / kK2BlockM;
             kp.slots = std::max(1, ix->sm_count / kp.m_tiles);
@@ -1275,9 +1198,6 @@ extern "C" int crb_tombstone_rows(crb_index* ix, const int64_t* h_rows_idx, int3
 extern "C" int crb_index_destroy(crb_index* ix) {
     if (!ix) return 0;
     DeviceGuard guard(ix->device);
-    if (ix->aux_stream) { cudaStreamSynchronize(ix->aux_stream); cudaStreamDestroy(ix->aux_stream); }
-    if (ix->aux_fork) cudaEventDestroy(ix->aux_fork);
-    if (ix->aux_join) cudaEventDestroy(ix->aux_join);
     for (auto& l : ix->lanes) {
         if (l.stream) cudaStreamSynchronize(l.stream);
         if (l.d_ws) cudaFree(l.d_ws);

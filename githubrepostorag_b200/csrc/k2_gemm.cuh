@@ -56,12 +56,6 @@ struct K2Params {
     int32_t debug;              // timing experiments only: 1 = no TMA after the first fill, 2 = no epilogue math
     int32_t lstride;            // candidate-list stride = query rows that own a list (<= 128)
     int32_t m_inner;            // pair kernel: query-tile pairs served per corpus tile by one CTA pair (>= 1)
-    // A launch may cover only corpus tiles [tile_lo, tile_hi) and write its candidate lists at
-    // slot_base.. of slots_total per query (two kernels splitting one shard run side by side).
-    int64_t tile_lo;
-    int64_t tile_hi;            // 0 = all tiles
-    int32_t slot_base;
-    int32_t slots_total;        // 0 = slots
 };
 
 // ---- PTX wrappers ------------------------------------------------------------------------------
@@ -645,9 +639,7 @@ k2_gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap map_q, const __grid
     const int pair = blockIdx.x >> 1;
     const int m_group = pair % p.m_tiles;
     const int slot = pair / p.m_tiles;
-    const int64_t all_tiles = (p.n_rows + kK2BlockN - 1) / kK2BlockN;
-    const int64_t n_tiles = p.tile_hi > 0 ? (p.tile_hi < all_tiles ? p.tile_hi : all_tiles) : all_tiles;
-    const int slots_total = p.slots_total > 0 ? p.slots_total : p.slots;
+    const int64_t n_tiles = (p.n_rows + kK2BlockN - 1) / kK2BlockN;
     const int k_blocks = (p.dim + kK2BlockK - 1) / kK2BlockK;
     // first query row of this CTA for inner index j
     auto m_row0 = [&](int j) { return (m_group * MI + j) * 256 + static_cast<int>(rank) * kK2BlockM; };
@@ -674,7 +666,7 @@ k2_gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap map_q, const __grid
         if (lane == 0) {
             int st = 0;
             uint32_t ph = 0;
-            for (int64_t t = p.tile_lo + slot; t < n_tiles; t += p.slots) {
+            for (int64_t t = slot; t < n_tiles; t += p.slots) {
                 for (int j = 0; j < MI; ++j) {
                     const int a_row = m_row0(j);
                     for (int kb = 0; kb < k_blocks; ++kb) {
@@ -703,7 +695,7 @@ k2_gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap map_q, const __grid
             int st = 0;
             uint32_t ph = 0;
             int64_t it = 0;
-            for (int64_t t = p.tile_lo + slot; t < n_tiles; t += p.slots) {
+            for (int64_t t = slot; t < n_tiles; t += p.slots) {
                 for (int j = 0; j < MI; ++j, ++it) {
                     const int buf = static_cast<int>(it & 1);
                     const uint32_t use = static_cast<uint32_t>(it >> 1);
@@ -749,7 +741,7 @@ k2_gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap map_q, const __grid
         };
         float pre[2] = {qnan, qnan};
         int64_t it = 0;
-        for (int64_t t = p.tile_lo + slot; t < n_tiles; t += p.slots) {
+        for (int64_t t = slot; t < n_tiles; t += p.slots) {
             const int64_t n0 = t * kK2BlockN;
             for (int j = 0; j < MI; ++j, ++it) {
                 const int buf = static_cast<int>(it & 1);
@@ -813,251 +805,11 @@ k2_gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap map_q, const __grid
         for (int j = 0; j < MI; ++j) {
             const int qrow = m_row0(j) + row;
             if (qrow < p.batch && row < p.lstride) {
-                uint64_t* out = p.cand + (static_cast<int64_t>(qrow) * slots_total + p.slot_base + slot) * p.kprime;
+                uint64_t* out = p.cand + (static_cast<int64_t>(qrow) * p.slots + slot) * p.kprime;
                 const uint64_t* my_list = lists + static_cast<size_t>(j) * list_elems + row;
                 const int count = static_cast<int>(s_state[j * 128 + row]);
                 for (int i = 0; i < p.kprime; ++i) out[i] = i < count ? my_list[i * p.lstride] : 0ull;
-                p.tau[static_cast<int64_t>(qrow) * slots_total + p.slot_base + slot] =
-                    count == p.kprime ? key_score(my_list[0]) : __uint_as_float(0xff800000u);
-            }
-        }
-    }
-
-    tc_fence_before();
-    cluster_sync_all();          // the peer may still be reading this CTA's smem / signalling its barriers
-    if (warp == 1) {
-        tc_fence_after();
-        tmem_dealloc_pair(tmem_base, kK2TmemCols);
-    }
-}
-
-CRB_DEVINL void tma_load_2d_pair_mc(const CUtensorMap* map, void* smem_dst, uint32_t bar_addr, int32_t c0, int32_t c1,
-                                    uint16_t cta_mask) {
-    asm volatile(
-        "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster"
-        " [%0], [%1, {%4, %5}], [%2], %3;"
-        ::"r"(smem_u32(smem_dst)), "l"(reinterpret_cast<uint64_t>(map)), "r"(bar_addr), "h"(cta_mask), "r"(c0), "r"(c1)
-        : "memory");
-}
-CRB_DEVINL void umma_commit_mask(uint64_t* bar, uint16_t mask) {
-    asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
-                 ::"r"(smem_u32(bar)), "h"(mask) : "memory");
-}
-
-// ---- 4-CTA cluster variant: two CTA pairs on adjacent corpus tiles share each query k-block ------------
-// Both pairs of a cluster work on the same query tile pair at the same time, so the A operand (query rows)
-// of CTA r is identical to that of CTA r+2: each fetches half of it and TMA-multicasts it to both, which
-// cuts the L2->SM traffic per flop by a quarter (24 KB instead of 32 KB per CTA per k-block).  A stage is
-// written by the sibling pair too, so it is released only when BOTH pairs' MMAs have consumed it
-// (empty barriers count 2, the leaders' commits go to all four CTAs).
-__global__ void __cluster_dims__(4, 1, 1) __launch_bounds__(kK2Threads, 1)
-k2_gemm_topk_quad_kernel(const __grid_constant__ CUtensorMap map_q64, const __grid_constant__ CUtensorMap map_c,
-                         const __grid_constant__ K2Params p) {
-    extern __shared__ __align__(1024) uint8_t smem_raw[];
-    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-    const int MI = p.m_inner;
-    uint8_t* stage_base = smem;
-    uint64_t* lists = reinterpret_cast<uint64_t*>(smem + static_cast<size_t>(p.stages) * kK2PairStageBytes);
-    const size_t list_elems = static_cast<size_t>(p.kprime) * p.lstride;        // one query tile's lists
-    float* s_inv = reinterpret_cast<float*>(lists + static_cast<size_t>(MI) * list_elems);
-    float* s_thr = s_inv + 2 * kK2BlockN;                                       // [MI][128]
-    uint32_t* s_state = reinterpret_cast<uint32_t*>(s_thr + MI * 128);          // [MI][128]
-    uint64_t* bars = reinterpret_cast<uint64_t*>(s_state + MI * 128);
-    uint64_t* full_bar = bars;
-    uint64_t* empty_bar = bars + p.stages;
-    uint64_t* tfull_bar = bars + 2 * p.stages;
-    uint64_t* tempty_bar = bars + 2 * p.stages + 2;
-    uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 2 * p.stages + 4);
-
-    const int warp = threadIdx.x >> 5;
-    const int lane = threadIdx.x & 31;
-    const uint32_t crank = cluster_ctarank();        // 0..3
-    const uint32_t pr = crank >> 1;                  // pair inside the cluster
-    const uint32_t rank = crank & 1u;                // CTA inside its pair
-    const bool leader = (rank == 0);
-    const uint32_t lead_rank = pr * 2u;              // cluster rank of this pair's leader
-    const int cid = blockIdx.x >> 2;
-    const int m_group = cid % p.m_tiles;
-    const int cslot = cid / p.m_tiles;
-    const int cslots = p.slots >> 1;                 // clusters per query group; p.slots = candidate lists per query
-    const int slot = cslot * 2 + static_cast<int>(pr);
-    const int64_t all_tiles = (p.n_rows + kK2BlockN - 1) / kK2BlockN;
-    const int64_t n_tiles = p.tile_hi > 0 ? (p.tile_hi < all_tiles ? p.tile_hi : all_tiles) : all_tiles;
-    const int slots_total = p.slots_total > 0 ? p.slots_total : p.slots;
-    const int64_t n_tile_pairs = (n_tiles - p.tile_lo + 1) / 2;  // both pairs run every iteration (a missing tile reads as zeros)
-    const int k_blocks = (p.dim + kK2BlockK - 1) / kK2BlockK;
-    // first query row of this CTA for inner index j
-    auto m_row0 = [&](int j) { return (m_group * MI + j) * 256 + static_cast<int>(rank) * kK2BlockM; };
-
-    if (threadIdx.x == 0) {
-        for (int s = 0; s < p.stages; ++s) {
-            mbar_init(&full_bar[s], 2);
-            mbar_init(&empty_bar[s], 2);      // released by BOTH pairs: the sibling pair multicasts into this stage
-        }
-        for (int b = 0; b < 2; ++b) {
-            mbar_init(&tfull_bar[b], 1);
-            mbar_init(&tempty_bar[b], 256);
-        }
-        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-    }
-    if (warp == 1) tmem_alloc_pair(tmem_ptr, kK2TmemCols);
-    tc_fence_before();
-    cluster_sync_all();          // barriers of BOTH CTAs are initialised before anyone signals them
-    tc_fence_after();
-    const uint32_t tmem_base = *tmem_ptr;
-
-    if (warp == 0) {
-        // ===== TMA producer (one per CTA): own A rows + own half of the corpus tile =====
-        if (lane == 0) {
-            int st = 0;
-            uint32_t ph = 0;
-            for (int64_t u = cslot; u < n_tile_pairs; u += cslots) {
-                const int64_t t = p.tile_lo + 2 * u + pr;
-                for (int j = 0; j < MI; ++j) {
-                    const int a_row = m_row0(j);
-                    for (int kb = 0; kb < k_blocks; ++kb) {
-                        mbar_wait(&empty_bar[st], ph ^ 1u);
-                        uint8_t* a = stage_base + static_cast<size_t>(st) * kK2PairStageBytes;
-                        uint8_t* b = a + kK2StageBytesA;
-                        const uint32_t full_leader = mapa_u32(smem_u32(&full_bar[st]), lead_rank);
-                        const uint32_t full_mc = smem_u32(&full_bar[st]) & 0xFEFFFFFFu;   // pair-leader barrier, per destination
-                        if (leader) mbar_expect_tx(&full_bar[st], 2 * kK2PairStageBytes);
-                        // query rows: this CTA fetches HALF of its 128-row A tile and multicasts it to the CTA of
-                        // the sibling pair that needs the same rows (ranks r and r+2); the sibling supplies the other half
-                        tma_load_2d_pair_mc(&map_q64, a + pr * (kK2StageBytesA / 2), full_mc, kb * kK2BlockK,
-                                            a_row + static_cast<int>(pr) * (kK2BlockM / 2),
-                                            static_cast<uint16_t>((1u << rank) | (1u << (rank + 2u))));
-                        tma_load_2d_pair(&map_c, b, full_leader, kb * kK2BlockK,
-                                         static_cast<int32_t>(t * kK2BlockN + rank * (kK2BlockN / 2)));
-                        if (!leader) mbar_arrive_cluster(full_leader);
-                        if (++st == p.stages) { st = 0; ph ^= 1u; }
-                    }
-                }
-            }
-        }
-    } else if (warp == 1) {
-        // ===== MMA issuer: the leader CTA only =====
-        if (leader && lane == 0) {
-            int st = 0;
-            uint32_t ph = 0;
-            int64_t it = 0;
-            for (int64_t u = cslot; u < n_tile_pairs; u += cslots) {
-                const int64_t t = p.tile_lo + 2 * u + pr;
-                for (int j = 0; j < MI; ++j, ++it) {
-                    const int buf = static_cast<int>(it & 1);
-                    const uint32_t use = static_cast<uint32_t>(it >> 1);
-                    mbar_wait(&tempty_bar[buf], (use & 1u) ^ 1u);
-                    tc_fence_after();
-                    const uint32_t d_tmem = tmem_base + static_cast<uint32_t>(buf * kK2BlockN);
-                    for (int kb = 0; kb < k_blocks; ++kb) {
-                        mbar_wait(&full_bar[st], ph);
-                        tc_fence_after();
-                        const uint32_t a_addr = smem_u32(stage_base + static_cast<size_t>(st) * kK2PairStageBytes);
-                        const uint32_t b_addr = a_addr + kK2StageBytesA;
-#pragma unroll
-                        for (int k = 0; k < kK2BlockK / kK2UmmaK; ++k) {
-                            const uint64_t da = umma_desc_sw128(a_addr + k * kK2UmmaK * 2);
-                            const uint64_t db = umma_desc_sw128(b_addr + k * kK2UmmaK * 2);
-                            umma_f16_pair(d_tmem, da, db, kK2PairIDesc, (kb | k) != 0 ? 1u : 0u);
-                        }
-                        umma_commit_mask(&empty_bar[st], 0xF);
-                        if (++st == p.stages) { st = 0; ph ^= 1u; }
-                    }
-                    umma_commit_mask(&tfull_bar[buf], static_cast<uint16_t>(0x3u << lead_rank));
-                }
-            }
-        }
-    } else {
-        // ===== epilogue: this CTA's 128 query rows of each query tile of the group =====
-        const int quarter = warp & 3;
-        const int row = quarter * 32 + lane;
-        const int tid_e = threadIdx.x - 64;
-        const bool cosine = (p.metric == 0);
-        const float qnan = __uint_as_float(0x7fc00000u);
-        for (int j = 0; j < MI; ++j) {
-            const bool v = (m_row0(j) + row) < p.batch && row < p.lstride;
-            s_thr[j * 128 + row] = v ? __uint_as_float(0xff800000u) : __uint_as_float(0x7f800000u);   // -inf / +inf
-            s_state[j * 128 + row] = 0u;
-        }
-        auto column_scale = [&](int64_t n) -> float {
-            if (n >= p.n_rows || n >= n_tiles * kK2BlockN) return qnan;   // also: a pair's dummy tile past this launch's range
-            if (p.mask && !((p.mask[n >> 5] >> (n & 31)) & 1u)) return qnan;
-            const float in = __ldg(p.inv_norm + n);          // NaN = deleted row
-            if (!cosine) return in == in ? 1.0f : qnan;
-            return in > 0.f ? in : qnan;
-        };
-        float pre[2] = {qnan, qnan};
-        int64_t it = 0;
-        for (int64_t u = cslot; u < n_tile_pairs; u += cslots) {
-                const int64_t t = p.tile_lo + 2 * u + pr;
-            const int64_t n0 = t * kK2BlockN;
-            for (int j = 0; j < MI; ++j, ++it) {
-                const int buf = static_cast<int>(it & 1);
-                const uint32_t use = static_cast<uint32_t>(it >> 1);
-                float* inv = s_inv + buf * kK2BlockN;
-                if (it == 0) { pre[0] = column_scale(n0 + tid_e); pre[1] = column_scale(n0 + tid_e + 128); }
-                inv[tid_e] = pre[0];
-                inv[tid_e + 128] = pre[1];
-                // scales of the NEXT item's corpus tile (the same tile until j wraps)
-                const int64_t nt = (j + 1 < MI) ? t : t + 2 * static_cast<int64_t>(cslots);
-                if (nt != t) {
-                    pre[0] = column_scale(nt * kK2BlockN + tid_e);
-                    pre[1] = column_scale(nt * kK2BlockN + tid_e + 128);
-                }
-                uint64_t* my_list = lists + static_cast<size_t>(j) * list_elems + row;
-                float thr = s_thr[j * 128 + row];
-                uint32_t state = s_state[j * 128 + row];
-                const int qrow_g = m_row0(j) + row;
-                const bool g_live = p.gthr && qrow_g < p.batch && row < p.lstride;
-                uint32_t* my_g = p.gthr + static_cast<int64_t>(qrow_g) * p.gthr_groups;
-                const bool g_read = g_live && k2_gthr_due(static_cast<int>(it / MI), p.gthr_every);
-                uint32_t gr[16];
-#pragma unroll
-                for (int i = 0; i < 16; ++i) gr[i] = 0u;
-                if (g_read) k2_gthr_issue16(my_g, gr);
-                epi_bar_sync();
-                mbar_wait(&tfull_bar[buf], use & 1u);
-                tc_fence_after();
-                uint32_t g_ord = k2_gthr_fold16(gr);
-                if (g_read && p.gthr_groups > 16) g_ord = min(g_ord, k2_gthr_min(my_g + 16, p.gthr_groups - 16));
-                thr = fmaxf(thr, k2_gthr_float(g_ord));
-                float item_best = __uint_as_float(0xff800000u);
-                const uint32_t t_row = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) +
-                                       static_cast<uint32_t>(buf * kK2BlockN);
-                const uint32_t inv_s = smem_u32(inv);
-                const int n_chunks = (p.debug & 2) ? 0 : kK2BlockN / 32;
-                if (p.gthr && p.gthr_prepass && it < MI)
-                    thr = k2_first_visit(t_row, inv_s, n_chunks, g_live, my_g, p.gthr_groups, t, thr);
-                const float thr0 = thr;
-                uint32_t va[32], vb[32];
-                if (n_chunks > 0) {
-                    tmem_ld32(t_row, va);
-                    tmem_ld_wait();
-                }
-#pragma unroll 1
-                for (int c = 0; c < n_chunks; c += 2) {
-                    tmem_ld32(t_row + (c + 1) * 32, vb);
-                    thr = k2_scan_chunk(va, inv_s + c * 128, thr, state, my_list, n0 + c * 32, p.kprime, p.lstride, item_best);
-                    tmem_ld_wait();
-                    if (c + 2 < n_chunks) tmem_ld32(t_row + (c + 2) * 32, va);
-                    thr = k2_scan_chunk(vb, inv_s + (c + 1) * 128, thr, state, my_list, n0 + (c + 1) * 32, p.kprime, p.lstride, item_best);
-                    tmem_ld_wait();
-                }
-                tc_fence_before();
-                mbar_arrive_cluster(mapa_u32(smem_u32(&tempty_bar[buf]), lead_rank));
-                s_thr[j * 128 + row] = thr;
-                s_state[j * 128 + row] = state;
-                if (g_live && item_best > thr0) k2_gthr_publish(my_g, p.gthr_groups, t, item_best);
-            }
-        }
-        for (int j = 0; j < MI; ++j) {
-            const int qrow = m_row0(j) + row;
-            if (qrow < p.batch && row < p.lstride) {
-                uint64_t* out = p.cand + (static_cast<int64_t>(qrow) * slots_total + p.slot_base + slot) * p.kprime;
-                const uint64_t* my_list = lists + static_cast<size_t>(j) * list_elems + row;
-                const int count = static_cast<int>(s_state[j * 128 + row]);
-                for (int i = 0; i < p.kprime; ++i) out[i] = i < count ? my_list[i * p.lstride] : 0ull;
-                p.tau[static_cast<int64_t>(qrow) * slots_total + p.slot_base + slot] =
+                p.tau[static_cast<int64_t>(qrow) * p.slots + slot] =
                     count == p.kprime ? key_score(my_list[0]) : __uint_as_float(0xff800000u);
             }
         }

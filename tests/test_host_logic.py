@@ -160,7 +160,9 @@ def test_tensor_core_kernels_are_tcgen05_tma_tmem_without_spills(lib):
             per_fn[cur] = []
         elif cur is not None:
             per_fn[cur].append(ln)
-    for tag in ("k2_gemm_topk_kernel", "k2_gemm_topk_pair_kernel", "k2_gemm_topk_quad_kernel"):
+    # every TMA load is a plain (non-multicast) tile load; the only cluster multicast is tcgen05.commit (UTCBAR)
+    assert not re.search(r"UTMALDG[.\w]*MULTICAST", sass), "a TMA multicast load is in the library"
+    for tag in ("k2_gemm_topk_kernel", "k2_gemm_topk_pair_kernel"):
         names = [n for n in per_fn if tag in n]
         assert names, f"{tag} not in the library"
         body = "\n".join(per_fn[names[0]])
