@@ -16,13 +16,13 @@ from typing import Optional
 _LIB_PATH = Path(__file__).resolve().parent / "_lib" / "libcoderag_b200.so"
 _lib: Optional[C.CDLL] = None
 
-ABI_VERSION = 1
+ABI_VERSION = 2
 METRIC_COSINE = 0
 METRIC_IP = 1
 FILT_ANY = -1
 FILT_IMPOSSIBLE = -2
 CODE_MISSING = -1
-MAX_KEYS = 8
+MAX_KEYS = 16
 MAX_TOPK = 128
 MAX_DIM = 4096
 NOALLOC_MAX_BATCH = 4
@@ -41,6 +41,7 @@ PROTOTYPES = {
     "crb_last_error": (C.c_char_p, []),
     "crb_index_create": (C.c_int, [C.POINTER(_vp), _vp, _vp, _vp, _i64, _i32, _i32, _i64, _i32]),
     "crb_index_destroy": (C.c_int, [_vp]),
+    "crb_index_reload_tuning": (C.c_int, [_vp]),
     "crb_index_rebind": (C.c_int, [_vp, _vp, _vp, _vp, _i64, _i64]),
     "crb_tombstone_rows": (C.c_int, [_vp, _vp, _i32]),
     "crb_encode_rows": (C.c_int, [_vp, _vp, _vp, _i64, _i32, _i32, _vp]),

@@ -73,10 +73,58 @@ struct DeviceGuard {
     }
 };
 
-static int env_int(const char* name, int dflt) {
-    const char* v = getenv(name);
-    return (v && *v) ? atoi(v) : dflt;
-}
+// Tuning knobs (CODERAG_B200_* environment variables).  They are read ONCE per index -- at crb_index_create,
+// and again only when the host calls crb_index_reload_tuning -- never on the search path: the worker runs ten
+// searching threads, and getenv next to a setenv elsewhere in the process is a data race.  None of them changes
+// a result bit; the result-changing timing experiments exist only in -DCRB_TUNING builds.
+struct Tuning {
+    int lanes = 4;            // CODERAG_B200_LANES: stream + staging lanes of the host-buffer entry points
+    int compact_mb = 1024;    // CODERAG_B200_COMPACT_MB: cap of the survivor-compaction buffer
+    int k1_rows = 0;          // _K1_ROWS: rows in flight per warp, single-query groups (0 = default per width)
+    int k1_ex = 1;            // _K1_EX: exact-width instantiation at dim 768
+    int k1_half = 1;          // _K1_HALF: half-warp layout for dim <= 512
+    int k1_e3 = 1;            // _K1_E3: exact three-slot half-warp instantiation at dim 384
+    int k1_half_pairs = 0;    // _K1_HALF_PAIRS: row pairs in flight, half-warp layout (0 = default)
+    int k1_group = 0;         // _K1_GROUP: queries per streaming group (0 = default)
+    int k1_fused = -1;        // _K1_FUSED: fused filter+score kernel for one query under one filter (-1 = plan decides)
+    int k1_balanced = 1;      // _K1_BALANCED: balanced kernel for fan-outs
+    int k2_pair = -1;         // _K2_PAIR: force the CTA-pair kernel on/off (-1 = by batch)
+    int k2_minner = 0;        // _K2_MINNER: query-tile pairs per corpus tile (0 = default)
+    int k2_gthr = 1;          // _K2_GTHR: shared admission bound
+    int k2_gthr_every = 0;    // _K2_GTHR_EVERY: fixed re-read cadence of the bound (0 = schedule)
+    int k2_prepass = 1;       // _K2_PREPASS: first accumulator tile read twice
+    int k2_kprime = 16;       // candidates per list for k <= 10 (CRB_TUNING builds read _K2_KPRIME)
+    int k2_prefetch = 0;      // CRB_TUNING builds only
+    int k2_debug = 0;         // CRB_TUNING builds only
+    static int env(const char* name, int dflt) {
+        const char* v = getenv(name);
+        return (v && *v) ? atoi(v) : dflt;
+    }
+    static Tuning from_env() {
+        Tuning t;
+        t.lanes = std::max(1, env("CODERAG_B200_LANES", t.lanes));
+        t.compact_mb = std::max(0, env("CODERAG_B200_COMPACT_MB", t.compact_mb));
+        t.k1_rows = env("CODERAG_B200_K1_ROWS", t.k1_rows);
+        t.k1_ex = env("CODERAG_B200_K1_EX", t.k1_ex);
+        t.k1_half = env("CODERAG_B200_K1_HALF", t.k1_half);
+        t.k1_e3 = env("CODERAG_B200_K1_E3", t.k1_e3);
+        t.k1_half_pairs = env("CODERAG_B200_K1_HALF_PAIRS", t.k1_half_pairs);
+        t.k1_group = env("CODERAG_B200_K1_GROUP", t.k1_group);
+        t.k1_fused = env("CODERAG_B200_K1_FUSED", t.k1_fused);
+        t.k1_balanced = env("CODERAG_B200_K1_BALANCED", t.k1_balanced);
+        t.k2_pair = env("CODERAG_B200_K2_PAIR", t.k2_pair);
+        t.k2_minner = env("CODERAG_B200_K2_MINNER", t.k2_minner);
+        t.k2_gthr = env("CODERAG_B200_K2_GTHR", t.k2_gthr);
+        t.k2_gthr_every = std::max(0, env("CODERAG_B200_K2_GTHR_EVERY", t.k2_gthr_every));
+        t.k2_prepass = env("CODERAG_B200_K2_PREPASS", t.k2_prepass);
+#ifdef CRB_TUNING
+        t.k2_kprime = env("CODERAG_B200_K2_KPRIME", t.k2_kprime);
+        t.k2_prefetch = env("CODERAG_B200_K2_PREFETCH", 0);
+        t.k2_debug = env("CODERAG_B200_K2_DEBUG", 0);
+#endif
+        return t;
+    }
+};
 
 // ---------------------------------------------------------------------------------------------
 // workspace layout
@@ -94,8 +142,8 @@ constexpr int64_t kK2SmallBatchRows = 131072;           // from here on even a 2
 // k' (candidates kept per query per CTA) for a requested k
 // (shared memory holds k' x 128 keys next to >= 2 pipeline stages, which caps k' at 120)
 constexpr int kK2MaxKPrime = 120;
-static inline int k2_kprime(int k) {
-    if (k <= 10) return std::max(k + 2, getenv("CODERAG_B200_K2_KPRIME") ? atoi(getenv("CODERAG_B200_K2_KPRIME")) : 16);
+static inline int k2_kprime(int k, int kprime_small = 16) {
+    if (k <= 10) return std::max(k + 2, kprime_small);
     return std::min<int>(kK2MaxKPrime, static_cast<int>(round_up(k + k / 2, 8)));
 }
 static inline bool k2_supports_k(int k) { return k2_kprime(k) >= k + 2; }
@@ -130,6 +178,7 @@ struct crb_index {
     bool k2_ok = false;            // corpus tensor map encoded
     CUtensorMap map_rows;          // fp16 [n_rows, dim], box 64 x 256, 128 B swizzle
     CUtensorMap map_rows_half;     // same, box 64 x 128 (one CTA's half tile in the pair kernel)
+    crb::Tuning tune;
     std::mutex mu;
     std::condition_variable cv;
     std::vector<crb::Lane> lanes;
@@ -165,7 +214,7 @@ static WsLayout ws_layout(const crb_index* ix, int batch, int k) {
     // batch is one tile, sm_count/2 when CTA pairs serve every query tile of the batch (m-inner)
     const size_t n_lists = std::max<size_t>(std::min<size_t>(nmax, kK2BlockM) * ix->sm_count, nmax * size_t(ix->sm_count / 2 + 1)) + nmax;
     L.tau = o;     o += round_up(n_lists * 4, 256);     // one float per list
-    L.cand2 = o;   o += round_up(n_lists * k2_kprime(k) * 8, 1024);
+    L.cand2 = o;   o += round_up(n_lists * k2_kprime(k, ix->tune.k2_kprime) * 8, 1024);
     L.filt = o;
     L.per_filter = size_t(list_stride_of(ix)) * 4 + size_t(mask_stride_of(ix)) * 4;
     return L;
@@ -236,11 +285,10 @@ static K1Fn k1_pick(int nq, int ch, int r, int k) {
 #undef CRB_K1_CASE
     return nullptr;
 }
-// default rows-in-flight per (NQ, CH); CODERAG_B200_K1_ROWS overrides for NQ == 1 (tuning sweeps)
-static int k1_default_rows(int nq, int ch) {
+// default rows-in-flight per (NQ, CH); Tuning::k1_rows overrides for NQ == 1 (tuning sweeps)
+static int k1_default_rows(int nq, int ch, int env = 0) {
     if (nq == 1) {
         const int def[5] = {0, 8, 6, 4, 3};
-        const int env = env_int("CODERAG_B200_K1_ROWS", 0);
         if (env > 0 && k1_pick(1, ch, env, 10)) return env;
         return def[ch];
     }
@@ -297,16 +345,17 @@ static int launch_k1(const crb_index* ix, const float* d_queries, int k, int met
     const int chunks = ix->dim / 8;
     const int ch = (chunks + 31) / 32;
     const bool generic = ch > 4;
-    int r1 = generic ? 2 : k1_default_rows(nq, ch);
+    const Tuning& tn = ix->tune;
+    int r1 = generic ? 2 : k1_default_rows(nq, ch, tn.k1_rows);
     K1Fn fn = generic ? k1_pick_generic(k) : k1_pick(nq, ch, r1, k);
-    if (!generic && nq == 1 && chunks == 32 * ch && env_int("CODERAG_B200_K1_EX", 1)) {
+    if (!generic && nq == 1 && chunks == 32 * ch && tn.k1_ex) {
         if (K1Fn ex_fn = k1_pick_exact(ch, r1, k)) fn = ex_fn;
     }
-    if (!generic && ch <= 2 && nq <= 2 && env_int("CODERAG_B200_K1_HALF", 1)) {
+    if (!generic && ch <= 2 && nq <= 2 && tn.k1_half) {
         // short rows: two rows per warp step (bit-identical scores, fewer instructions per row)
         // dim = 384 has its own instantiation (exactly three chunks per half-lane, fewer registers): 4 pairs in flight
-        const bool e3 = ix->dim == 384 && nq == 1 && env_int("CODERAG_B200_K1_E3", 1);
-        const int rp = nq == 1 ? std::min(std::max(env_int("CODERAG_B200_K1_HALF_PAIRS", e3 ? 4 : 3), 2), 4) : (nq == 2 ? 2 : 1);
+        const bool e3 = ix->dim == 384 && nq == 1 && tn.k1_e3;
+        const int rp = nq == 1 ? std::min(std::max(tn.k1_half_pairs > 0 ? tn.k1_half_pairs : (e3 ? 4 : 3), 2), 4) : (nq == 2 ? 2 : 1);
         fn = k1_pick_half(nq, rp, k, e3);
         r1 = 2 * rp;
     }
@@ -440,7 +489,7 @@ static int launch_k1_balanced(const crb_index* ix, const float* d_queries, int k
     }
 #undef CRB_BAL
     // dim <= 512: the half-warp layout (two rows per warp step); dim = 384 has the exact three-slot instantiation
-    if (ch <= 2 && env_int("CODERAG_B200_K1_HALF", 1)) {
+    if (ch <= 2 && ix->tune.k1_half) {
         if (ix->dim == 384)
             fn = k <= 32 ? static_cast<BalFn>(k1_balanced_kernel<2, 3, 1, 3>) : static_cast<BalFn>(k1_balanced_kernel<2, 3, 4, 3>);
         else
@@ -512,11 +561,11 @@ static int launch_k2(crb_index* ix, const float* d_queries, int batch, int k, in
                      const uint32_t* surv_list = nullptr, const uint32_t* surv_count = nullptr,
                      int64_t n_surv = -1, uint8_t* compact_buf = nullptr, size_t compact_cap = 0,
                      const ExchangeDev* ex = nullptr) {
-    const int kprime = k2_kprime(k);
+    const int kprime = k2_kprime(k, ix->tune.k2_kprime);
 
     // Filtered set with a known, small survivor count: gather the survivors into a dense buffer and
     // run the GEMM on those rows only (flops and bytes scale with selectivity, not with the shard).
-    const __half* k2_rows = ix->rows;
+
     const float* k2_inv = ix->inv_norm;
     int64_t k2_n = ix->n_rows;
     const CUtensorMap* map_full = &ix->map_rows;
@@ -537,13 +586,13 @@ static int launch_k2(crb_index* ix, const float* d_queries, int batch, int k, in
             }
             if (int rc = make_map_f16(&cmap_full, c_rows, n_surv, ix->dim, kK2BlockN)) return rc;
             if (int rc = make_map_f16(&cmap_half, c_rows, n_surv, ix->dim, kK2BlockN / 2)) return rc;
-            k2_rows = c_rows; k2_inv = c_inv; k2_n = n_surv;
+            k2_inv = c_inv; k2_n = n_surv;
             map_full = &cmap_full; map_half = &cmap_half;
             remap = surv_list;
             mask = nullptr;
         }
     }
-    (void)k2_rows;
+
     const size_t tail_bytes = 2 * kK2BlockN * 4 + 256;
     // opt in to 227 KB of dynamic shared memory: a per-device attribute, set once per device ordinal
     {
@@ -557,8 +606,8 @@ static int launch_k2(crb_index* ix, const float* d_queries, int batch, int k, in
             attr_done[dv] = true;
         }
     }
-    // CTA pairs (cta_group::2) pay off once there are >= 2 query tiles; CODERAG_B200_K2_PAIR=0/1 forces.
-    const int pair_env = env_int("CODERAG_B200_K2_PAIR", -1);
+    // CTA pairs (cta_group::2) pay off once there are >= 2 query tiles; Tuning::k2_pair = 0/1 forces.
+    const int pair_env = ix->tune.k2_pair;
 
     __half* q16 = reinterpret_cast<__half*>(ws + L.q16);
     float* invq = reinterpret_cast<float*>(ws + L.invq);
@@ -589,10 +638,10 @@ static int launch_k2(crb_index* ix, const float* d_queries, int batch, int k, in
         if (int rc = make_map_f16(&map_q, q16, n_pad, ix->dim, kK2BlockM)) return rc;
         K2Params kp;
         memset(&kp, 0, sizeof kp);
-        kp.gthr = env_int("CODERAG_B200_K2_GTHR", 1) ? reinterpret_cast<uint32_t*>(ws + L.gthr) : nullptr;
+        kp.gthr = ix->tune.k2_gthr ? reinterpret_cast<uint32_t*>(ws + L.gthr) : nullptr;
         kp.gthr_groups = groups;
-        kp.gthr_every = std::max(0, env_int("CODERAG_B200_K2_GTHR_EVERY", 0));   // 0 = dense first, then four reads per octave
-        kp.gthr_prepass = env_int("CODERAG_B200_K2_PREPASS", 1);
+        kp.gthr_every = ix->tune.k2_gthr_every;   // 0 = dense first, then four reads per octave
+        kp.gthr_prepass = ix->tune.k2_prepass;
         kp.inv_norm = k2_inv;
         kp.mask = mask;
         kp.cand = cand2;
@@ -610,8 +659,8 @@ static int launch_k2(crb_index* ix, const float* d_queries, int batch, int k, in
         const int stages1 = static_cast<int>(std::min<size_t>(smem_room / kK2StageBytes, 4));
         if (stages1 < 2) return fail("internal: K2 does not fit shared memory for k'=%d", kprime);
         const bool use_pair = pair_env >= 0 ? (pair_env != 0) : (n > kK2BlockM);
-        kp.prefetch = env_int("CODERAG_B200_K2_PREFETCH", 0);
-        kp.debug = env_int("CODERAG_B200_K2_DEBUG", 0);
+        kp.prefetch = ix->tune.k2_prefetch;
+        kp.debug = ix->tune.k2_debug;
         if (use_pair) {
             const int m_pairs = (n + 255) / 256;                // query tile PAIRS
             // m-inner: one CTA pair serves up to 4 query-tile pairs per corpus tile while their candidate
@@ -622,7 +671,7 @@ static int launch_k2(crb_index* ix, const float* d_queries, int batch, int k, in
             //  interleaved A/B -- and 4 pairs read the corpus from HBM once instead of 1.4 times (ncu: 15.4 vs 21.6 GB);
             //  2 pairs stay 4 % ahead on shards of a few million rows, where HBM is idle anyway)
             const int mi_default = m_pairs <= 4 ? (n_tiles >= 20000 ? 4 : 2) : 4;
-            int mi = std::min(m_pairs, std::max(1, env_int("CODERAG_B200_K2_MINNER", mi_default)));
+            int mi = std::min(m_pairs, std::max(1, ix->tune.k2_minner > 0 ? ix->tune.k2_minner : mi_default));
             auto pair_stages = [&](int mi_) {
                 const size_t fixed_b = size_t(mi_) * list_bytes + tail_bytes + size_t(mi_) * 1024;
                 return static_cast<int>(std::min<size_t>((size_t(227) * 1024 - 1024 - fixed_b) / kK2PairStageBytes, 8));
@@ -785,13 +834,13 @@ static int search_impl(crb_index* ix, const float* d_queries, int batch, int k, 
     // everywhere (1M x 384, 10 % filter, B=4: 0.132 ms vs 0.089 ms; unfiltered 12.5M x 384: 10.3 ms vs 2 x 3.9 ms),
     // because the streaming kernel is instruction-bound and the four-query variant fits one CTA per SM only
     // (profiles/group_width_probe.py, small_batch_dispatch.py).
-    const int nq_group = std::max(1, std::min(nq_cap, env_int("CODERAG_B200_K1_GROUP", ch > 4 ? 1 : 2)));
+    const int nq_group = std::max(1, std::min(nq_cap, ix->tune.k1_group > 0 ? ix->tune.k1_group : (ch > 4 ? 1 : 2)));
 
     // one query under one satisfiable filter: filter and score in one pass, no survivor list.  OPT-IN
     // (CODERAG_B200_K1_FUSED=1): measured 6 % faster than K3 + K1 at 1 % selectivity (10M x 1024: 84.8 vs 89.9 us)
     // but slower when most rows pass (the scan and the scoring share one warp's registers and serialise their
     // memory latencies), and the plan has no selectivity estimate to choose by.
-    if (batch == 1 && F == 1 && ch <= 4 && algo != 2 && ix->n_rows > 0 && env_int("CODERAG_B200_K1_FUSED", 0)) {
+    if (batch == 1 && F == 1 && ch <= 4 && algo != 2 && ix->n_rows > 0 && ix->tune.k1_fused > 0) {
         bool impossible = false;
         for (int m = 0; m < M; ++m) impossible |= (filters[0][m] == CRB_FILT_IMPOSSIBLE);
         if (!impossible)
@@ -920,7 +969,7 @@ static int search_impl(crb_index* ix, const float* d_queries, int batch, int k, 
             // single-query groups over different row sets (the adjacent() fan-out): split the grid by rows, not by group
             bool any_filtered = false;
             for (const QueryGroup& g : groups) any_filtered |= (g.filter >= 0);
-            const bool balanced = max_group == 1 && groups.size() >= 2 && any_filtered && env_int("CODERAG_B200_K1_BALANCED", 1);
+            const bool balanced = max_group == 1 && groups.size() >= 2 && any_filtered && ix->tune.k1_balanced;
             int rc = balanced ? launch_k1_balanced(ix, d_queries, k, metric, groups, slot_of_filter, ws, lists, d_scores,
                                                    d_rows, d_n_valid, d_keys, stream, ex)
                               : launch_k1(ix, d_queries, k, metric, groups, slot_of_filter, nq, ws, lists, d_scores,
@@ -1149,7 +1198,8 @@ extern "C" int crb_index_create(crb_index** out, const void* d_rows_f16, const f
     ix->row_offset = row_offset;
     ix->dim = dim;
     ix->n_keys = n_keys;
-    ix->lanes.resize(std::max(1, env_int("CODERAG_B200_LANES", 4)));
+    ix->tune = Tuning::from_env();
+    ix->lanes.resize(ix->tune.lanes);
     if (int rc = bind_buffers(ix, d_rows_f16, d_inv_norm, d_codes, n_rows, n_rows)) {
         delete ix;
         return rc;
@@ -1170,6 +1220,14 @@ extern "C" int crb_index_rebind(crb_index* ix, const void* d_rows_f16, const flo
     DeviceGuard guard(ix->device);
     CRB_CUDA(guard.status);
     return bind_buffers(ix, d_rows_f16, d_inv_norm, d_codes, n_rows, code_stride);
+}
+
+extern "C" int crb_index_reload_tuning(crb_index* ix) {
+    if (!ix) return fail("index is NULL");
+    const int lanes = ix->tune.lanes;
+    ix->tune = Tuning::from_env();
+    ix->tune.lanes = lanes;          // the lane pool is sized at creation
+    return 0;
 }
 
 extern "C" int crb_tombstone_rows(crb_index* ix, const int64_t* h_rows_idx, int32_t n) {
@@ -1243,7 +1301,7 @@ extern "C" size_t crb_workspace_bytes(const crb_index* ix, int32_t batch, int32_
     if (lists > 0 && batch > 1) {
         // room to compact the survivors of a filtered tensor-core batch (up to a quarter of the shard,
         // capped by CODERAG_B200_COMPACT_MB, default 1024)
-        const size_t cap = size_t(std::max(env_int("CODERAG_B200_COMPACT_MB", 1024), 0)) << 20;
+        const size_t cap = size_t(ix->tune.compact_mb) << 20;
         const size_t quarter = size_t(ix->n_rows / 4 + 1) * (size_t(ix->dim) * 2 + 4) + 4096;
         total = round_up(total, 1024) + std::min(cap, quarter);
     }

@@ -9,10 +9,11 @@
 
 namespace crb {
 
-constexpr int kMaxKeys = 8;      // CRB_MAX_KEYS
+constexpr int kMaxKeys = 16;     // CRB_MAX_KEYS
 constexpr int kMaxTopK = 128;    // CRB_MAX_TOPK
 constexpr int kMaxGroups = 64;   // query groups per launch
 constexpr int kMaxFilters = 32;  // distinct filters per launch (one u32 pass-bit each in K3)
+static_assert(kMaxKeys == 16, "kMaxKeys must equal CRB_MAX_KEYS of include/coderag_b200.h");
 
 // ---- order-preserving (score, row) keys ------------------------------------------------
 // key = ord(score) << 32 | global_row.  Larger key == better hit; among equal scores the

@@ -52,11 +52,21 @@ struct K2Params {
     int32_t m_tiles;
     int32_t slots;              // CTAs per m-tile; grid = m_tiles * slots
     int32_t stages;
-    int32_t prefetch;           // L2-prefetch the next corpus tile
-    int32_t debug;              // timing experiments only: 1 = no TMA after the first fill, 2 = no epilogue math
+    int32_t prefetch;           // CRB_TUNING builds only: L2-prefetch the next corpus tile
+    int32_t debug;              // CRB_TUNING builds only (timing experiments that change results): 1 = no TMA after the first fill, 2 = no epilogue math
     int32_t lstride;            // candidate-list stride = query rows that own a list (<= 128)
     int32_t m_inner;            // pair kernel: query-tile pairs served per corpus tile by one CTA pair (>= 1)
 };
+
+// Timing experiments (stale tiles, no epilogue, L2 prefetch) exist only in -DCRB_TUNING builds; the shipped
+// library has none of those branches.
+#ifdef CRB_TUNING
+#define CRB_K2_DEBUG(p) ((p).debug)
+#define CRB_K2_PREFETCH(p) ((p).prefetch)
+#else
+#define CRB_K2_DEBUG(p) 0
+#define CRB_K2_PREFETCH(p) 0
+#endif
 
 // ---- PTX wrappers ------------------------------------------------------------------------------
 CRB_DEVINL uint32_t smem_u32(const void* p) { return static_cast<uint32_t>(__cvta_generic_to_shared(p)); }
@@ -310,6 +320,76 @@ CRB_DEVINL float k2_first_visit(uint32_t t_row, uint32_t inv_s, int n_chunks, bo
     return g_live ? fmaxf(thr, k2_gthr_float(gm)) : thr;
 }
 
+// Per-column scale of corpus row n: inverse norm (cosine) or 1 (inner product); NaN = "this column is not a
+// hit" (past the end, filtered out, deleted or zero-norm) -- NaN never passes `>`.
+CRB_DEVINL float k2_column_scale(const K2Params& p, int64_t n) {
+    const float qnan = __uint_as_float(0x7fc00000u);
+    if (n >= p.n_rows) return qnan;
+    if (p.mask && !((p.mask[n >> 5] >> (n & 31)) & 1u)) return qnan;
+    const float in = __ldg(p.inv_norm + n);          // NaN = deleted row
+    if (p.metric != 0) return in == in ? 1.0f : qnan;
+    return in > 0.f ? in : qnan;
+}
+
+// One accumulator tile (128 query rows x 256 corpus rows) through the epilogue, for the thread that owns query
+// row `qrow` (TMEM lane quarter*32 + lane): fold the shared bound, wait for the tile, scan it into the thread's
+// list.  Shared by the single-CTA and the CTA-pair kernel; the caller stages the column scales in `inv`,
+// releases the accumulator buffer afterwards and keeps `thr` / `state` between tiles.
+//   visit       how many corpus tiles this list has seen (schedules the re-reads of the bound)
+//   first_pass  true on the list's first tile (read twice, see k2_first_visit)
+CRB_DEVINL void k2_epilogue_tile(const K2Params& p, const float* inv, uint64_t* tfull, uint32_t tfull_parity,
+                                 uint32_t t_row, uint64_t* my_list, float& thr, uint32_t& state, int qrow,
+                                 bool q_live, int visit, bool first_pass, int64_t tile) {
+    const int64_t n0 = tile * kK2BlockN;
+    uint32_t* my_g = p.gthr + static_cast<int64_t>(qrow) * p.gthr_groups;
+    const bool g_live = p.gthr && q_live;
+    const bool g_read = g_live && k2_gthr_due(visit, p.gthr_every);
+    uint32_t gr[16];
+#pragma unroll
+    for (int i = 0; i < 16; ++i) gr[i] = 0u;
+    if (g_read) k2_gthr_issue16(my_g, gr);
+    epi_bar_sync();
+    mbar_wait(tfull, tfull_parity);
+    tc_fence_after();
+    uint32_t g_ord = k2_gthr_fold16(gr);
+    if (g_read && p.gthr_groups > 16) g_ord = min(g_ord, k2_gthr_min(my_g + 16, p.gthr_groups - 16));
+    thr = fmaxf(thr, k2_gthr_float(g_ord));
+    float item_best = __uint_as_float(0xff800000u);
+    // TMEM -> registers one 32-column chunk ahead of the chunk being examined.  The common case per chunk is:
+    // 8 broadcast LDS.128 of the column scales, 32 FMUL, a max tree and ONE branch; only a chunk that holds a
+    // new candidate walks its 32 columns.
+    const uint32_t inv_s = smem_u32(inv);
+    const int n_chunks = (CRB_K2_DEBUG(p) & 2) ? 0 : kK2BlockN / 32;
+    if (p.gthr && p.gthr_prepass && first_pass)
+        thr = k2_first_visit(t_row, inv_s, n_chunks, g_live, my_g, p.gthr_groups, tile, thr);
+    const float thr0 = thr;
+    uint32_t va[32], vb[32];
+    if (n_chunks > 0) {
+        tmem_ld32(t_row, va);
+        tmem_ld_wait();
+    }
+#pragma unroll 1
+    for (int c = 0; c < n_chunks; c += 2) {
+        tmem_ld32(t_row + (c + 1) * 32, vb);
+        thr = k2_scan_chunk(va, inv_s + c * 128, thr, state, my_list, n0 + c * 32, p.kprime, p.lstride, item_best);
+        tmem_ld_wait();
+        if (c + 2 < n_chunks) tmem_ld32(t_row + (c + 2) * 32, va);
+        thr = k2_scan_chunk(vb, inv_s + (c + 1) * 128, thr, state, my_list, n0 + (c + 1) * 32, p.kprime, p.lstride, item_best);
+        tmem_ld_wait();
+    }
+    tc_fence_before();
+    if (g_live && item_best > thr0) k2_gthr_publish(my_g, p.gthr_groups, tile, item_best);
+}
+
+// Flush a thread's list: the candidates, and tau = the best score the list may have dropped (the root of a
+// full min-heap; -inf while the list never filled).
+CRB_DEVINL void k2_flush_list(const K2Params& p, const uint64_t* my_list, int count, int qrow, int slot) {
+    uint64_t* out = p.cand + (static_cast<int64_t>(qrow) * p.slots + slot) * p.kprime;
+    for (int i = 0; i < p.kprime; ++i) out[i] = i < count ? my_list[i * p.lstride] : 0ull;
+    p.tau[static_cast<int64_t>(qrow) * p.slots + slot] =
+        count == p.kprime ? key_score(my_list[0]) : __uint_as_float(0xff800000u);
+}
+
 // ---- query preparation -------------------------------------------------------------------------
 // q_hat = q / ||q|| (canonical norm), q16 = fp16(q_hat); eps = ||q_hat - q16||_2 + 2^-16.
 __global__ void __launch_bounds__(128) k2_prep_queries_kernel(const float* __restrict__ queries,
@@ -403,7 +483,7 @@ k2_gemm_topk_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_cons
             for (int64_t t = slot; t < n_tiles; t += p.slots) {
                 // One CTA of each slot pulls the slot's NEXT corpus tile into L2 a whole tile-time
                 // ahead, so the demand loads below (and those of the other query tiles) hit L2.
-                if (p.prefetch && m_tile == 0 && t + p.slots < n_tiles) {
+                if (CRB_K2_PREFETCH(p) && m_tile == 0 && t + p.slots < n_tiles) {
                     for (int kb = 0; kb < k_blocks; ++kb)
                         tma_prefetch_l2_2d(&map_c, kb * kK2BlockK, static_cast<int32_t>((t + p.slots) * kK2BlockN));
                 }
@@ -411,7 +491,7 @@ k2_gemm_topk_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_cons
                     mbar_wait(&empty_bar[st], ph ^ 1u);
                     uint8_t* a = stage_base + static_cast<size_t>(st) * kK2StageBytes;
                     uint8_t* b = a + kK2StageBytesA;
-                    if ((p.debug & 1) && (t != slot || kb >= p.stages)) {
+                    if ((CRB_K2_DEBUG(p) & 1) && (t != slot || kb >= p.stages)) {
                         mbar_arrive(&full_bar[st]);
                     } else {
                         mbar_expect_tx(&full_bar[st], kK2StageBytes);
@@ -454,22 +534,14 @@ k2_gemm_topk_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_cons
     } else {
         // ===== epilogue: 4 warps = 128 TMEM lanes = 128 query rows =====
         const int quarter = warp & 3;                 // TMEM lane quarter this warp may access
-        const int row = quarter * 32 + lane;          // query row inside the tile
-        const int et = row;                           // list column of this thread
+        const int row = quarter * 32 + lane;          // query row inside the tile = list column of this thread
         const int tid_e = threadIdx.x - 64;           // 0..127 (staging role only)
-        const bool q_valid = (m_tile * kK2BlockM + row) < p.batch && row < p.lstride;
-        const bool cosine = (p.metric == 0);
-        uint64_t* my_list = lists + et;               // entry i at my_list[i * lstride]
+        const int qrow = m_tile * kK2BlockM + row;
+        const bool q_valid = qrow < p.batch && row < p.lstride;
+        uint64_t* my_list = lists + row;              // entry i at my_list[i * lstride]
         uint32_t state = 0;                           // entries in the list
         float thr = q_valid ? __uint_as_float(0xff800000u) : __uint_as_float(0x7f800000u);  // -inf / +inf
         const float qnan = __uint_as_float(0x7fc00000u);
-        auto column_scale = [&](int64_t n) -> float {
-            if (n >= p.n_rows) return qnan;
-            if (p.mask && !((p.mask[n >> 5] >> (n & 31)) & 1u)) return qnan;
-            const float in = __ldg(p.inv_norm + n);          // NaN = deleted row
-            if (!cosine) return in == in ? 1.0f : qnan;
-            return in > 0.f ? in : qnan;
-        };
         float pre[2] = {qnan, qnan};
 
         int64_t it = 0;
@@ -477,68 +549,23 @@ k2_gemm_topk_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_cons
             const int buf = static_cast<int>(it & 1);
             const uint32_t use = static_cast<uint32_t>(it >> 1);
             const int64_t n0 = t * kK2BlockN;
-            // per-column scale: inv_norm (cosine) or 1 (ip); NaN = "this column is not a hit".
-            // The values for THIS tile were fetched from global memory during the previous tile.
+            // The column scales for THIS tile were fetched from global memory during the previous tile.
             float* inv = s_inv + buf * kK2BlockN;
-            if (it == 0) { pre[0] = column_scale(n0 + tid_e); pre[1] = column_scale(n0 + tid_e + 128); }
+            if (it == 0) { pre[0] = k2_column_scale(p, n0 + tid_e); pre[1] = k2_column_scale(p, n0 + tid_e + 128); }
             inv[tid_e] = pre[0];
             inv[tid_e + 128] = pre[1];
             if (t + p.slots < n_tiles) {
                 const int64_t nn = (t + p.slots) * kK2BlockN;
-                pre[0] = column_scale(nn + tid_e);
-                pre[1] = column_scale(nn + tid_e + 128);
+                pre[0] = k2_column_scale(p, nn + tid_e);
+                pre[1] = k2_column_scale(p, nn + tid_e + 128);
             }
-            uint32_t* my_g = p.gthr + static_cast<int64_t>(m_tile * kK2BlockM + row) * p.gthr_groups;
-            const bool g_live = p.gthr && q_valid;
-            const bool g_read = g_live && k2_gthr_due(static_cast<int>(it), p.gthr_every);
-            uint32_t gr[16];
-#pragma unroll
-            for (int i = 0; i < 16; ++i) gr[i] = 0u;
-            if (g_read) k2_gthr_issue16(my_g, gr);
-            epi_bar_sync();
-            mbar_wait(&tfull_bar[buf], use & 1u);
-            tc_fence_after();
-            uint32_t g_ord = k2_gthr_fold16(gr);
-            if (g_read && p.gthr_groups > 16) g_ord = min(g_ord, k2_gthr_min(my_g + 16, p.gthr_groups - 16));
-            thr = fmaxf(thr, k2_gthr_float(g_ord));
-            float item_best = __uint_as_float(0xff800000u);
             const uint32_t t_row = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) +
                                    static_cast<uint32_t>(buf * kK2BlockN);
-            // TMEM -> registers one 32-column chunk ahead of the chunk being examined.  The common
-            // case per chunk is: 8 broadcast LDS.128 of the column scales, 32 FMUL, a max tree and
-            // ONE branch; only a chunk that holds a new candidate walks its 32 columns.
-            const uint32_t inv_s = smem_u32(inv);
-            const int n_chunks = (p.debug & 2) ? 0 : kK2BlockN / 32;
-            if (p.gthr && p.gthr_prepass && it == 0)
-                thr = k2_first_visit(t_row, inv_s, n_chunks, g_live, my_g, p.gthr_groups, t, thr);
-            const float thr0 = thr;
-            uint32_t va[32], vb[32];
-            if (n_chunks > 0) {
-                tmem_ld32(t_row, va);
-                tmem_ld_wait();
-            }
-#pragma unroll 1
-            for (int c = 0; c < n_chunks; c += 2) {
-                tmem_ld32(t_row + (c + 1) * 32, vb);
-                thr = k2_scan_chunk(va, inv_s + c * 128, thr, state, my_list, n0 + c * 32, p.kprime, p.lstride, item_best);
-                tmem_ld_wait();
-                if (c + 2 < n_chunks) tmem_ld32(t_row + (c + 2) * 32, va);
-                thr = k2_scan_chunk(vb, inv_s + (c + 1) * 128, thr, state, my_list, n0 + (c + 1) * 32, p.kprime, p.lstride, item_best);
-                tmem_ld_wait();
-            }
-            tc_fence_before();
+            k2_epilogue_tile(p, inv, &tfull_bar[buf], use & 1u, t_row, my_list, thr, state, qrow, q_valid,
+                             static_cast<int>(it), it == 0, t);
             mbar_arrive(&tempty_bar[buf]);
-            if (g_live && item_best > thr0) k2_gthr_publish(my_g, p.gthr_groups, t, item_best);
         }
-        // flush this CTA's list for the query
-        if (q_valid) {
-            uint64_t* out = p.cand + (static_cast<int64_t>(m_tile * kK2BlockM + row) * p.slots + slot) * p.kprime;
-            const int count = static_cast<int>(state);
-            for (int i = 0; i < p.kprime; ++i) out[i] = i < count ? my_list[i * p.lstride] : 0ull;
-            // a full list is a min-heap: its root is the best score it may have dropped
-            p.tau[static_cast<int64_t>(m_tile * kK2BlockM + row) * p.slots + slot] =
-                count == p.kprime ? key_score(my_list[0]) : __uint_as_float(0xff800000u);
-        }
+        if (q_valid) k2_flush_list(p, my_list, static_cast<int>(state), qrow, slot);
     }
 
     tc_fence_before();
@@ -674,7 +701,7 @@ k2_gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap map_q, const __grid
                         uint8_t* a = stage_base + static_cast<size_t>(st) * kK2PairStageBytes;
                         uint8_t* b = a + kK2StageBytesA;
                         const uint32_t full_leader = mapa_u32(smem_u32(&full_bar[st]), 0);
-                        if ((p.debug & 1) && (t != slot || j != 0 || kb >= p.stages)) {
+                        if ((CRB_K2_DEBUG(p) & 1) && (t != slot || j != 0 || kb >= p.stages)) {
                             // timing experiment: no TMA after the first fill (MMA runs on stale tiles)
                             if (leader) mbar_arrive(&full_bar[st]); else mbar_arrive_cluster(full_leader);
                         } else {
@@ -725,20 +752,12 @@ k2_gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap map_q, const __grid
         const int quarter = warp & 3;
         const int row = quarter * 32 + lane;
         const int tid_e = threadIdx.x - 64;
-        const bool cosine = (p.metric == 0);
         const float qnan = __uint_as_float(0x7fc00000u);
         for (int j = 0; j < MI; ++j) {
             const bool v = (m_row0(j) + row) < p.batch && row < p.lstride;
             s_thr[j * 128 + row] = v ? __uint_as_float(0xff800000u) : __uint_as_float(0x7f800000u);   // -inf / +inf
             s_state[j * 128 + row] = 0u;
         }
-        auto column_scale = [&](int64_t n) -> float {
-            if (n >= p.n_rows) return qnan;
-            if (p.mask && !((p.mask[n >> 5] >> (n & 31)) & 1u)) return qnan;
-            const float in = __ldg(p.inv_norm + n);          // NaN = deleted row
-            if (!cosine) return in == in ? 1.0f : qnan;
-            return in > 0.f ? in : qnan;
-        };
         float pre[2] = {qnan, qnan};
         int64_t it = 0;
         for (int64_t t = slot; t < n_tiles; t += p.slots) {
@@ -747,71 +766,33 @@ k2_gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap map_q, const __grid
                 const int buf = static_cast<int>(it & 1);
                 const uint32_t use = static_cast<uint32_t>(it >> 1);
                 float* inv = s_inv + buf * kK2BlockN;
-                if (it == 0) { pre[0] = column_scale(n0 + tid_e); pre[1] = column_scale(n0 + tid_e + 128); }
+                if (it == 0) { pre[0] = k2_column_scale(p, n0 + tid_e); pre[1] = k2_column_scale(p, n0 + tid_e + 128); }
                 inv[tid_e] = pre[0];
                 inv[tid_e + 128] = pre[1];
                 // scales of the NEXT item's corpus tile (the same tile until j wraps)
                 const int64_t nt = (j + 1 < MI) ? t : t + p.slots;
                 if (nt < n_tiles && nt != t) {
-                    pre[0] = column_scale(nt * kK2BlockN + tid_e);
-                    pre[1] = column_scale(nt * kK2BlockN + tid_e + 128);
+                    pre[0] = k2_column_scale(p, nt * kK2BlockN + tid_e);
+                    pre[1] = k2_column_scale(p, nt * kK2BlockN + tid_e + 128);
                 }
                 uint64_t* my_list = lists + static_cast<size_t>(j) * list_elems + row;
                 float thr = s_thr[j * 128 + row];
                 uint32_t state = s_state[j * 128 + row];
-                const int qrow_g = m_row0(j) + row;
-                const bool g_live = p.gthr && qrow_g < p.batch && row < p.lstride;
-                uint32_t* my_g = p.gthr + static_cast<int64_t>(qrow_g) * p.gthr_groups;
-                const bool g_read = g_live && k2_gthr_due(static_cast<int>(it / MI), p.gthr_every);
-                uint32_t gr[16];
-#pragma unroll
-                for (int i = 0; i < 16; ++i) gr[i] = 0u;
-                if (g_read) k2_gthr_issue16(my_g, gr);
-                epi_bar_sync();
-                mbar_wait(&tfull_bar[buf], use & 1u);
-                tc_fence_after();
-                uint32_t g_ord = k2_gthr_fold16(gr);
-                if (g_read && p.gthr_groups > 16) g_ord = min(g_ord, k2_gthr_min(my_g + 16, p.gthr_groups - 16));
-                thr = fmaxf(thr, k2_gthr_float(g_ord));
-                float item_best = __uint_as_float(0xff800000u);
+                const int qrow = m_row0(j) + row;
                 const uint32_t t_row = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) +
                                        static_cast<uint32_t>(buf * kK2BlockN);
-                const uint32_t inv_s = smem_u32(inv);
-                const int n_chunks = (p.debug & 2) ? 0 : kK2BlockN / 32;
-                if (p.gthr && p.gthr_prepass && it < MI)
-                    thr = k2_first_visit(t_row, inv_s, n_chunks, g_live, my_g, p.gthr_groups, t, thr);
-                const float thr0 = thr;
-                uint32_t va[32], vb[32];
-                if (n_chunks > 0) {
-                    tmem_ld32(t_row, va);
-                    tmem_ld_wait();
-                }
-#pragma unroll 1
-                for (int c = 0; c < n_chunks; c += 2) {
-                    tmem_ld32(t_row + (c + 1) * 32, vb);
-                    thr = k2_scan_chunk(va, inv_s + c * 128, thr, state, my_list, n0 + c * 32, p.kprime, p.lstride, item_best);
-                    tmem_ld_wait();
-                    if (c + 2 < n_chunks) tmem_ld32(t_row + (c + 2) * 32, va);
-                    thr = k2_scan_chunk(vb, inv_s + (c + 1) * 128, thr, state, my_list, n0 + (c + 1) * 32, p.kprime, p.lstride, item_best);
-                    tmem_ld_wait();
-                }
-                tc_fence_before();
+                k2_epilogue_tile(p, inv, &tfull_bar[buf], use & 1u, t_row, my_list, thr, state, qrow,
+                                 qrow < p.batch && row < p.lstride, static_cast<int>(it / MI), it < MI, t);
                 mbar_arrive_cluster(mapa_u32(smem_u32(&tempty_bar[buf]), 0));
                 s_thr[j * 128 + row] = thr;
                 s_state[j * 128 + row] = state;
-                if (g_live && item_best > thr0) k2_gthr_publish(my_g, p.gthr_groups, t, item_best);
             }
         }
         for (int j = 0; j < MI; ++j) {
             const int qrow = m_row0(j) + row;
-            if (qrow < p.batch && row < p.lstride) {
-                uint64_t* out = p.cand + (static_cast<int64_t>(qrow) * p.slots + slot) * p.kprime;
-                const uint64_t* my_list = lists + static_cast<size_t>(j) * list_elems + row;
-                const int count = static_cast<int>(s_state[j * 128 + row]);
-                for (int i = 0; i < p.kprime; ++i) out[i] = i < count ? my_list[i * p.lstride] : 0ull;
-                p.tau[static_cast<int64_t>(qrow) * p.slots + slot] =
-                    count == p.kprime ? key_score(my_list[0]) : __uint_as_float(0xff800000u);
-            }
+            if (qrow < p.batch && row < p.lstride)
+                k2_flush_list(p, lists + static_cast<size_t>(j) * list_elems + row, static_cast<int>(s_state[j * 128 + row]),
+                              qrow, slot);
         }
     }
 

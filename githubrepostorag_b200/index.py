@@ -129,8 +129,10 @@ class DeviceShard:
         self._lib = lib
         if cap != n_rows:
             N.check(lib.crb_index_rebind(self._h, _ptr(rows), _ptr(inv_norm), _ptr(codes), n_rows, cap))
-        self._ws_lock = threading.Lock()
-        self._ws: Optional[torch.Tensor] = None
+        # scratch for search_device calls that bring no workspace: one per calling thread, because the worker's
+        # threads search concurrently (rag_worker/src/worker/worker.py:136-139,185) and a workspace serves one
+        # call at a time -- counters, survivor lists and candidate lists all live in it
+        self._ws_local = threading.local()
 
     @property
     def capacity(self) -> int:
@@ -245,6 +247,11 @@ class DeviceShard:
         if len(idx):
             N.check(self._lib.crb_tombstone_rows(self._h, _np_ptr(idx), len(idx)))
 
+    def reload_tuning(self) -> None:
+        """Re-read the ``CODERAG_B200_*`` knobs (they are otherwise read once, when the shard is created).
+        No search may be in flight."""
+        N.check(self._lib.crb_index_reload_tuning(self._h))
+
     def close(self) -> None:
         if getattr(self, "_h", None):
             self._lib.crb_index_destroy(self._h)
@@ -339,10 +346,14 @@ class DeviceShard:
             nf = len({(rows_f[i], ids_m[i]) for i in range(b)
                       if ids_m[i] or any(c != N.FILT_ANY for c in rows_f[i])})
             need = self.workspace_bytes(b, k, nf)
-            with self._ws_lock:
-                if self._ws is None or self._ws.numel() < need:
-                    self._ws = torch.zeros(need, dtype=torch.uint8, device=self.device)
-                workspace = self._ws
+            stream_id = torch.cuda.current_stream(self.device).cuda_stream
+            held = getattr(self._ws_local, "ws", None)
+            # (a thread that moves to another stream gets a fresh workspace: work queued on the old stream may
+            #  still be using the old one; torch's allocator keeps a freed block until its stream has passed it)
+            if held is None or held[0] != stream_id or held[1].numel() < need:
+                held = (stream_id, torch.zeros(need, dtype=torch.uint8, device=self.device))
+                self._ws_local.ws = held
+            workspace = held[1]
         stream = torch.cuda.current_stream(self.device).cuda_stream
         if mask_ptrs is None:
             N.check(self._lib.crb_search(self._h, queries.data_ptr(), b, k, self._metric(metric), _np_ptr(f),

@@ -13,8 +13,14 @@ from typing import Any, Iterable, Mapping
 
 import numpy as np
 
-TABLES_BY_SCOPE = {"catalog": "embeddings_catalog", "repo": "embeddings_repo", "module": "embeddings_module",
-                   "file": "embeddings_file", "chunk": "embeddings"}
+from .vector_store import TABLES_BY_SCOPE, B200VectorStore, scope_of_table  # noqa: F401  (re-exported)
+
+
+def store_for_table(table_name: str, *, dim: int = 384, embedding: Any = None, device: int = 0) -> B200VectorStore:
+    """An empty store for one of the reference's embeddings tables, filterable on the keys the ingest writer
+    indexes for that table's scope plus the keys it keeps on every row
+    (``ingest/src/app/services/vector_write_service.py:28-43,58-64``)."""
+    return B200VectorStore(embedding, dim=dim, table_name=table_name, device=device, scope=scope_of_table(table_name))
 
 
 def _field(row: Any, name: str, pos: int):

@@ -141,6 +141,15 @@ class GraphRetrieverFactory:
         self._device, self._dim = device, dim
         self._stores: Dict[str, B200VectorStore] = {}
 
+    def _scope_of(self, table_name: str) -> Optional[str]:
+        """The writer's scope of one of this factory's tables (``vector_write_service.py:37-43``): it decides
+        which metadata keys the table is filterable on."""
+        for scope, name in (("repo", self.tables.repo), ("module", self.tables.module), ("file", self.tables.file),
+                            ("chunk", self.tables.chunk)):
+            if name == table_name:
+                return scope
+        return None
+
     def _store(self, table_name: str) -> B200VectorStore:
         st = self._stores.get(table_name)
         if st:
@@ -150,7 +159,8 @@ class GraphRetrieverFactory:
             if getattr(st, "embeddings", None) is None:
                 st.embeddings = self._emb
         else:
-            st = B200VectorStore(self._emb, dim=self._dim, table_name=table_name, device=self._device)
+            st = B200VectorStore(self._emb, dim=self._dim, table_name=table_name, device=self._device,
+                                 scope=self._scope_of(table_name))
         self._stores[table_name] = st
         return st
 

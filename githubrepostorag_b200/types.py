@@ -25,6 +25,7 @@ class FilterOperator(str, Enum):
 
 class FilterCondition(str, Enum):
     AND = "and"
+    OR = "or"
 
 
 @dataclass
@@ -36,7 +37,7 @@ class MetadataFilter:
 
 @dataclass
 class MetadataFilters:
-    filters: List[MetadataFilter] = field(default_factory=list)
+    filters: List[Any] = field(default_factory=list)      # MetadataFilter leaves or nested MetadataFilters
     condition: FilterCondition = FilterCondition.AND
 
     @classmethod

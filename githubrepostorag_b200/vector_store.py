@@ -30,13 +30,51 @@ from .index import DeviceShard, MetadataDictionary
 from .types import (Content, Document, FilterCondition, FilterOperator, MetadataFilter, MetadataFilters, NodeWithScore,
                     TextNode, VectorStoreQuery, VectorStoreQueryResult)
 
-# keys the reference filters or traverses on (agent_graph.py:200-233; graph_rag_retrievers.py:82-100;
-# north star adds branch / component_kind, written at ingest_controller.py:169-173)
-DEFAULT_FILTER_KEYS = ("namespace", "repo", "module", "file_path", "branch", "component_kind", "scope", "language")
 # list-valued metadata the ingest writer shreds into key->value entries for traversal
 # (ingest/src/app/services/vector_write_service.py:28-34,152-154): a filter on one of these keys
 # means MEMBERSHIP ("the row's list contains the value"), served by a per-query row mask.
 DEFAULT_MULTI_VALUED_KEYS = ("topics", "imports", "labels")
+# The writer's per-scope allow-lists of INDEXED (= filterable) metadata keys, as in the reference
+# (ingest/src/app/services/vector_write_service.py:28-34) ...
+ALLOW_FIELDS_BY_SCOPE = {
+    "catalog": ("namespace", "repo", "owner", "language", "topics", "labels", "component_kind"),
+    "repo": ("namespace", "repo", "owner", "language", "topics", "labels"),
+    "module": ("namespace", "repo", "module", "language", "topics", "imports", "labels"),
+    "file": ("namespace", "repo", "module", "file_path", "language", "topics", "imports", "labels"),
+    "chunk": ("namespace", "repo", "module", "file_path", "symbol", "language", "topics", "imports"),
+}
+# ... and the keys it keeps on every row whatever the scope (vector_write_service.py:58-64; `row_id` is the
+# primary key, not a filter).  Stored keys are made filterable too: a superset of what SAI indexes, so every
+# filter the reference can run (agent_graph.py:200-233; graph_rag_retrievers.py:82-100; the north star's
+# branch / component_kind, ingest_controller.py:169-173) runs here.
+KEEP_ALWAYS_KEYS = ("scope", "namespace", "repo", "module", "file_path", "symbol", "owner", "component_kind",
+                    "branch", "language")
+# scope <-> table (vector_write_service.py:37-43; agent_graph.py:163-168)
+TABLES_BY_SCOPE = {"catalog": "embeddings_catalog", "repo": "embeddings_repo", "module": "embeddings_module",
+                   "file": "embeddings_file", "chunk": "embeddings"}
+
+
+def filter_keys_for_scope(scope: Optional[str]) -> Tuple[Tuple[str, ...], Tuple[str, ...]]:
+    """(single-valued coded keys, list-valued keys) a table of ``scope`` filters on: the scope's allow-list
+    plus the always-kept keys; ``None`` / unknown scope = the union over all scopes."""
+    allow: List[str] = []
+    for sc in ([scope] if scope in ALLOW_FIELDS_BY_SCOPE else list(ALLOW_FIELDS_BY_SCOPE)):
+        allow += [k for k in ALLOW_FIELDS_BY_SCOPE[sc] if k not in allow]
+    coded = [k for k in allow if k not in DEFAULT_MULTI_VALUED_KEYS]
+    coded += [k for k in KEEP_ALWAYS_KEYS if k not in coded]
+    multi = [k for k in allow if k in DEFAULT_MULTI_VALUED_KEYS]
+    return tuple(coded), tuple(multi)
+
+
+def scope_of_table(table_name: str) -> Optional[str]:
+    for sc, tb in TABLES_BY_SCOPE.items():
+        if tb == table_name:
+            return sc
+    return None
+
+
+# every key the reference can filter or traverse on, whatever the table
+DEFAULT_FILTER_KEYS = filter_keys_for_scope(None)[0]
 
 
 def _retrieval_histogram():
@@ -169,10 +207,16 @@ class B200VectorStore:
     flat_metadata: bool = True
 
     def __init__(self, embedding: Any = None, *, dim: Optional[int] = None,
-                 filter_keys: Sequence[str] = DEFAULT_FILTER_KEYS, device: int = 0,
+                 filter_keys: Optional[Sequence[str]] = None, device: int = 0,
                  table_name: str = "embeddings", metric: str = "cosine",
-                 multi_valued_keys: Sequence[str] = DEFAULT_MULTI_VALUED_KEYS):
+                 multi_valued_keys: Optional[Sequence[str]] = None, scope: Optional[str] = None):
         N.load()  # fail loudly at construction when the CUDA library is missing
+        # filterable keys: given explicitly, else the writer's lists for the table's scope (``scope=...``; the
+        # retriever factory and the migration loader pass it), else the union over all scopes
+        sc_coded, sc_multi = filter_keys_for_scope(scope)
+        filter_keys = sc_coded if filter_keys is None else filter_keys
+        multi_valued_keys = (sc_multi if scope else DEFAULT_MULTI_VALUED_KEYS) if multi_valued_keys is None else multi_valued_keys
+        self.scope = scope
         self.embeddings = embedding          # object with embed_query / embed_documents
         self.table_name = table_name
         self.metric = metric
@@ -190,6 +234,7 @@ class B200VectorStore:
         self.multi_valued_keys = tuple(k for k in multi_valued_keys if k not in self.dictionary.keys)
         self._postings: Dict[Tuple[str, str], List[int]] = {}
         self._mask_cache: Dict[Any, Any] = {}
+        self._mask_lock = threading.Lock()
         self._hist = _retrieval_histogram()
 
     # ------------------------------------------------------------------ construction / writes
@@ -447,59 +492,97 @@ class B200VectorStore:
     def _search_locked(self, queries, k, filt, split, algo):
         with self._gate.read():
             if not any(extra for _, extra in split):
-                return self._shard.search_host(queries, k, metric=self.metric, filt=filt, algo=algo)
-            # predicates one code per key cannot express ride on a per-query row mask (device path)
-            import torch
-            masks = [self._row_mask(extra) if extra else None for _, extra in split]
-            q = torch.from_numpy(np.ascontiguousarray(queries, dtype=np.float32)).to(self._shard.device)
-            s_, r_, v_ = self._shard.search_device(q, k, metric=self.metric, filt=filt, algo=algo, row_masks=masks)
-            return s_.cpu().numpy(), r_.cpu().numpy(), v_.cpu().numpy()
+                s_, r_, v_ = self._shard.search_host(queries, k, metric=self.metric, filt=filt, algo=algo)
+            else:
+                # predicates one code per key cannot express ride on a per-query row mask (device path)
+                import torch
+                masks = [self._row_mask(extra) if extra else None for _, extra in split]
+                q = torch.from_numpy(np.ascontiguousarray(queries, dtype=np.float32)).to(self._shard.device)
+                s_, r_, v_ = self._shard.search_device(q, k, metric=self.metric, filt=filt, algo=algo, row_masks=masks)
+                s_, r_, v_ = s_.cpu().numpy(), r_.cpu().numpy(), v_.cpu().numpy()
+            # the device returns GLOBAL rows (row_offset + local); everything host-side is indexed by LOCAL row
+            off = self._shard.row_offset
+            if off:
+                r_ = np.where(r_ >= 0, r_ - off, r_)
+            return s_, r_, v_
+
+    # ---- filter vocabulary --------------------------------------------------------------------------
+    # A filter is a flat dict, ANDed (the only shape the reference emits, agent_graph.py:198-239):
+    #   key: value                 equality on a coded key; MEMBERSHIP on a list-valued key
+    #   key: ("in", [values])      IN on a coded key; "shares a member with" on a list-valued key
+    #   "__any_of__": [group, ..]  each group a list of alternative filter dicts: OR inside a group, AND across
+    #                              groups (LlamaIndex FilterCondition.OR and nested MetadataFilters)
+    @staticmethod
+    def _canon(flt: Mapping[str, Any]) -> tuple:
+        """Hashable canonical form: sorted ``(key, ("eq", v) | ("in", (v, ...)))`` items; ``__any_of__`` groups
+        as tuples of canonical alternatives."""
+        items = []
+        for key, val in flt.items():
+            if key == "__any_of__":
+                items.append((key, tuple(tuple(B200VectorStore._canon(alt) for alt in group) for group in val)))
+            elif isinstance(val, tuple) and len(val) == 2 and val[0] == "in":
+                items.append((str(key), ("in", tuple(sorted(str(v) for v in val[1])))))
+            else:
+                items.append((str(key), ("eq", str(val))))
+        return tuple(sorted(items, key=repr))
 
     def _split_filter(self, flt: Optional[Mapping[str, Any]]):
-        """``{key: value | ("in", [values]) }`` -> (equalities on coded keys, extra predicates).
-        Extra predicates: membership on a list-valued key, IN on a coded key."""
+        """filter dict -> (equalities on coded keys -- they go to the filter kernel as codes --, extra
+        predicates in canonical form -- they ride on a row mask)."""
         if not flt:
             return None, ()
         eq: Dict[str, Any] = {}
         extra = []
-        for key, val in flt.items():
-            if isinstance(val, tuple) and len(val) == 2 and val[0] == "in":
-                extra.append(("in", key, tuple(sorted(str(v) for v in val[1]))))
-            elif key in self.multi_valued_keys:
-                extra.append(("has", key, str(val)))
+        for key, spec in self._canon(flt):
+            if key != "__any_of__" and spec[0] == "eq" and key not in self.multi_valued_keys:
+                eq[key] = spec[1]
             else:
-                eq[key] = val
-        return (eq or None), tuple(sorted(extra))
+                extra.append((key, spec))
+        return (eq or None), tuple(extra)
 
-    def _row_mask(self, extra):
-        """Device pass-bit mask of the rows satisfying every extra predicate (cached until the next write)."""
+    def _keep_items(self, items) -> "torch.Tensor":
+        """bool [n_rows] on the device: rows satisfying every canonical predicate of ``items``."""
         import torch
-        cached = self._mask_cache.get(extra)
-        if cached is not None:
-            return cached
         sh = self._shard
         keep = torch.ones(sh.n_rows, dtype=torch.bool, device=sh.device)
-        for kind, key, arg in extra:
-            if kind == "has":
-                rows = [r for r in self._postings.get((key, arg), ()) if r < sh.n_rows]
+        for key, spec in items:
+            if key == "__any_of__":
+                for group in spec:
+                    union = torch.zeros(sh.n_rows, dtype=torch.bool, device=sh.device)
+                    for alt in group:
+                        union |= self._keep_items(alt)
+                    keep &= union
+                continue
+            values = [spec[1]] if spec[0] == "eq" else list(spec[1])
+            if key in self.multi_valued_keys:
+                # membership in the row's list: the union of the values' postings
+                rows = sorted({r for v in values for r in self._postings.get((key, v), ()) if r < sh.n_rows})
                 hit = torch.zeros(sh.n_rows, dtype=torch.bool, device=sh.device)
                 if rows:
                     hit[torch.as_tensor(rows, dtype=torch.int64, device=sh.device)] = True
                 keep &= hit
-            else:   # "in" on a coded key
-                pos = self.dictionary._pos.get(key)
-                if pos is None or sh.codes is None:
-                    keep.zero_()
-                    continue
-                codes = [self.dictionary.values[pos][v] for v in arg if v in self.dictionary.values[pos]]
-                if not codes:
-                    keep.zero_()
-                    continue
+                continue
+            pos = self.dictionary._pos.get(key)
+            codes = [] if pos is None else [self.dictionary.values[pos][v] for v in values if v in self.dictionary.values[pos]]
+            if not codes or sh.codes is None:
+                keep.zero_()                         # unknown key or value: no row has it
+            elif len(codes) == 1:
+                keep &= sh.codes[pos] == codes[0]
+            else:
                 keep &= torch.isin(sh.codes[pos], torch.as_tensor(codes, dtype=torch.int32, device=sh.device))
-        mask = sh.pack_row_mask(keep)
-        if len(self._mask_cache) > 256:
-            self._mask_cache.clear()
-        self._mask_cache[extra] = mask
+        return keep
+
+    def _row_mask(self, extra):
+        """Device pass-bit mask of the rows satisfying every extra predicate (cached until the next write)."""
+        with self._mask_lock:
+            cached = self._mask_cache.get(extra)
+        if cached is not None:
+            return cached
+        mask = self._shard.pack_row_mask(self._keep_items(extra))
+        with self._mask_lock:
+            if len(self._mask_cache) > 256:
+                self._mask_cache.clear()
+            self._mask_cache[extra] = mask
         return mask
 
     def _embed_query(self, text: str) -> List[float]:
@@ -509,15 +592,20 @@ class B200VectorStore:
 
     @staticmethod
     def _filters_to_dict(filters: Any) -> Optional[Dict[str, Any]]:
+        """LlamaIndex ``MetadataFilters`` (EQ / IN / CONTAINS leaves, AND / OR conditions, nesting) -> filter dict."""
         if filters is None:
             return None
         if isinstance(filters, Mapping):
             return dict(filters)
         cond = getattr(filters, "condition", FilterCondition.AND)
-        if cond is not None and str(getattr(cond, "value", cond)).lower() != "and":
-            raise NotImplementedError("only AND of equality filters is supported (what the reference emits)")
-        out: Dict[str, Any] = {}
+        cond = "and" if cond is None else str(getattr(cond, "value", cond)).lower()
+        if cond not in ("and", "or"):
+            raise NotImplementedError(f"filter condition {cond!r} is not supported (AND, OR)")
+        leaves, nested = [], []
         for f in getattr(filters, "filters", []) or []:
+            if hasattr(f, "filters"):
+                nested.append(B200VectorStore._filters_to_dict(f) or {})
+                continue
             op = getattr(f, "operator", FilterOperator.EQ)
             name = str(getattr(op, "value", op)).lower()
             if name in ("==", "contains"):        # CONTAINS on a list-valued key == membership
@@ -526,9 +614,17 @@ class B200VectorStore:
                 val = ("in", list(f.value))
             else:
                 raise NotImplementedError(f"filter operator {op!r} is not supported (EQ, IN, CONTAINS)")
-            if f.key in out and out[f.key] != val:
+            leaves.append((f.key, val))
+        if cond == "or":
+            alts = [{k: v} for k, v in leaves] + nested
+            return {"__any_of__": [alts]} if alts else None
+        out: Dict[str, Any] = {}
+        for key, val in leaves:
+            if key in out and out[key] != val:
                 return {"__impossible__": "1"}  # k == a AND k == b
-            out[f.key] = val
+            out[key] = val
+        if nested:
+            out["__any_of__"] = [[nd] for nd in nested]
         return out
 
     # ------------------------------------------------------------------ face A: LlamaIndex

@@ -31,7 +31,7 @@
 extern "C" {
 #endif
 
-#define CRB_ABI_VERSION 1
+#define CRB_ABI_VERSION 2
 
 /* similarity modes: VectorStoreQueryMode.DEFAULT (cosine; the SAI index is created with
  * similarity_function cosine, helm/templates/cassandra-initdb-configmap.yaml:99-102) and
@@ -45,7 +45,8 @@ extern "C" {
                                     lacking the map entry never matches metadata_s['k']='v') */
 #define CRB_CODE_MISSING (-1)    /* row has no value for this key */
 
-#define CRB_MAX_KEYS 8    /* filterable metadata keys per index */
+#define CRB_MAX_KEYS 16   /* filterable metadata keys per index: covers the writer's allow-lists plus its
+                             always-kept keys (ingest/src/app/services/vector_write_service.py:28-34,58-64) */
 #define CRB_MAX_TOPK 128  /* largest k (reference uses k <= 10, agent_graph.py:171-176) */
 #define CRB_MAX_DIM 4096
 
@@ -66,6 +67,12 @@ int crb_index_create(crb_index **out, const void *d_rows_f16, const float *d_inv
                      const int32_t *d_codes, int64_t n_rows, int32_t dim, int32_t n_keys,
                      int64_t row_offset, int32_t device);
 int crb_index_destroy(crb_index *index);
+
+/* Tuning knobs (the CODERAG_B200_* environment variables of INTEGRATION.md; the reference's config is
+ * environment variables read at import, rag_shared/config.py:1-47) are read once, inside
+ * crb_index_create -- no search call reads the environment.  A host that changed them afterwards
+ * (A/B probes, tests) applies them with this call; no search may be in flight on the index. */
+int crb_index_reload_tuning(crb_index *index);
 
 /* Write path (stands for LCCassandra.add_documents / CQL INSERT and DELETE on the embeddings
  * tables: ingest/src/app/services/vector_write_service.py:136-159).  The store appends rows to
@@ -113,7 +120,10 @@ size_t crb_workspace_bytes(const crb_index *index, int32_t batch, int32_t k, int
  *   d_workspace / workspace_bytes  scratch of at least crb_workspace_bytes(...).  Its first
  *              4096 bytes must be ZERO before the first call that uses it (cudaMemset /
  *              torch.zeros); the kernels leave them zero again.  One workspace serves one call
- *              at a time (concurrent calls need one workspace each).
+ *              at a time (concurrent calls need one workspace each).  It must be ordinary device
+ *              memory of the index's own GPU (cudaMalloc / a torch tensor) -- never symmetric,
+ *              peer-mapped or IPC memory: the tensor-core kernel reads its query tile from here
+ *              through a TMA tensor map.
  *   algo       0 = choose by batch size, 1 = force the streaming kernel, 2 = force the
  *              tensor-core kernel */
 int crb_search(crb_index *index, const float *d_queries, int32_t batch, int32_t k, int32_t metric,

@@ -20,7 +20,7 @@ for name, wants in (("12 edges under namespace=default", [[0, -1, -1, -1], [0, 1
     ws = sh.new_workspace(len(wants), k, len(wants))
     out = {}
     for bal in ("0", "1"):
-        os.environ["CODERAG_B200_K1_BALANCED"] = bal
+        os.environ["CODERAG_B200_K1_BALANCED"] = bal; sh.reload_tuning()
         for _ in range(5): sh.search_device(q, k, filt=filt, workspace=ws)
         torch.cuda.synchronize()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)

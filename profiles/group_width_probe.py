@@ -13,7 +13,7 @@ for n, d in ((1_000_000, 384), (100_000, 384), (1_000_000, 768)):
         ws = sh.new_workspace(b, 10, 1)
         out = {}
         for grp in ("1", "2", "4"):
-            os.environ["CODERAG_B200_K1_GROUP"] = grp
+            os.environ["CODERAG_B200_K1_GROUP"] = grp; sh.reload_tuning()
             for _ in range(5): sh.search_device(q, 10, filt=f, workspace=ws, algo=1)
             torch.cuda.synchronize()
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -21,6 +21,6 @@ for n, d in ((1_000_000, 384), (100_000, 384), (1_000_000, 768)):
             for _ in range(50): sh.search_device(q, 10, filt=f, workspace=ws, algo=1)
             e1.record(); torch.cuda.synchronize()
             out[f"group{grp}_ms"] = round(e0.elapsed_time(e1) / 50, 4)
-        os.environ.pop("CODERAG_B200_K1_GROUP", None)
+        os.environ.pop("CODERAG_B200_K1_GROUP", None); sh.reload_tuning()
         print(json.dumps({"n": n, "dim": d, "batch": b, "filtered_10pct": filt, **out}), flush=True)
     sh.close(); del rows

@@ -10,6 +10,7 @@ ws = sh.new_workspace(1, 10, 0)
 for knobs in ({}, {"CODERAG_B200_K1_E3": "0"}, {"CODERAG_B200_K1_HALF_PAIRS": "2"}, {"CODERAG_B200_K1_HALF_PAIRS": "4"},
               {"CODERAG_B200_K1_E3": "0", "CODERAG_B200_K1_HALF_PAIRS": "4"}, {"CODERAG_B200_K1_HALF": "0"}, {}):
     for k_, v in knobs.items(): os.environ[k_] = v
+    sh.reload_tuning()
     for _ in range(5): sh.search_device(q, 10, workspace=ws, algo=1)
     torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)

@@ -220,12 +220,16 @@ def test_skewed_fan_out_balanced_kernel(torch_cuda, d, k):
     keys_b = torch.empty_like(keys_a)
     os.environ["CODERAG_B200_K1_BALANCED"] = "1"
     try:
+        sh.reload_tuning()
         sa, ra, va = [t.clone() for t in sh.search_device(qd, k, filt=filt, keys_out=keys_a)]
+        torch.cuda.synchronize()
         os.environ["CODERAG_B200_K1_BALANCED"] = "0"
+        sh.reload_tuning()
         sb, rb, vb = [t.clone() for t in sh.search_device(qd, k, filt=filt, keys_out=keys_b)]
+        torch.cuda.synchronize()
     finally:
         os.environ.pop("CODERAG_B200_K1_BALANCED", None)
-    torch.cuda.synchronize()
+        sh.reload_tuning()
     assert torch.equal(ra, rb) and torch.equal(va, vb) and torch.equal(sa.view(torch.int32), sb.view(torch.int32))
     assert torch.equal(keys_a, keys_b)
     keep = np.ones((len(wants), n), dtype=bool)
@@ -268,12 +272,14 @@ def test_fused_filter_and_score_single_query(torch_cuda, n, d, k):
         for fused in ("1", "0"):
             os.environ["CODERAG_B200_K1_FUSED"] = fused
             try:
+                sh.reload_tuning()
                 keys = torch.empty((1, k), dtype=torch.int64, device="cuda")
                 s_, r_, v_ = sh.search_device(qd, k, filt=filt, keys_out=keys, row_masks=None if mask is None else [mask])
                 torch.cuda.synchronize()
                 out[fused] = (s_.clone(), r_.clone(), v_.clone(), keys.clone())
             finally:
                 os.environ.pop("CODERAG_B200_K1_FUSED", None)
+                sh.reload_tuning()
         a, b = out["1"], out["0"]
         assert torch.equal(a[1], b[1]) and torch.equal(a[2], b[2]), f"rows differ for {want}"
         assert torch.equal(a[0].view(torch.int32), b[0].view(torch.int32)) and torch.equal(a[3], b[3])
@@ -313,10 +319,12 @@ def test_exact_width_instantiations_return_the_same_bits(torch_cuda, d, knob):
             for v in ("1", "0"):
                 os.environ[knob] = v
                 try:
+                    sh.reload_tuning()
                     out[v] = [t.clone() for t in sh.search_device(qd, k, filt=filt, algo=1)]
                     torch.cuda.synchronize()
                 finally:
                     os.environ.pop(knob, None)
+                    sh.reload_tuning()
             a, b = out["1"], out["0"]
             assert torch.equal(a[1], b[1]) and torch.equal(a[2], b[2]) and torch.equal(a[0].view(torch.int32), b[0].view(torch.int32))
     sh.close()

@@ -78,7 +78,7 @@ def test_metadata_dictionary_codes_and_filters(lib):
     assert d.encode_filter({"repo": "zzz"}).tolist() == [N.FILT_ANY, N.FILT_IMPOSSIBLE, N.FILT_ANY]
     assert d.encode_filter({"owner": "x"}).tolist() == [N.FILT_IMPOSSIBLE] * 3
     with pytest.raises(ValueError):
-        MetadataDictionary([str(i) for i in range(9)])
+        MetadataDictionary([str(i) for i in range(N.MAX_KEYS + 1)])
 
 
 def test_store_host_bookkeeping(lib):
