@@ -32,7 +32,8 @@ MAX_PEERS = 8
 class Exchange(C.Structure):
     """``crb_exchange`` of include/coderag_b200.h."""
     _fields_ = [("rank", C.c_int32), ("world", C.c_int32), ("cap_keys", C.c_uint64),
-                ("peer_keys", C.c_void_p * MAX_PEERS), ("peer_counters", C.c_void_p * MAX_PEERS)]
+                ("peer_keys", C.c_void_p * MAX_PEERS), ("peer_counters", C.c_void_p * MAX_PEERS),
+                ("dest_mask", C.c_uint32)]
 
 # every symbol include/coderag_b200.h declares: name -> (restype, argtypes)
 _vp, _i32, _i64, _sz = C.c_void_p, C.c_int32, C.c_int64, C.c_size_t
@@ -42,6 +43,7 @@ PROTOTYPES = {
     "crb_index_create": (C.c_int, [C.POINTER(_vp), _vp, _vp, _vp, _i64, _i32, _i32, _i64, _i32]),
     "crb_index_destroy": (C.c_int, [_vp]),
     "crb_index_reload_tuning": (C.c_int, [_vp]),
+    "crb_index_set_k5_stats": (C.c_int, [_vp, _vp]),
     "crb_index_rebind": (C.c_int, [_vp, _vp, _vp, _vp, _i64, _i64]),
     "crb_tombstone_rows": (C.c_int, [_vp, _vp, _i32]),
     "crb_encode_rows": (C.c_int, [_vp, _vp, _vp, _i64, _i32, _i32, _vp]),
@@ -53,6 +55,8 @@ PROTOTYPES = {
     "crb_merge_keys": (C.c_int, [_vp, _i32, _i32, _i32, _i32, _vp, _i32, _vp, _vp, _vp, _vp, _i32, _vp]),
     "crb_search_exchange": (C.c_int, [_vp, _vp, _i32, _i32, _i32, _vp, _vp, _vp, _vp, _vp, _vp, _sz, _i32, _vp,
                                        _vp, C.c_uint32, C.c_uint32]),
+    "crb_search_exchange_host": (C.c_int, [_vp, _vp, _i32, _i32, _i32, _vp, _vp, _vp, _vp, _vp, _i32, _vp,
+                                            C.c_uint32, C.c_uint32]),
     "crb_fetch_rows_host": (C.c_int, [_vp, _vp, _i32, _vp]),
     "crb_search_noalloc": (C.c_int, [_vp, _vp, _i32, _i32, _i32, _vp, _vp, _vp, _vp]),
     "crb_launch_count": (_i64, []),

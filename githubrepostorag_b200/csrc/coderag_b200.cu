@@ -179,6 +179,7 @@ struct crb_index {
     CUtensorMap map_rows;          // fp16 [n_rows, dim], box 64 x 256, 128 B swizzle
     CUtensorMap map_rows_half;     // same, box 64 x 128 (one CTA's half tile in the pair kernel)
     crb::Tuning tune;
+    float* k5_stats = nullptr;     // diagnostics buffer (crb_index_set_k5_stats) or nullptr
     std::mutex mu;
     std::condition_variable cv;
     std::vector<crb::Lane> lanes;
@@ -716,6 +717,7 @@ static int launch_k2(crb_index* ix, const float* d_queries, int batch, int k, in
         rp.gthr_groups = groups;
         rp.flagged = flagged;
         rp.n_flagged = nflag;
+        rp.stats = ix->k5_stats;
         rp.max_norm = ix->max_norm;
         rp.row_offset = static_cast<uint32_t>(ix->row_offset);
         rp.dim = ix->dim;
@@ -1230,6 +1232,12 @@ extern "C" int crb_index_reload_tuning(crb_index* ix) {
     return 0;
 }
 
+extern "C" int crb_index_set_k5_stats(crb_index* ix, float* d_stats) {
+    if (!ix) return fail("index is NULL");
+    ix->k5_stats = d_stats;
+    return 0;
+}
+
 extern "C" int crb_tombstone_rows(crb_index* ix, const int64_t* h_rows_idx, int32_t n) {
     if (!ix) return fail("index is NULL");
     if (n <= 0) return 0;
@@ -1392,6 +1400,46 @@ extern "C" int crb_merge_keys(const uint64_t* d_keys_in, int32_t n_lists, int32_
     return 0;
 }
 
+namespace crb {
+// crb_exchange -> the device-side descriptor of one call
+static int make_exchange_dev(const crb_exchange* exch, int batch, int k, uint32_t call_index, ExchangeDev* out) {
+    if (!exch) return fail("exchange descriptor is NULL");
+    if (exch->world < 1 || exch->world > CRB_MAX_PEERS || exch->rank < 0 || exch->rank >= exch->world)
+        return fail("exchange: world must be in [1, %d] and rank in [0, world)", CRB_MAX_PEERS);
+    if (uint64_t(batch) * uint64_t(k) > exch->cap_keys)
+        return fail("exchange: batch*k = %lld exceeds the gather slot capacity %llu", (long long)batch * k,
+                    (unsigned long long)exch->cap_keys);
+    const uint32_t all = exch->world >= 32 ? 0xffffffffu : ((1u << exch->world) - 1u);
+    ExchangeDev ex;
+    memset(&ex, 0, sizeof ex);
+    ex.world = exch->world;
+    ex.rank = exch->rank;
+    ex.parity = static_cast<int32_t>(call_index & 1u);
+    ex.dest_mask = exch->dest_mask ? (exch->dest_mask & all) : all;
+    if (!ex.dest_mask) return fail("exchange: dest_mask names no rank of the world");
+    ex.cap = exch->cap_keys;
+    for (int p = 0; p < exch->world; ++p) {
+        if (!exch->peer_keys[p] || !exch->peer_counters[p]) return fail("exchange: peer %d pointers are NULL", p);
+        ex.keys[p] = exch->peer_keys[p];
+        ex.counters[p] = exch->peer_counters[p];
+    }
+    *out = ex;
+    return 0;
+}
+// the receiving half: wait for every source's arrivals and merge (only on ranks the keys are sent to)
+static int launch_merge_wait(const crb_index* ix, const crb_exchange* exch, const ExchangeDev& ex, const float* d_queries,
+                             int batch, int k, int metric, float* d_scores, int64_t* d_rows, int32_t* d_n_valid,
+                             uint64_t* d_keys, uint32_t expected_total, cudaStream_t stream) {
+    if (!((ex.dest_mask >> ex.rank) & 1u)) return 0;
+    const uint64_t* my_gather = exch->peer_keys[exch->rank] + uint64_t(ex.parity) * uint64_t(ex.world) * ex.cap;
+    merge_wait_kernel<<<batch, 256, 0, stream>>>(my_gather, ex.cap, exch->peer_counters[exch->rank], expected_total,
+                                                 ex.world, batch, k, metric, d_queries, ix->dim, d_scores, d_rows,
+                                                 d_n_valid, d_keys);
+    CRB_LAUNCH_CHECK();
+    return 0;
+}
+}  // namespace crb
+
 extern "C" int crb_search_exchange(crb_index* ix, const float* d_queries, int32_t batch, int32_t k,
                                    int32_t metric, const int32_t* h_filt, float* d_scores, int64_t* d_rows,
                                    int32_t* d_n_valid, uint64_t* d_keys, void* d_workspace,
@@ -1400,34 +1448,74 @@ extern "C" int crb_search_exchange(crb_index* ix, const float* d_queries, int32_
     if (int rc = validate_search(ix, batch, k, metric)) return rc;
     if (!d_queries || !d_scores || !d_rows || !d_n_valid || !d_workspace)
         return fail("NULL device pointer passed to crb_search_exchange");
-    if (!exch) return fail("exchange descriptor is NULL");
-    if (exch->world < 1 || exch->world > CRB_MAX_PEERS || exch->rank < 0 || exch->rank >= exch->world)
-        return fail("exchange: world must be in [1, %d] and rank in [0, world)", CRB_MAX_PEERS);
-    if (uint64_t(batch) * uint64_t(k) > exch->cap_keys)
-        return fail("exchange: batch*k = %lld exceeds the gather slot capacity %llu", (long long)batch * k,
-                    (unsigned long long)exch->cap_keys);
     ExchangeDev ex;
-    memset(&ex, 0, sizeof ex);
-    ex.world = exch->world;
-    ex.rank = exch->rank;
-    ex.parity = static_cast<int32_t>(call_index & 1u);
-    ex.cap = exch->cap_keys;
-    for (int p = 0; p < exch->world; ++p) {
-        if (!exch->peer_keys[p] || !exch->peer_counters[p]) return fail("exchange: peer %d pointers are NULL", p);
-        ex.keys[p] = exch->peer_keys[p];
-        ex.counters[p] = exch->peer_counters[p];
-    }
+    if (int rc = make_exchange_dev(exch, batch, k, call_index, &ex)) return rc;
     cudaStream_t stream = static_cast<cudaStream_t>(stream_);
     DeviceGuard guard(ix->device);
     CRB_CUDA(guard.status);
     if (int rc = search_impl(ix, d_queries, batch, k, metric, h_filt, d_scores, d_rows, d_n_valid, nullptr,
                              d_workspace, workspace_bytes, algo, stream, &ex))
         return rc;
-    const uint64_t* my_gather = exch->peer_keys[exch->rank] + uint64_t(ex.parity) * uint64_t(ex.world) * ex.cap;
-    merge_wait_kernel<<<batch, 256, 0, stream>>>(my_gather, ex.cap, exch->peer_counters[exch->rank], expected_total,
-                                                 ex.world, batch, k, metric, d_queries, ix->dim, d_scores, d_rows,
-                                                 d_n_valid, d_keys);
-    CRB_LAUNCH_CHECK();
+    return launch_merge_wait(ix, exch, ex, d_queries, batch, k, metric, d_scores, d_rows, d_n_valid, d_keys,
+                             expected_total, stream);
+}
+
+extern "C" int crb_search_exchange_host(crb_index* ix, const float* h_queries, int32_t batch, int32_t k,
+                                        int32_t metric, const int32_t* h_filt,
+                                        const uint32_t* const* h_row_mask_ptrs, float* h_scores, int64_t* h_rows,
+                                        int32_t* h_n_valid, int32_t algo, const crb_exchange* exch,
+                                        uint32_t call_index, uint32_t expected_total) {
+    if (int rc = validate_search(ix, batch, k, metric)) return rc;
+    if (!h_queries) return fail("NULL query pointer passed to crb_search_exchange_host");
+    ExchangeDev ex;
+    if (int rc = make_exchange_dev(exch, batch, k, call_index, &ex)) return rc;
+    const bool receives = (ex.dest_mask >> ex.rank) & 1u;
+    if (receives && (!h_scores || !h_rows || !h_n_valid))
+        return fail("crb_search_exchange_host: this rank receives the merged result and needs output arrays");
+    DeviceGuard guard(ix->device);
+    CRB_CUDA(guard.status);
+    LaneHold hold{ix, checkout_lane(ix)};
+    Lane* l = hold.lane;
+
+    const size_t q_bytes = size_t(batch) * ix->dim * sizeof(float);
+    const size_t s_bytes = size_t(batch) * k * sizeof(float);
+    const size_t r_bytes = size_t(batch) * k * sizeof(int64_t);
+    const size_t v_bytes = size_t(batch) * sizeof(int32_t);
+    const size_t off_rows = round_up(q_bytes, 256);
+    const size_t off_scores = off_rows + round_up(r_bytes, 256);
+    const size_t off_valid = off_scores + round_up(s_bytes, 256);
+    const size_t io_bytes = off_valid + round_up(v_bytes, 256);
+    int n_filters = count_distinct_filters(h_filt, batch, ix->n_keys);
+    if (h_row_mask_ptrs) n_filters = std::min<int>(kMaxFilters, n_filters + batch);   // masks split filter classes further
+    const size_t ws_bytes = crb_workspace_bytes(ix, batch, k, n_filters);
+    if (int rc = lane_reserve(l, ws_bytes, io_bytes, io_bytes)) return rc;
+
+    uint8_t* d_io = static_cast<uint8_t*>(l->d_io);
+    uint8_t* h_io = static_cast<uint8_t*>(l->h_pin);
+    memcpy(h_io, h_queries, q_bytes);
+    CRB_CUDA(cudaMemcpyAsync(d_io, h_io, q_bytes, cudaMemcpyHostToDevice, l->stream));
+    const float* d_q = reinterpret_cast<const float*>(d_io);
+    float* d_scores = reinterpret_cast<float*>(d_io + off_scores);
+    int64_t* d_rows = reinterpret_cast<int64_t*>(d_io + off_rows);
+    int32_t* d_valid = reinterpret_cast<int32_t*>(d_io + off_valid);
+    int rc = search_impl(ix, d_q, batch, k, metric, h_filt, d_scores, d_rows, d_valid, nullptr, l->d_ws, l->ws_cap,
+                         algo, l->stream, &ex, h_row_mask_ptrs);
+    if (!rc) rc = launch_merge_wait(ix, exch, ex, d_q, batch, k, metric, d_scores, d_rows, d_valid, nullptr,
+                                    expected_total, l->stream);
+    if (rc) { cudaStreamSynchronize(l->stream); return rc; }
+    if (receives)
+        CRB_CUDA(cudaMemcpyAsync(h_io + off_rows, d_io + off_rows, io_bytes - off_rows, cudaMemcpyDeviceToHost, l->stream));
+    // every rank waits for its own stream: the staging buffers are free again, and a sender knows its keys left
+    CRB_CUDA(cudaStreamSynchronize(l->stream));
+    if (receives) {
+        memcpy(h_rows, h_io + off_rows, r_bytes);
+        memcpy(h_scores, h_io + off_scores, s_bytes);
+        memcpy(h_n_valid, h_io + off_valid, v_bytes);
+        for (int b = 0; b < batch; ++b)
+            if (h_n_valid[b] == -2)
+                return fail("sharded search: a peer did not publish query %d before the wait ran out (lost or stalled rank); "
+                            "the exchange counters are out of step -- reset the exchange on every rank", b);
+    }
     return 0;
 }
 

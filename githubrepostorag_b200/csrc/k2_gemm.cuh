@@ -12,9 +12,9 @@
 // every candidate with the library's canonical fp32 order (common.cuh) and proves the result
 // exact with a margin test, flagging the rare query that needs the K1 fallback:
 //   any row NOT kept by a full slot list has approx <= tau_slot, hence exact <= tau_max + eps,
-//   eps = ||q_hat - fp16(q_hat)||_2 (Cauchy-Schwarz, rigorous) + 2^-16 (tensor-core fp32
-//   accumulation allowance, cosine units; scaled by max row norm for inner product).
-//   The exact top-k is proven when its k-th score exceeds tau_max + eps.
+//   eps = ||q_hat - fp16(q_hat)||_2 (Cauchy-Schwarz) + the worst-case rounding of the two evaluations
+//   being compared (k2_rounding_allowance: linear in dim; cosine units, scaled by the largest row
+//   norm for inner product).  The exact top-k is proven when its k-th score exceeds tau_max + eps.
 //
 // Bound: tensor pipe for batch >= ~256 (2*B*N*d flop), HBM below that (N*d*2 bytes).
 #pragma once
@@ -391,7 +391,20 @@ CRB_DEVINL void k2_flush_list(const K2Params& p, const uint64_t* my_list, int co
 }
 
 // ---- query preparation -------------------------------------------------------------------------
-// q_hat = q / ||q|| (canonical norm), q16 = fp16(q_hat); eps = ||q_hat - q16||_2 + 2^-16.
+// Worst-case distance between the two evaluations K5's proof compares, for unit-norm operands (|sum of
+// |q_i x_i|| <= 1 by Cauchy-Schwarz), NOT counting the fp16 rounding of the query (that is the other term of eps):
+//  * tensor core: the fp16 x fp16 products are exact; the fp32 accumulator takes dim/16 additions of a
+//    16-term partial sum, each allowed 2 ulp (2^-22 relative: the adder aligns and TRUNCATES, so the error is
+//    biased and adds up linearly, not as sqrt(steps)) of a running sum of magnitude <= 1:  (dim/16) * 2^-22;
+//  * canonical fp32 score: dim/32 sequential FMAs per lane + 5 butterfly adds + the norm multiplies, each
+//    rounded to nearest (2^-24 relative of a partial sum <= 1):  (dim/32 + 8) * 2^-24.
+// dim = 384: 5.9e-6, 768: 1.3e-5, 1024: 1.8e-5, 4096: 6.9e-5.  tests/test_gpu_k2.py measures the observed
+// distance on fp16-exact queries (where it is the ONLY error) and asserts it stays under a quarter of this.
+CRB_DEVINL float k2_rounding_allowance(int dim) {
+    return static_cast<float>(dim / 16 + 1) * 2.384185791015625e-07f + static_cast<float>(dim / 32 + 8) * 5.9604644775390625e-08f;
+}
+
+// q_hat = q / ||q|| (canonical norm), q16 = fp16(q_hat); eps = ||q_hat - q16||_2 + k2_rounding_allowance(dim).
 __global__ void __launch_bounds__(128) k2_prep_queries_kernel(const float* __restrict__ queries,
                                                               const int32_t* __restrict__ q_map, int n,
                                                               int dim, __half* __restrict__ q16,
@@ -428,7 +441,7 @@ __global__ void __launch_bounds__(128) k2_prep_queries_kernel(const float* __res
     if (threadIdx.x == 0) {
         const float e2 = s_part[0] + s_part[1] + s_part[2] + s_part[3];
         invq[slot] = iq;
-        eps[slot] = sqrtf(e2) * 1.0001f + 1.52587890625e-05f;
+        eps[slot] = sqrtf(e2) * 1.0001f + k2_rounding_allowance(dim);
     }
 }
 
@@ -823,6 +836,8 @@ struct K5Params {
     int32_t gthr_groups;
     int32_t* flagged;           // [n] slots whose result is not proven
     int32_t* n_flagged;
+    float* stats;               // diagnostics (crb_index_set_k5_stats) or nullptr: per query slot
+                                // {max |approx - exact| over re-scored candidates, margin, re-scored count, proven 1/0}
     float max_norm;             // largest row norm (inner-product margin)
     uint32_t row_offset;
     int32_t dim;
@@ -882,8 +897,10 @@ __global__ void __launch_bounds__(256) k5_rescore_kernel(const __grid_constant__
     __shared__ uint64_t s_c[kK5Gather];
     __shared__ float s_tau[8];
     __shared__ int s_n;
+    __shared__ unsigned s_err_bits, s_rescored;      // diagnostics only (p.stats)
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int slot_q = blockIdx.x;
+    if (threadIdx.x == 0) { s_err_bits = 0u; s_rescored = 0u; }
     const int qi = p.q_map ? p.q_map[slot_q] : slot_q;
     const bool cosine = (p.metric == 0);
     const int chunks = p.dim >> 3;
@@ -948,6 +965,10 @@ __global__ void __launch_bounds__(256) k5_rescore_kernel(const __grid_constant__
             const uint64_t e = s_c[c];
             const uint64_t key = k5_exact_key(p, e, s_q, chunks, cosine, lane);
             if (lane == 0) s_c[c] = key;
+            if (p.stats && lane == 0 && key != 0ull) {
+                atomicMax(&s_err_bits, __float_as_uint(fabsf(key_score(e) - key_score(key) * p.invq[slot_q])));
+                atomicAdd(&s_rescored, 1u);
+            }
         }
         int mp = 32;
         while (mp < m) mp <<= 1;
@@ -986,7 +1007,12 @@ __global__ void __launch_bounds__(256) k5_rescore_kernel(const __grid_constant__
             while (live) {
                 const int src = __ffs(live) - 1;
                 live &= live - 1u;
-                const uint64_t key = k5_exact_key(p, __shfl_sync(CRB_FULL_MASK, el, src), s_q, chunks, cosine, lane);
+                const uint64_t esrc = __shfl_sync(CRB_FULL_MASK, el, src);
+                const uint64_t key = k5_exact_key(p, esrc, s_q, chunks, cosine, lane);
+                if (p.stats && lane == 0 && key != 0ull) {
+                    atomicMax(&s_err_bits, __float_as_uint(fabsf(key_score(esrc) - key_score(key) * p.invq[slot_q])));
+                    atomicAdd(&s_rescored, 1u);
+                }
                 if (key > top.thr) top.insert(key, lane);
             }
         }
@@ -1034,6 +1060,13 @@ __global__ void __launch_bounds__(256) k5_rescore_kernel(const __grid_constant__
     if (threadIdx.x == 0) {
         *sink.n_valid = nv;
         sink.finish();
+        if (p.stats) {
+            float* st = p.stats + 4 * static_cast<int64_t>(qi);
+            st[0] = __uint_as_float(s_err_bits);
+            st[1] = margin;
+            st[2] = static_cast<float>(s_rescored);
+            st[3] = proven ? 1.0f : 0.0f;
+        }
         if (!proven) {
             const int at = atomicAdd(p.n_flagged, 1);
             p.flagged[at] = slot_q;

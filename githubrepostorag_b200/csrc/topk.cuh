@@ -92,7 +92,7 @@ struct ExchangeDev {
     int32_t world;          // 0 = no exchange
     int32_t rank;
     int32_t parity;         // gather buffers are double-buffered by call parity
-    int32_t pad;
+    uint32_t dest_mask;     // bit p set: rank p receives the keys (serving: only the rank that owns the store face)
     uint64_t cap;           // keys per (parity, source) slot
     uint64_t* keys[kMaxPeers];      // peer p's gather buffer: [2][world][cap]
     uint32_t* counters[kMaxPeers];  // peer p's arrival counters: [world], monotonic
@@ -120,14 +120,17 @@ struct TopKSink {
         if (ex) {
             const uint64_t off = (static_cast<uint64_t>(ex->parity) * ex->world + ex->rank) * ex->cap +
                                  static_cast<uint64_t>(qi) * k + r;
-            for (int p = 0; p < ex->world; ++p) ex->keys[p][off] = key;
+            for (int p = 0; p < ex->world; ++p)
+                if ((ex->dest_mask >> p) & 1u) ex->keys[p][off] = key;
         }
     }
-    // called once by the emitting thread after the k-th emit
+    // called once, by one thread, after every emit of the query is visible to it (block barrier, or the same
+    // thread emitted): system-scope fence, then one arrival per destination
     CRB_DEVINL void finish() const {
         if (ex) {
             __threadfence_system();
-            for (int p = 0; p < ex->world; ++p) atomicAdd_system(ex->counters[p] + ex->rank, 1u);
+            for (int p = 0; p < ex->world; ++p)
+                if ((ex->dest_mask >> p) & 1u) atomicAdd_system(ex->counters[p] + ex->rank, 1u);
         }
     }
 };
@@ -139,6 +142,7 @@ template <int LPT>
 CRB_DEVINL void block_merge_sorted_lists(const uint64_t* __restrict__ lists, int n_lists, int k,
                                          int64_t stride, const TopKSink& sink,
                                          uint64_t (*xchg)[32], int lane, int warp, int nwarps) {
+    __shared__ uint64_t s_win[kMaxTopK];
     const int T = nwarps * 32;
     uint64_t head[LPT], nxt[LPT];
     int pos[LPT];
@@ -169,11 +173,18 @@ CRB_DEVINL void block_merge_sorted_lists(const uint64_t* __restrict__ lists, int
                 nxt[j] = (pos[j] + 1 < k) ? ld_cg_u64(lists + l * stride + pos[j] + 1) : 0ull;
             }
         }
-        if (threadIdx.x == 0) sink.emit(r, best);
+        if (threadIdx.x == 0) s_win[r] = best;
     }
+    const int nv = r;
+    __syncthreads();
+    // every rank of the result is written (and, in a sharded search, stored to the peers) by its own thread
+    for (int i = threadIdx.x; i < k; i += T) {
+        sink.emit(i, i < nv ? s_win[i] : 0ull);
+        if (sink.ex) __threadfence_system();
+    }
+    __syncthreads();
     if (threadIdx.x == 0) {
-        *sink.n_valid = r;
-        for (; r < k; ++r) sink.emit(r, 0ull);
+        *sink.n_valid = nv;
         sink.finish();
     }
     __syncthreads();

@@ -252,6 +252,14 @@ class DeviceShard:
         No search may be in flight."""
         N.check(self._lib.crb_index_reload_tuning(self._h))
 
+    def set_k5_stats(self, stats: Optional[torch.Tensor]) -> None:
+        """Diagnostics (``crb_index_set_k5_stats``): fp32 CUDA ``[batch, 4]`` the tensor-core plan fills with
+        {max |approx - exact|, margin, re-scored candidates, proven} per query; ``None`` switches it off."""
+        if stats is not None and (not stats.is_cuda or stats.dtype != torch.float32 or not stats.is_contiguous()):
+            raise ValueError("stats must be a contiguous fp32 CUDA tensor")
+        self._k5_stats = stats
+        N.check(self._lib.crb_index_set_k5_stats(self._h, _ptr(stats)))
+
     def close(self) -> None:
         if getattr(self, "_h", None):
             self._lib.crb_index_destroy(self._h)

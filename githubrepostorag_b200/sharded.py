@@ -87,6 +87,60 @@ def cuda_searcher(shard, *, metric: str = "cosine", algo: int = 0,
     return ShardedSearcher(local_search, merge, group)
 
 
+class NVLinkExchange:
+    """The peer-memory side of a row-sharded search (``crb_exchange`` of include/coderag_b200.h): one
+    symmetric-memory buffer per rank (``torch.distributed._symmetric_memory``: the same allocation mapped into
+    every rank of the box over NVLink) holding this rank's gather slots ``uint64 [2][world][cap_keys]`` and its
+    ``uint32 [world]`` arrival counters, plus the call bookkeeping every rank must keep in step."""
+
+    COUNTER_SLOTS = 64   # uint32 counters live in the last 256 bytes of the buffer
+
+    def __init__(self, device, group, cap_keys: int = 1 << 17):
+        import torch.distributed._symmetric_memory as symm
+
+        from . import _native as N
+        self.group = group if group is not None else dist.group.WORLD
+        self.world = dist.get_world_size(self.group)
+        self.rank = dist.get_rank(self.group)
+        if self.world > N.MAX_PEERS:
+            raise ValueError(f"at most {N.MAX_PEERS} ranks per box")
+        self.device = device
+        self.cap_keys = int(cap_keys)
+        n_words = 2 * self.world * self.cap_keys + self.COUNTER_SLOTS // 2
+        self.buf = symm.empty(n_words, dtype=torch.int64, device=device)
+        self.buf.zero_()
+        torch.cuda.synchronize(device)
+        self.handle = symm.rendezvous(self.buf, self.group.group_name)
+        ptrs = [int(p) for p in self.handle.buffer_ptrs]
+        ex = N.Exchange()
+        ex.rank, ex.world, ex.cap_keys, ex.dest_mask = self.rank, self.world, self.cap_keys, 0
+        for p in range(self.world):
+            ex.peer_keys[p] = ptrs[p]
+            ex.peer_counters[p] = ptrs[p] + 8 * 2 * self.world * self.cap_keys
+        self.struct = ex
+        self.calls = 0
+        self.published = 0
+        dist.barrier(self.group)      # every rank's counters are zero before anyone publishes
+
+    def next_call(self, batch: int) -> Tuple[int, int]:
+        """(call_index, expected_total) of the next collective search of ``batch`` queries."""
+        self.published += batch
+        call = self.calls
+        self.calls += 1
+        return call & 0xFFFFFFFF, self.published & 0xFFFFFFFF
+
+    def reset(self) -> None:
+        """Collective: after a failed call (a rank lost or stalled, ``n_valid == -2``) the arrival counters and the
+        call parity of the ranks are out of step; with no search in flight anywhere, zero them and start over."""
+        torch.cuda.synchronize(self.device)
+        dist.barrier(self.group)
+        self.buf.zero_()
+        self.calls = 0
+        self.published = 0
+        torch.cuda.synchronize(self.device)
+        dist.barrier(self.group)
+
+
 class FusedExchangeSearcher:
     """Row-sharded search with the exchange fused into the search kernels (``crb_search_exchange``).
 
@@ -100,13 +154,9 @@ class FusedExchangeSearcher:
     Collective: all ranks must call :meth:`search` the same number of times with the same batch/k.
     """
 
-    COUNTER_SLOTS = 64   # uint32 counters live in the last 256 bytes of the buffer
-
     def __init__(self, shard, *, cap_keys: int = 1 << 17, metric: str = "cosine", algo: int = 0,
-                 group: Optional[dist.ProcessGroup] = None):
+                 group: Optional[dist.ProcessGroup] = None, dest_rank: Optional[int] = None):
         import ctypes as C
-
-        import torch.distributed._symmetric_memory as symm
 
         from . import _native as N
         from .index import DeviceShard
@@ -114,28 +164,13 @@ class FusedExchangeSearcher:
         self.shard = shard
         self.metric = DeviceShard._metric(metric)
         self.algo = algo
-        self.group = group if group is not None else dist.group.WORLD
-        self.world = dist.get_world_size(self.group)
-        self.rank = dist.get_rank(self.group)
-        if self.world > N.MAX_PEERS:
-            raise ValueError(f"at most {N.MAX_PEERS} ranks per box")
-        self.cap_keys = int(cap_keys)
-        n_words = 2 * self.world * self.cap_keys + self.COUNTER_SLOTS // 2
-        self.buf = symm.empty(n_words, dtype=torch.int64, device=shard.device)
-        self.buf.zero_()
-        torch.cuda.synchronize(shard.device)
-        self.handle = symm.rendezvous(self.buf, self.group.group_name)
-        ptrs = [int(p) for p in self.handle.buffer_ptrs]
-        ex = N.Exchange()
-        ex.rank, ex.world, ex.cap_keys = self.rank, self.world, self.cap_keys
-        for p in range(self.world):
-            ex.peer_keys[p] = ptrs[p]
-            ex.peer_counters[p] = ptrs[p] + 8 * 2 * self.world * self.cap_keys
-        self._ex = ex
-        self._calls = 0
-        self._published = 0
+        self.exchange = NVLinkExchange(shard.device, group, cap_keys)
+        # dest_rank: only that rank receives the keys and merges (the serving layout: one rank owns the store
+        # face); None = every rank ends up with the merged result
+        self.exchange.struct.dest_mask = 0 if dest_rank is None else (1 << dest_rank)
+        self.group, self.world, self.rank = self.exchange.group, self.exchange.world, self.exchange.rank
+        self.cap_keys = self.exchange.cap_keys
         self._ws = None
-        dist.barrier(self.group)      # every rank's counters are zero before anyone publishes
 
     def search(self, queries: torch.Tensor, k: int, *, broadcast: bool = False, filt=None):
         N, C = self._N, self._C
@@ -157,12 +192,22 @@ class FusedExchangeSearcher:
         need = self.shard.workspace_bytes(b, k, nf)
         if self._ws is None or self._ws.numel() < need:
             self._ws = torch.zeros(need, dtype=torch.uint8, device=dev)
-        self._published += b
+        call, total = self.exchange.next_call(b)
         lib = N.load()
         N.check(lib.crb_search_exchange(
             self.shard._h, queries.data_ptr(), b, k, self.metric, None if f is None else f.ctypes.data_as(C.c_void_p),
             scores.data_ptr(), rows.data_ptr(), n_valid.data_ptr(), None, self._ws.data_ptr(), self._ws.numel(),
-            self.algo, torch.cuda.current_stream(dev).cuda_stream, C.byref(self._ex),
-            self._calls & 0xFFFFFFFF, self._published & 0xFFFFFFFF))
-        self._calls += 1
+            self.algo, torch.cuda.current_stream(dev).cuda_stream, C.byref(self.exchange.struct), call, total))
         return scores, rows, n_valid, None
+
+    @staticmethod
+    def check(n_valid: torch.Tensor) -> None:
+        """Raise if a query of a finished call timed out waiting for a peer (``n_valid == -2``).  Synchronises; call
+        it where the result is consumed -- a ``range(n_valid)`` over -2 would read as an empty, successful answer.
+        Afterwards :meth:`reset` (collective) brings the ranks back in step."""
+        if bool((n_valid == -2).any()):
+            raise RuntimeError("sharded search: a peer did not publish before the wait ran out (lost or stalled rank); "
+                               "call reset() on every rank before searching again")
+
+    def reset(self) -> None:
+        self.exchange.reset()

@@ -256,6 +256,22 @@ class B200VectorStore:
         st._shard = DeviceShard.from_host(embeddings, codes, device=device, row_offset=row_offset)
         return st
 
+    @classmethod
+    def from_shard(cls, shard: DeviceShard, dictionary: Optional[MetadataDictionary] = None, *,
+                   id_fn: Callable[[int], str], meta_fn: Optional[Callable[[int], Dict[str, Any]]] = None,
+                   text_fn: Optional[Callable[[int], str]] = None, embedding: Any = None, metric: str = "cosine"
+                   ) -> "B200VectorStore":
+        """A read-only store over rows that are already resident (a shard built on the device); ids, text and
+        metadata are produced on demand from the LOCAL row number."""
+        st = cls(embedding, dim=shard.dim, filter_keys=dictionary.keys if dictionary is not None else (),
+                 device=shard.device.index or 0, metric=metric)
+        if dictionary is not None:
+            st.dictionary = dictionary
+        st._rows.id_fn, st._rows.meta_fn, st._rows.text_fn = id_fn, meta_fn, text_fn
+        st._rows.n_lazy = shard.n_rows
+        st._shard = shard
+        return st
+
     def _append(self, ids: Sequence[str], embeddings: np.ndarray, texts: Sequence[str],
                 metadatas: Sequence[Mapping[str, Any]]) -> List[str]:
         """Upsert rows.  New rows are encoded straight into the device shard's spare capacity
@@ -585,6 +601,25 @@ class B200VectorStore:
             self._mask_cache[extra] = mask
         return mask
 
+    def _fetch_vectors(self, rows: Sequence[int]) -> np.ndarray:
+        """Stored vectors of host rows, upcast to fp32 (the ``embedding`` of LCCassandra's result triples)."""
+        return self._shard.fetch_rows(rows)
+
+    def search_rows(self, queries: np.ndarray, k: int, filters: Optional[Sequence[Optional[Mapping[str, Any]]]] = None
+                    ) -> Tuple[np.ndarray, np.ndarray, np.ndarray]:
+        """The array-level call under all three faces: fp32 ``queries [B, dim]`` (host), one filter dict per query (or
+        None) -> ``(scores fp32 [B, k], rows int64 [B, k], n_valid int32 [B])`` on the host; ``rows`` index this
+        store's ids / text / metadata (``row_id(r)``).  One host-to-device copy of the queries and one device-to-host
+        copy of the result inside."""
+        self._ensure_built()
+        q = np.ascontiguousarray(queries, dtype=np.float32)
+        if q.ndim == 1:
+            q = q[None, :]
+        return self._search(q, k, list(filters) if filters is not None else [None] * len(q))
+
+    def row_id(self, row: int) -> str:
+        return self._rows.id(int(row))
+
     def _embed_query(self, text: str) -> List[float]:
         if self.embeddings is None:
             raise RuntimeError("text query needs an embedder (embedding=...)")
@@ -676,7 +711,7 @@ class B200VectorStore:
         if body_search:
             raise NotImplementedError("body_search is not supported")
         hits = self._hits(embedding, k, filter)
-        vecs = self._shard.fetch_rows([r for r, _ in hits])
+        vecs = self._fetch_vectors([r for r, _ in hits])
         return [(self._doc(r, s), vecs[i].tolist(), self._rows.id(r)) for i, (r, s) in enumerate(hits)]
 
     @_reading
@@ -706,10 +741,14 @@ class B200VectorStore:
     def _row_of(self, rid: str) -> Optional[int]:
         if self._rows.id_fn:
             try:
-                r = int(str(rid).rsplit("-", 1)[-1])
+                g = int(str(rid).rsplit("-", 1)[-1])
             except ValueError:
                 return None
-            return r if 0 <= r < len(self._rows) and self._rows.id(r) == str(rid) else None
+            off = self._shard.row_offset if self._shard is not None else 0
+            for r in (g, g - off):           # ids made from the local or from the global row number
+                if 0 <= r < len(self._rows) and self._rows.id(r) == str(rid):
+                    return r
+            return None
         return self._rows.pos.get(str(rid))
 
     def as_retriever(self, **kwargs: Any) -> "B200Retriever":
@@ -728,7 +767,7 @@ class B200VectorStore:
     @_reading
     def search(self, embedding: Sequence[float], k: int = 4, filter: Optional[Dict[str, Any]] = None, **kw) -> List[Content]:
         hits = self._hits(embedding, k, filter)
-        vecs = self._shard.fetch_rows([r for r, _ in hits])
+        vecs = self._fetch_vectors([r for r, _ in hits])
         return [self._content(r, vecs[i]) for i, (r, _) in enumerate(hits)]
 
     @_reading
@@ -741,7 +780,7 @@ class B200VectorStore:
             if filter and any(str(self._rows.meta(r).get(k)) != str(v) for k, v in filter.items()):
                 continue
             rows.append(r)
-        vecs = self._shard.fetch_rows(rows)
+        vecs = self._fetch_vectors(rows)
         return [self._content(r, vecs[i]) for i, r in enumerate(rows)]
 
     @_reading
@@ -783,7 +822,7 @@ class B200VectorStore:
                 if r not in best or s > best[r]:
                     best[r] = s
         top = sorted(best.items(), key=lambda t: (-t[1], -t[0]))[:k]
-        vecs = self._shard.fetch_rows([r for r, _ in top])
+        vecs = self._fetch_vectors([r for r, _ in top])
         return [self._content(r, vecs[i]) for i, (r, _) in enumerate(top)]
 
 

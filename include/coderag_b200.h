@@ -165,7 +165,8 @@ int crb_merge_keys(const uint64_t *d_keys_in, int32_t n_lists, int32_t batch, in
  * rank's search kernels store the k exact keys of every finished query straight into EVERY
  * rank's gather buffer over NVLink peer memory and bump a per-source arrival counter there
  * (system-scope release); a final kernel on each rank waits for `expected_total` arrivals from
- * every source and merges -- no collective launch between search and merge.
+ * every source and merges -- no collective launch between search and merge.  A query some source never
+ * published (bounded wait) comes back with n_valid = -2: the caller must treat that as a failure.
  *   peer_keys[p]     device pointer, valid on this rank, to rank p's gather buffer:
  *                    uint64 [2 (call parity)][world][cap_keys]   (e.g. torch symmetric memory)
  *   peer_counters[p] device pointer to rank p's uint32 [world] arrival counters (zeroed once)
@@ -180,12 +181,28 @@ typedef struct crb_exchange {
     uint64_t cap_keys;
     uint64_t *peer_keys[CRB_MAX_PEERS];
     uint32_t *peer_counters[CRB_MAX_PEERS];
+    uint32_t dest_mask; /* bit p set: rank p receives every rank's keys and merges; 0 = all ranks.  The
+                           serving store sets only the bit of the rank that owns the Python face (the
+                           reference runs ONE worker process, helm/templates/rag-worker-deployment.yaml:8):
+                           the other ranks send, wait for nothing and write no result. */
 } crb_exchange;
 int crb_search_exchange(crb_index *index, const float *d_queries, int32_t batch, int32_t k,
                         int32_t metric, const int32_t *h_filt, float *d_scores, int64_t *d_rows,
                         int32_t *d_n_valid, uint64_t *d_keys, void *d_workspace,
                         size_t workspace_bytes, int32_t algo, void *stream,
                         const crb_exchange *exchange, uint32_t call_index, uint32_t expected_total);
+
+/* crb_search_exchange through HOST buffers, the call a serving rank makes per request (the sharded counterpart
+ * of crb_search_host; stands for the same retriever.invoke() -> store call, agent_graph.py:249,268): copies the
+ * queries in from `h_queries` (every rank is handed the same request by the host-side dispatcher), searches its
+ * shard, sends its keys to the ranks of `dest_mask`, and -- on those ranks -- waits for all sources, merges, copies
+ * the merged result out and checks it: a source that never published makes the call FAIL (it does not return a
+ * short result).  Ranks outside `dest_mask` may pass NULL outputs.  `h_row_mask_ptrs` as in crb_search_masked
+ * (device pointers to THIS rank's slice of each mask; may be NULL).  Returns when this rank's work is done. */
+int crb_search_exchange_host(crb_index *index, const float *h_queries, int32_t batch, int32_t k,
+                             int32_t metric, const int32_t *h_filt, const uint32_t *const *h_row_mask_ptrs,
+                             float *h_scores, int64_t *h_rows, int32_t *h_n_valid, int32_t algo,
+                             const crb_exchange *exchange, uint32_t call_index, uint32_t expected_total);
 
 /* Fetch stored rows as fp32 (the `embedding` member of the (Document, embedding, id) triples
  * LCCassandra returns; graph-retriever re-scores from it).  h_rows_idx are LOCAL row indices. */
@@ -222,6 +239,14 @@ int crb_fetch_rows_host(crb_index *index, const int64_t *h_rows_idx, int32_t n, 
 int crb_search_noalloc(crb_index *index, const float *d_queries, int32_t batch, int32_t k,
                        int32_t metric, float *d_scores, int64_t *d_rows, int32_t *d_n_valid,
                        void *stream);
+
+/* Diagnostics of the tensor-core plan (no counterpart in the reference; used by this repository's tests to
+ * MEASURE the margin its exactness proof relies on).  While `d_stats` (fp32 [4 * batch] on the index's device) is
+ * set, every tensor-core search writes for query b:  [4b+0] max |approximate - exact| score over the candidates it
+ * re-scored (normalised-query units), [4b+1] the margin the proof allowed, [4b+2] how many it re-scored,
+ * [4b+3] 1 if the result was proven exact, 0 if the query was handed to the streaming fallback.  NULL switches it
+ * off (the default).  Results are not affected.  Not thread-safe: set it with no search in flight. */
+int crb_index_set_k5_stats(crb_index *index, float *d_stats);
 
 /* Number of kernels this library has launched in the calling process (bench.py's
  * `gpu_launches`). */

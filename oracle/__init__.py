@@ -24,9 +24,11 @@ from .simple_vector_store import (  # noqa: F401
     MODE_DOT,
     similarity,
     prefilter_mask,
+    filter_passes,
     get_top_k_embeddings,
     query_literal,
     query_vectorised,
+    query_blocks,
     score_rows,
     score_rows_f64,
     lc_score,

@@ -8,7 +8,7 @@ algorithm.  Upstream symbols restated (llama-index-core >= 0.10.0, the floor pin
 * ``llama_index/core/base/embeddings/base.py::similarity``            -> :func:`similarity`
 * ``llama_index/core/indices/query/embedding_utils.py::get_top_k_embeddings``
                                                                      -> :func:`get_top_k_embeddings`
-* ``llama_index/core/vector_stores/simple.py::_build_metadata_filter_fn`` (EQ / AND only)
+* ``llama_index/core/vector_stores/simple.py::_build_metadata_filter_fn`` (EQ / IN / CONTAINS, AND / OR)
                                                                      -> :func:`prefilter_mask`
 * ``llama_index/core/vector_stores/simple.py::SimpleVectorStore.query`` -> :func:`query_literal`
 
@@ -54,24 +54,55 @@ def similarity(embedding1: np.ndarray, embedding2: np.ndarray, mode: str = MODE_
     return product / norm
 
 
+def _filter_match(md: Mapping[str, Any], key: str, value: Any) -> bool:
+    """Upstream ``_process_filter_match`` for the operators this path uses.  ``value`` is a plain value (EQ; on
+    a list-valued metadata entry CONTAINS -- upstream's ``value in metadata_value``) or ``("in", [values])``
+    (IN: ``metadata_value in value``).  For list-valued metadata IN means "shares a member": the ingest writer
+    shreds such lists into one ``key -> member`` entry each
+    (``ingest/src/app/services/vector_write_service.py:152-154``), so each member is matched on its own.
+    A row lacking the key never matches."""
+    have = md.get(key)
+    if have is None:
+        return False
+    members = list(have) if isinstance(have, (list, tuple, set, frozenset)) else None
+    if isinstance(value, tuple) and len(value) == 2 and value[0] == "in":
+        allowed = set(value[1])
+        return any(m in allowed for m in members) if members is not None else have in allowed
+    return value in members if members is not None else have == value
+
+
+def filter_passes(md: Mapping[str, Any], filters: Optional[Mapping[str, Any]], condition: str = "and") -> bool:
+    """One row against a filter dict.  Upstream ``_build_metadata_filter_fn``: every leaf is evaluated, then
+    ``all`` (condition AND, the only one the reference emits) or ``any`` (OR).  The key ``"__any_of__"`` holds
+    nested groups -- a list of groups, each a list of alternative filter dicts, OR inside a group -- which is
+    how LlamaIndex's nested ``MetadataFilters`` / ``FilterCondition.OR`` reach the store under test."""
+    if not filters:
+        return True
+    results = []
+    for key, value in filters.items():
+        if key == "__any_of__":
+            results.extend(any(filter_passes(md, alt) for alt in group) for group in value)
+        else:
+            results.append(_filter_match(md, key, value))
+    return all(results) if condition == "and" else any(results)
+
+
 def prefilter_mask(
     metadatas: Sequence[Mapping[str, Any]],
-    filters: Optional[Mapping[str, str]] = None,
+    filters: Optional[Mapping[str, Any]] = None,
     *,
     ids: Optional[Sequence[str]] = None,
     node_ids: Optional[Sequence[str]] = None,
+    condition: str = "and",
 ) -> np.ndarray:
-    """Upstream ``_build_metadata_filter_fn`` restricted to what the reference emits:
-    AND of EQ predicates; a row lacking the key has ``metadata.get(key) is None`` and is
-    excluded.  ``node_ids`` is the optional allow-set of ``VectorStoreQuery.node_ids``."""
+    """Upstream ``_build_metadata_filter_fn``: AND (or OR) of EQ / IN / CONTAINS predicates; a row lacking the
+    key has ``metadata.get(key) is None`` and is excluded.  ``node_ids`` is the optional allow-set of
+    ``VectorStoreQuery.node_ids``."""
     n = len(metadatas)
     keep = np.ones(n, dtype=bool)
     if filters:
         for i, md in enumerate(metadatas):
-            for key, value in filters.items():
-                if md.get(key) != value:
-                    keep[i] = False
-                    break
+            keep[i] = filter_passes(md, filters, condition)
     if node_ids is not None:
         assert ids is not None
         allow = set(node_ids)
@@ -185,6 +216,50 @@ def query_vectorised(
             best_s, best_r = best_s[order], best_r[order]
     order = np.lexsort((-best_r, -best_s))[:k]
     return best_s[order], best_r[order]
+
+
+def query_blocks(
+    queries: np.ndarray,
+    blocks,
+    k: int,
+    *,
+    mode: str = MODE_COSINE,
+) -> List[Tuple[np.ndarray, np.ndarray]]:
+    """:func:`query_vectorised` for several queries over a corpus that arrives block by block (the 10M-100M row
+    configurations do not fit in host memory as fp32): ``blocks`` yields ``(first_row, rows[, keep])`` with rows
+    float16 or float32.  Same arithmetic per row -- fp32 dot, fp32 norms, ``dot / (|q| * |e|)`` -- with the row
+    norms computed once per block and the dots of all queries taken in one ``rows @ Q.T``; same ordering rule
+    (similarity descending, then row descending).  Returns one ``(similarities, rows)`` per query."""
+    Q = np.atleast_2d(np.asarray(queries, dtype=np.float32))
+    qn = np.linalg.norm(Q, axis=1).astype(np.float32)
+    best = [(np.empty(0, np.float32), np.empty(0, np.int64)) for _ in range(len(Q))]
+    for item in blocks:
+        first, blk = int(item[0]), np.asarray(item[1], dtype=np.float32)
+        keep = None if len(item) < 3 or item[2] is None else np.asarray(item[2], dtype=bool)
+        dots = blk @ Q.T
+        ok = np.ones(len(blk), dtype=bool) if keep is None else keep.copy()
+        norms = None
+        if mode == MODE_COSINE:
+            norms = _row_norms(blk)
+            ok &= norms > 0
+        idx = np.flatnonzero(ok)
+        if idx.size == 0:
+            continue
+        for b in range(len(Q)):
+            s = dots[idx, b]
+            if mode == MODE_COSINE:
+                s = s / (qn[b] * norms[idx])
+            s = s.astype(np.float32)
+            ids = idx
+            if ids.size > k:
+                part = np.argpartition(-s, k - 1)[:k]
+                sel = np.flatnonzero(s >= s[part].min())       # every row tied with the k-th stays in
+                s, ids = s[sel], ids[sel]
+            bs = np.concatenate([best[b][0], s])
+            br = np.concatenate([best[b][1], ids.astype(np.int64) + first])
+            order = np.lexsort((-br, -bs))[:k]
+            best[b] = (bs[order], br[order])
+    return best
 
 
 def score_rows(query_embedding: np.ndarray, rows: np.ndarray, mode: str = MODE_COSINE) -> np.ndarray:

@@ -1,0 +1,186 @@
+"""GPU tests of the filter vocabulary behind the store faces: the ingest writer's per-scope key set (`owner`,
+`symbol`, ... -- ingest/src/app/services/vector_write_service.py:28-34,58-64), OR / nested conditions, IN on
+list-valued keys, stores over a row-sharded range, and concurrent masked searches.  Every answer is checked against
+the oracle's `prefilter_mask` + `query_vectorised` on the same rows."""
+import threading
+
+import numpy as np
+import pytest
+
+import oracle
+from githubrepostorag_b200 import synthetic as S
+
+pytestmark = pytest.mark.gpu
+
+
+def _corpus(seed, n, d):
+    rng = np.random.default_rng(seed)
+    emb = rng.standard_normal((n, d), dtype=np.float32).astype(np.float16).astype(np.float32)
+    vocab = ["kafka", "jms", "redis", "grpc", "auth", "sql"]
+    metas = []
+    for i in range(n):
+        md = {"namespace": "default" if i % 5 else "acme", "repo": f"r{i % 7}", "owner": f"o{i % 3}",
+              "module": f"m{i % 23}", "file_path": f"src/f{i % 211}.py", "symbol": f"fn{i % 97}",
+              "language": ["python", "java", "go"][i % 3], "scope": "chunk", "branch": "main" if i % 10 else "dev",
+              "component_kind": "service" if i % 4 else "standalone"}
+        t = [vocab[j] for j in range(len(vocab)) if rng.random() < 0.25]
+        if t:
+            md["topics"] = t
+        md["imports"] = [f"lib{i % 31}", "os"]
+        if i % 2:
+            md["labels"] = [f"L{i % 4}"]
+        metas.append(md)
+    return rng, emb, metas, [S.row_id(i) for i in range(n)]
+
+
+def _expect(q, emb, metas, ids, k, flt, condition="and"):
+    keep = oracle.prefilter_mask(metas, flt, condition=condition)
+    s, r = oracle.query_vectorised(q, emb.astype(np.float16), k, keep=keep)
+    return [ids[int(i)] for i in r], s
+
+
+@pytest.mark.parametrize("scope,table", [("repo", "embeddings_repo"), ("chunk", "embeddings"), ("file", "embeddings_file")])
+def test_every_writer_key_filters_on_its_table(scope, table):
+    """`filter={"owner": ...}` / `{"symbol": ...}` (and every other key the writer indexes or always keeps) return
+    the oracle's rows on the table of that scope -- through the LangChain face, the LlamaIndex face and adjacent()."""
+    from githubrepostorag_b200.migrate import store_for_table
+    from githubrepostorag_b200.types import VectorStoreQuery
+    from githubrepostorag_b200.vector_store import filter_keys_for_scope
+    n, d, k = 4000, 64, 8
+    rng, emb, metas, ids = _corpus(17, n, d)
+    st = store_for_table(table, dim=d)
+    assert st.scope == scope
+    st.add_embeddings(ids, emb, [f"t{i}" for i in range(n)], metas)
+    q = rng.standard_normal(d, dtype=np.float32)
+    coded, multi = filter_keys_for_scope(scope)
+    for key in coded:
+        flt = {key: metas[11][key]}
+        want_ids, want_s = _expect(q, emb, metas, ids, k, flt)
+        got = st.similarity_search_with_score_id_by_vector(q.tolist(), k=k, filter=flt)
+        assert [i for _, _, i in got] == want_ids, key
+        assert np.allclose([2 * s - 1 for _, s, _ in got], want_s, rtol=1e-5, atol=2e-6), key
+    for key in multi:
+        flt = {key: next(m for m in metas if key in m)[key][0]}
+        assert [i for _, _, i in st.similarity_search_with_score_id_by_vector(q.tolist(), k=k, filter=flt)] == \
+            _expect(q, emb, metas, ids, k, flt)[0], key
+    flt = {"owner": "o1", "symbol": "fn5", "namespace": "default"}
+    res = st.query(VectorStoreQuery(query_embedding=q.tolist(), similarity_top_k=k, filters=flt))
+    assert res.ids == _expect(q, emb, metas, ids, k, flt)[0]
+    # edges on the new keys (GraphRetrieverFactory.py:107-145 lists owner / symbol / language as edges)
+    adj = st.adjacent({("owner", "o2"), ("symbol", "fn3")}, q.tolist(), k=k, filter={"namespace": "default"})
+    want = _expect(q, emb, metas, ids, k, {"namespace": "default", "__any_of__": [[{"owner": "o2"}, {"symbol": "fn3"}]]})[0]
+    assert [c.id for c in adj] == want
+    assert st.similarity_search_with_score_id_by_vector(q.tolist(), k=k, filter={"owner": "nobody"}) == []
+    st.close()
+
+
+def test_or_nested_and_in_filters_match_the_oracle():
+    from githubrepostorag_b200.types import (FilterCondition, FilterOperator, MetadataFilter, MetadataFilters,
+                                             VectorStoreQuery)
+    from githubrepostorag_b200.vector_store import B200VectorStore
+    n, d, k = 6000, 48, 10
+    rng, emb, metas, ids = _corpus(23, n, d)
+    st = B200VectorStore(dim=d)
+    st.add_embeddings(ids, emb, None, metas)
+    q = rng.standard_normal(d, dtype=np.float32)
+    F = MetadataFilter
+
+    def ask(filters):
+        return st.query(VectorStoreQuery(query_embedding=q.tolist(), similarity_top_k=k, filters=filters)).ids
+
+    # flat OR of equalities on coded and list-valued keys
+    got = ask(MetadataFilters([F("repo", "r3"), F("owner", "o1"), F("topics", "sql", FilterOperator.CONTAINS)],
+                              condition=FilterCondition.OR))
+    assert got == _expect(q, emb, metas, ids, k, {"repo": "r3", "owner": "o1", "topics": "sql"}, condition="or")[0]
+    # AND of an equality and a nested OR
+    got = ask(MetadataFilters([F("namespace", "default"),
+                               MetadataFilters([F("symbol", "fn7"), F("language", ["go", "rust"], FilterOperator.IN)],
+                                               condition=FilterCondition.OR)]))
+    want = _expect(q, emb, metas, ids, k, {"namespace": "default",
+                                           "__any_of__": [[{"symbol": "fn7"}, {"language": ("in", ["go", "rust"])}]]})[0]
+    assert got == want
+    # IN on a list-valued key: the row's list shares a member with the IN list
+    got = ask(MetadataFilters([F("topics", ["kafka", "grpc", "nope"], FilterOperator.IN), F("branch", "main")]))
+    assert got == _expect(q, emb, metas, ids, k, {"topics": ("in", ["kafka", "grpc", "nope"]), "branch": "main"})[0]
+    assert ask(MetadataFilters([F("topics", ["nope"], FilterOperator.IN)])) == []
+    # OR whose alternatives are all unknown matches nothing; an unknown alternative next to a known one is ignored
+    assert ask(MetadataFilters([F("repo", "zz"), F("nokey", "1")], condition=FilterCondition.OR)) == []
+    got = ask(MetadataFilters([F("repo", "zz"), F("repo", "r1")], condition=FilterCondition.OR))
+    assert got == _expect(q, emb, metas, ids, k, {"repo": "r1"})[0]
+    # the same OR through the LangChain face (dict form) and after a write (mask cache invalidated)
+    flt = {"__any_of__": [[{"owner": "o0"}, {"labels": "L3"}]]}
+    assert [i for _, _, i in st.similarity_search_with_score_id_by_vector(q.tolist(), k=k, filter=flt)] == \
+        _expect(q, emb, metas, ids, k, flt)[0]
+    st.delete(ids[int(_expect(q, emb, metas, ids, 1, flt)[0][0][4:])])
+    metas2 = list(metas)
+    metas2[int(_expect(q, emb, metas, ids, 1, flt)[0][0][4:])] = {}
+    assert [i for _, _, i in st.similarity_search_with_score_id_by_vector(q.tolist(), k=k, filter=flt)] == \
+        _expect(q, emb, metas2, ids, k, flt)[0]
+    st.close()
+
+
+def test_store_over_a_row_shard_with_offset():
+    """A store whose device shard starts at global row `lo` (row-sharding): searches return global rows, while
+    ids / text / metadata / stored vectors are looked up by LOCAL row."""
+    from githubrepostorag_b200.index import MetadataDictionary
+    from githubrepostorag_b200.vector_store import B200VectorStore
+    n, d, k, lo = 5000, 64, 6, 123_456
+    rng = np.random.default_rng(31)
+    emb16 = rng.standard_normal((n, d), dtype=np.float32).astype(np.float16)
+    repo = (np.arange(n) % 9).astype(np.int32)
+    dic = MetadataDictionary(["repo"])
+    dic.register_vocab("repo", [f"r{i}" for i in range(9)])
+    st = B200VectorStore.from_arrays(emb16, repo[None, :].copy(), dic, id_fn=lambda r: S.row_id(lo + r),
+                                     meta_fn=lambda r: {"repo": f"r{r % 9}"}, text_fn=lambda r: f"text {lo + r}",
+                                     row_offset=lo)
+    q = rng.standard_normal(d, dtype=np.float32)
+    for flt, keep in ((None, None), ({"repo": "r4"}, repo == 4)):
+        s_ref, r_ref = oracle.query_vectorised(q, emb16, k, keep=keep)
+        got = st.similarity_search_with_embedding_id_by_vector(q.tolist(), k=k, filter=flt)
+        assert [i for _, _, i in got] == [S.row_id(lo + int(r)) for r in r_ref]
+        for (doc, vec, rid), r in zip(got, r_ref):
+            assert np.array_equal(np.asarray(vec, np.float32), emb16[int(r)].astype(np.float32))
+            assert doc.page_content == f"text {lo + int(r)}" and doc.metadata["repo"] == f"r{int(r) % 9}"
+        assert np.allclose([d_.metadata["score"] for d_, _, _ in got], s_ref, rtol=1e-5, atol=2e-7)
+    adj = st.adjacent({("repo", "r1"), ("repo", "r2")}, q.tolist(), k=k)
+    s_ref, r_ref = oracle.query_vectorised(q, emb16, k, keep=(repo == 1) | (repo == 2))
+    assert [c.id for c in adj] == [S.row_id(lo + int(r)) for r in r_ref]
+    assert st.get([S.row_id(lo + 5)])[0].content == f"text {lo + 5}"
+    st.close()
+
+
+def test_concurrent_masked_searches_do_not_share_scratch():
+    """The worker runs up to 10 jobs on a thread pool against ONE store (rag_worker/src/worker/worker.py:136-139,185),
+    and the agent routinely filters on `topics` (agent_graph.py:230-233) -- a list-valued key, i.e. the device path
+    with a row mask.  Threads searching under different masks at the same time must each get the serial answer."""
+    from githubrepostorag_b200.vector_store import B200VectorStore
+    n, d, k = 60_000, 96, 10
+    rng, emb, metas, ids = _corpus(41, n, d)
+    st = B200VectorStore(dim=d)
+    st.add_embeddings(ids, emb, None, metas)
+    topics = ["kafka", "jms", "redis", "grpc", "auth", "sql"]
+    qs = rng.standard_normal((12, d), dtype=np.float32)
+    jobs = [(qs[i], {"topics": topics[i % 6], **({"repo": f"r{i % 7}"} if i % 2 else {})}) for i in range(12)]
+    serial = [[i for _, _, i in st.similarity_search_with_score_id_by_vector(q.tolist(), k=k, filter=f)] for q, f in jobs]
+    for j, (q, f) in enumerate(jobs[:4]):
+        assert serial[j] == _expect(q, emb, metas, ids, k, f)[0]
+    errors = []
+    start = threading.Barrier(len(jobs))
+
+    def run(j):
+        q, f = jobs[j]
+        try:
+            start.wait()
+            for _ in range(25):
+                got = [i for _, _, i in st.similarity_search_with_score_id_by_vector(q.tolist(), k=k, filter=f)]
+                if got != serial[j]:
+                    errors.append((j, got, serial[j]))
+                    return
+        except Exception as e:  # noqa: BLE001
+            errors.append((j, repr(e)))
+
+    ts = [threading.Thread(target=run, args=(j,)) for j in range(len(jobs))]
+    [t.start() for t in ts]
+    [t.join() for t in ts]
+    assert not errors, errors[:2]
+    st.close()

@@ -307,3 +307,104 @@ def test_k2_large_batches_k_boundary_and_threads(torch_cuda):
     [t.join() for t in ts]
     assert not errors, errors[:2]
     sh.close()
+
+
+def _unit_queries_exact_in_fp16(rng, batch, d):
+    """Queries with ||q|| == 1 EXACTLY whose entries are fp16 numbers (+-2^-e or +-2^-(e-1), a couple of zeros when
+    the count does not work out): the device normalises them to themselves and rounds them to fp16 without error,
+    so the tensor-core score and the canonical fp32 score differ by accumulation rounding ONLY."""
+    e = 0
+    while d > 4 ** e:
+        e += 1
+    used = d
+    while (4 ** e - used) % 3 != 0:
+        used -= 1
+    big = (4 ** e - used) // 3
+    assert 0 <= big <= used
+    q = np.zeros((batch, d), np.float32)
+    for b in range(batch):
+        pos = rng.permutation(d)[:used]
+        mag = np.full(used, 2.0 ** -e, np.float32)
+        mag[:big] = 2.0 ** -(e - 1)
+        q[b, pos] = mag * rng.choice([-1.0, 1.0], used).astype(np.float32)
+        assert float(np.sum(q[b].astype(np.float64) ** 2)) == 1.0
+    return q
+
+
+@pytest.mark.parametrize("n,d", [(40_000, 384), (40_000, 768), (30_000, 1024), (20_000, 2048), (17_000, 4096)])
+def test_k2_measured_rounding_stays_inside_the_proof_margin(torch_cuda, n, d):
+    """The exactness proof allows k2_rounding_allowance(dim) for the distance between the tensor-core score and the
+    canonical fp32 score.  Measure it (crb_index_set_k5_stats) where it is the only error -- unit queries that are
+    exact in fp16 -- on rows built to make truncation bias add up (every product positive), on Gaussian rows, and
+    under both metrics: the observed maximum must stay under a QUARTER of the allowance, Gaussian queries must be
+    proven (no fallback), and K2 must equal K1 bit for bit throughout (also the first K2 == K1 test at dim >= 2048)."""
+    torch = torch_cuda
+    rng = np.random.default_rng(d)
+    batch, k = 48, 10
+    q = _unit_queries_exact_in_fp16(rng, batch, d)
+    rows = rng.standard_normal((n, d), dtype=np.float32)
+    # rows aligned with a query so that every product q_i * x_i is positive: 40 per query, the top hits
+    for b in range(batch):
+        g = np.abs(rng.standard_normal((40, d), dtype=np.float32)) * np.sign(q[b]) + 0.3 * rng.standard_normal((40, d), dtype=np.float32)
+        rows[1000 + 40 * b: 1040 + 40 * b] = g
+    rows16 = rows.astype(np.float16)
+    sh = _shard(torch, rows16)
+    allowance = (d // 16 + 1) * 2.0 ** -22 + (d // 32 + 8) * 2.0 ** -24
+    stats = torch.zeros((batch, 4), dtype=torch.float32, device="cuda")
+    for mode in (oracle.MODE_COSINE, oracle.MODE_DOT):
+        sh.set_k5_stats(stats)
+        (s1, r1, v1), (s2, r2, v2) = _both(sh, torch, q, k, mode)
+        sh.set_k5_stats(None)
+        assert torch.equal(r1, r2) and torch.equal(v1, v2) and torch.equal(s1.view(torch.int32), s2.view(torch.int32))
+        st = stats.cpu().numpy()
+        max_norm = float(np.linalg.norm(rows16.astype(np.float32), axis=1).max()) if mode == oracle.MODE_DOT else 1.0
+        # the margin is the allowance alone (times the largest row norm for inner product): the query rounding term is 0
+        assert np.allclose(st[:, 1], allowance * max_norm, rtol=1e-3), (st[:3], allowance * max_norm)
+        assert (st[:, 2] >= k).all()
+        worst = float((st[:, 0] / st[:, 1]).max())
+        assert worst <= 0.25, f"d={d} {mode}: observed |approx - exact| reaches {worst:.3f} of the allowed margin"
+        _check(q[:2], rows16, s2.cpu().numpy()[:2], r2.cpu().numpy()[:2], v2.cpu().numpy()[:2], k, mode, what=f"margin d={d}")
+    # ordinary (Gaussian) queries: rounding of the query dominates eps; nothing may need the fallback
+    qg = rng.standard_normal((batch, d), dtype=np.float32)
+    sh.set_k5_stats(stats)
+    (s1, r1, v1), (s2, r2, v2) = _both(sh, torch, qg, k, oracle.MODE_COSINE)
+    sh.set_k5_stats(None)
+    st = stats.cpu().numpy()
+    assert torch.equal(r1, r2) and torch.equal(s1.view(torch.int32), s2.view(torch.int32))
+    assert float((st[:, 0] / st[:, 1]).max()) <= 0.25
+    assert st[:, 3].sum() >= batch - 1, f"{batch - int(st[:, 3].sum())} of {batch} Gaussian queries fell back"
+    sh.close()
+
+
+@pytest.mark.parametrize("d,metric", [(768, oracle.MODE_COSINE), (384, oracle.MODE_COSINE), (1024, oracle.MODE_DOT)])
+def test_k2_adversarial_cluster_at_the_kth_boundary(torch_cuda, d, metric):
+    """Thousands of rows within 1e-5 of the k-th score (a centroid + 1e-3 noise, which fp16 quantises into
+    near-duplicates and duplicates): the margin test cannot separate them, so the ids must still be the oracle's
+    (tie-aware) and identical to the streaming kernel's, bit for bit -- through the proof or through the fallback."""
+    torch = torch_cuda
+    rng = np.random.default_rng(900 + d)
+    n, k = 60_000, 10
+    rows = rng.standard_normal((n, d), dtype=np.float32)
+    c = rng.standard_normal(d, dtype=np.float32)
+    rows[5_000:25_000] = c + 1e-3 * rng.standard_normal((20_000, d), dtype=np.float32)
+    rows16 = rows.astype(np.float16)
+    q = np.stack([c, c + 1e-4 * rng.standard_normal(d, dtype=np.float32), c + 0.05 * rng.standard_normal(d, dtype=np.float32),
+                  rng.standard_normal(d, dtype=np.float32)] * 3).astype(np.float32)
+    sh = _shard(torch, rows16)
+    stats = torch.zeros((len(q), 4), dtype=torch.float32, device="cuda")
+    sh.set_k5_stats(stats)
+    (s1, r1, v1), (s2, r2, v2) = _both(sh, torch, q, k, metric)
+    sh.set_k5_stats(None)
+    assert torch.equal(r1, r2) and torch.equal(v1, v2) and torch.equal(s1.view(torch.int32), s2.view(torch.int32))
+    _check(q[:4], rows16, s2.cpu().numpy()[:4], r2.cpu().numpy()[:4], v2.cpu().numpy()[:4], k, metric, what=f"cluster d={d}")
+    # the cluster really is inside the margin: how many rows score within 1e-5 of the k-th
+    e32 = rows16[5_000:25_000].astype(np.float32)
+    if metric == oracle.MODE_COSINE:
+        sc = e32 @ q[0] / (np.linalg.norm(e32, axis=1) * np.linalg.norm(q[0]))
+        kth = np.sort(sc)[-k]
+        assert int((np.abs(sc - kth) < 1e-5).sum()) > 1000
+    else:       # inner products spread with the row norms: count the rows within 1e-4 (relative) of the k-th
+        sc = e32 @ q[0]
+        kth = np.sort(sc)[-k]
+        assert int((np.abs(sc - kth) < 1e-4 * abs(kth)).sum()) > 1000
+    sh.close()

@@ -223,3 +223,53 @@ def test_adjacent_searches_each_distinct_filter_once(lib, monkeypatch):
     assert sum("__impossible__" in f for f in flt) == 1            # namespace=other contradicts the caller's filter
     assert seen["queries"].shape == (4, 8)
     assert [c.id for c in out] == ["n0", "n1", "n2", "n3"]          # best four rows over all edges, de-duplicated
+
+
+def test_per_scope_filter_keys_follow_the_ingest_writer(lib):
+    """Every key the reference's writer indexes for a scope, and every key it keeps on all rows, is filterable on
+    that scope's table (ingest/src/app/services/vector_write_service.py:28-34,58-64); list-valued keys are served by
+    postings, the rest by one code column each, and all of them fit CRB_MAX_KEYS."""
+    from githubrepostorag_b200 import _native as N
+    from githubrepostorag_b200.retrievers import GraphRetrieverFactory, TableNames
+    from githubrepostorag_b200.vector_store import (ALLOW_FIELDS_BY_SCOPE, KEEP_ALWAYS_KEYS, B200VectorStore,
+                                                    filter_keys_for_scope, scope_of_table)
+    for scope, allow in ALLOW_FIELDS_BY_SCOPE.items():
+        coded, multi = filter_keys_for_scope(scope)
+        assert set(coded) | set(multi) == set(allow) | set(KEEP_ALWAYS_KEYS)
+        assert set(multi) == set(allow) & {"topics", "imports", "labels"}
+        assert len(coded) <= N.MAX_KEYS and len(set(coded)) == len(coded)
+    assert {"owner", "symbol"} <= set(filter_keys_for_scope("repo")[0]) and "symbol" in filter_keys_for_scope("chunk")[0]
+    assert scope_of_table("embeddings") == "chunk" and scope_of_table("embeddings_repo") == "repo"
+    fac = GraphRetrieverFactory(tables=TableNames(repo="embeddings_repo", module="embeddings_module",
+                                                  file="embeddings_file", chunk="embeddings"), dim=8)
+    st = fac.for_repo().store
+    assert st.scope == "repo" and "owner" in st.dictionary.keys and "labels" in st.multi_valued_keys
+    assert fac.for_chunk().store.scope == "chunk" and "imports" in fac.for_chunk().store.multi_valued_keys
+    # a filter on `owner` is an ordinary coded equality, not the impossible filter
+    st.add_embeddings(["r1"], np.ones((1, 8), np.float32), ["t"], [{"owner": "acme", "repo": "x"}])
+    eq, extra = st._split_filter({"owner": "acme"})
+    assert extra == () and st.dictionary.encode_filter(eq)[st.dictionary.keys.index("owner")] == 0
+    assert isinstance(B200VectorStore(dim=8).dictionary.keys, list)
+
+
+def test_llamaindex_filters_or_nested_in(lib):
+    """MetadataFilters -> filter dict: AND leaves stay flat (served by codes); OR and nesting become `__any_of__`
+    groups; IN and CONTAINS keep their operators; contradictory equalities are the impossible filter."""
+    from githubrepostorag_b200.types import FilterCondition, FilterOperator, MetadataFilter, MetadataFilters
+    from githubrepostorag_b200.vector_store import B200VectorStore
+    conv = B200VectorStore._filters_to_dict
+    F = MetadataFilter
+    assert conv(MetadataFilters([F("repo", "a"), F("owner", "o")])) == {"repo": "a", "owner": "o"}
+    assert conv(MetadataFilters([F("repo", "a"), F("repo", "b")])) == {"__impossible__": "1"}
+    got = conv(MetadataFilters([F("repo", "a"), F("owner", "o")], condition=FilterCondition.OR))
+    assert got == {"__any_of__": [[{"repo": "a"}, {"owner": "o"}]]}
+    nested = MetadataFilters([F("namespace", "ns"),
+                              MetadataFilters([F("topics", "x", FilterOperator.CONTAINS), F("repo", ["a", "b"], FilterOperator.IN)],
+                                              condition=FilterCondition.OR)])
+    assert conv(nested) == {"namespace": "ns", "__any_of__": [[{"__any_of__": [[{"topics": "x"}, {"repo": ("in", ["a", "b"])}]]}]]}
+    st = B200VectorStore(dim=8)
+    eq, extra = st._split_filter(conv(nested))
+    assert eq == {"namespace": "ns"} and len(extra) == 1 and extra[0][0] == "__any_of__"
+    eq, extra = st._split_filter({"topics": ("in", ["b", "a"]), "symbol": "f"})
+    assert eq == {"symbol": "f"} and extra == (("topics", ("in", ("a", "b"))),)
+    hash(extra)     # the mask cache key

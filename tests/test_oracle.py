@@ -89,3 +89,68 @@ def test_prefilter_semantics():
 
 def test_lc_score_convention():
     assert oracle.lc_score(1.0) == 1.0 and oracle.lc_score(-1.0) == 0.0 and oracle.lc_score(0.0) == 0.5
+
+
+@pytest.mark.parametrize("n,d,k", [(2000, 384, 10), (777, 768, 5), (4096, 64, 40)])
+def test_oracle_agrees_with_scikit_learn_brute_force(n, d, k):
+    """An independent second implementation (scikit-learn's cosine_similarity / brute-force NearestNeighbors)
+    ranks the same rows as the oracle restatement and scores them within 1e-6.  It does not pin the oracle to
+    the reference (nothing can: the reference holds no vector), but the goldens are no longer self-confirmed."""
+    sk_pair = pytest.importorskip("sklearn.metrics.pairwise")
+    sk_nn = pytest.importorskip("sklearn.neighbors")
+    rng = np.random.default_rng(7 * n + d)
+    e16 = rng.standard_normal((n, d), dtype=np.float32).astype(np.float16)
+    e64 = e16.astype(np.float64)
+    q = rng.standard_normal(d, dtype=np.float32)
+    ids = [f"row-{i:09d}" for i in range(n)]
+    sims, out = oracle.query_literal(q, e16.astype(np.float32), ids, k)
+    s_vec, r_vec = oracle.query_vectorised(q, e16, k)
+    cos = sk_pair.cosine_similarity(q[None, :].astype(np.float64), e64)[0]
+    order = np.lexsort((-np.arange(n), -cos))[:k]
+    assert [_row(i) for i in out] == order.tolist() == r_vec.tolist()
+    np.testing.assert_allclose(sims, cos[order], rtol=0, atol=1e-6)
+    nn = sk_nn.NearestNeighbors(n_neighbors=k, algorithm="brute", metric="cosine").fit(e64)
+    dist, idx = nn.kneighbors(q[None, :].astype(np.float64))
+    assert idx[0].tolist() == order.tolist()
+    np.testing.assert_allclose(1.0 - dist[0], sims, rtol=0, atol=1e-6)
+    # inner product against a plain float64 matrix product
+    sims_ip, out_ip = oracle.query_literal(q, e16.astype(np.float32), ids, k, mode=oracle.MODE_DOT)
+    dots = e64 @ q.astype(np.float64)
+    assert [_row(i) for i in out_ip] == np.lexsort((-np.arange(n), -dots))[:k].tolist()
+
+
+def test_prefilter_or_in_contains_semantics():
+    """AND / OR of EQ, IN and CONTAINS leaves (upstream `_build_metadata_filter_fn`), rows lacking a key never match."""
+    mds = [{"repo": "a", "owner": "acme", "topics": ["x", "y"]}, {"repo": "b", "owner": "acme"},
+           {"repo": "c", "topics": ["y"]}, {"owner": "zed", "topics": []}, {}]
+    m = lambda f, **kw: oracle.prefilter_mask(mds, f, **kw).tolist()   # noqa: E731
+    assert m({"owner": "acme"}) == [True, True, False, False, False]
+    assert m({"owner": "acme", "repo": "b"}) == [False, True, False, False, False]
+    assert m({"owner": "acme", "repo": "c"}, condition="or") == [True, True, True, False, False]
+    assert m({"topics": "y"}) == [True, False, True, False, False]                       # CONTAINS on a list
+    assert m({"topics": ("in", ["x", "q"])}) == [True, False, False, False, False]      # shares a member
+    assert m({"repo": ("in", ["a", "c", "zz"])}) == [True, False, True, False, False]
+    assert m({"__any_of__": [[{"repo": "a"}, {"owner": "zed"}]]}) == [True, False, False, True, False]
+    assert m({"owner": "acme", "__any_of__": [[{"repo": "b"}, {"topics": "x"}]]}) == [True, True, False, False, False]
+    assert m({"nope": "1"}) == [False] * 5
+
+
+@pytest.mark.parametrize("mode", [oracle.MODE_COSINE, oracle.MODE_DOT])
+def test_blockwise_multi_query_form_equals_the_vectorised_form(mode):
+    """`query_blocks` (what the full-size GPU tests stream 10M-row corpora through) ranks like `query_vectorised`."""
+    rng = np.random.default_rng(99)
+    n, d, k = 5000, 96, 12
+    e16 = rng.standard_normal((n, d), dtype=np.float32).astype(np.float16)
+    e16[100] = 0
+    e16[200:230] = e16[200]                         # exact ties across a block boundary
+    Q = rng.standard_normal((5, d), dtype=np.float32)
+    Q[1] = e16[200].astype(np.float32)
+    keep = rng.random(n) < 0.7
+    keep[200:230] = True
+    for kp in (None, keep):
+        blocks = [(lo, e16[lo:lo + 211], None if kp is None else kp[lo:lo + 211]) for lo in range(0, n, 211)]
+        got = oracle.query_blocks(Q, blocks, k, mode=mode)
+        for b in range(len(Q)):
+            s, r = oracle.query_vectorised(Q[b], e16, k, mode=mode, keep=kp)
+            assert got[b][1].tolist() == r.tolist()
+            np.testing.assert_allclose(got[b][0], s, rtol=2e-6, atol=1e-6)
