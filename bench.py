@@ -113,9 +113,10 @@ def host_queries(seed: int, batch: int, dim: int, which: int) -> np.ndarray:
 
 def device_codes(torch, lo: int, hi: int, seed: int, device):
     """C4's filterable columns (namespace ~ Zipf over 4, repo ~ Zipf(1.1) over 2000, component_kind 80/20;
-    SURVEY.md §8d) for rows [lo, hi), int32 [3, n], block-seeded like the rows."""
+    SURVEY.md §8d) for rows [lo, hi), block-seeded like the rows: one column per key, as narrow as the key's
+    dictionary allows (int8, int16, int8) -- what a store built from real metadata holds."""
     n = hi - lo
-    out = torch.empty((3, n), dtype=torch.int32, device=device)
+    out = [torch.empty((n,), dtype=dt, device=device) for dt in (torch.int8, torch.int16, torch.int8)]
     p_ns = torch.tensor([1.0 / (i + 1) for i in range(4)], device=device)
     p_repo = 1.0 / torch.arange(1, 2001, device=device, dtype=torch.float32) ** 1.1
     g = torch.Generator(device=device)
@@ -127,8 +128,8 @@ def device_codes(torch, lo: int, hi: int, seed: int, device):
         repo = torch.multinomial(p_repo, GEN_BLOCK, replacement=True, generator=g)
         ck = (torch.rand(GEN_BLOCK, generator=g, device=device) < 0.20).to(torch.int64)
         s, e = max(lo, first) - first, min(hi, first + GEN_BLOCK) - first
-        blk = torch.stack([ns, repo, ck]).to(torch.int32)
-        out[:, first + s - lo:first + e - lo] = blk[:, s:e]
+        for col, src in zip(out, (ns, repo, ck)):
+            col[first + s - lo:first + e - lo] = src[s:e].to(col.dtype)
         b += 1
     return out
 
@@ -324,7 +325,7 @@ class Bench:
         filt, sel = None, None
         if w["filtered"]:
             # the (namespace, repo, component_kind) triple whose joint selectivity is closest to 1 % (whole corpus)
-            combo = (codes[0].to(torch.int64) * 2000 + codes[1]) * 2 + codes[2]
+            combo = (codes[0].to(torch.int64) * 2000 + codes[1].to(torch.int64)) * 2 + codes[2].to(torch.int64)
             counts = torch.bincount(combo, minlength=4 * 2000 * 2).to(torch.float64)
             if self.world > 1:
                 self.dist.all_reduce(counts)
@@ -385,7 +386,7 @@ class Bench:
         tensor_plan = B >= 2 and n_local >= 131072 and c["filt"] is None
         if c["filt"] is not None:
             surv = c["sel"] * n_local
-            widths = c["shard"].code_bytes_per_row(3) if hasattr(c["shard"], "code_bytes_per_row") else 12
+            widths = sum(c["shard"].code_widths[:3])
             by = n_local * widths + surv * w["d"] * 2
             achieved = by / per_step_s / 1e9
             return {"bound": "hbm", "kernel": "k3_filter_kernel + k1_stream_kernel (gather)" if B <= 2 else "k3_filter + compact + k2 on survivors",
@@ -420,13 +421,24 @@ class Bench:
         w, shard = c["w"], c["shard"]
         k = w["k"]
         q_host = [host_queries(w["seed"], B, w["d"], i) for i in range(N_QUERY_SETS)]
-        flt = None
+        flt, dic = None, None
+        if c["filt"] is not None:
+            # the store encodes filter DICTS: give it the vocabulary the synthetic codes stand for
+            from githubrepostorag_b200 import synthetic as S
+            from githubrepostorag_b200.index import MetadataDictionary
+            keys = ("namespace", "repo", "component_kind")
+            dic = MetadataDictionary(keys)
+            for key in keys:
+                dic.register_vocab(key, S.vocab()[key])
+            one = {key: S.vocab()[key][int(code)] for key, code in zip(keys, c["filt"])}
+            flt = [one] * B
         store = None
         if self.world == 1:
-            store = B200VectorStore.from_shard(shard, id_fn=lambda r: f"row-{r:09d}")
+            store = B200VectorStore.from_shard(shard, dic, id_fn=lambda r: f"row-{r:09d}")
         else:
             from githubrepostorag_b200.sharded_store import CudaRankEngine, ShardedB200VectorStore
-            store = ShardedB200VectorStore(CudaRankEngine(_NoCloseShard(shard), cap_keys=1 << 17), max_batch=max(B, 64))
+            store = ShardedB200VectorStore(CudaRankEngine(_NoCloseShard(shard), cap_keys=1 << 17), dictionary=dic,
+                                           max_batch=max(B, 64))
         el = 0.0
         if self.rank == 0:
             for i in range(min(warmup, 5)):
@@ -466,12 +478,12 @@ class Bench:
         try:
             if self.rank == 0 and len(sample16):
                 n_s = min(len(sample16), c["hi"] - c["lo"])
-                sub = DeviceShard.from_device(c["rows"][:n_s], None if c["codes"] is None else c["codes"][:, :n_s].contiguous())
+                sub = DeviceShard.from_device(c["rows"][:n_s], None if c["codes"] is None else [col[:n_s].contiguous() for col in c["codes"]])
                 q = host_queries(w["seed"], 4, w["d"], 99)
                 keep = None
                 filt = None
                 if c["filt"] is not None:
-                    hc = c["codes"][:, :n_s].cpu().numpy()
+                    hc = [col[:n_s].cpu().numpy() for col in c["codes"]]
                     keep = (hc[0] == c["filt"][0]) & (hc[1] == c["filt"][1]) & (hc[2] == c["filt"][2])
                     filt = np.tile(c["filt"], (1, 1))
                 e32 = None

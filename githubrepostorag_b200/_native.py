@@ -45,6 +45,7 @@ PROTOTYPES = {
     "crb_index_reload_tuning": (C.c_int, [_vp]),
     "crb_index_set_k5_stats": (C.c_int, [_vp, _vp]),
     "crb_index_rebind": (C.c_int, [_vp, _vp, _vp, _vp, _i64, _i64]),
+    "crb_index_rebind_columns": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _i64]),
     "crb_tombstone_rows": (C.c_int, [_vp, _vp, _i32]),
     "crb_encode_rows": (C.c_int, [_vp, _vp, _vp, _i64, _i32, _i32, _vp]),
     "crb_row_inv_norms": (C.c_int, [_vp, _vp, _i64, _i32, _i32, _vp]),
@@ -52,6 +53,7 @@ PROTOTYPES = {
     "crb_search": (C.c_int, [_vp, _vp, _i32, _i32, _i32, _vp, _vp, _vp, _vp, _vp, _vp, _sz, _i32, _vp]),
     "crb_search_masked": (C.c_int, [_vp, _vp, _i32, _i32, _i32, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _sz, _i32, _vp]),
     "crb_search_host": (C.c_int, [_vp, _vp, _i32, _i32, _i32, _vp, _vp, _vp, _vp, _i32]),
+    "crb_search_host_vectors": (C.c_int, [_vp, _vp, _i32, _i32, _i32, _vp, _vp, _vp, _vp, _vp, _i32]),
     "crb_merge_keys": (C.c_int, [_vp, _i32, _i32, _i32, _i32, _vp, _i32, _vp, _vp, _vp, _vp, _i32, _vp]),
     "crb_search_exchange": (C.c_int, [_vp, _vp, _i32, _i32, _i32, _vp, _vp, _vp, _vp, _vp, _vp, _sz, _i32, _vp,
                                        _vp, C.c_uint32, C.c_uint32]),

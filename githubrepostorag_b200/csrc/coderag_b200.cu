@@ -166,8 +166,10 @@ struct Lane {
 struct crb_index {
     const __half* rows = nullptr;
     const float* inv_norm = nullptr;
-    const int32_t* codes = nullptr;
+    const int32_t* codes = nullptr;   // int32 [n_keys, code_stride] matrix, or nullptr when the columns were bound one by one
     int64_t code_stride = 0;       // elements between key columns of `codes`
+    const void* cols[CRB_MAX_KEYS] = {};   // column of key m (what the kernels read): width[m] bytes per row
+    uint8_t width[CRB_MAX_KEYS] = {};
     int64_t n_rows = 0;
     int32_t dim = 0;
     int32_t n_keys = 0;
@@ -332,17 +334,15 @@ static int k1_occupancy(K1Fn fn, size_t dyn_smem) {
     return n;
 }
 
-struct QueryGroup {
-    std::vector<int> queries;
-    int filter;  // index into the call's distinct-filter table, -1 = none
+// The streaming instantiation for groups of `nq` queries on this index: width class, rows in flight, the
+// half-warp layout for dim <= 512 and the exact-width forms for dim 384 / 768.  One picker for every entry point.
+struct K1Choice {
+    K1Fn fn = nullptr;
+    bool generic = false;          // dim > 1024: query in shared memory, one query per group
+    size_t dyn_smem = 0;
+    int rows_per_warp_iter = 0;
 };
-
-// Launch K1 for `groups` (all with at most `nq` queries, filter slots already remapped to the
-// lists currently in the workspace).
-static int launch_k1(const crb_index* ix, const float* d_queries, int k, int metric,
-                     const std::vector<QueryGroup>& groups, const std::vector<int>& slot_of_filter,
-                     int nq, uint8_t* ws, const uint32_t* lists, float* d_scores, int64_t* d_rows,
-                     int32_t* d_n_valid, uint64_t* d_keys, cudaStream_t stream, const ExchangeDev* ex = nullptr) {
+static int k1_choose(const crb_index* ix, int nq, int k, K1Choice* out) {
     const int chunks = ix->dim / 8;
     const int ch = (chunks + 31) / 32;
     const bool generic = ch > 4;
@@ -361,8 +361,30 @@ static int launch_k1(const crb_index* ix, const float* d_queries, int k, int met
         r1 = 2 * rp;
     }
     if (!fn) return fail("internal: no K1 instantiation for nq=%d ch=%d", nq, ch);
-    const size_t dyn = generic ? size_t(ix->dim) * sizeof(float) : 0;
-    const int rows_per_warp_iter = r1;
+    out->fn = fn;
+    out->generic = generic;
+    out->dyn_smem = generic ? size_t(ix->dim) * sizeof(float) : 0;
+    out->rows_per_warp_iter = r1;
+    return 0;
+}
+
+struct QueryGroup {
+    std::vector<int> queries;
+    int filter;  // index into the call's distinct-filter table, -1 = none
+};
+
+// Launch K1 for `groups` (all with at most `nq` queries, filter slots already remapped to the
+// lists currently in the workspace).
+static int launch_k1(const crb_index* ix, const float* d_queries, int k, int metric,
+                     const std::vector<QueryGroup>& groups, const std::vector<int>& slot_of_filter,
+                     int nq, uint8_t* ws, const uint32_t* lists, float* d_scores, int64_t* d_rows,
+                     int32_t* d_n_valid, uint64_t* d_keys, cudaStream_t stream, const ExchangeDev* ex = nullptr) {
+    K1Choice c;
+    if (int rc = k1_choose(ix, nq, k, &c)) return rc;
+    const K1Fn fn = c.fn;
+    const bool generic = c.generic;
+    const size_t dyn = c.dyn_smem;
+    const int rows_per_warp_iter = c.rows_per_warp_iter;
     const int resident = k1_occupancy(fn, dyn) * ix->sm_count;
 
     for (size_t g0 = 0; g0 < groups.size(); g0 += kMaxGroups) {
@@ -842,7 +864,7 @@ static int search_impl(crb_index* ix, const float* d_queries, int batch, int k, 
     // (CODERAG_B200_K1_FUSED=1): measured 6 % faster than K3 + K1 at 1 % selectivity (10M x 1024: 84.8 vs 89.9 us)
     // but slower when most rows pass (the scan and the scoring share one warp's registers and serialise their
     // memory latencies), and the plan has no selectivity estimate to choose by.
-    if (batch == 1 && F == 1 && ch <= 4 && algo != 2 && ix->n_rows > 0 && ix->tune.k1_fused > 0) {
+    if (batch == 1 && F == 1 && ch <= 4 && algo != 2 && ix->n_rows > 0 && ix->tune.k1_fused > 0 && ix->codes) {
         bool impossible = false;
         for (int m = 0; m < M; ++m) impossible |= (filters[0][m] == CRB_FILT_IMPOSSIBLE);
         if (!impossible)
@@ -884,13 +906,16 @@ static int search_impl(crb_index* ix, const float* d_queries, int batch, int k, 
         if (f_hi > f_lo) {
             K3Params kp;
             memset(&kp, 0, sizeof kp);
-            kp.codes = ix->codes;
+            for (int m = 0; m < M; ++m) {
+                kp.cols[m] = ix->cols[m];
+                kp.width[m] = ix->width[m];
+                kp.vec_ok[m] = reinterpret_cast<uintptr_t>(ix->cols[m]) % 16 == 0 ? 1 : 0;
+            }
             kp.lists = lists;
             kp.counts = reinterpret_cast<uint32_t*>(ws + kWsCountsOffset);
             kp.masks = any_k2_filtered ? masks : nullptr;
             kp.mask_stride = mstride;
             kp.n_rows = ix->n_rows;
-            kp.code_stride = ix->code_stride;
             kp.list_stride = stride;
             kp.n_keys = M;
             kp.n_filters = f_hi - f_lo;
@@ -1137,6 +1162,10 @@ static int bind_buffers(crb_index* ix, const void* d_rows_f16, const float* d_in
     ix->inv_norm = d_inv_norm;
     ix->codes = d_codes;
     ix->code_stride = code_stride;
+    for (int m = 0; m < ix->n_keys; ++m) {
+        ix->cols[m] = d_codes ? d_codes + int64_t(m) * code_stride : nullptr;
+        ix->width[m] = 4;
+    }
     ix->n_rows = n_rows;
     ix->k2_ok = false;
     ix->max_norm = 0.f;
@@ -1222,6 +1251,30 @@ extern "C" int crb_index_rebind(crb_index* ix, const void* d_rows_f16, const flo
     DeviceGuard guard(ix->device);
     CRB_CUDA(guard.status);
     return bind_buffers(ix, d_rows_f16, d_inv_norm, d_codes, n_rows, code_stride);
+}
+
+extern "C" int crb_index_rebind_columns(crb_index* ix, const void* d_rows_f16, const float* d_inv_norm,
+                                        const void* const* h_code_cols, const int32_t* h_code_widths, int64_t n_rows) {
+    if (!ix) return fail("index is NULL");
+    if (n_rows < 0) return fail("n_rows must be >= 0");
+    if (n_rows > 0 && (!d_rows_f16 || !d_inv_norm)) return fail("rows / inv_norm pointers are NULL");
+    if (ix->n_keys > 0 && (!h_code_cols || !h_code_widths)) return fail("column pointers / widths are NULL with n_keys > 0");
+    for (int m = 0; m < ix->n_keys; ++m) {
+        const int w = h_code_widths[m];
+        if (w != 1 && w != 2 && w != 4) return fail("code column %d: width must be 1, 2 or 4 bytes (got %d)", m, w);
+        if (n_rows > 0 && !h_code_cols[m]) return fail("code column %d is NULL", m);
+        if (reinterpret_cast<uintptr_t>(h_code_cols[m]) % w != 0) return fail("code column %d is not aligned to its width", m);
+    }
+    if (reinterpret_cast<uintptr_t>(d_rows_f16) % 16 != 0) return fail("rows must be 16-byte aligned");
+    if (ix->row_offset + n_rows > int64_t(0xffffffffll)) return fail("row_offset + n_rows must fit in 32 bits");
+    DeviceGuard guard(ix->device);
+    CRB_CUDA(guard.status);
+    if (int rc = bind_buffers(ix, d_rows_f16, d_inv_norm, nullptr, n_rows, n_rows)) return rc;
+    for (int m = 0; m < ix->n_keys; ++m) {
+        ix->cols[m] = h_code_cols[m];
+        ix->width[m] = static_cast<uint8_t>(h_code_widths[m]);
+    }
+    return 0;
 }
 
 extern "C" int crb_index_reload_tuning(crb_index* ix) {
@@ -1343,9 +1396,11 @@ extern "C" int crb_search_masked(crb_index* ix, const float* d_queries, int32_t 
                        h_row_mask_ptrs);
 }
 
-extern "C" int crb_search_host(crb_index* ix, const float* h_queries, int32_t batch, int32_t k,
-                               int32_t metric, const int32_t* h_filt, float* h_scores,
-                               int64_t* h_rows, int32_t* h_n_valid, int32_t algo) {
+namespace crb {
+// crb_search_host and crb_search_host_vectors: host buffers in, host buffers out, one lane per caller
+static int search_host_impl(crb_index* ix, const float* h_queries, int32_t batch, int32_t k, int32_t metric,
+                            const int32_t* h_filt, float* h_scores, int64_t* h_rows, int32_t* h_n_valid,
+                            float* h_vectors, int32_t algo) {
     if (int rc = validate_search(ix, batch, k, metric)) return rc;
     if (!h_queries || !h_scores || !h_rows || !h_n_valid) return fail("NULL host pointer passed to crb_search_host");
     DeviceGuard guard(ix->device);
@@ -1357,11 +1412,13 @@ extern "C" int crb_search_host(crb_index* ix, const float* h_queries, int32_t ba
     const size_t s_bytes = size_t(batch) * k * sizeof(float);
     const size_t r_bytes = size_t(batch) * k * sizeof(int64_t);
     const size_t v_bytes = size_t(batch) * sizeof(int32_t);
-    // device io: [queries | rows (8B aligned) | scores | n_valid]; pinned mirrors the same layout
+    const size_t e_bytes = h_vectors ? size_t(batch) * k * ix->dim * sizeof(float) : 0;
+    // device io: [queries | rows (8B aligned) | scores | n_valid | vectors]; pinned mirrors the same layout
     const size_t off_rows = round_up(q_bytes, 256);
     const size_t off_scores = off_rows + round_up(r_bytes, 256);
     const size_t off_valid = off_scores + round_up(s_bytes, 256);
-    const size_t io_bytes = off_valid + round_up(v_bytes, 256);
+    const size_t off_vec = off_valid + round_up(v_bytes, 256);
+    const size_t io_bytes = off_vec + round_up(e_bytes, 256);
     const size_t ws_bytes = crb_workspace_bytes(ix, batch, k, count_distinct_filters(h_filt, batch, ix->n_keys));
     if (int rc = lane_reserve(l, ws_bytes, io_bytes, io_bytes)) return rc;
 
@@ -1375,12 +1432,37 @@ extern "C" int crb_search_host(crb_index* ix, const float* h_queries, int32_t ba
                          reinterpret_cast<int32_t*>(d_io + off_valid), nullptr, l->d_ws, l->ws_cap,
                          algo, l->stream);
     if (rc) { cudaStreamSynchronize(l->stream); return rc; }
+    if (h_vectors && ix->n_rows > 0) {
+        const int n = batch * k;
+        const unsigned blocks = static_cast<unsigned>(std::min<int64_t>((int64_t(n) * ix->dim + 255) / 256, int64_t(ix->sm_count) * 8));
+        fetch_result_rows_kernel<<<blocks, 256, 0, l->stream>>>(ix->rows, reinterpret_cast<const int64_t*>(d_io + off_rows), n,
+                                                                ix->row_offset, ix->dim, reinterpret_cast<float*>(d_io + off_vec));
+        CRB_LAUNCH_CHECK();
+    }
     CRB_CUDA(cudaMemcpyAsync(h_io + off_rows, d_io + off_rows, io_bytes - off_rows, cudaMemcpyDeviceToHost, l->stream));
     CRB_CUDA(cudaStreamSynchronize(l->stream));
     memcpy(h_rows, h_io + off_rows, r_bytes);
     memcpy(h_scores, h_io + off_scores, s_bytes);
     memcpy(h_n_valid, h_io + off_valid, v_bytes);
+    if (h_vectors) {
+        if (ix->n_rows > 0) memcpy(h_vectors, h_io + off_vec, e_bytes);
+        else memset(h_vectors, 0, e_bytes);
+    }
     return 0;
+}
+}  // namespace crb
+
+extern "C" int crb_search_host(crb_index* ix, const float* h_queries, int32_t batch, int32_t k,
+                               int32_t metric, const int32_t* h_filt, float* h_scores,
+                               int64_t* h_rows, int32_t* h_n_valid, int32_t algo) {
+    return search_host_impl(ix, h_queries, batch, k, metric, h_filt, h_scores, h_rows, h_n_valid, nullptr, algo);
+}
+
+extern "C" int crb_search_host_vectors(crb_index* ix, const float* h_queries, int32_t batch, int32_t k,
+                                       int32_t metric, const int32_t* h_filt, float* h_scores,
+                                       int64_t* h_rows, int32_t* h_n_valid, float* h_vectors, int32_t algo) {
+    if (!h_vectors) return fail("NULL vector buffer passed to crb_search_host_vectors");
+    return search_host_impl(ix, h_queries, batch, k, metric, h_filt, h_scores, h_rows, h_n_valid, h_vectors, algo);
 }
 
 extern "C" int crb_merge_keys(const uint64_t* d_keys_in, int32_t n_lists, int32_t batch, int32_t k,
@@ -1597,22 +1679,19 @@ extern "C" int crb_search_noalloc(crb_index* ix, const float* d_queries, int32_t
     unsigned char* scratch = nullptr;
     if (int rc = noalloc_scratch(ix->device, &scratch)) return rc;
 
-    // plan: consecutive queries share a group of up to nq_cap (no filters here)
-    const int chunks = ix->dim / 8;
-    const int ch = (chunks + 31) / 32;
-    const bool generic = ch > 4;
-    const int nq_cap = generic ? 1 : (ch <= 2 ? 4 : 2);
+    // plan: as crb_search plans its streaming groups -- consecutive queries pair up (one query per group for
+    // dim > 1024), and the instantiation comes from the same picker (half-warp and exact-width forms included)
+    const int ch = (ix->dim / 8 + 31) / 32;
+    const int nq_cap = ch > 4 ? 1 : std::max(1, std::min(2, ix->tune.k1_group > 0 ? ix->tune.k1_group : 2));
     const int ng = (batch + nq_cap - 1) / nq_cap;
-    const int widest = std::min<int>(batch, nq_cap);
-    const int nq = widest <= 1 ? 1 : (widest <= 2 ? 2 : 4);
-    const int r1 = generic ? 2 : k1_default_rows(nq, ch);
-    K1Fn fn = generic ? k1_pick_generic(k) : k1_pick(nq, ch, r1, k);
-    if (!fn) return fail("internal: no K1 instantiation for nq=%d ch=%d", nq, ch);
-    const size_t dyn = generic ? size_t(ix->dim) * sizeof(float) : 0;
-    const int rows_per_warp_iter = r1;
-    int per_sm = 0;
-    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fn, kK1Threads, dyn) != cudaSuccess || per_sm < 1) per_sm = 1;
-    const int resident = per_sm * ix->sm_count;
+    const int nq = std::min<int>(batch, nq_cap);
+    K1Choice c;
+    if (int rc = k1_choose(ix, nq, k, &c)) return rc;
+    const K1Fn fn = c.fn;
+    const bool generic = c.generic;
+    const size_t dyn = c.dyn_smem;
+    const int rows_per_warp_iter = c.rows_per_warp_iter;
+    const int resident = k1_occupancy(fn, dyn) * ix->sm_count;
 
     K1Params p;
     memset(&p, 0, sizeof p);

@@ -6,7 +6,11 @@
 // graph_rag_retrievers.py:82-100).  One pass over the code columns evaluates up to 32
 // filters at once (one pass-bit per filter per row) and appends the surviving local row
 // indices of each filter to its list; K1/K2 then touch only surviving rows.
-// Bound: HBM.  Algorithmic bytes = n_rows * used_keys * 4 (codes) + survivors * 4 (lists).
+//
+// Code columns are as narrow as their dictionary allows (1, 2 or 4 bytes per row: `namespace`,
+// `branch`, `component_kind`, `scope` have a handful of values, `repo` thousands), one column per
+// key, and a thread reads 16 consecutive rows of a column with 16-byte loads.
+// Bound: HBM.  Algorithmic bytes = n_rows * sum(width of the used keys) + survivors * 4 (lists).
 #pragma once
 #include "common.cuh"
 
@@ -14,16 +18,17 @@ namespace crb {
 
 constexpr int kK3Threads = 256;
 constexpr int kK3Warps = kK3Threads / 32;
-constexpr int kK3RowsPerThread = 8;
+constexpr int kK3RowsPerThread = 16;     // consecutive rows: one 16-byte load of an int8 column
 
 struct K3Params {
-    const int32_t* codes;  // [n_keys, n_rows]
+    const void* cols[kMaxKeys];   // column of key m: [n_rows] codes of width[m] bytes, -1 = key absent
+    uint8_t width[kMaxKeys];      // 1, 2 or 4
+    uint8_t vec_ok[kMaxKeys];     // column start is 16-byte aligned: vector loads
     uint32_t* lists;       // [n_filters, list_stride]
     uint32_t* counts;      // [n_filters], zero on entry
     uint32_t* masks;       // [n_filters, mask_stride] one pass bit per row (for K2), or nullptr
     int64_t mask_stride;
     int64_t n_rows;
-    int64_t code_stride;   // elements between consecutive key columns (>= n_rows)
     int64_t list_stride;
     int32_t n_keys;
     int32_t n_filters;
@@ -32,6 +37,42 @@ struct K3Params {
     const uint32_t* extra[kMaxFilters];   // optional caller-built pass-bit mask ANDed into filter f (or nullptr)
 };
 
+// 16 consecutive codes of one column, sign-extended to int32 (the "missing" code -1 survives narrowing).
+CRB_DEVINL void k3_load_codes(const void* col, int width, bool vec, int64_t row0, int n_ok, int32_t (&code)[kK3RowsPerThread]) {
+    if (vec && n_ok == kK3RowsPerThread) {
+        if (width == 1) {
+            const uint4 v = __ldg(reinterpret_cast<const uint4*>(static_cast<const int8_t*>(col) + row0));
+            const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+            for (int j = 0; j < 16; ++j) code[j] = static_cast<int32_t>(static_cast<int8_t>((w[j >> 2] >> (8 * (j & 3))) & 0xffu));
+        } else if (width == 2) {
+            const uint4* p = reinterpret_cast<const uint4*>(static_cast<const int16_t*>(col) + row0);
+            const uint4 a = __ldg(p), b = __ldg(p + 1);
+            const uint32_t w[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+#pragma unroll
+            for (int j = 0; j < 16; ++j) code[j] = static_cast<int32_t>(static_cast<int16_t>((w[j >> 1] >> (16 * (j & 1))) & 0xffffu));
+        } else {
+            const int4* p = reinterpret_cast<const int4*>(static_cast<const int32_t*>(col) + row0);
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const int4 v = __ldg(p + i);
+                code[4 * i] = v.x; code[4 * i + 1] = v.y; code[4 * i + 2] = v.z; code[4 * i + 3] = v.w;
+            }
+        }
+        return;
+    }
+#pragma unroll
+    for (int j = 0; j < kK3RowsPerThread; ++j) {
+        int32_t c = -1;
+        if (j < n_ok) {
+            if (width == 1) c = __ldg(static_cast<const int8_t*>(col) + row0 + j);
+            else if (width == 2) c = __ldg(static_cast<const int16_t*>(col) + row0 + j);
+            else c = __ldg(static_cast<const int32_t*>(col) + row0 + j);
+        }
+        code[j] = c;
+    }
+}
+
 __global__ void __launch_bounds__(kK3Threads) k3_filter_kernel(const __grid_constant__ K3Params p) {
     __shared__ uint32_t s_cnt[kMaxFilters];
     __shared__ uint32_t s_base[kMaxFilters];
@@ -39,26 +80,21 @@ __global__ void __launch_bounds__(kK3Threads) k3_filter_kernel(const __grid_cons
 
     const int lane = threadIdx.x & 31;
     const int warp = threadIdx.x >> 5;
-    const int64_t blk0 = static_cast<int64_t>(blockIdx.x) * (kK3Threads * kK3RowsPerThread);
+    const int64_t row0 = (static_cast<int64_t>(blockIdx.x) * kK3Threads + threadIdx.x) * kK3RowsPerThread;
+    const int64_t left = p.n_rows - row0;
+    const int n_ok = left >= kK3RowsPerThread ? kK3RowsPerThread : (left > 0 ? static_cast<int>(left) : 0);
     const uint32_t all = p.n_filters >= 32 ? 0xffffffffu : ((1u << p.n_filters) - 1u);
 
     if (threadIdx.x < kMaxFilters) s_cnt[threadIdx.x] = 0u;
 
-    // pass[j]: bit f set when row j of this thread survives filter f
+    // pass[j]: bit f set when row row0 + j survives filter f
     uint32_t pass[kK3RowsPerThread];
 #pragma unroll
-    for (int j = 0; j < kK3RowsPerThread; ++j) {
-        const int64_t row = blk0 + j * kK3Threads + threadIdx.x;
-        pass[j] = row < p.n_rows ? all : 0u;
-    }
+    for (int j = 0; j < kK3RowsPerThread; ++j) pass[j] = j < n_ok ? all : 0u;
     for (int m = 0; m < p.n_keys; ++m) {
         if (!((p.used_keys >> m) & 1u)) continue;
         int32_t code[kK3RowsPerThread];
-#pragma unroll
-        for (int j = 0; j < kK3RowsPerThread; ++j) {
-            const int64_t row = blk0 + j * kK3Threads + threadIdx.x;
-            code[j] = row < p.n_rows ? __ldg(p.codes + static_cast<int64_t>(m) * p.code_stride + row) : -1;
-        }
+        k3_load_codes(p.cols[m], p.width[m], p.vec_ok[m] != 0, row0, n_ok, code);
         for (int f = 0; f < p.n_filters; ++f) {
             const int32_t w = p.want[f][m];
             if (w == -1) continue;  // CRB_FILT_ANY
@@ -67,25 +103,31 @@ __global__ void __launch_bounds__(kK3Threads) k3_filter_kernel(const __grid_cons
                 if (code[j] != w) pass[j] &= ~(1u << f);
         }
     }
-    // caller-built row masks (membership in list-valued metadata, IN lists, ...): one bit per row
+    // caller-built row masks (membership in list-valued metadata, IN lists, OR ...): one bit per row; the
+    // thread's 16 rows are one half of a mask word
     for (int f = 0; f < p.n_filters; ++f) {
         const uint32_t* ex = p.extra[f];
-        if (!ex) continue;
+        if (!ex || n_ok == 0) continue;
+        const uint32_t half = (__ldg(ex + (row0 >> 5)) >> (row0 & 31)) & 0xffffu;
 #pragma unroll
-        for (int j = 0; j < kK3RowsPerThread; ++j) {
-            const int64_t row = blk0 + j * kK3Threads + threadIdx.x;
-            if (row < p.n_rows && !((__ldg(ex + (row >> 5)) >> (row & 31)) & 1u)) pass[j] &= ~(1u << f);
-        }
+        for (int j = 0; j < kK3RowsPerThread; ++j)
+            if (!((half >> j) & 1u)) pass[j] &= ~(1u << f);
     }
     __syncthreads();
 
-    // count per filter: warp totals -> block totals -> one global atomic per filter per block
+    // per filter: this thread's 16-bit survivor mask; the warp's total claims the warp's place in the block
     for (int f = 0; f < p.n_filters; ++f) {
-        uint32_t cnt = 0;
+        uint32_t pm = 0u;
 #pragma unroll
-        for (int j = 0; j < kK3RowsPerThread; ++j)
-            cnt += __popc(__ballot_sync(CRB_FULL_MASK, (pass[j] >> f) & 1u));
-        if (lane == 0) s_wbase[warp][f] = cnt ? atomicAdd(&s_cnt[f], cnt) : 0u;
+        for (int j = 0; j < kK3RowsPerThread; ++j) pm |= ((pass[j] >> f) & 1u) << j;
+        const uint32_t cnt = __popc(pm);
+        const uint32_t tot = __reduce_add_sync(CRB_FULL_MASK, cnt);
+        if (lane == 0) s_wbase[warp][f] = tot ? atomicAdd(&s_cnt[f], tot) : 0u;
+        // the pass-bit words of K2's masks: two lanes share a word
+        if (p.masks) {
+            const uint32_t hi = __shfl_down_sync(CRB_FULL_MASK, pm, 1);
+            if (!(lane & 1) && row0 < p.n_rows) p.masks[static_cast<int64_t>(f) * p.mask_stride + (row0 >> 5)] = pm | (hi << 16);
+        }
     }
     __syncthreads();
     if (threadIdx.x < p.n_filters) {
@@ -94,19 +136,25 @@ __global__ void __launch_bounds__(kK3Threads) k3_filter_kernel(const __grid_cons
     }
     __syncthreads();
 
-    const uint32_t lt = (1u << lane) - 1u;
     for (int f = 0; f < p.n_filters; ++f) {
-        uint32_t off = s_base[f] + s_wbase[warp][f];
-        uint32_t* list = p.lists + static_cast<int64_t>(f) * p.list_stride;
+        uint32_t pm = 0u;
 #pragma unroll
-        for (int j = 0; j < kK3RowsPerThread; ++j) {
-            const uint32_t bit = (pass[j] >> f) & 1u;
-            const uint32_t b = __ballot_sync(CRB_FULL_MASK, bit);
-            const int64_t row = blk0 + j * kK3Threads + threadIdx.x;
-            if (bit) list[off + __popc(b & lt)] = static_cast<uint32_t>(row);
-            // the warp's 32 rows are consecutive and 32-aligned: one mask word per ballot
-            if (p.masks && lane == 0 && row < p.n_rows) p.masks[static_cast<int64_t>(f) * p.mask_stride + (row >> 5)] = b;
-            off += __popc(b);
+        for (int j = 0; j < kK3RowsPerThread; ++j) pm |= ((pass[j] >> f) & 1u) << j;
+        if (__ballot_sync(CRB_FULL_MASK, pm != 0u) == 0u) continue;
+        // exclusive prefix of the lanes' survivor counts
+        const uint32_t cnt = __popc(pm);
+        uint32_t incl = cnt;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t v = __shfl_up_sync(CRB_FULL_MASK, incl, o);
+            if (lane >= o) incl += v;
+        }
+        uint32_t off = s_base[f] + s_wbase[warp][f] + incl - cnt;
+        uint32_t* list = p.lists + static_cast<int64_t>(f) * p.list_stride;
+        while (pm) {
+            const int j = __ffs(pm) - 1;
+            pm &= pm - 1u;
+            list[off++] = static_cast<uint32_t>(row0 + j);
         }
     }
 }
@@ -191,6 +239,21 @@ __global__ void __launch_bounds__(256) fetch_rows_kernel(const __half* __restric
         const int r = static_cast<int>(i / dim);
         const int c = static_cast<int>(i - static_cast<int64_t>(r) * dim);
         out[i] = __half2float(rows[idx[r] * dim + c]);
+    }
+}
+
+// The stored vectors of a finished search's hits, fp32: out[i] = row (result_rows[i] - row_offset), zeros where the
+// result slot is padding (-1).  Lets the (Document, embedding, id) triples leave with the search's own copy.
+__global__ void __launch_bounds__(256) fetch_result_rows_kernel(const __half* __restrict__ rows,
+                                                                const int64_t* __restrict__ result_rows, int n,
+                                                                int64_t row_offset, int dim, float* __restrict__ out) {
+    const int64_t total = static_cast<int64_t>(n) * dim;
+    for (int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
+         i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
+        const int r = static_cast<int>(i / dim);
+        const int c = static_cast<int>(i - static_cast<int64_t>(r) * dim);
+        const int64_t g = result_rows[r];
+        out[i] = g >= 0 ? __half2float(rows[(g - row_offset) * dim + c]) : 0.f;
     }
 }
 

@@ -6,7 +6,9 @@ embeddings table (``helm/templates/cassandra-initdb-configmap.yaml:86-102``) lai
 
 * ``rows``      fp16 ``[n_rows, dim]`` row-major (the north star's corpus dtype),
 * ``inv_norm``  fp32 ``[n_rows]``,
-* ``codes``     int32 ``[n_keys, n_rows]`` dictionary codes of the filterable ``metadata_s`` entries.
+* ``codes``     one column per filterable ``metadata_s`` key: dictionary codes ``[n_rows]``, int8 / int16 / int32 --
+  as narrow as the key's dictionary allows, because the filter kernel is bound by these bytes (an int32
+  ``[n_keys, n_rows]`` matrix is accepted too).
 
 torch owns the device memory and streams; every computation goes through the C ABI
 (``include/coderag_b200.h``) by raw pointer.  There is no CPU fallback.
@@ -101,8 +103,13 @@ class DeviceShard:
     (:meth:`tombstone`, inverse norm := NaN) and never returned.
     """
 
-    def __init__(self, rows: torch.Tensor, inv_norm: torch.Tensor, codes: Optional[torch.Tensor],
-                 row_offset: int = 0, n_rows: Optional[int] = None):
+    @staticmethod
+    def _width_for(max_code: int) -> torch.dtype:
+        """Narrowest signed type that holds codes ``-1 .. max_code`` (-1 = key absent)."""
+        return torch.int8 if max_code <= 127 else (torch.int16 if max_code <= 32767 else torch.int32)
+
+    def __init__(self, rows: torch.Tensor, inv_norm: torch.Tensor, codes, row_offset: int = 0,
+                 n_rows: Optional[int] = None):
         lib = N.load()
         if not rows.is_cuda or rows.dtype != torch.float16 or rows.dim() != 2 or not rows.is_contiguous():
             raise ValueError("rows must be a contiguous fp16 CUDA tensor [capacity, dim]")
@@ -113,7 +120,17 @@ class DeviceShard:
         if inv_norm.dtype != torch.float32 or inv_norm.numel() != cap or not inv_norm.is_cuda:
             raise ValueError("inv_norm must be fp32 CUDA [capacity]")
         n_keys = 0
-        if codes is not None:
+        self._cols: Optional[List[torch.Tensor]] = None        # per-key columns (mixed widths) ...
+        if isinstance(codes, (list, tuple)):
+            cols = list(codes)
+            for c in cols:
+                if c.dim() != 1 or c.numel() != cap or not c.is_cuda or not c.is_contiguous() or \
+                        c.dtype not in (torch.int8, torch.int16, torch.int32):
+                    raise ValueError("code columns must be contiguous int8/int16/int32 CUDA tensors [capacity]")
+            n_keys = len(cols)
+            self._cols = cols if cols else None
+            codes = None
+        elif codes is not None:                                 # ... or one int32 matrix
             if codes.dtype != torch.int32 or codes.dim() != 2 or codes.shape[1] != cap or not codes.is_contiguous():
                 raise ValueError("codes must be a contiguous int32 CUDA tensor [n_keys, capacity]")
             n_keys = codes.shape[0]
@@ -122,13 +139,18 @@ class DeviceShard:
         self.row_offset = int(row_offset)
         self.device = rows.device
         handle = C.c_void_p()
-        N.check(lib.crb_index_create(C.byref(handle), _ptr(rows), _ptr(inv_norm), _ptr(codes),
-                                     self.n_rows, self.dim, self.n_keys, self.row_offset,
-                                     self.device.index or 0))
+        if self._cols is not None:
+            # created empty, then bound to the columns
+            N.check(lib.crb_index_create(C.byref(handle), _ptr(rows), _ptr(inv_norm), None, 0, self.dim, self.n_keys,
+                                         self.row_offset, self.device.index or 0))
+        else:
+            N.check(lib.crb_index_create(C.byref(handle), _ptr(rows), _ptr(inv_norm), _ptr(codes),
+                                         self.n_rows, self.dim, self.n_keys, self.row_offset,
+                                         self.device.index or 0))
         self._h = handle
         self._lib = lib
-        if cap != n_rows:
-            N.check(lib.crb_index_rebind(self._h, _ptr(rows), _ptr(inv_norm), _ptr(codes), n_rows, cap))
+        if self._cols is not None or cap != n_rows:
+            self._bind()
         # scratch for search_device calls that bring no workspace: one per calling thread, because the worker's
         # threads search concurrently (rag_worker/src/worker/worker.py:136-139,185) and a workspace serves one
         # call at a time -- counters, survivor lists and candidate lists all live in it
@@ -146,17 +168,40 @@ class DeviceShard:
     def inv_norm(self) -> torch.Tensor:
         return self._inv_buf[:self.n_rows]
 
+    def _bind(self) -> None:
+        """Point the index at the current buffers and row count."""
+        if self._cols is not None:
+            ptrs = (C.c_void_p * self.n_keys)(*[c.data_ptr() for c in self._cols])
+            widths = (C.c_int32 * self.n_keys)(*[c.element_size() for c in self._cols])
+            N.check(self._lib.crb_index_rebind_columns(self._h, _ptr(self._rows_buf), _ptr(self._inv_buf), ptrs, widths,
+                                                       self.n_rows))
+        else:
+            N.check(self._lib.crb_index_rebind(self._h, _ptr(self._rows_buf), _ptr(self._inv_buf), _ptr(self._codes_buf),
+                                               self.n_rows, self.capacity))
+
     @property
-    def codes(self) -> Optional[torch.Tensor]:
+    def codes(self):
+        """Key m's codes are ``codes[m]`` (``[n_rows]``): a list of columns, or rows of the int32 matrix."""
+        if self._cols is not None:
+            return [c[:self.n_rows] for c in self._cols]
         return None if self._codes_buf is None else self._codes_buf[:, :self.n_rows]
+
+    @property
+    def code_widths(self) -> List[int]:
+        """Bytes per row of each key's column."""
+        if self._cols is not None:
+            return [c.element_size() for c in self._cols]
+        return [4] * self.n_keys
 
     # ---- construction ------------------------------------------------------------------
     @classmethod
     def from_host(cls, embeddings: np.ndarray, codes: Optional[np.ndarray] = None, *,
-                  device: int | torch.device = 0, row_offset: int = 0, capacity: Optional[int] = None
-                  ) -> "DeviceShard":
+                  device: int | torch.device = 0, row_offset: int = 0, capacity: Optional[int] = None,
+                  narrow: bool = True) -> "DeviceShard":
         """Upload host rows.  fp32 input is rounded to fp16 on the device (``crb_encode_rows``);
-        fp16 input is copied as is and its inverse norms are computed on the device."""
+        fp16 input is copied as is and its inverse norms are computed on the device.  ``codes`` is int32
+        ``[n_keys, n_rows]`` on the host; with ``narrow`` each key gets its own column of the narrowest type
+        its codes fit (widened on a later append if the dictionary outgrows it)."""
         dev = torch.device("cuda", device) if isinstance(device, int) else device
         emb = np.ascontiguousarray(embeddings)
         if emb.ndim != 2:
@@ -167,12 +212,17 @@ class DeviceShard:
         inv = torch.empty((cap,), dtype=torch.float32, device=dev)
         codes_t = None
         if codes is not None and codes.shape[0] > 0:
-            codes_t = torch.full((codes.shape[0], cap), N.CODE_MISSING, dtype=torch.int32, device=dev)
+            if narrow:
+                codes_t = [torch.full((cap,), N.CODE_MISSING, device=dev,
+                                      dtype=cls._width_for(int(codes[m].max()) if codes.shape[1] else 0))
+                           for m in range(codes.shape[0])]
+            else:
+                codes_t = torch.full((codes.shape[0], cap), N.CODE_MISSING, dtype=torch.int32, device=dev)
         cls._upload(rows, inv, codes_t, 0, emb, codes)
         return cls(rows, inv, codes_t, row_offset, n_rows=n)
 
     @staticmethod
-    def _upload(rows: torch.Tensor, inv: torch.Tensor, codes_t: Optional[torch.Tensor], at: int,
+    def _upload(rows: torch.Tensor, inv: torch.Tensor, codes_t, at: int,
                 emb: np.ndarray, codes: Optional[np.ndarray]) -> None:
         """Encode ``emb`` into ``rows[at:at+m]`` / ``inv[at:at+m]`` and copy its code columns."""
         lib = N.load()
@@ -195,15 +245,22 @@ class DeviceShard:
             N.check(lib.crb_row_inv_norms(rows[at:at + m].data_ptr(), inv[at:at + m].data_ptr(), m, d,
                                           dev.index or 0, stream))
         if codes_t is not None and m > 0:
-            if codes is None or codes.shape != (codes_t.shape[0], m):
-                raise ValueError(f"codes must be [{codes_t.shape[0]}, {m}]")
-            codes_t[:, at:at + m].copy_(torch.from_numpy(np.ascontiguousarray(codes, dtype=np.int32)))
+            nk = len(codes_t)
+            if codes is None or codes.shape != (nk, m):
+                raise ValueError(f"codes must be [{nk}, {m}]")
+            host = torch.from_numpy(np.ascontiguousarray(codes, dtype=np.int32))
+            if isinstance(codes_t, list):
+                for k_, col in enumerate(codes_t):
+                    col[at:at + m].copy_(host[k_].to(col.dtype))
+            else:
+                codes_t[:, at:at + m].copy_(host)
         torch.cuda.current_stream(dev).synchronize()
 
     @classmethod
     def from_device(cls, rows: torch.Tensor, codes: Optional[torch.Tensor] = None, *,
                     row_offset: int = 0) -> "DeviceShard":
-        """Wrap fp16 rows already in HBM; computes the inverse norms on the device."""
+        """Wrap fp16 rows already in HBM; computes the inverse norms on the device.  ``codes``: an int32 matrix
+        ``[n_keys, n_rows]`` or a list of per-key columns (int8 / int16 / int32)."""
         lib = N.load()
         n, d = rows.shape
         inv = torch.empty((n,), dtype=torch.float32, device=rows.device)
@@ -230,15 +287,27 @@ class DeviceShard:
             inv = torch.empty((cap,), dtype=torch.float32, device=self.device)
             rows[:first].copy_(self._rows_buf[:first])
             inv[:first].copy_(self._inv_buf[:first])
-            codes_t = None
             if self._codes_buf is not None:
                 codes_t = torch.full((self.n_keys, cap), N.CODE_MISSING, dtype=torch.int32, device=self.device)
                 codes_t[:, :first].copy_(self._codes_buf[:, :first])
-            self._rows_buf, self._inv_buf, self._codes_buf = rows, inv, codes_t
-        self._upload(self._rows_buf, self._inv_buf, self._codes_buf, first, emb, codes)
+                self._codes_buf = codes_t
+            if self._cols is not None:
+                grown = []
+                for col in self._cols:
+                    g = torch.full((cap,), N.CODE_MISSING, dtype=col.dtype, device=self.device)
+                    g[:first].copy_(col[:first])
+                    grown.append(g)
+                self._cols = grown
+            self._rows_buf, self._inv_buf = rows, inv
+        if self._cols is not None and codes is not None and codes.shape[1] > 0:
+            # a dictionary that outgrew its column's type: widen that column (codes keep their values)
+            for k_, col in enumerate(self._cols):
+                need = self._width_for(int(codes[k_].max()))
+                if need.itemsize > col.element_size():
+                    self._cols[k_] = col.to(need)
+        self._upload(self._rows_buf, self._inv_buf, self._cols if self._cols is not None else self._codes_buf, first, emb, codes)
         self.n_rows = first + m
-        N.check(self._lib.crb_index_rebind(self._h, _ptr(self._rows_buf), _ptr(self._inv_buf), _ptr(self._codes_buf),
-                                           self.n_rows, self.capacity))
+        self._bind()
         return first
 
     def tombstone(self, local_rows: Sequence[int]) -> None:
@@ -291,9 +360,10 @@ class DeviceShard:
         return f
 
     def search_host(self, queries: np.ndarray, k: int, *, metric: str | int = "cosine",
-                    filt: Optional[np.ndarray] = None, algo: int = 0
-                    ) -> Tuple[np.ndarray, np.ndarray, np.ndarray]:
-        """Host buffers in, host buffers out (``crb_search_host``): the per-``invoke`` call."""
+                    filt: Optional[np.ndarray] = None, algo: int = 0, vectors: bool = False):
+        """Host buffers in, host buffers out (``crb_search_host``): the per-``invoke`` call.  With ``vectors``
+        the hits' stored rows come back too, fp32 ``[batch, k, dim]`` (``crb_search_host_vectors``), as a
+        fourth result."""
         q = np.ascontiguousarray(queries, dtype=np.float32)
         if q.ndim == 1:
             q = q[None, :]
@@ -304,6 +374,11 @@ class DeviceShard:
         scores = np.empty((b, k), dtype=np.float32)
         rows = np.empty((b, k), dtype=np.int64)
         n_valid = np.empty((b,), dtype=np.int32)
+        if vectors:
+            vecs = np.empty((b, k, self.dim), dtype=np.float32)
+            N.check(self._lib.crb_search_host_vectors(self._h, _np_ptr(q), b, k, self._metric(metric), _np_ptr(f),
+                                                      _np_ptr(scores), _np_ptr(rows), _np_ptr(n_valid), _np_ptr(vecs), algo))
+            return scores, rows, n_valid, vecs
         N.check(self._lib.crb_search_host(self._h, _np_ptr(q), b, k, self._metric(metric), _np_ptr(f),
                                           _np_ptr(scores), _np_ptr(rows), _np_ptr(n_valid), algo))
         return scores, rows, n_valid

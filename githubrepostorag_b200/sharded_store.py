@@ -211,7 +211,7 @@ class CudaRankEngine:
             _, pos, codes = tree
             if sh.codes is None:
                 return torch.zeros(sh.n_rows, dtype=torch.bool, device=sh.device)
-            return torch.isin(sh.codes[pos], torch.as_tensor(list(codes), dtype=torch.int32, device=sh.device))
+            return torch.isin(sh.codes[pos], torch.as_tensor(list(codes), dtype=sh.codes[pos].dtype, device=sh.device))
         if kind == "rows":
             hit = torch.zeros(sh.n_rows, dtype=torch.bool, device=sh.device)
             rows = np.asarray(tree[1], dtype=np.int64) - sh.row_offset
@@ -470,7 +470,8 @@ class ShardedB200VectorStore(B200VectorStore):
                 self.ctl.close()
 
     # ---- the hot path ---------------------------------------------------------------------------------
-    def _search_locked(self, queries, k, filt, split, algo):
+    def _search_locked(self, queries, k, filt, split, algo, vectors=False):
+        # (vectors: the base class fetches them from the owning ranks after the merge)
         q = np.ascontiguousarray(queries, dtype=np.float32)
         b = q.shape[0]
         if b > self.ctl.max_batch:

@@ -364,7 +364,7 @@ class B200VectorStore:
             old = self._shard
             rows = old.rows.index_select(0, idx).contiguous()
             inv = old.inv_norm.index_select(0, idx).contiguous()
-            codes = None if old.codes is None else old.codes.index_select(1, idx).contiguous()
+            codes = None if old.codes is None else [c.index_select(0, idx).contiguous() for c in old.codes]
             if rows.shape[0] == 0:
                 rows = torch.empty((0, old.dim), dtype=torch.float16, device=old.device)
             self._shard = DeviceShard(rows, inv, codes, old.row_offset)
@@ -461,7 +461,8 @@ class B200VectorStore:
                     "keys": self.dictionary.keys, "values": self.dictionary.values,
                     "ids": self._rows.ids, "texts": self._rows.texts, "metas": self._rows.metas}
             blob = np.frombuffer(json.dumps(meta).encode("utf-8"), dtype=np.uint8)
-            codes = sh.codes.cpu().numpy() if sh.codes is not None else np.empty((0, sh.n_rows), np.int32)
+            codes = np.stack([c.cpu().numpy().astype(np.int32) for c in sh.codes]) if sh.codes is not None and sh.n_keys \
+                else np.empty((0, sh.n_rows), np.int32)
             with open(path, "wb") as f:
                 np.savez(f, rows16=sh.rows.cpu().numpy(), codes=codes, meta=blob)
 
@@ -487,7 +488,9 @@ class B200VectorStore:
 
     # ------------------------------------------------------------------ the hot path
     def _search(self, queries: np.ndarray, k: int, filters: Sequence[Optional[Mapping[str, Any]]],
-                algo: int = 0) -> Tuple[np.ndarray, np.ndarray, np.ndarray]:
+                algo: int = 0, vectors: bool = False):
+        """``(scores, rows, n_valid)`` -- and, with ``vectors``, the hits' stored vectors fp32 ``[B, k, dim]`` as a fourth
+        result, brought back by the search's own device-to-host copy where the plan allows."""
         k = int(k)
         if k < 1:
             raise ValueError("k must be >= 1")
@@ -500,15 +503,28 @@ class B200VectorStore:
         import time
         t0 = time.perf_counter()
         try:
-            return self._search_locked(queries, k, filt, split, algo)
+            res = self._search_locked(queries, k, filt, split, algo, vectors)
+            if vectors and len(res) == 3:       # this plan could not carry them: one fetch for all hits
+                s_, r_, v_ = res
+                vecs = np.zeros((r_.shape[0], k, self.dim), dtype=np.float32)
+                where = [(b, j) for b in range(r_.shape[0]) for j in range(int(v_[b]))]
+                if where:
+                    got = self._fetch_vectors([int(r_[b, j]) for b, j in where])
+                    for (b, j), vec in zip(where, got):
+                        vecs[b, j] = vec
+                res = (s_, r_, v_, vecs)
+            return res
         finally:
             if self._hist is not None:
                 self._hist.labels(self.table_name, "masked" if any(e for _, e in split) else "host").observe(time.perf_counter() - t0)
 
-    def _search_locked(self, queries, k, filt, split, algo):
+    def _search_locked(self, queries, k, filt, split, algo, vectors=False):
         with self._gate.read():
+            vecs = None
             if not any(extra for _, extra in split):
-                s_, r_, v_ = self._shard.search_host(queries, k, metric=self.metric, filt=filt, algo=algo)
+                got = self._shard.search_host(queries, k, metric=self.metric, filt=filt, algo=algo, vectors=vectors)
+                s_, r_, v_ = got[:3]
+                vecs = got[3] if vectors else None
             else:
                 # predicates one code per key cannot express ride on a per-query row mask (device path)
                 import torch
@@ -520,7 +536,7 @@ class B200VectorStore:
             off = self._shard.row_offset
             if off:
                 r_ = np.where(r_ >= 0, r_ - off, r_)
-            return s_, r_, v_
+            return (s_, r_, v_) if vecs is None else (s_, r_, v_, vecs)
 
     # ---- filter vocabulary --------------------------------------------------------------------------
     # A filter is a flat dict, ANDed (the only shape the reference emits, agent_graph.py:198-239):
@@ -585,7 +601,7 @@ class B200VectorStore:
             elif len(codes) == 1:
                 keep &= sh.codes[pos] == codes[0]
             else:
-                keep &= torch.isin(sh.codes[pos], torch.as_tensor(codes, dtype=torch.int32, device=sh.device))
+                keep &= torch.isin(sh.codes[pos], torch.as_tensor(codes, dtype=sh.codes[pos].dtype, device=sh.device))
         return keep
 
     def _row_mask(self, extra):
@@ -704,14 +720,20 @@ class B200VectorStore:
         scores, rows, n_valid = self._search(q, k, [dict(filter) if filter else None])
         return [(int(rows[0, j]), float(scores[0, j])) for j in range(int(n_valid[0]))]
 
+    def _hits_with_vectors(self, embedding: Sequence[float], k: int, filter: Optional[Mapping[str, Any]]):
+        """Hits and their stored vectors from ONE search call (the vectors ride on the result copy)."""
+        q = np.asarray(embedding, dtype=np.float32)[None, :]
+        scores, rows, n_valid, vecs = self._search(q, k, [dict(filter) if filter else None], vectors=True)
+        nv = int(n_valid[0])
+        return [(int(rows[0, j]), float(scores[0, j])) for j in range(nv)], vecs[0, :nv]
+
     @_reading
     def similarity_search_with_embedding_id_by_vector(
             self, embedding: List[float], k: int = 4, filter: Optional[Dict[str, str]] = None,
             body_search: Any = None) -> List[Tuple[Document, List[float], str]]:
         if body_search:
             raise NotImplementedError("body_search is not supported")
-        hits = self._hits(embedding, k, filter)
-        vecs = self._fetch_vectors([r for r, _ in hits])
+        hits, vecs = self._hits_with_vectors(embedding, k, filter)
         return [(self._doc(r, s), vecs[i].tolist(), self._rows.id(r)) for i, (r, s) in enumerate(hits)]
 
     @_reading
@@ -766,8 +788,7 @@ class B200VectorStore:
 
     @_reading
     def search(self, embedding: Sequence[float], k: int = 4, filter: Optional[Dict[str, Any]] = None, **kw) -> List[Content]:
-        hits = self._hits(embedding, k, filter)
-        vecs = self._fetch_vectors([r for r, _ in hits])
+        hits, vecs = self._hits_with_vectors(embedding, k, filter)
         return [self._content(r, vecs[i]) for i, (r, _) in enumerate(hits)]
 
     @_reading
@@ -813,17 +834,16 @@ class B200VectorStore:
         # the results are merged by row below, and single-query groups keep the fan-out on the balanced kernel
         flts = list({tuple(sorted((str(a), str(b)) for a, b in f.items())): f for f in flts}.values())
         q = np.repeat(np.asarray(query_embedding, dtype=np.float32)[None, :], len(flts), axis=0)
-        scores, rows, n_valid = self._search(q, k, flts)
-        best: Dict[int, float] = {}
+        scores, rows, n_valid, vecs = self._search(q, k, flts, vectors=True)
+        best: Dict[int, Tuple[float, int, int]] = {}
         for i in range(len(flts)):
             for j in range(int(n_valid[i])):
                 r = int(rows[i, j])
                 s = float(scores[i, j])
-                if r not in best or s > best[r]:
-                    best[r] = s
-        top = sorted(best.items(), key=lambda t: (-t[1], -t[0]))[:k]
-        vecs = self._fetch_vectors([r for r, _ in top])
-        return [self._content(r, vecs[i]) for i, (r, _) in enumerate(top)]
+                if r not in best or s > best[r][0]:
+                    best[r] = (s, i, j)
+        top = sorted(best.items(), key=lambda t: (-t[1][0], -t[0]))[:k]
+        return [self._content(r, vecs[i, j]) for r, (_, i, j) in top]
 
 
 class B200Retriever:

@@ -81,6 +81,14 @@ int crb_index_reload_tuning(crb_index *index);
  * be over-allocated).  No search may be in flight on the index during the call. */
 int crb_index_rebind(crb_index *index, const void *d_rows_f16, const float *d_inv_norm,
                      const int32_t *d_codes, int64_t n_rows, int64_t code_stride);
+/* The same re-bind with one code column per key, each as narrow as its dictionary allows: h_code_cols[m] is a
+ * DEVICE pointer to key m's column, [>= n_rows] signed codes of h_code_widths[m] = 1, 2 or 4 bytes
+ * (CRB_CODE_MISSING = -1 in every width).  The filter kernel is bound by the bytes of these columns, and the
+ * reference's filter keys have 2 (`component_kind`, ingest/src/app/services/transform_service.py:112-127), 5
+ * (`scope`, ingest_controller.py:179-188), a few (`namespace`, `branch`) or thousands (`repo`) of values: one or
+ * two bytes instead of four.  The host widens a column when its dictionary outgrows it. */
+int crb_index_rebind_columns(crb_index *index, const void *d_rows_f16, const float *d_inv_norm,
+                             const void *const *h_code_cols, const int32_t *h_code_widths, int64_t n_rows);
 /* Delete rows (LOCAL indices): their inverse norm and the first 16 bytes of the row become NaN, so
  * no search returns them under either metric.  Returns when the device has been updated. */
 int crb_tombstone_rows(crb_index *index, const int64_t *h_rows_idx, int32_t n);
@@ -150,6 +158,15 @@ int crb_search_masked(crb_index *index, const float *d_queries, int32_t batch, i
 int crb_search_host(crb_index *index, const float *h_queries, int32_t batch, int32_t k,
                     int32_t metric, const int32_t *h_filt, float *h_scores, int64_t *h_rows,
                     int32_t *h_n_valid, int32_t algo);
+
+/* crb_search_host that also returns the hits' STORED vectors, fp32 [batch, k, dim] (zeros in padding slots), in the
+ * same device-to-host copy: LCCassandra.similarity_search_with_embedding_id_by_vector returns
+ * (Document, embedding, id) triples and graph-retriever re-scores from `embedding`
+ * (call sites rag_worker/src/worker/services/graph_rag_retrievers.py:104-134), so every traversal step needs the
+ * vectors -- one round trip instead of a search followed by crb_fetch_rows_host. */
+int crb_search_host_vectors(crb_index *index, const float *h_queries, int32_t batch, int32_t k,
+                            int32_t metric, const int32_t *h_filt, float *h_scores, int64_t *h_rows,
+                            int32_t *h_n_valid, float *h_vectors, int32_t algo);
 
 /* Cross-shard merge (no reference counterpart in-tree: the reference runs `replicas: 1`,
  * helm/values.yaml:113; this is the k-way merge a row-sharded store needs after the

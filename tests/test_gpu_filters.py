@@ -184,3 +184,67 @@ def test_concurrent_masked_searches_do_not_share_scratch():
     [t.join() for t in ts]
     assert not errors, errors[:2]
     st.close()
+
+
+def test_narrow_code_columns_equal_the_int32_matrix_and_widen_on_append():
+    """Code columns are stored as narrow as their dictionaries allow (int8 / int16 / int32, the filter kernel is bound
+    by their bytes).  Same survivors as the int32 matrix -- odd row counts (scalar tail), many filters in one pass,
+    missing codes, caller row masks, the pass-bit masks the tensor-core plan reads -- and a column is widened in place
+    when an append brings a code its type cannot hold."""
+    import torch
+    from githubrepostorag_b200.index import DeviceShard
+    rng = np.random.default_rng(77)
+    n, d, k = 70_003, 64, 12
+    rows16 = rng.standard_normal((n, d), dtype=np.float32).astype(np.float16)
+    codes = np.stack([rng.integers(-1, 4, n), rng.integers(-1, 2000, n), rng.integers(0, 2, n),
+                      rng.integers(0, 70_000, n)]).astype(np.int32)          # int8, int16, int8, int32 columns
+    wide = DeviceShard.from_host(rows16, codes, device=0, narrow=False)
+    slim = DeviceShard.from_host(rows16, codes, device=0)
+    assert wide.code_widths == [4, 4, 4, 4] and slim.code_widths == [1, 2, 1, 4]
+    wants = [[0, -1, -1, -1], [-1, 7, -1, -1], [3, -1, 1, -1], [-1, -1, -1, 123], [2, 1999, 0, -1], [-1, -1, 1, -1],
+             [1, -1, -1, -1], [-2, -1, -1, -1], [-1, 0, 0, -1], [-1, -1, 0, -1], [-1, 5, 1, -1], [0, 0, 0, 0]]
+    extra = rng.random(n) < 0.4
+    for batch_wants, masked in ((wants, False), (wants[:3], True), ([wants[5]] * 40, False)):
+        b = len(batch_wants)
+        filt = np.asarray(batch_wants, np.int32)
+        q = torch.from_numpy(rng.standard_normal((b, d), dtype=np.float32)).cuda()
+        res = []
+        for sh in (wide, slim):
+            masks = [sh.pack_row_mask(torch.from_numpy(extra).cuda())] * b if masked else None
+            for algo in ((0, 2) if b == 40 else (0,)):
+                s_, r_, v_ = sh.search_device(q, k, filt=filt, row_masks=masks, algo=algo)
+                torch.cuda.synchronize()
+                res.append((s_.clone(), r_.clone(), v_.clone()))
+        for other in res[1:]:
+            assert torch.equal(res[0][1], other[1]) and torch.equal(res[0][2], other[2])
+            assert torch.equal(res[0][0].view(torch.int32), other[0].view(torch.int32))
+        qn = q.cpu().numpy()
+        for i in (0, b - 1):
+            keep = np.ones(n, bool)
+            for m, w in enumerate(batch_wants[i]):
+                if w == -2:
+                    keep[:] = False
+                elif w >= 0:
+                    keep &= codes[m] == w
+            if masked:
+                keep &= extra
+            s_ref, r_ref = oracle.query_vectorised(qn[i], rows16, k, keep=keep)
+            assert res[0][1][i, :len(r_ref)].cpu().numpy().tolist() == r_ref.tolist()
+    # an append whose codes outgrow int8 / int16 widens those columns; old and new rows stay filterable
+    more = rng.standard_normal((500, d), dtype=np.float32).astype(np.float16)
+    more_codes = np.stack([np.full(500, 300), np.full(500, 40_000), np.zeros(500, int), np.arange(500)]).astype(np.int32)
+    slim.append(more, more_codes)
+    assert slim.code_widths == [2, 4, 1, 4] and slim.n_rows == n + 500
+    allrows = np.concatenate([rows16, more])
+    allcodes = np.concatenate([codes, more_codes], axis=1)
+    qv = rng.standard_normal((1, d), dtype=np.float32)
+    for want in ([300, -1, -1, -1], [-1, 40_000, 0, -1], [2, -1, 1, -1], [-1, 1999, -1, -1]):
+        keep = np.ones(n + 500, bool)
+        for m, w in enumerate(want):
+            if w >= 0:
+                keep &= allcodes[m] == w
+        s_ref, r_ref = oracle.query_vectorised(qv[0], allrows, k, keep=keep)
+        s_, r_, v_ = slim.search_host(qv, k, filt=np.asarray([want], np.int32))
+        assert int(v_[0]) == len(r_ref) and r_[0, :len(r_ref)].tolist() == r_ref.tolist(), want
+    wide.close()
+    slim.close()

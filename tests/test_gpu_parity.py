@@ -20,9 +20,9 @@ def torch_cuda():
     return torch
 
 
-def _shard(torch_cuda, rows16, codes=None, row_offset=0):
+def _shard(torch_cuda, rows16, codes=None, row_offset=0, narrow=True):
     from githubrepostorag_b200.index import DeviceShard
-    return DeviceShard.from_host(rows16, codes, device=0, row_offset=row_offset)
+    return DeviceShard.from_host(rows16, codes, device=0, row_offset=row_offset, narrow=narrow)
 
 
 def _check(q, rows16, got_scores, got_rows, n_valid, k, mode, keep=None, what="", row_offset=0):
@@ -259,7 +259,7 @@ def test_fused_filter_and_score_single_query(torch_cuda, n, d, k):
     rng = np.random.default_rng(n + d)
     rows16 = rng.standard_normal((n, d), dtype=np.float32).astype(np.float16)
     code_mat = np.stack([rng.integers(0, 2, n), (rng.zipf(1.5, n) % 40), rng.integers(0, 1000, n)]).astype(np.int32)
-    sh = _shard(torch, rows16, code_mat)
+    sh = _shard(torch, rows16, code_mat, narrow=False)      # the fused kernel reads the int32 code matrix
     q = rng.standard_normal((1, d), dtype=np.float32)
     qd = torch.from_numpy(q).cuda()
     extra = rng.random(n) < 0.3

@@ -192,7 +192,8 @@ def test_adjacent_searches_each_distinct_filter_once(lib, monkeypatch):
                      embedding=[float(i + 1)] * 8) for i in range(6)])
     seen = {}
 
-    def fake_search(queries, k, filters, algo=0):
+    def fake_search(queries, k, filters, algo=0, vectors=False):
+        assert vectors                      # the fan-out takes the hits' vectors from the search's own result copy
         seen["filters"] = [dict(f) for f in filters]
         seen["queries"] = np.asarray(queries)
         b = len(filters)
@@ -206,7 +207,7 @@ def test_adjacent_searches_each_distinct_filter_once(lib, monkeypatch):
             for j, r in enumerate(hit):
                 scores[i, j], rows[i, j] = 1.0 - 0.1 * r, r
             nv[i] = len(hit)
-        return scores, rows, nv
+        return scores, rows, nv, np.zeros((b, k, 8), np.float32)
 
     class FakeShard:
         def fetch_rows(self, rows):

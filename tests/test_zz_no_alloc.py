@@ -4,15 +4,17 @@ plugin host that owns the memory budget).  Collected last on purpose (file name)
 stops at the first failure has already exercised every other test.
 
 It calls the entry point through the C ABI on raw device pointers and checks it against the
-existing ``crb_search`` on the same inputs, with the tolerance the other GPU tests use, on two
-calls in a row (the second must not be disturbed by what the first left in the shared scratch
+existing ``crb_search`` on the same inputs -- the header promises identical results, so rows, counts AND score
+bits must be equal (which is inside the tolerance the other GPU tests use) -- and once against the oracle
+directly, on calls in a row (a call must not be disturbed by what the previous one left in the shared scratch
 array).  It passes both alone in a fresh process and after the rest of the suite.
 """
 import numpy as np
 import pytest
 
+import oracle
 from githubrepostorag_b200 import synthetic as S
-from tests.helpers import SCORE_ATOL_UNIT, SCORE_RTOL
+from tests.helpers import SCORE_ATOL_UNIT, SCORE_RTOL, assert_topk_parity
 
 pytestmark = pytest.mark.gpu
 
@@ -39,14 +41,24 @@ def test_noalloc_matches_crb_search_twice_in_a_row():
         shard = DeviceShard.from_host(rows16, None, device=0)
         for call, (batch, k, metric) in enumerate(((1, 10, N.METRIC_COSINE), (4, 100, N.METRIC_IP), (3, 5, N.METRIC_COSINE))):
             q = torch.from_numpy(S.queries(4242 + call, batch, d)).cuda()
-            want_s, want_r, want_v = shard.search_device(q, k, metric=metric)
+            want_s, want_r, want_v = shard.search_device(q, k, metric=metric, algo=1)
             rc, got_s, got_r, got_v = _noalloc(lib, shard, q, k, metric, torch)
             assert rc == 0, lib.crb_last_error()
             torch.cuda.synchronize()
             assert torch.equal(got_v, want_v) and torch.equal(got_r, want_r), (n, d, call)
+            assert torch.equal(got_s.view(torch.int32), want_s.view(torch.int32)), (n, d, call)     # "identical": the bits
             ws, gs = want_s.cpu().numpy(), got_s.cpu().numpy()
             scale = 1.0 if metric == N.METRIC_COSINE else float(np.abs(ws).max())
             assert np.all(np.abs(gs - ws) <= SCORE_RTOL * np.abs(ws) + SCORE_ATOL_UNIT * scale), (n, d, call)
+            # and the oracle itself, without crb_search in between
+            mode = oracle.MODE_COSINE if metric == N.METRIC_COSINE else oracle.MODE_DOT
+            qn = q.cpu().numpy()
+            e32 = rows16.astype(np.float32)
+            osc = 1.0 if mode == oracle.MODE_COSINE else float(np.linalg.norm(qn[0]) * np.linalg.norm(e32, axis=1).max())
+            s_ref, r_ref = oracle.query_vectorised(qn[0], rows16, k, mode=mode)
+            assert_topk_parity(got_r[0].cpu().numpy(), gs[0], r_ref, s_ref,
+                               lambda row: oracle.score_rows(qn[0], e32[row:row + 1], mode)[0], scale=osc,
+                               what=f"noalloc n={n} d={d} call={call}")
         shard.close()
 
 
