@@ -93,6 +93,7 @@ struct Tuning {
     int k2_gthr = 1;          // _K2_GTHR: shared admission bound
     int k2_gthr_every = 0;    // _K2_GTHR_EVERY: fixed re-read cadence of the bound (0 = schedule)
     int k2_prepass = 1;       // _K2_PREPASS: first accumulator tile read twice
+    int k1_fold = 1;          // _K1_FOLD: sharded batch-1 calls merge in the streaming kernel's last CTA (one launch per rank)
     int k2_kprime = 16;       // candidates per list for k <= 10 (CRB_TUNING builds read _K2_KPRIME)
     int k2_prefetch = 0;      // CRB_TUNING builds only
     int k2_debug = 0;         // CRB_TUNING builds only
@@ -112,6 +113,7 @@ struct Tuning {
         t.k1_group = env("CODERAG_B200_K1_GROUP", t.k1_group);
         t.k1_fused = env("CODERAG_B200_K1_FUSED", t.k1_fused);
         t.k1_balanced = env("CODERAG_B200_K1_BALANCED", t.k1_balanced);
+        t.k1_fold = env("CODERAG_B200_K1_FOLD", t.k1_fold);
         t.k2_pair = env("CODERAG_B200_K2_PAIR", t.k2_pair);
         t.k2_minner = env("CODERAG_B200_K2_MINNER", t.k2_minner);
         t.k2_gthr = env("CODERAG_B200_K2_GTHR", t.k2_gthr);
@@ -432,6 +434,19 @@ static int launch_k1(const crb_index* ix, const float* d_queries, int k, int met
 }
 
 // One query under one filter: filter and score in a single pass (k1_fused_filter_kernel).
+// Eligible when the constrained keys are at most kFusedMaxKeys columns of 1 or 2 bytes, 16-byte aligned.
+static bool fused_eligible(const crb_index* ix, const int32_t* want) {
+    int used = 0;
+    for (int m = 0; m < ix->n_keys; ++m) {
+        if (want[m] == CRB_FILT_ANY) continue;
+        if (want[m] < 0) return false;
+        if (ix->width[m] > 2 || reinterpret_cast<uintptr_t>(ix->cols[m]) % 16 != 0) return false;
+        if (ix->width[m] == 1 && want[m] > 127) return false;       // a code the column cannot hold matches no row:
+        if (ix->width[m] == 2 && want[m] > 32767) return false;     // leave that to the general path
+        ++used;
+    }
+    return used <= kFusedMaxKeys;
+}
 static int launch_k1_fused(const crb_index* ix, const float* d_query, int qi, int k, int metric,
                            const int32_t* want, const uint32_t* row_mask, uint8_t* ws, float* d_scores,
                            int64_t* d_rows, int32_t* d_n_valid, uint64_t* d_keys, cudaStream_t stream,
@@ -441,10 +456,11 @@ static int launch_k1_fused(const crb_index* ix, const float* d_query, int qi, in
     FusedFn fn;
 #define CRB_FUSED(CH_, R_) (k <= 32 ? static_cast<FusedFn>(k1_fused_filter_kernel<CH_, R_, 1>) : static_cast<FusedFn>(k1_fused_filter_kernel<CH_, R_, 4>))
     switch (ch) {
+        // rows in flight per warp: what fits next to the prefetched code words without spilling at 2 CTAs per SM
         case 1: fn = CRB_FUSED(1, 8); break;
-        case 2: fn = CRB_FUSED(2, 6); break;
-        case 3: fn = CRB_FUSED(3, 4); break;
-        default: fn = CRB_FUSED(4, 3); break;
+        case 2: fn = CRB_FUSED(2, 4); break;
+        case 3: fn = CRB_FUSED(3, 3); break;
+        default: fn = CRB_FUSED(4, 2); break;
     }
 #undef CRB_FUSED
     static std::mutex mu;
@@ -465,7 +481,6 @@ static int launch_k1_fused(const crb_index* ix, const float* d_query, int qi, in
     p.rows = ix->rows;
     p.inv_norm = ix->inv_norm;
     p.query = d_query;
-    p.codes = ix->codes;
     p.row_mask = row_mask;
     p.cand = reinterpret_cast<uint64_t*>(ws + kWsHeaderBytes);
     p.counter = reinterpret_cast<unsigned*>(ws);
@@ -474,15 +489,19 @@ static int launch_k1_fused(const crb_index* ix, const float* d_query, int qi, in
     p.out_nvalid = d_n_valid + qi;
     p.out_keys = d_keys ? d_keys + size_t(qi) * k : nullptr;
     p.n_rows = ix->n_rows;
-    p.code_stride = ix->code_stride;
     p.row_offset = static_cast<uint32_t>(ix->row_offset);
     p.dim = ix->dim;
     p.k = k;
     p.metric = metric;
     p.qi = qi;
-    p.n_keys = ix->n_keys;
-    for (int m = 0; m < kMaxKeys; ++m) p.want[m] = m < ix->n_keys ? want[m] : CRB_FILT_ANY;
-    p.vec_ok = (reinterpret_cast<uintptr_t>(ix->codes) % 16 == 0 && ix->code_stride % 4 == 0) ? 1 : 0;
+    for (int m = 0; m < ix->n_keys; ++m) {
+        if (want[m] == CRB_FILT_ANY) continue;
+        p.cols[p.n_used] = ix->cols[m];
+        p.want[p.n_used] = want[m];
+        p.width[p.n_used] = ix->width[m];
+        ++p.n_used;
+    }
+    for (int u = p.n_used; u < kFusedMaxKeys; ++u) p.width[u] = 1;
     if (ex) p.ex = *ex;
     const int64_t stripes = (ix->n_rows + kFusedStripe - 1) / kFusedStripe;
     int64_t grid = int64_t(occ) * ix->sm_count;
@@ -807,7 +826,7 @@ static int search_impl(crb_index* ix, const float* d_queries, int batch, int k, 
                        const int32_t* h_filt, float* d_scores, int64_t* d_rows,
                        int32_t* d_n_valid, uint64_t* d_keys, void* d_workspace,
                        size_t workspace_bytes, int algo, cudaStream_t stream, const ExchangeDev* ex = nullptr,
-                       const uint32_t* const* h_mask_ptrs = nullptr) {
+                       const uint32_t* const* h_mask_ptrs = nullptr, bool* folded = nullptr) {
     uint8_t* ws = static_cast<uint8_t*>(d_workspace);
     const int M = ix->n_keys;
     if (algo < 0 || algo > 2) return fail("algo must be 0 (auto), 1 (streaming) or 2 (tensor core)");
@@ -864,7 +883,8 @@ static int search_impl(crb_index* ix, const float* d_queries, int batch, int k, 
     // (CODERAG_B200_K1_FUSED=1): measured 6 % faster than K3 + K1 at 1 % selectivity (10M x 1024: 84.8 vs 89.9 us)
     // but slower when most rows pass (the scan and the scoring share one warp's registers and serialise their
     // memory latencies), and the plan has no selectivity estimate to choose by.
-    if (batch == 1 && F == 1 && ch <= 4 && algo != 2 && ix->n_rows > 0 && ix->tune.k1_fused > 0 && ix->codes) {
+    if (batch == 1 && F == 1 && ch <= 4 && algo != 2 && ix->n_rows > 0 && ix->tune.k1_fused != 0 &&
+        fused_eligible(ix, filters[0].data())) {
         bool impossible = false;
         for (int m = 0; m < M; ++m) impossible |= (filters[0][m] == CRB_FILT_IMPOSSIBLE);
         if (!impossible)
@@ -997,10 +1017,21 @@ static int search_impl(crb_index* ix, const float* d_queries, int batch, int k, 
             bool any_filtered = false;
             for (const QueryGroup& g : groups) any_filtered |= (g.filter >= 0);
             const bool balanced = max_group == 1 && groups.size() >= 2 && any_filtered && ix->tune.k1_balanced;
+            // A sharded call that is exactly ONE streaming launch (the batch-1 request): its last CTA also waits for
+            // the peers and merges, so no second launch follows.
+            ExchangeDev ex_fold;
+            const ExchangeDev* ex_k1 = ex;
+            if (ex && folded && !balanced && first && f_hi == F && k1_sets.size() == by_filter.size() &&
+                groups.size() <= size_t(kMaxGroups) && ix->tune.k1_fold) {
+                ex_fold = *ex;
+                ex_fold.fold = 1;
+                ex_k1 = &ex_fold;
+                *folded = true;
+            }
             int rc = balanced ? launch_k1_balanced(ix, d_queries, k, metric, groups, slot_of_filter, ws, lists, d_scores,
                                                    d_rows, d_n_valid, d_keys, stream, ex)
                               : launch_k1(ix, d_queries, k, metric, groups, slot_of_filter, nq, ws, lists, d_scores,
-                                          d_rows, d_n_valid, d_keys, stream, ex);
+                                          d_rows, d_n_valid, d_keys, stream, ex_k1);
             if (rc) return rc;
         }
         first = false;
@@ -1484,7 +1515,8 @@ extern "C" int crb_merge_keys(const uint64_t* d_keys_in, int32_t n_lists, int32_
 
 namespace crb {
 // crb_exchange -> the device-side descriptor of one call
-static int make_exchange_dev(const crb_exchange* exch, int batch, int k, uint32_t call_index, ExchangeDev* out) {
+static int make_exchange_dev(const crb_exchange* exch, int batch, int k, uint32_t call_index, uint32_t expected_total,
+                             ExchangeDev* out) {
     if (!exch) return fail("exchange descriptor is NULL");
     if (exch->world < 1 || exch->world > CRB_MAX_PEERS || exch->rank < 0 || exch->rank >= exch->world)
         return fail("exchange: world must be in [1, %d] and rank in [0, world)", CRB_MAX_PEERS);
@@ -1500,6 +1532,7 @@ static int make_exchange_dev(const crb_exchange* exch, int batch, int k, uint32_
     ex.dest_mask = exch->dest_mask ? (exch->dest_mask & all) : all;
     if (!ex.dest_mask) return fail("exchange: dest_mask names no rank of the world");
     ex.cap = exch->cap_keys;
+    ex.expected = expected_total;
     for (int p = 0; p < exch->world; ++p) {
         if (!exch->peer_keys[p] || !exch->peer_counters[p]) return fail("exchange: peer %d pointers are NULL", p);
         ex.keys[p] = exch->peer_keys[p];
@@ -1531,13 +1564,16 @@ extern "C" int crb_search_exchange(crb_index* ix, const float* d_queries, int32_
     if (!d_queries || !d_scores || !d_rows || !d_n_valid || !d_workspace)
         return fail("NULL device pointer passed to crb_search_exchange");
     ExchangeDev ex;
-    if (int rc = make_exchange_dev(exch, batch, k, call_index, &ex)) return rc;
+    if (int rc = make_exchange_dev(exch, batch, k, call_index, expected_total, &ex)) return rc;
     cudaStream_t stream = static_cast<cudaStream_t>(stream_);
     DeviceGuard guard(ix->device);
     CRB_CUDA(guard.status);
+    bool folded = false;
+    // (a caller that wants the merged KEYS back needs the separate merge kernel: the folded merge writes scores / rows only)
     if (int rc = search_impl(ix, d_queries, batch, k, metric, h_filt, d_scores, d_rows, d_n_valid, nullptr,
-                             d_workspace, workspace_bytes, algo, stream, &ex))
+                             d_workspace, workspace_bytes, algo, stream, &ex, nullptr, d_keys ? nullptr : &folded))
         return rc;
+    if (folded) return 0;
     return launch_merge_wait(ix, exch, ex, d_queries, batch, k, metric, d_scores, d_rows, d_n_valid, d_keys,
                              expected_total, stream);
 }
@@ -1550,7 +1586,7 @@ extern "C" int crb_search_exchange_host(crb_index* ix, const float* h_queries, i
     if (int rc = validate_search(ix, batch, k, metric)) return rc;
     if (!h_queries) return fail("NULL query pointer passed to crb_search_exchange_host");
     ExchangeDev ex;
-    if (int rc = make_exchange_dev(exch, batch, k, call_index, &ex)) return rc;
+    if (int rc = make_exchange_dev(exch, batch, k, call_index, expected_total, &ex)) return rc;
     const bool receives = (ex.dest_mask >> ex.rank) & 1u;
     if (receives && (!h_scores || !h_rows || !h_n_valid))
         return fail("crb_search_exchange_host: this rank receives the merged result and needs output arrays");
@@ -1580,10 +1616,11 @@ extern "C" int crb_search_exchange_host(crb_index* ix, const float* h_queries, i
     float* d_scores = reinterpret_cast<float*>(d_io + off_scores);
     int64_t* d_rows = reinterpret_cast<int64_t*>(d_io + off_rows);
     int32_t* d_valid = reinterpret_cast<int32_t*>(d_io + off_valid);
+    bool folded = false;
     int rc = search_impl(ix, d_q, batch, k, metric, h_filt, d_scores, d_rows, d_valid, nullptr, l->d_ws, l->ws_cap,
-                         algo, l->stream, &ex, h_row_mask_ptrs);
-    if (!rc) rc = launch_merge_wait(ix, exch, ex, d_q, batch, k, metric, d_scores, d_rows, d_valid, nullptr,
-                                    expected_total, l->stream);
+                         algo, l->stream, &ex, h_row_mask_ptrs, &folded);
+    if (!rc && !folded) rc = launch_merge_wait(ix, exch, ex, d_q, batch, k, metric, d_scores, d_rows, d_valid, nullptr,
+                                               expected_total, l->stream);
     if (rc) { cudaStreamSynchronize(l->stream); return rc; }
     if (receives)
         CRB_CUDA(cudaMemcpyAsync(h_io + off_rows, d_io + off_rows, io_bytes - off_rows, cudaMemcpyDeviceToHost, l->stream));

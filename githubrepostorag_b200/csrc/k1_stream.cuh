@@ -74,6 +74,42 @@ __device__ __noinline__ void k1_merge_query(const K1Params& p, int qi, int64_t l
     block_merge_sorted_lists<kK1MergeLPT>(lists, gridDim.x, p.k, p.k, sink, xchg, lane, warp, kK1Warps);
 }
 
+// Row-sharded search with the receiving half folded in (ExchangeDev::fold): the group's last CTA has sent the
+// shard's keys of ALL its queries to the destination ranks; if this rank is one of them it now waits for every
+// source and merges their lists (its own included) into the final answers -- the step costs one launch per rank,
+// not two.  Called by the whole CTA after the group's local merges.
+__device__ __noinline__ void k1_fold_exchange(const K1Params& p, const int32_t* q_idx, int nq, uint64_t (*xchg)[32],
+                                              float* s_invq) {
+    if (!(p.ex.world > 0 && p.ex.fold && ((p.ex.dest_mask >> p.ex.rank) & 1u))) return;
+    const int lane = threadIdx.x & 31;
+    const int warp = threadIdx.x >> 5;
+    const bool arrived = exchange_wait_all(p.ex);
+    for (int q = 0; q < nq; ++q) {
+        const int qi = q_idx[q];
+        if (qi < 0) continue;
+        if (!arrived) {
+            if (threadIdx.x == 0) p.out_nvalid[qi] = -2;
+            continue;
+        }
+        if (warp == 0) {
+            const float iq = (p.metric == 0) ? warp_inv_qnorm(p.queries + static_cast<int64_t>(qi) * p.dim, p.dim, lane) : 1.0f;
+            if (lane == 0) *s_invq = iq;
+        }
+        __syncthreads();
+        TopKSink sink;
+        sink.scores = p.out_scores + static_cast<int64_t>(qi) * p.k;
+        sink.rows = p.out_rows + static_cast<int64_t>(qi) * p.k;
+        sink.n_valid = p.out_nvalid + qi;
+        sink.keys = p.out_keys ? p.out_keys + static_cast<int64_t>(qi) * p.k : nullptr;
+        sink.scale = *s_invq;
+        sink.qi = qi;
+        sink.k = p.k;
+        const uint64_t* gather = p.ex.keys[p.ex.rank] + static_cast<uint64_t>(p.ex.parity) * p.ex.world * p.ex.cap +
+                                 static_cast<uint64_t>(qi) * p.k;
+        block_merge_sorted_lists<1>(gather, p.ex.world, p.k, static_cast<int64_t>(p.ex.cap), sink, xchg, lane, warp, kK1Warps);
+    }
+}
+
 // EX: the row has exactly 32 * CH chunks (dim = 256 * CH, e.g. 768 and 1024): no per-chunk range tests in the loop.
 template <int NQ, int CH, int R, int KPL, int MINB = 1, bool EX = false>
 __global__ void __launch_bounds__(kK1Threads, MINB)
@@ -215,6 +251,7 @@ k1_stream_kernel(const __grid_constant__ K1Params p) {
         k1_merge_query(p, qi, static_cast<int64_t>(blockIdx.y) * NQ + q,
                        p.queries + static_cast<int64_t>(qi) * p.dim, xchg, &s_invq);
     }
+    k1_fold_exchange(p, G.q_idx, NQ, xchg, &s_invq);
     if (threadIdx.x == 0) p.counters[blockIdx.y] = 0u;
 }
 
@@ -369,6 +406,7 @@ k1_stream_half_kernel(const __grid_constant__ K1Params p) {
         k1_merge_query(p, qi, static_cast<int64_t>(blockIdx.y) * NQ + q,
                        p.queries + static_cast<int64_t>(qi) * p.dim, xchg, &s_invq);
     }
+    k1_fold_exchange(p, G.q_idx, NQ, xchg, &s_invq);
     if (threadIdx.x == 0) p.counters[blockIdx.y] = 0u;
 }
 
@@ -453,6 +491,7 @@ k1_stream_generic_kernel(const __grid_constant__ K1Params p) {
     __threadfence();
 
     k1_merge_query(p, qi, static_cast<int64_t>(blockIdx.y), s_q, xchg, &s_invq);
+    k1_fold_exchange(p, G.q_idx, 1, xchg, &s_invq);
     if (threadIdx.x == 0) p.counters[blockIdx.y] = 0u;
 }
 
@@ -877,16 +916,26 @@ k1_balanced_kernel(const __grid_constant__ BalParams p) {
 // ---------------------------------------------------------------------------------------------
 // Fused filter + score: ONE query under ONE filter -- what every retriever.invoke(q, filter={namespace,
 // repo, ...}) starts with (agent_graph.py:249) -- in a single pass and a single launch.  K3 + K1 read the
-// code columns, write a survivor list, launch again, read the list and gather; here a warp reads the
-// code columns of a 128-row stripe (one 16-byte load per key per lane), evaluates the AND of equalities
-// (and the caller's row mask), queues the survivors' row numbers in shared memory and scores them R at
-// a time with the canonical summation order as soon as R are waiting.  No list, no counters, no second
-// launch: algorithmic bytes = n_rows * used_keys * 4 + survivors * dim * 2, all in one HBM stream.
+// code columns, write a survivor list, launch again, read the list and gather: two ramps, two tails, and
+// neither short kernel gets near the HBM rate (ncu, 10M x 1024 at 1 %: 40 MB in 22 us + 205 MB in 52 us).
+// Here a warp owns 512-row stripes: a lane reads the codes of 16 consecutive rows of each constrained key
+// (one 16-byte load for an int8 column, two for int16), compares them to the wanted code four (two) at a
+// time inside 32-bit words, ANDs the keys' 16-bit pass masks (and the caller's row mask), queues the
+// survivors' row numbers in shared memory and scores them R at a time in the canonical summation order as
+// soon as R are waiting.  The NEXT stripe's codes are in flight while the current stripe's survivors are
+// gathered, so a warp's dependent round trips are the gathers only.  No list, no counters, no second
+// launch: algorithmic bytes = n_rows * sum(widths of the constrained keys) + survivors * dim * 2.
+constexpr int kFusedMaxKeys = 4;     // constrained keys the fused plan takes (each a column of 1 or 2 bytes)
+constexpr int kFusedStripe = 512;    // rows per warp step of the scan: 16 consecutive rows per lane
+
 struct FusedParams {
     const __half* rows;
     const float* inv_norm;
     const float* query;            // [dim] fp32
-    const int32_t* codes;          // [n_keys, code_stride]
+    const void* cols[kFusedMaxKeys];   // columns of the constrained keys, 16-byte aligned
+    int32_t want[kFusedMaxKeys];       // wanted code of each (>= 0)
+    int32_t width[kFusedMaxKeys];      // 1 or 2 bytes
+    int32_t n_used;
     const uint32_t* row_mask;      // optional caller pass bits (or nullptr)
     uint64_t* cand;                // [grid, k] scratch
     unsigned* counter;             // arrival counter, zero between launches
@@ -895,25 +944,45 @@ struct FusedParams {
     int32_t* out_nvalid;
     uint64_t* out_keys;            // or nullptr
     int64_t n_rows;
-    int64_t code_stride;
     uint32_t row_offset;
     int32_t dim;
     int32_t k;
     int32_t metric;
     int32_t qi;                    // query index in the batch (exchange slot)
-    int32_t n_keys;
-    int32_t want[kMaxKeys];        // -1 = any
-    int32_t vec_ok;                // code columns are 16-byte aligned: vector loads
     ExchangeDev ex;
 };
 
-constexpr int kFusedStripe = 1024;  // rows per warp step of the scan
+// 16-bit mask of the bytes (16-bit halves) of `v` equal to the replicated wanted code: bit j <-> element j.
+// A zero byte of x = w ^ want becomes 0x80 exactly (no borrow between bytes), the four flags are gathered by a
+// multiply whose partial products cannot collide.
+CRB_DEVINL uint32_t eq_mask_bytes(const uint4& v, uint32_t want4) {
+    const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+    uint32_t m = 0u;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const uint32_t x = w[i] ^ want4;
+        const uint32_t t = ~((((x & 0x7f7f7f7fu) + 0x7f7f7f7fu) | x) | 0x7f7f7f7fu);      // 0x80 where the byte of x is 0
+        m |= (((t >> 7) * 0x01020408u) >> 24) << (4 * i);
+    }
+    return m;
+}
+CRB_DEVINL uint32_t eq_mask_halves(const uint4& v, uint32_t want2) {      // 8 elements -> 8 bits
+    const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+    uint32_t m = 0u;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const uint32_t x = w[i] ^ want2;
+        const uint32_t t = ~((((x & 0x7fff7fffu) + 0x7fff7fffu) | x) | 0x7fff7fffu);      // 0x8000 where the half of x is 0
+        m |= (((t >> 15) & 1u) | ((t >> 30) & 2u)) << (2 * i);
+    }
+    return m;
+}
 
 template <int CH, int R, int KPL>
 __global__ void __launch_bounds__(kK1Threads, 2)
 k1_fused_filter_kernel(const __grid_constant__ FusedParams p) {
     __shared__ uint64_t xchg[2][32];
-    __shared__ uint32_t s_queue[kK1Warps][128 + 8];
+    __shared__ uint32_t s_queue[kK1Warps][kFusedStripe + 8];
     __shared__ float s_invq;
     __shared__ int s_last;
 
@@ -921,7 +990,6 @@ k1_fused_filter_kernel(const __grid_constant__ FusedParams p) {
     const int warp = threadIdx.x >> 5;
     const int chunks = p.dim >> 3;
     const bool cosine = (p.metric == 0);
-    const uint32_t lt = (1u << lane) - 1u;
 
     float qr[CH][8];
 #pragma unroll
@@ -982,74 +1050,103 @@ k1_fused_filter_kernel(const __grid_constant__ FusedParams p) {
         }
     };
 
-    // A warp scans 1024 rows per step: per key, eight 16-byte loads per lane in flight (4 KB per warp), folded
-    // into one 32-bit pass word before the next key's loads reuse the registers -- with one 128-row stripe per
-    // step the scan was latency-bound (24 KB in flight per SM) and slower than the two-kernel path.
+    // the wanted codes, replicated across a 32-bit word for the in-word compares
+    uint32_t want_w[kFusedMaxKeys];
+#pragma unroll
+    for (int u = 0; u < kFusedMaxKeys; ++u) {
+        const uint32_t w = static_cast<uint32_t>(p.want[u]);
+        want_w[u] = p.width[u] == 1 ? (w & 0xffu) * 0x01010101u : (w & 0xffffu) * 0x00010001u;
+    }
+    // codes of one stripe: two 16-byte slots per key (an int8 column uses the first only)
+    uint4 pf[kFusedMaxKeys][2];
+    auto fetch = [&](int64_t st) {
+        const int64_t r0 = st * kFusedStripe + 16 * lane;
+#pragma unroll
+        for (int u = 0; u < kFusedMaxKeys; ++u) {
+            if (u < p.n_used) {
+                if (p.width[u] == 1) {
+                    pf[u][0] = __ldg(reinterpret_cast<const uint4*>(static_cast<const uint8_t*>(p.cols[u]) + r0));
+                } else {
+                    const uint4* src = reinterpret_cast<const uint4*>(static_cast<const uint16_t*>(p.cols[u]) + r0);
+                    pf[u][0] = __ldg(src);
+                    pf[u][1] = __ldg(src + 1);
+                }
+            }
+        }
+    };
+    // 16-bit pass mask of this lane's rows from the fetched codes
+    auto evaluate = [&]() -> uint32_t {
+        uint32_t pass = 0xffffu;
+#pragma unroll
+        for (int u = 0; u < kFusedMaxKeys; ++u) {
+            if (u < p.n_used) {
+                if (p.width[u] == 1) pass &= eq_mask_bytes(pf[u][0], want_w[u]);
+                else pass &= eq_mask_halves(pf[u][0], want_w[u]) | (eq_mask_halves(pf[u][1], want_w[u]) << 8);
+            }
+        }
+        return pass;
+    };
+    // the ragged last stripe: element-wise, bounds-checked
+    auto evaluate_tail = [&](int64_t st) -> uint32_t {
+        const int64_t r0 = st * kFusedStripe + 16 * lane;
+        uint32_t pass = 0u;
+        for (int j = 0; j < 16; ++j) {
+            const int64_t r = r0 + j;
+            if (r >= p.n_rows) break;
+            bool ok = true;
+            for (int u = 0; u < p.n_used; ++u) {
+                const int32_t c = p.width[u] == 1 ? static_cast<int32_t>(__ldg(static_cast<const int8_t*>(p.cols[u]) + r))
+                                                  : static_cast<int32_t>(__ldg(static_cast<const int16_t*>(p.cols[u]) + r));
+                ok = ok && (c == p.want[u]);
+            }
+            pass |= ok ? (1u << j) : 0u;
+        }
+        return pass;
+    };
+
     const int64_t n_stripes = (p.n_rows + kFusedStripe - 1) / kFusedStripe;
+    const int64_t n_whole = p.n_rows / kFusedStripe;              // stripes the vector loads may read completely
     const int64_t step = static_cast<int64_t>(gridDim.x) * kK1Warps;
-    for (int64_t st = static_cast<int64_t>(blockIdx.x) * kK1Warps + warp; st < n_stripes; st += step) {
-        const int64_t base = st * kFusedStripe;
-        const int64_t r0 = base + 4 * lane;                       // sub-stripe i holds rows r0 + 128 i .. + 3
-        const bool whole = base + kFusedStripe <= p.n_rows;       // warp-uniform
-        uint32_t pass = 0xffffffffu;                              // bit 4 i + j <-> row r0 + 128 i + j
-        if (!whole) {
-            pass = 0u;
-#pragma unroll
-            for (int i = 0; i < 8; ++i)
-#pragma unroll
-                for (int j = 0; j < 4; ++j)
-                    if (r0 + 128 * i + j < p.n_rows) pass |= 1u << (4 * i + j);
-        }
-        for (int m = 0; m < p.n_keys; ++m) {
-            const int32_t w = p.want[m];
-            if (w == -1) continue;
-            const int32_t* col = p.codes + static_cast<int64_t>(m) * p.code_stride + r0;
-            if (whole && p.vec_ok) {
-                int4 c[8];
-#pragma unroll
-                for (int i = 0; i < 8; ++i) c[i] = __ldg(reinterpret_cast<const int4*>(col + 128 * i));
-#pragma unroll
-                for (int i = 0; i < 8; ++i) {
-                    uint32_t bad = (c[i].x != w ? 1u : 0u) | (c[i].y != w ? 2u : 0u) | (c[i].z != w ? 4u : 0u) | (c[i].w != w ? 8u : 0u);
-                    pass &= ~(bad << (4 * i));
-                }
-            } else {
-#pragma unroll
-                for (int i = 0; i < 8; ++i)
-#pragma unroll
-                    for (int j = 0; j < 4; ++j)
-                        if (((pass >> (4 * i + j)) & 1u) && __ldg(col + 128 * i + j) != w) pass &= ~(1u << (4 * i + j));
-            }
-        }
-        if (p.row_mask) {
-            // rows r0 + 128 i .. + 3 sit in one mask word (r0 is a multiple of 4)
-#pragma unroll
-            for (int i = 0; i < 8; ++i) {
-                if ((pass >> (4 * i)) & 0xfu) {
-                    const int64_t r = r0 + 128 * i;
-                    const uint32_t word = __ldg(p.row_mask + (r >> 5));
-                    pass &= ~(0xfu << (4 * i)) | (((word >> (r & 31)) & 0xfu) << (4 * i));
-                }
-            }
+    int64_t st = static_cast<int64_t>(blockIdx.x) * kK1Warps + warp;
+    if (st < n_whole) fetch(st);
+    for (; st < n_stripes; st += step) {
+        uint32_t pass = st < n_whole ? evaluate() : evaluate_tail(st);
+        if (st + step < n_whole) fetch(st + step);                // in flight while this stripe's survivors are gathered
+        const int64_t r0 = st * kFusedStripe + 16 * lane;
+        if (p.row_mask && pass) {
+            // the lane's 16 rows are one half of a mask word (r0 is a multiple of 16)
+            pass &= (__ldg(p.row_mask + (r0 >> 5)) >> (r0 & 31)) & 0xffffu;
         }
         // queue the survivors (order is irrelevant: keys carry the row), scoring whenever R are waiting
-        if (__ballot_sync(CRB_FULL_MASK, pass != 0u) == 0u) continue;
-#pragma unroll 1
-        for (int i = 0; i < 8; ++i) {
+        const int mine = __popc(pass);
+        int incl = mine;
 #pragma unroll
-            for (int j = 0; j < 4; ++j) {
-                const uint32_t bit = (pass >> (4 * i + j)) & 1u;
-                const uint32_t b = __ballot_sync(CRB_FULL_MASK, bit);
-                if (bit) queue[queued + __popc(b & lt)] = static_cast<uint32_t>(r0 + 128 * i + j);
-                queued += __popc(b);
-            }
-            __syncwarp();
-            while (queued >= R) {          // at most 128 pushed since the last drain: the queue cannot overflow
-                queued -= R;
-                score_batch(queued, R);
-            }
-            __syncwarp();
+        for (int o = 1; o < 32; o <<= 1) {
+            const int vv = __shfl_up_sync(CRB_FULL_MASK, incl, o);
+            if (lane >= o) incl += vv;
         }
+        const int total = __shfl_sync(CRB_FULL_MASK, incl, 31);
+        if (total == 0) continue;
+        int at = queued + incl - mine;
+        while (pass) {
+            const int j = __ffs(pass) - 1;
+            pass &= pass - 1u;
+            queue[at++] = static_cast<uint32_t>(r0 + j);
+        }
+        queued += total;
+        __syncwarp();
+        // drain from the front in whole batches; what is left (< R rows) moves to the front of the queue
+        int head = 0;
+        while (queued - head >= R) {
+            score_batch(head, R);
+            head += R;
+        }
+        const int rest = queued - head;           // < R <= 32
+        const uint32_t keep = lane < rest ? queue[head + lane] : 0u;
+        __syncwarp();
+        if (lane < rest) queue[lane] = keep;
+        queued = rest;
+        __syncwarp();
     }
     __syncwarp();
     if (queued > 0) score_batch(0, queued);

@@ -96,7 +96,25 @@ struct ExchangeDev {
     uint64_t cap;           // keys per (parity, source) slot
     uint64_t* keys[kMaxPeers];      // peer p's gather buffer: [2][world][cap]
     uint32_t* counters[kMaxPeers];  // peer p's arrival counters: [world], monotonic
+    uint32_t expected;      // arrivals per source once this call is complete (see crb_search_exchange)
+    int32_t fold;           // 1: the streaming kernel's last CTA also waits for the peers and merges (no second launch)
 };
+
+// Wait (bounded) until every source rank has published `expected` queries into THIS rank's gather buffer.
+// Called by a whole CTA; returns false when a source never arrived.
+CRB_DEVINL bool exchange_wait_all(const ExchangeDev& ex) {
+    int ok = 1;
+    if (threadIdx.x < ex.world) {
+        const volatile uint32_t* c = ex.counters[ex.rank] + threadIdx.x;
+        long long spins = 0;
+        while (static_cast<int32_t>(*c - ex.expected) < 0) {
+            if (++spins > (1ll << 27)) { ok = 0; break; }
+            __nanosleep(32);
+        }
+        __threadfence_system();
+    }
+    return __syncthreads_and(ok) != 0;
+}
 
 // Output of one finished query: scores (times inv_qnorm), global rows, n_valid, keys.
 struct TopKSink {

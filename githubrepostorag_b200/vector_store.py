@@ -447,39 +447,85 @@ class B200VectorStore:
                 self._shard = None
 
     # ------------------------------------------------------------------ persistence
+    SAVE_BLOCK_ROWS = 1 << 18
+
     def save(self, path: str) -> None:
-        """Checkpoint the store to one ``.npz`` file: the fp16 rows, code columns, dictionary, ids,
-        text and metadata (live rows only).  The reference's equivalent is the Cassandra PVC
-        (``helm/values.yaml:25-28``)."""
+        """Checkpoint the store (live rows only).  The reference's equivalent is the Cassandra PVC
+        (``helm/values.yaml:25-28``).  A path ending in ``.npz`` writes one file (small tables: everything passes
+        through host memory at once); any other path is a DIRECTORY written in a streaming fashion -- the fp16 rows
+        and code columns go from the device to ``rows16.npy`` / ``codes.npy`` in 2**18-row blocks through a memory map,
+        ids / text / metadata as one JSON line per row -- so a 10M-row table needs a block of host memory, not the
+        table."""
         import json
+        import os
         with self._gate.write():
             if self._rows.id_fn:
                 raise RuntimeError("bulk-loaded (from_arrays) stores keep no ids/text to save")
             self.compact() if self._rows.n_dead else None
             sh = self._ensure_built()
-            meta = {"format": 1, "dim": self.dim, "metric": self.metric, "table_name": self.table_name,
-                    "keys": self.dictionary.keys, "values": self.dictionary.values,
-                    "ids": self._rows.ids, "texts": self._rows.texts, "metas": self._rows.metas}
-            blob = np.frombuffer(json.dumps(meta).encode("utf-8"), dtype=np.uint8)
-            codes = np.stack([c.cpu().numpy().astype(np.int32) for c in sh.codes]) if sh.codes is not None and sh.n_keys \
-                else np.empty((0, sh.n_rows), np.int32)
-            with open(path, "wb") as f:
-                np.savez(f, rows16=sh.rows.cpu().numpy(), codes=codes, meta=blob)
+            head = {"format": 2, "dim": self.dim, "metric": self.metric, "table_name": self.table_name, "scope": self.scope,
+                    "keys": self.dictionary.keys, "values": self.dictionary.values, "n_rows": sh.n_rows,
+                    "multi_valued_keys": list(self.multi_valued_keys)}
+            if str(path).endswith(".npz"):
+                meta = dict(head, format=1, ids=self._rows.ids, texts=self._rows.texts, metas=self._rows.metas)
+                blob = np.frombuffer(json.dumps(meta).encode("utf-8"), dtype=np.uint8)
+                codes = np.stack([c.cpu().numpy().astype(np.int32) for c in sh.codes]) if sh.codes is not None and sh.n_keys \
+                    else np.empty((0, sh.n_rows), np.int32)
+                with open(path, "wb") as f:
+                    np.savez(f, rows16=sh.rows.cpu().numpy(), codes=codes, meta=blob)
+                return
+            os.makedirs(path, exist_ok=True)
+            n, blk = sh.n_rows, self.SAVE_BLOCK_ROWS
+            rows_mm = np.lib.format.open_memmap(os.path.join(path, "rows16.npy"), mode="w+", dtype=np.float16, shape=(n, self.dim))
+            codes_mm = np.lib.format.open_memmap(os.path.join(path, "codes.npy"), mode="w+", dtype=np.int32, shape=(sh.n_keys, n))
+            for lo in range(0, n, blk):
+                hi = min(n, lo + blk)
+                rows_mm[lo:hi] = sh.rows[lo:hi].cpu().numpy()
+                for m in range(sh.n_keys):
+                    codes_mm[m, lo:hi] = sh.codes[m][lo:hi].cpu().numpy()
+            rows_mm.flush(); codes_mm.flush()
+            del rows_mm, codes_mm
+            with open(os.path.join(path, "rows.jsonl"), "w", encoding="utf-8") as f:
+                for rid, text, md in zip(self._rows.ids, self._rows.texts, self._rows.metas):
+                    f.write(json.dumps({"id": rid, "text": text, "metadata": md}) + "\n")
+            with open(os.path.join(path, "meta.json"), "w", encoding="utf-8") as f:
+                json.dump(head, f)
+
+    @staticmethod
+    def read_saved(path: str):
+        """``(head, rows16, codes, ids, texts, metas)`` of a saved table; the two arrays are memory-mapped for the
+        directory format, so a caller can take a row range without reading the rest (the sharded loader does)."""
+        import json
+        import os
+        if os.path.isdir(path):
+            with open(os.path.join(path, "meta.json"), encoding="utf-8") as f:
+                head = json.load(f)
+            rows16 = np.load(os.path.join(path, "rows16.npy"), mmap_mode="r")
+            codes = np.load(os.path.join(path, "codes.npy"), mmap_mode="r")
+            ids, texts, metas = [], [], []
+            with open(os.path.join(path, "rows.jsonl"), encoding="utf-8") as f:
+                for line in f:
+                    rec = json.loads(line)
+                    ids.append(rec["id"]); texts.append(rec["text"]); metas.append(rec["metadata"])
+            return head, rows16, codes, ids, texts, metas
+        with np.load(path) as z:
+            head = json.loads(bytes(z["meta"]).decode("utf-8"))
+            rows16, codes = z["rows16"], z["codes"]
+        return head, rows16, codes, list(head.pop("ids")), list(head.pop("texts")), list(head.pop("metas"))
 
     @classmethod
     def load(cls, path: str, *, embedding: Any = None, device: int = 0) -> "B200VectorStore":
-        import json
-        with np.load(path) as z:
-            meta = json.loads(bytes(z["meta"]).decode("utf-8"))
-            rows16, codes = z["rows16"], z["codes"]
-        st = cls(embedding, dim=int(meta["dim"]), filter_keys=meta["keys"], device=device,
-                 table_name=meta.get("table_name", "embeddings"), metric=meta.get("metric", "cosine"))
-        st.dictionary.values = [dict(v) for v in meta["values"]]
-        st._rows.ids, st._rows.texts, st._rows.metas = list(meta["ids"]), list(meta["texts"]), list(meta["metas"])
+        head, rows16, codes, ids, texts, metas = cls.read_saved(path)
+        st = cls(embedding, dim=int(head["dim"]), filter_keys=head["keys"], device=device,
+                 table_name=head.get("table_name", "embeddings"), metric=head.get("metric", "cosine"),
+                 multi_valued_keys=head.get("multi_valued_keys"), scope=head.get("scope"))
+        st.dictionary.values = [dict(v) for v in head["values"]]
+        st._rows.ids, st._rows.texts, st._rows.metas = ids, texts, metas
         st._rows.pos = {rid: i for i, rid in enumerate(st._rows.ids)}
         for i, md in enumerate(st._rows.metas):
             st._post(i, md)
-        st._shard = DeviceShard.from_host(rows16, codes if codes.shape[0] else None, device=device,
+        # (from_host uploads in 2**18-row blocks, so a memory-mapped table never sits in host memory whole)
+        st._shard = DeviceShard.from_host(rows16, np.asarray(codes) if codes.shape[0] else None, device=device,
                                           capacity=max(1024, len(rows16)))
         return st
 

@@ -259,7 +259,7 @@ def test_fused_filter_and_score_single_query(torch_cuda, n, d, k):
     rng = np.random.default_rng(n + d)
     rows16 = rng.standard_normal((n, d), dtype=np.float32).astype(np.float16)
     code_mat = np.stack([rng.integers(0, 2, n), (rng.zipf(1.5, n) % 40), rng.integers(0, 1000, n)]).astype(np.int32)
-    sh = _shard(torch, rows16, code_mat, narrow=False)      # the fused kernel reads the int32 code matrix
+    sh = _shard(torch, rows16, code_mat)                    # int8, int8 and int16 columns: what the fused kernel reads
     q = rng.standard_normal((1, d), dtype=np.float32)
     qd = torch.from_numpy(q).cuda()
     extra = rng.random(n) < 0.3

@@ -105,7 +105,15 @@ def test_save_load_roundtrip_and_cassandra_loader(tmp_path):
     assert len(st2) == n - 1 and st2.get_by_document_id("id-7").page_content == "body 7"
     st2.add_embeddings(["id-new"], q[None, :], ["fresh"], [{"repo": "repo4"}])
     assert _query(st2, q, 1, {"repo": "repo4"}).ids == ["id-new"]
-    st.close(); st2.close()
+    # the streaming (directory) format: rows and codes go through a memory map block by block
+    B200VectorStore.SAVE_BLOCK_ROWS = 1000                         # several blocks even for this small table
+    st.save(str(tmp_path / "table_dir"))
+    assert sorted(p.name for p in (tmp_path / "table_dir").iterdir()) == ["codes.npy", "meta.json", "rows.jsonl", "rows16.npy"]
+    st3 = B200VectorStore.load(str(tmp_path / "table_dir"))
+    b3 = _query(st3, q, 6, {"repo": "repo4"})
+    assert b3.ids == b1.ids and b3.similarities == b1.similarities and b3.nodes[0].text == b1.nodes[0].text
+    assert len(st3) == n - 1 and st3.get_by_document_id("id-7").metadata["repo"] == "repo0"
+    st.close(); st2.close(); st3.close()
 
 
 def test_readers_race_a_writer():
