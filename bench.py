@@ -389,7 +389,8 @@ class Bench:
             widths = sum(c["shard"].code_widths[:3])
             by = n_local * widths + surv * w["d"] * 2
             achieved = by / per_step_s / 1e9
-            return {"bound": "hbm", "kernel": "k3_filter_kernel + k1_stream_kernel (gather)" if B <= 2 else "k3_filter + compact + k2 on survivors",
+            return {"bound": "hbm", "kernel": "k1_fused_filter_kernel, or k3_filter_kernel + k1_stream_kernel (gather), by estimated selectivity" if B == 1
+                    else ("k3_filter_kernel + k1_stream_kernel (gather)" if B <= 2 else "k3_filter + compact + k2 on survivors"),
                     "achieved": achieved, "peak": pk["hbm_gbs"], "unit": "GB/s", "frac": achieved / pk["hbm_gbs"], "traffic": None,
                     "peak_source": pk["source"], "algorithmic_bytes_per_launch": by,
                     "note": f"bytes = rows x {widths} B of code columns (3 keys) + survivors x dim x 2 ({c['sel'] * 100:.3f} % pass); "

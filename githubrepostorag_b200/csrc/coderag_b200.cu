@@ -172,6 +172,9 @@ struct crb_index {
     int64_t code_stride = 0;       // elements between key columns of `codes`
     const void* cols[CRB_MAX_KEYS] = {};   // column of key m (what the kernels read): width[m] bytes per row
     uint8_t width[CRB_MAX_KEYS] = {};
+    // rows per code of the narrow columns (bin code + 1; bin 0 = key absent), counted when the columns are bound:
+    // the plan's selectivity estimate (product of the constrained keys' frequencies)
+    std::vector<uint32_t> hist[CRB_MAX_KEYS];
     int64_t n_rows = 0;
     int32_t dim = 0;
     int32_t n_keys = 0;
@@ -223,6 +226,42 @@ static WsLayout ws_layout(const crb_index* ix, int batch, int k) {
     L.filt = o;
     L.per_filter = size_t(list_stride_of(ix)) * 4 + size_t(mask_stride_of(ix)) * 4;
     return L;
+}
+
+// Rows per code of one narrow column: hist[code + 1] (code -1 = key absent -> bin 0).
+__global__ void __launch_bounds__(256) code_histogram_kernel(const void* __restrict__ col, int width, int64_t n,
+                                                             unsigned* __restrict__ hist) {
+    __shared__ unsigned s_h[130];
+    if (width == 1) {
+        for (int i = threadIdx.x; i < 130; i += blockDim.x) s_h[i] = 0u;
+        __syncthreads();
+    }
+    for (int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < n;
+         i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
+        if (width == 1) atomicAdd(&s_h[static_cast<int>(static_cast<const int8_t*>(col)[i]) + 1], 1u);
+        else atomicAdd(&hist[static_cast<int>(static_cast<const int16_t*>(col)[i]) + 1], 1u);
+    }
+    if (width == 1) {
+        __syncthreads();
+        for (int i = threadIdx.x; i < 130; i += blockDim.x)
+            if (s_h[i]) atomicAdd(&hist[i], s_h[i]);
+    }
+}
+
+// Estimated fraction of the shard's rows that pass an AND of equalities: the product of the constrained keys'
+// code frequencies (keys taken as independent).  -1 when a constrained key has no histogram (a 4-byte column).
+static double estimate_selectivity(const crb_index* ix, const int32_t* want) {
+    if (ix->n_rows <= 0) return -1.0;
+    double sel = 1.0;
+    for (int m = 0; m < ix->n_keys; ++m) {
+        if (want[m] == CRB_FILT_ANY) continue;
+        if (want[m] < 0) return 0.0;
+        const std::vector<uint32_t>& h = ix->hist[m];
+        if (h.empty()) return -1.0;
+        const size_t bin = size_t(want[m]) + 1;
+        sel *= bin < h.size() ? double(h[bin]) / double(ix->n_rows) : 0.0;
+    }
+    return sel;
 }
 
 // cuTensorMapEncodeTiled through the runtime's driver entry point (no link-time libcuda).
@@ -883,8 +922,18 @@ static int search_impl(crb_index* ix, const float* d_queries, int batch, int k, 
     // (CODERAG_B200_K1_FUSED=1): measured 6 % faster than K3 + K1 at 1 % selectivity (10M x 1024: 84.8 vs 89.9 us)
     // but slower when most rows pass (the scan and the scoring share one warp's registers and serialise their
     // memory latencies), and the plan has no selectivity estimate to choose by.
+    // (measured, profiles/fused_sweep.py: the fused kernel wins up to ~1 % of the rows passing -- 10M x 768 at 0.1 %:
+    //  25 vs 39 us, at 0.5 %: 46 vs 56 us -- is level at 1 % and loses when many rows pass, 10 %: 320 vs 279 us.)
+    bool use_fused = false;
     if (batch == 1 && F == 1 && ch <= 4 && algo != 2 && ix->n_rows > 0 && ix->tune.k1_fused != 0 &&
         fused_eligible(ix, filters[0].data())) {
+        if (ix->tune.k1_fused > 0) use_fused = true;
+        else {
+            const double est = estimate_selectivity(ix, filters[0].data());
+            use_fused = est >= 0.0 && est <= 0.015;
+        }
+    }
+    if (use_fused) {
         bool impossible = false;
         for (int m = 0; m < M; ++m) impossible |= (filters[0][m] == CRB_FILT_IMPOSSIBLE);
         if (!impossible)
@@ -947,6 +996,8 @@ static int search_impl(crb_index* ix, const float* d_queries, int batch, int k, 
                     if (m < M && filters[f][m] != CRB_FILT_ANY) kp.used_keys |= (1u << m);
                 }
             }
+            for (int m = 0; m < M; ++m)
+                if ((kp.used_keys >> m) & 1u) kp.ukeys[kp.n_used++] = static_cast<uint8_t>(m);
             CRB_CUDA(cudaMemsetAsync(ws + kWsCountsOffset, 0, kMaxFilters * sizeof(uint32_t), stream));
             const int64_t rows_per_block = int64_t(kK3Threads) * kK3RowsPerThread;
             const unsigned blocks = static_cast<unsigned>((ix->n_rows + rows_per_block - 1) / rows_per_block);
@@ -1196,6 +1247,7 @@ static int bind_buffers(crb_index* ix, const void* d_rows_f16, const float* d_in
     for (int m = 0; m < ix->n_keys; ++m) {
         ix->cols[m] = d_codes ? d_codes + int64_t(m) * code_stride : nullptr;
         ix->width[m] = 4;
+        ix->hist[m].clear();
     }
     ix->n_rows = n_rows;
     ix->k2_ok = false;
@@ -1301,10 +1353,29 @@ extern "C" int crb_index_rebind_columns(crb_index* ix, const void* d_rows_f16, c
     DeviceGuard guard(ix->device);
     CRB_CUDA(guard.status);
     if (int rc = bind_buffers(ix, d_rows_f16, d_inv_norm, nullptr, n_rows, n_rows)) return rc;
+    unsigned* d_hist = nullptr;
     for (int m = 0; m < ix->n_keys; ++m) {
         ix->cols[m] = h_code_cols[m];
         ix->width[m] = static_cast<uint8_t>(h_code_widths[m]);
+        ix->hist[m].clear();
+        if (h_code_widths[m] > 2 || n_rows == 0) continue;
+        const size_t bins = h_code_widths[m] == 1 ? 130 : 32770;
+        if (!d_hist) CRB_CUDA(cudaMalloc(&d_hist, 32770 * sizeof(unsigned)));
+        cudaError_t e = cudaMemset(d_hist, 0, bins * sizeof(unsigned));
+        if (e == cudaSuccess) {
+            code_histogram_kernel<<<static_cast<unsigned>(std::min<int64_t>((n_rows + 255) / 256, int64_t(ix->sm_count) * 8)), 256>>>(
+                h_code_cols[m], h_code_widths[m], n_rows, d_hist);
+            g_launches.fetch_add(1, std::memory_order_relaxed);
+            ix->hist[m].resize(bins);
+            e = cudaMemcpy(ix->hist[m].data(), d_hist, bins * sizeof(unsigned), cudaMemcpyDeviceToHost);
+        }
+        if (e != cudaSuccess) {
+            cudaFree(d_hist);
+            ix->hist[m].clear();
+            return fail("code histogram failed: %s", cudaGetErrorString(e));
+        }
     }
+    if (d_hist) cudaFree(d_hist);
     return 0;
 }
 

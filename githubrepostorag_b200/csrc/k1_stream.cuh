@@ -952,32 +952,6 @@ struct FusedParams {
     ExchangeDev ex;
 };
 
-// 16-bit mask of the bytes (16-bit halves) of `v` equal to the replicated wanted code: bit j <-> element j.
-// A zero byte of x = w ^ want becomes 0x80 exactly (no borrow between bytes), the four flags are gathered by a
-// multiply whose partial products cannot collide.
-CRB_DEVINL uint32_t eq_mask_bytes(const uint4& v, uint32_t want4) {
-    const uint32_t w[4] = {v.x, v.y, v.z, v.w};
-    uint32_t m = 0u;
-#pragma unroll
-    for (int i = 0; i < 4; ++i) {
-        const uint32_t x = w[i] ^ want4;
-        const uint32_t t = ~((((x & 0x7f7f7f7fu) + 0x7f7f7f7fu) | x) | 0x7f7f7f7fu);      // 0x80 where the byte of x is 0
-        m |= (((t >> 7) * 0x01020408u) >> 24) << (4 * i);
-    }
-    return m;
-}
-CRB_DEVINL uint32_t eq_mask_halves(const uint4& v, uint32_t want2) {      // 8 elements -> 8 bits
-    const uint32_t w[4] = {v.x, v.y, v.z, v.w};
-    uint32_t m = 0u;
-#pragma unroll
-    for (int i = 0; i < 4; ++i) {
-        const uint32_t x = w[i] ^ want2;
-        const uint32_t t = ~((((x & 0x7fff7fffu) + 0x7fff7fffu) | x) | 0x7fff7fffu);      // 0x8000 where the half of x is 0
-        m |= (((t >> 15) & 1u) | ((t >> 30) & 2u)) << (2 * i);
-    }
-    return m;
-}
-
 template <int CH, int R, int KPL>
 __global__ void __launch_bounds__(kK1Threads, 2)
 k1_fused_filter_kernel(const __grid_constant__ FusedParams p) {

@@ -18,15 +18,19 @@ for n, d, k in ((10_000_000, 1024, 20), (10_000_000, 768, 10), (1_000_000, 384, 
                        ("0.001%", [-1, -1, -1, 7, 5])):
         filt = np.asarray([want], np.int32)
         out = {}
-        for fused in ("1", "0"):
-            os.environ["CODERAG_B200_K1_FUSED"] = fused; sh.reload_tuning()
+        for fused in ("1", "0", "auto"):
+            if fused == "auto":
+                os.environ.pop("CODERAG_B200_K1_FUSED", None)
+            else:
+                os.environ["CODERAG_B200_K1_FUSED"] = fused
+            sh.reload_tuning()
             for _ in range(5): sh.search_device(q, k, filt=filt, workspace=ws)
             torch.cuda.synchronize()
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             e0.record()
             for _ in range(40): s_, r_, v_ = sh.search_device(q, k, filt=filt, workspace=ws)
             e1.record(); torch.cuda.synchronize()
-            out["fused_us" if fused == "1" else "k3_k1_us"] = round(e0.elapsed_time(e1) / 40 * 1e3, 1)
+            out[{"1": "fused_us", "0": "k3_k1_us", "auto": "default_plan_us"}[fused]] = round(e0.elapsed_time(e1) / 40 * 1e3, 1)
         print(json.dumps({"rows": n, "dim": d, "k": k, "filter": name, **out}), flush=True)
     os.environ.pop("CODERAG_B200_K1_FUSED", None)
     sh.close(); del rows, cols
