@@ -59,6 +59,8 @@ PROTOTYPES = {
                                        _vp, C.c_uint32, C.c_uint32]),
     "crb_search_exchange_host": (C.c_int, [_vp, _vp, _i32, _i32, _i32, _vp, _vp, _vp, _vp, _vp, _i32, _vp,
                                             C.c_uint32, C.c_uint32]),
+    "crb_host_register": (C.c_int, [_vp, _sz]),
+    "crb_host_unregister": (C.c_int, [_vp]),
     "crb_fetch_rows_host": (C.c_int, [_vp, _vp, _i32, _vp]),
     "crb_search_noalloc": (C.c_int, [_vp, _vp, _i32, _i32, _i32, _vp, _vp, _vp, _vp]),
     "crb_launch_count": (_i64, []),

@@ -93,6 +93,7 @@ struct Tuning {
     int k2_gthr = 1;          // _K2_GTHR: shared admission bound
     int k2_gthr_every = 0;    // _K2_GTHR_EVERY: fixed re-read cadence of the bound (0 = schedule)
     int k2_prepass = 1;       // _K2_PREPASS: first accumulator tile read twice
+    int zero_copy = 1;        // _ZEROCOPY: small results are written by the kernels straight into pinned host memory
     int k1_fold = 1;          // _K1_FOLD: sharded batch-1 calls merge in the streaming kernel's last CTA (one launch per rank)
     int k2_kprime = 16;       // candidates per list for k <= 10 (CRB_TUNING builds read _K2_KPRIME)
     int k2_prefetch = 0;      // CRB_TUNING builds only
@@ -114,6 +115,7 @@ struct Tuning {
         t.k1_fused = env("CODERAG_B200_K1_FUSED", t.k1_fused);
         t.k1_balanced = env("CODERAG_B200_K1_BALANCED", t.k1_balanced);
         t.k1_fold = env("CODERAG_B200_K1_FOLD", t.k1_fold);
+        t.zero_copy = env("CODERAG_B200_ZEROCOPY", t.zero_copy);
         t.k2_pair = env("CODERAG_B200_K2_PAIR", t.k2_pair);
         t.k2_minner = env("CODERAG_B200_K2_MINNER", t.k2_minner);
         t.k2_gthr = env("CODERAG_B200_K2_GTHR", t.k2_gthr);
@@ -160,6 +162,8 @@ struct Lane {
     size_t d_io_cap = 0;
     void* h_pin = nullptr;
     size_t h_cap = 0;
+    volatile uint32_t* h_flag = nullptr;   // pinned word a signal kernel writes when a zero-copy result is complete
+    uint32_t flag_seq = 0;
     bool busy = false;
 };
 
@@ -1189,8 +1193,43 @@ struct LaneHold {
     ~LaneHold() { checkin_lane(ix, lane); }
 };
 
+// Small results skip the device-to-host copy and the stream synchronisation: the search kernels write scores / rows /
+// n_valid straight into the lane's pinned host buffer (device-visible under unified addressing), a one-thread kernel
+// behind them on the stream writes a sequence number into a pinned word, and the host spins on that word.
+constexpr size_t kZeroCopyMaxBytes = 4096;
+__global__ void signal_flag_kernel(volatile uint32_t* flag, uint32_t seq) {
+    __threadfence_system();
+    *flag = seq;
+}
+static int lane_signal(Lane* l) {
+    l->flag_seq += 1;
+    signal_flag_kernel<<<1, 1, 0, l->stream>>>(l->h_flag, l->flag_seq);
+    CRB_LAUNCH_CHECK();
+    return 0;
+}
+static int lane_wait_flag(Lane* l) {
+    const uint32_t want = l->flag_seq;
+    for (uint64_t spins = 0;; ++spins) {
+        if (*l->h_flag == want) return 0;
+        if ((spins & 4095) == 4095) {                 // a failed launch never raises the flag: ask the stream now and then
+            const cudaError_t e = cudaStreamQuery(l->stream);
+            if (e == cudaSuccess) { if (*l->h_flag == want) return 0; }
+            else if (e != cudaErrorNotReady) return fail("search failed on the device: %s", cudaGetErrorString(e));
+        }
+#if defined(__x86_64__)
+        __builtin_ia32_pause();
+#endif
+    }
+}
+
 static int lane_reserve(Lane* l, size_t ws_bytes, size_t io_bytes, size_t pin_bytes) {
     if (!l->stream) CRB_CUDA(cudaStreamCreateWithFlags(&l->stream, cudaStreamNonBlocking));
+    if (!l->h_flag) {
+        void* f = nullptr;
+        CRB_CUDA(cudaMallocHost(&f, 64));
+        memset(f, 0, 64);
+        l->h_flag = static_cast<volatile uint32_t*>(f);
+    }
     if (l->ws_cap < ws_bytes) {
         if (l->d_ws) CRB_CUDA(cudaFree(l->d_ws));
         l->d_ws = nullptr; l->ws_cap = 0;
@@ -1211,6 +1250,14 @@ static int lane_reserve(Lane* l, size_t ws_bytes, size_t io_bytes, size_t pin_by
         l->h_cap = pin_bytes;
     }
     return 0;
+}
+
+// Is this host pointer page-locked (cudaHostRegister / cudaMallocHost)?  Then a copy can DMA straight from it and
+// the staging memcpy into the lane's own pinned buffer is skipped (worth asking only for large batches).
+static bool host_is_pinned(const void* p) {
+    cudaPointerAttributes a;
+    if (cudaPointerGetAttributes(&a, p) != cudaSuccess) { (void)cudaGetLastError(); return false; }
+    return a.type == cudaMemoryTypeHost;
 }
 
 static int count_distinct_filters(const int32_t* h_filt, int batch, int M) {
@@ -1424,6 +1471,7 @@ extern "C" int crb_index_destroy(crb_index* ix) {
         if (l.d_ws) cudaFree(l.d_ws);
         if (l.d_io) cudaFree(l.d_io);
         if (l.h_pin) cudaFreeHost(l.h_pin);
+        if (l.h_flag) cudaFreeHost(const_cast<uint32_t*>(l.h_flag));
         if (l.stream) cudaStreamDestroy(l.stream);
     }
     delete ix;
@@ -1528,12 +1576,22 @@ static int search_host_impl(crb_index* ix, const float* h_queries, int32_t batch
     uint8_t* h_io = static_cast<uint8_t*>(l->h_pin);
     memcpy(h_io, h_queries, q_bytes);
     CRB_CUDA(cudaMemcpyAsync(d_io, h_io, q_bytes, cudaMemcpyHostToDevice, l->stream));
+    const bool zc = ix->tune.zero_copy && !h_vectors && (io_bytes - off_rows) <= kZeroCopyMaxBytes;
+    uint8_t* o_io = zc ? h_io : d_io;          // where the kernels write the result
     int rc = search_impl(ix, reinterpret_cast<const float*>(d_io), batch, k, metric, h_filt,
-                         reinterpret_cast<float*>(d_io + off_scores),
-                         reinterpret_cast<int64_t*>(d_io + off_rows),
-                         reinterpret_cast<int32_t*>(d_io + off_valid), nullptr, l->d_ws, l->ws_cap,
+                         reinterpret_cast<float*>(o_io + off_scores),
+                         reinterpret_cast<int64_t*>(o_io + off_rows),
+                         reinterpret_cast<int32_t*>(o_io + off_valid), nullptr, l->d_ws, l->ws_cap,
                          algo, l->stream);
     if (rc) { cudaStreamSynchronize(l->stream); return rc; }
+    if (zc) {
+        if (int rs = lane_signal(l)) { cudaStreamSynchronize(l->stream); return rs; }
+        if (int rw = lane_wait_flag(l)) return rw;
+        memcpy(h_rows, h_io + off_rows, r_bytes);
+        memcpy(h_scores, h_io + off_scores, s_bytes);
+        memcpy(h_n_valid, h_io + off_valid, v_bytes);
+        return 0;
+    }
     if (h_vectors && ix->n_rows > 0) {
         const int n = batch * k;
         const unsigned blocks = static_cast<unsigned>(std::min<int64_t>((int64_t(n) * ix->dim + 255) / 256, int64_t(ix->sm_count) * 8));
@@ -1681,22 +1739,34 @@ extern "C" int crb_search_exchange_host(crb_index* ix, const float* h_queries, i
 
     uint8_t* d_io = static_cast<uint8_t*>(l->d_io);
     uint8_t* h_io = static_cast<uint8_t*>(l->h_pin);
-    memcpy(h_io, h_queries, q_bytes);
-    CRB_CUDA(cudaMemcpyAsync(d_io, h_io, q_bytes, cudaMemcpyHostToDevice, l->stream));
+    if (q_bytes >= (size_t(64) << 10) && host_is_pinned(h_queries)) {
+        // (the serving store registers its shared-memory command block: a 3 MB batch goes to the GPU without a second host copy)
+        CRB_CUDA(cudaMemcpyAsync(d_io, h_queries, q_bytes, cudaMemcpyHostToDevice, l->stream));
+    } else {
+        memcpy(h_io, h_queries, q_bytes);
+        CRB_CUDA(cudaMemcpyAsync(d_io, h_io, q_bytes, cudaMemcpyHostToDevice, l->stream));
+    }
     const float* d_q = reinterpret_cast<const float*>(d_io);
-    float* d_scores = reinterpret_cast<float*>(d_io + off_scores);
-    int64_t* d_rows = reinterpret_cast<int64_t*>(d_io + off_rows);
-    int32_t* d_valid = reinterpret_cast<int32_t*>(d_io + off_valid);
+    const bool zc = receives && ix->tune.zero_copy && (io_bytes - off_rows) <= kZeroCopyMaxBytes;
+    uint8_t* o_io = zc ? h_io : d_io;          // where the kernels write the result
+    float* d_scores = reinterpret_cast<float*>(o_io + off_scores);
+    int64_t* d_rows = reinterpret_cast<int64_t*>(o_io + off_rows);
+    int32_t* d_valid = reinterpret_cast<int32_t*>(o_io + off_valid);
     bool folded = false;
     int rc = search_impl(ix, d_q, batch, k, metric, h_filt, d_scores, d_rows, d_valid, nullptr, l->d_ws, l->ws_cap,
                          algo, l->stream, &ex, h_row_mask_ptrs, &folded);
     if (!rc && !folded) rc = launch_merge_wait(ix, exch, ex, d_q, batch, k, metric, d_scores, d_rows, d_valid, nullptr,
                                                expected_total, l->stream);
     if (rc) { cudaStreamSynchronize(l->stream); return rc; }
-    if (receives)
-        CRB_CUDA(cudaMemcpyAsync(h_io + off_rows, d_io + off_rows, io_bytes - off_rows, cudaMemcpyDeviceToHost, l->stream));
-    // every rank waits for its own stream: the staging buffers are free again, and a sender knows its keys left
-    CRB_CUDA(cudaStreamSynchronize(l->stream));
+    if (zc) {
+        if (int rs = lane_signal(l)) { cudaStreamSynchronize(l->stream); return rs; }
+        if (int rw = lane_wait_flag(l)) return rw;
+    } else {
+        if (receives)
+            CRB_CUDA(cudaMemcpyAsync(h_io + off_rows, d_io + off_rows, io_bytes - off_rows, cudaMemcpyDeviceToHost, l->stream));
+        // every rank waits for its own stream: the staging buffers are free again, and a sender knows its keys left
+        CRB_CUDA(cudaStreamSynchronize(l->stream));
+    }
     if (receives) {
         memcpy(h_rows, h_io + off_rows, r_bytes);
         memcpy(h_scores, h_io + off_scores, s_bytes);
@@ -1705,6 +1775,26 @@ extern "C" int crb_search_exchange_host(crb_index* ix, const float* h_queries, i
             if (h_n_valid[b] == -2)
                 return fail("sharded search: a peer did not publish query %d before the wait ran out (lost or stalled rank); "
                             "the exchange counters are out of step -- reset the exchange on every rank", b);
+    }
+    return 0;
+}
+
+extern "C" int crb_host_register(void* h_ptr, size_t bytes) {
+    if (!h_ptr || bytes == 0) return fail("crb_host_register: empty range");
+    const cudaError_t e = cudaHostRegister(h_ptr, bytes, cudaHostRegisterDefault);
+    if (e != cudaSuccess) {
+        (void)cudaGetLastError();       // not a sticky error: leave the runtime clean for the caller
+        return fail("cudaHostRegister failed: %s", cudaGetErrorString(e));
+    }
+    return 0;
+}
+
+extern "C" int crb_host_unregister(void* h_ptr) {
+    if (!h_ptr) return 0;
+    const cudaError_t e = cudaHostUnregister(h_ptr);
+    if (e != cudaSuccess) {
+        (void)cudaGetLastError();
+        return fail("cudaHostUnregister failed: %s", cudaGetErrorString(e));
     }
     return 0;
 }

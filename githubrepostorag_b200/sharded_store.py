@@ -161,8 +161,22 @@ class CudaRankEngine:
         self.world = dist.get_world_size(self.group)
         self.rank = dist.get_rank(self.group)
         self.exchange = NVLinkExchange(shard.device, self.group, cap_keys)
+        import ctypes as C
+        self._ex_ref = C.byref(self.exchange.struct)
         self.limit = limit            # first global row this rank may NOT use (None = no bound but the 32-bit key)
         self._masks: Dict[int, Any] = {}
+        self._out: Dict[Tuple[int, int], tuple] = {}       # result arrays and their ctypes pointers per (batch, k)
+        self._registered = None
+
+    def register_host(self, buf) -> None:
+        """Page-lock the store's shared-memory command block so query batches DMA straight out of it."""
+        addr = int(np.frombuffer(buf, dtype=np.uint8).ctypes.data)
+        self._registered = addr if N.load().crb_host_register(addr, len(buf)) == 0 else None
+
+    def unregister_host(self) -> None:
+        if self._registered is not None:
+            N.load().crb_host_unregister(self._registered)
+            self._registered = None
 
     # what the store needs to know about a rank
     def state(self) -> Dict[str, int]:
@@ -177,9 +191,12 @@ class CudaRankEngine:
         lib, ex = N.load(), self.exchange
         b = queries.shape[0]
         receives = self.rank == dest_rank
-        out = None
+        out, optr = None, (None, None, None)
         if receives:
+            # fresh arrays per call (the caller keeps them); their ctypes pointers are the cheap part to cache is not
+            # possible for fresh arrays, so allocate in one go
             out = (np.empty((b, k), np.float32), np.empty((b, k), np.int64), np.empty((b,), np.int32))
+            optr = (out[0].ctypes.data, out[1].ctypes.data, out[2].ctypes.data)
         ptrs = None
         if mask_ids is not None and (mask_ids >= 0).any():
             ptrs = (C.c_void_p * b)()
@@ -188,12 +205,11 @@ class CudaRankEngine:
                     ptrs[i] = self._masks[mid].data_ptr()
         ex.struct.dest_mask = 1 << dest_rank
         call, total = ex.next_call(b)
-        vp = C.c_void_p
-        N.check(lib.crb_search_exchange_host(
-            self.shard._h, queries.ctypes.data_as(vp), b, k, metric,
-            None if filt is None else filt.ctypes.data_as(vp), ptrs,
-            None if out is None else out[0].ctypes.data_as(vp), None if out is None else out[1].ctypes.data_as(vp),
-            None if out is None else out[2].ctypes.data_as(vp), algo, C.byref(ex.struct), call, total))
+        rc = lib.crb_search_exchange_host(
+            self.shard._h, queries.ctypes.data, b, k, metric, None if filt is None else filt.ctypes.data, ptrs,
+            optr[0], optr[1], optr[2], algo, self._ex_ref, call, total)
+        if rc:
+            N.check(rc)
         return out
 
     def set_mask(self, mask_id: int, tree) -> None:
@@ -317,6 +333,10 @@ class ShardedB200VectorStore(B200VectorStore):
         if self.rank != 0:
             self.ctl = ControlBlock(self.world, st["dim"], max_batch, payload_mb << 20, reply, name=names[0])
         self._seq = 0
+        if hasattr(engine, "register_host"):
+            engine.register_host(self.ctl.shm.buf)
+        self._ack_peers = self.ctl.ack[1:self.world]
+        self._status_peers = self.ctl.status[1:self.world]
         # every rank's row range
         states = [st]
         if self.world > 1:
@@ -347,17 +367,16 @@ class ShardedB200VectorStore(B200VectorStore):
         """Rank 0: wait until every rank finished the previous command, then publish this one."""
         ctl = self.ctl
         seq = self._seq
-        if self.world > 1:
+        if self.world > 1 and not (self._ack_peers == seq).all():
             _spin_until(lambda: bool((ctl.ack[1:self.world] == seq).all()), self.timeout_s, "the ranks to finish the previous command")
+        if self.world > 1 and self._status_peers.any():
             bad = [r for r in range(1, self.world) if ctl.status[r] != 0]
-            if bad:
-                err = ctl.get_reply(bad[0])
-                ctl.status[bad[0]] = 0
-                raise RuntimeError(f"sharded store: rank {bad[0]} failed the previous command: {err}")
-        h = ctl.hdr
-        h[0] = cmd
-        for i, key in enumerate(("batch", "k", "metric", "algo", "has_filt", "has_masks", "payload", "aux"), start=1):
-            h[i] = int(hdr.get(key, 0))
+            err = ctl.get_reply(bad[0])
+            ctl.status[bad[0]] = 0
+            raise RuntimeError(f"sharded store: rank {bad[0]} failed the previous command: {err}")
+        g = hdr.get
+        ctl.hdr[:9] = (cmd, g("batch", 0), g("k", 0), g("metric", 0), g("algo", 0), g("has_filt", 0), g("has_masks", 0),
+                       g("payload", 0), g("aux", 0))
         self._seq = seq + 1
         ctl.seq[0] = self._seq
         return self._seq
@@ -397,19 +416,23 @@ class ShardedB200VectorStore(B200VectorStore):
             if cmd == CMD_SHUTDOWN:
                 break
         self._closed = True
+        self._ack_peers = self._status_peers = None
+        if hasattr(self.engine, "unregister_host"):
+            self.engine.unregister_host()
         self.engine.close()
         self.ctl.close()
 
     def _execute(self, cmd: int):
         """One command on this rank (rank 0 runs the same code for its own share)."""
-        ctl, h, eng = self.ctl, self.ctl.hdr, self.engine
+        ctl, eng = self.ctl, self.engine
+        h = ctl.hdr[:9].tolist()
         if cmd == CMD_SEARCH:
-            b, k = int(h[1]), int(h[2])
+            b, k = h[1], h[2]
             q = ctl.queries[:b * self.dim].reshape(b, self.dim)
             nk = self.dictionary.n_keys
             filt = ctl.filt[:b * nk].reshape(b, nk) if h[5] else None
             mids = ctl.mask_ids[:b] if h[6] else None
-            return eng.search(q, k, int(h[3]), filt, mids, int(h[4]), 0)
+            return eng.search(q, k, h[3], filt, mids, h[4], 0)
         if cmd == CMD_SET_MASK:
             trees = ctl.get_payload(int(h[7]))
             eng.set_mask(int(h[8]), trees[self.rank] if isinstance(trees, dict) else trees)
@@ -466,6 +489,9 @@ class ShardedB200VectorStore(B200VectorStore):
             try:
                 self._run(CMD_SHUTDOWN)
             finally:
+                self._ack_peers = self._status_peers = None
+                if hasattr(self.engine, "unregister_host"):
+                    self.engine.unregister_host()
                 self.engine.close()
                 self.ctl.close()
 
@@ -500,6 +526,18 @@ class ShardedB200VectorStore(B200VectorStore):
                 self._execute(CMD_RESET)
                 self._wait_acks()
                 raise
+
+    def search_rows(self, queries, k: int, filters=None):
+        """Array-level search (see :meth:`B200VectorStore.search_rows`); unfiltered requests skip the filter plumbing."""
+        if filters is None or all(f is None for f in filters):
+            q = np.ascontiguousarray(queries, dtype=np.float32)
+            if q.ndim == 1:
+                q = q[None, :]
+            k = int(k)
+            if not 1 <= k <= N.MAX_TOPK:
+                raise ValueError(f"k must be in [1, {N.MAX_TOPK}]")
+            return self._search_locked(q, k, None, (), 0)
+        return super().search_rows(queries, k, filters)
 
     def _metric_code(self) -> int:
         return N.METRIC_COSINE if self.metric in ("cosine", "default", "cos", N.METRIC_COSINE) else N.METRIC_IP

@@ -221,6 +221,12 @@ int crb_search_exchange_host(crb_index *index, const float *h_queries, int32_t b
                              float *h_scores, int64_t *h_rows, int32_t *h_n_valid, int32_t algo,
                              const crb_exchange *exchange, uint32_t call_index, uint32_t expected_total);
 
+/* Page-lock / release a host range the caller owns (no reference counterpart; plumbing of the serving store): the
+ * shared-memory block its ranks exchange requests through is registered so that crb_search_exchange_host copies
+ * large query batches to the GPU straight out of it.  Failure leaves the CUDA runtime's error state clean. */
+int crb_host_register(void *h_ptr, size_t bytes);
+int crb_host_unregister(void *h_ptr);
+
 /* Fetch stored rows as fp32 (the `embedding` member of the (Document, embedding, id) triples
  * LCCassandra returns; graph-retriever re-scores from it).  h_rows_idx are LOCAL row indices. */
 int crb_fetch_rows_host(crb_index *index, const int64_t *h_rows_idx, int32_t n, float *h_out);
