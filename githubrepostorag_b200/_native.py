@@ -35,6 +35,12 @@ class Exchange(C.Structure):
                 ("peer_keys", C.c_void_p * MAX_PEERS), ("peer_counters", C.c_void_p * MAX_PEERS),
                 ("dest_mask", C.c_uint32)]
 
+class Ctl(C.Structure):
+    """``crb_ctl`` of include/coderag_b200.h."""
+    _fields_ = [("seq_off", C.c_uint64), ("hdr_off", C.c_uint64), ("ack_off", C.c_uint64), ("status_off", C.c_uint64),
+                ("queries_off", C.c_uint64), ("filt_off", C.c_uint64), ("rank", C.c_int32), ("world", C.c_int32)]
+
+
 # every symbol include/coderag_b200.h declares: name -> (restype, argtypes)
 _vp, _i32, _i64, _sz = C.c_void_p, C.c_int32, C.c_int64, C.c_size_t
 PROTOTYPES = {
@@ -59,6 +65,9 @@ PROTOTYPES = {
                                        _vp, C.c_uint32, C.c_uint32]),
     "crb_search_exchange_host": (C.c_int, [_vp, _vp, _i32, _i32, _i32, _vp, _vp, _vp, _vp, _vp, _i32, _vp,
                                             C.c_uint32, C.c_uint32]),
+    "crb_serve_post_search": (C.c_int, [_vp, _vp, _vp, _vp, _i32, _i32, _i32, _vp, _vp, _vp, _vp, _i32, _vp, _vp, _vp,
+                                         C.c_double]),
+    "crb_serve_next": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp]),
     "crb_host_register": (C.c_int, [_vp, _sz]),
     "crb_host_unregister": (C.c_int, [_vp]),
     "crb_fetch_rows_host": (C.c_int, [_vp, _vp, _i32, _vp]),

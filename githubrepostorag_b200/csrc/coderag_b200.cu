@@ -11,6 +11,7 @@
 #include <cstdlib>
 #include <cmath>
 #include <cstring>
+#include <ctime>
 #include <map>
 #include <mutex>
 #include <string>
@@ -499,23 +500,26 @@ static int launch_k1_fused(const crb_index* ix, const float* d_query, int qi, in
     FusedFn fn;
 #define CRB_FUSED(CH_, R_) (k <= 32 ? static_cast<FusedFn>(k1_fused_filter_kernel<CH_, R_, 1>) : static_cast<FusedFn>(k1_fused_filter_kernel<CH_, R_, 4>))
     switch (ch) {
-        // rows in flight per warp: what fits next to the prefetched code words without spilling at 2 CTAs per SM
+        // rows in flight per warp: the next stripe's codes wait in shared memory (cp.async), so the registers go to rows
         case 1: fn = CRB_FUSED(1, 8); break;
-        case 2: fn = CRB_FUSED(2, 4); break;
-        case 3: fn = CRB_FUSED(3, 3); break;
-        default: fn = CRB_FUSED(4, 2); break;
+        case 2: fn = CRB_FUSED(2, 6); break;
+        case 3: fn = CRB_FUSED(3, 5); break;
+        default: fn = CRB_FUSED(4, 4); break;
     }
 #undef CRB_FUSED
+    const size_t dyn = size_t(kK1Warps) * sizeof(FusedWarpSmem);
     static std::mutex mu;
-    static std::map<const void*, int> cache;
+    static std::map<std::pair<const void*, int>, int> cache;
     int occ = 0;
     {
         std::lock_guard<std::mutex> lk(mu);
-        auto it = cache.find(reinterpret_cast<const void*>(fn));
+        auto key = std::make_pair(reinterpret_cast<const void*>(fn), ix->device);
+        auto it = cache.find(key);
         if (it == cache.end()) {
+            CRB_CUDA(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(dyn)));
             int n = 0;
-            if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, fn, kK1Threads, 0) != cudaSuccess || n < 1) n = 1;
-            it = cache.emplace(reinterpret_cast<const void*>(fn), n).first;
+            if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, fn, kK1Threads, dyn) != cudaSuccess || n < 1) n = 1;
+            it = cache.emplace(key, n).first;
         }
         occ = it->second;
     }
@@ -551,7 +555,7 @@ static int launch_k1_fused(const crb_index* ix, const float* d_query, int qi, in
     grid = std::min<int64_t>(grid, std::max<int64_t>((stripes + kK1Warps - 1) / kK1Warps, 1));
     grid = std::min<int64_t>(grid, kK1MaxGridX);
     grid = std::min<int64_t>(grid, int64_t(kWsCandBytes) / (int64_t(k) * 8));
-    fn<<<static_cast<unsigned>(grid), kK1Threads, 0, stream>>>(p);
+    fn<<<static_cast<unsigned>(grid), kK1Threads, dyn, stream>>>(p);
     CRB_LAUNCH_CHECK();
     return 0;
 }
@@ -926,15 +930,18 @@ static int search_impl(crb_index* ix, const float* d_queries, int batch, int k, 
     // (CODERAG_B200_K1_FUSED=1): measured 6 % faster than K3 + K1 at 1 % selectivity (10M x 1024: 84.8 vs 89.9 us)
     // but slower when most rows pass (the scan and the scoring share one warp's registers and serialise their
     // memory latencies), and the plan has no selectivity estimate to choose by.
-    // (measured, profiles/fused_sweep.py: the fused kernel wins up to ~1 % of the rows passing -- 10M x 768 at 0.1 %:
-    //  25 vs 39 us, at 0.5 %: 46 vs 56 us -- is level at 1 % and loses when many rows pass, 10 %: 320 vs 279 us.)
+    // (measured, profiles/fused_sweep.py, fused vs K3 + K1: 10M x 1024 at 100 / 10 / 1 / 0.1 % passing 3.03 vs 3.44 ms, 368 vs
+    //  394 us, 70 vs 83 us, 36 vs 48 us; 10M x 768: 2.32 vs 2.46 ms, 289 vs 289, 56 vs 65, 27 vs 40 us; 1M x 384: 195 vs 138,
+    //  38 vs 35, 19.5 vs 24.8, 20 vs 25 us.)
     bool use_fused = false;
     if (batch == 1 && F == 1 && ch <= 4 && algo != 2 && ix->n_rows > 0 && ix->tune.k1_fused != 0 &&
         fused_eligible(ix, filters[0].data())) {
         if (ix->tune.k1_fused > 0) use_fused = true;
         else {
+            // wide rows (dim > 512): the fused kernel wins at every selectivity measured; short rows: only when
+            // few rows pass (its per-row queueing costs more than the streaming kernel's whole row step)
             const double est = estimate_selectivity(ix, filters[0].data());
-            use_fused = est >= 0.0 && est <= 0.015;
+            use_fused = est >= 0.0 && est <= (ch >= 3 ? 1.0 : 0.03);
         }
     }
     if (use_fused) {
@@ -1777,6 +1784,89 @@ extern "C" int crb_search_exchange_host(crb_index* ix, const float* h_queries, i
                             "the exchange counters are out of step -- reset the exchange on every rank", b);
     }
     return 0;
+}
+
+// ---------------------------------------------------------------------------------------------
+// The serving ranks' request path in C: what ShardedB200VectorStore does per plain search, without Python between
+// the shared-memory command word and the kernel launch.
+// ---------------------------------------------------------------------------------------------
+namespace crb {
+constexpr int32_t kCmdSearch = 1;      // sharded_store.py::CMD_SEARCH
+static inline uint64_t ctl_load_u64(const void* base, uint64_t off) {
+    return __atomic_load_n(reinterpret_cast<const uint64_t*>(static_cast<const uint8_t*>(base) + off), __ATOMIC_ACQUIRE);
+}
+static inline void ctl_store_u64(void* base, uint64_t off, uint64_t v) {
+    __atomic_store_n(reinterpret_cast<uint64_t*>(static_cast<uint8_t*>(base) + off), v, __ATOMIC_RELEASE);
+}
+static inline void cpu_relax() {
+#if defined(__x86_64__)
+    __builtin_ia32_pause();
+#endif
+}
+static double now_s() {
+    timespec ts;
+    clock_gettime(CLOCK_MONOTONIC, &ts);
+    return double(ts.tv_sec) + 1e-9 * double(ts.tv_nsec);
+}
+}  // namespace crb
+
+extern "C" int crb_serve_post_search(crb_index* ix, void* ctl_base, const crb_ctl* ctl, const float* h_queries,
+                                     int32_t batch, int32_t k, int32_t metric, const int32_t* h_filt, float* h_scores,
+                                     int64_t* h_rows, int32_t* h_n_valid, int32_t algo, const crb_exchange* exch,
+                                     uint32_t* call_state, uint64_t* seq_state, double timeout_s) {
+    if (!ix || !ctl_base || !ctl || !exch || !call_state || !seq_state) return fail("NULL argument passed to crb_serve_post_search");
+    if (int rc = validate_search(ix, batch, k, metric)) return rc;
+    uint8_t* base = static_cast<uint8_t*>(ctl_base);
+    const uint64_t seq = *seq_state;
+    // every rank has finished (and acknowledged) the previous command
+    const double t0 = now_s();
+    for (int r = 1; r < ctl->world; ++r) {
+        uint64_t spins = 0;
+        while (ctl_load_u64(base, ctl->ack_off + 8 * uint64_t(r)) != seq) {
+            cpu_relax();
+            if ((++spins & 0xfffff) == 0 && now_s() - t0 > timeout_s)
+                return fail("sharded store: timed out waiting for rank %d to finish the previous command", r);
+        }
+        if (reinterpret_cast<const int32_t*>(base + ctl->status_off)[r] != 0) return 2;     // the host reads the rank's error reply
+    }
+    int32_t* hdr = reinterpret_cast<int32_t*>(base + ctl->hdr_off);
+    hdr[0] = kCmdSearch; hdr[1] = batch; hdr[2] = k; hdr[3] = metric; hdr[4] = algo;
+    hdr[5] = h_filt ? 1 : 0; hdr[6] = 0; hdr[7] = 0; hdr[8] = 0;
+    float* q_ctl = reinterpret_cast<float*>(base + ctl->queries_off);
+    memcpy(q_ctl, h_queries, size_t(batch) * ix->dim * sizeof(float));
+    if (h_filt) memcpy(base + ctl->filt_off, h_filt, size_t(batch) * ix->n_keys * sizeof(int32_t));
+    *seq_state = seq + 1;
+    ctl_store_u64(base, ctl->seq_off, seq + 1);
+    // this rank's share of the command (the queries are read from the page-locked block, like every rank does)
+    call_state[1] += static_cast<uint32_t>(batch);
+    const uint32_t call = call_state[0]++;
+    return crb_search_exchange_host(ix, q_ctl, batch, k, metric, h_filt, nullptr, h_scores, h_rows, h_n_valid, algo, exch,
+                                    call, call_state[1]);
+}
+
+extern "C" int crb_serve_next(crb_index* ix, void* ctl_base, const crb_ctl* ctl, const crb_exchange* exch,
+                              uint32_t* call_state, uint64_t* last_seq) {
+    if (!ix || !ctl_base || !ctl || !exch || !call_state || !last_seq) return fail("NULL argument passed to crb_serve_next"), -1;
+    uint8_t* base = static_cast<uint8_t*>(ctl_base);
+    for (;;) {
+        // wait for the next command: spin (the hand-off is on the request's critical path), ease off when idle
+        uint64_t spins = 0, seq;
+        while ((seq = ctl_load_u64(base, ctl->seq_off)) == *last_seq) {
+            cpu_relax();
+            if (++spins > (1ull << 22)) { timespec ts{0, 200000}; nanosleep(&ts, nullptr); }
+        }
+        *last_seq = seq;
+        const int32_t* hdr = reinterpret_cast<const int32_t*>(base + ctl->hdr_off);
+        if (hdr[0] != kCmdSearch || hdr[6] != 0) return 0;       // not a plain search: the host side executes it
+        const int32_t batch = hdr[1], k = hdr[2], metric = hdr[3], algo = hdr[4];
+        const int32_t* filt = hdr[5] ? reinterpret_cast<const int32_t*>(base + ctl->filt_off) : nullptr;
+        call_state[1] += static_cast<uint32_t>(batch);
+        const uint32_t call = call_state[0]++;
+        const int rc = crb_search_exchange_host(ix, reinterpret_cast<const float*>(base + ctl->queries_off), batch, k, metric,
+                                                filt, nullptr, nullptr, nullptr, nullptr, algo, exch, call, call_state[1]);
+        if (rc) return -1;                                        // the host reports crb_last_error() and acknowledges
+        ctl_store_u64(base, ctl->ack_off + 8 * uint64_t(ctl->rank), seq);
+    }
 }
 
 extern "C" int crb_host_register(void* h_ptr, size_t bytes) {

@@ -952,11 +952,24 @@ struct FusedParams {
     ExchangeDev ex;
 };
 
+// Shared memory of the fused kernel, per warp: the survivor queue and the NEXT stripe's code words (staged with
+// cp.async, so the prefetch costs no registers and the registers go to rows in flight instead).
+// (Tried on top of this and dropped, profiles/README.md: four stripes of codes in flight instead of one -- no gain, the
+// scan is not what a selective search waits for; prefetching the survivors' rows into L2 when they are queued and
+// scoring them one stripe later -- no gain at 1 %, 30-60 % slower from 10 % of the rows passing upwards.)
+struct FusedWarpSmem {
+    uint32_t queue[kFusedStripe + 32];
+    uint4 codes[kFusedMaxKeys][2][32];      // [key][16-byte slot][lane]
+};
+CRB_DEVINL void cp_async_16(void* smem_dst, const void* gmem_src) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" ::"r"(static_cast<uint32_t>(__cvta_generic_to_shared(smem_dst))), "l"(gmem_src) : "memory");
+}
+
 template <int CH, int R, int KPL>
 __global__ void __launch_bounds__(kK1Threads, 2)
 k1_fused_filter_kernel(const __grid_constant__ FusedParams p) {
+    extern __shared__ __align__(16) uint8_t fused_smem_raw[];
     __shared__ uint64_t xchg[2][32];
-    __shared__ uint32_t s_queue[kK1Warps][kFusedStripe + 8];
     __shared__ float s_invq;
     __shared__ int s_last;
 
@@ -964,6 +977,7 @@ k1_fused_filter_kernel(const __grid_constant__ FusedParams p) {
     const int warp = threadIdx.x >> 5;
     const int chunks = p.dim >> 3;
     const bool cosine = (p.metric == 0);
+    FusedWarpSmem& sm = reinterpret_cast<FusedWarpSmem*>(fused_smem_raw)[warp];
 
     float qr[CH][8];
 #pragma unroll
@@ -982,7 +996,7 @@ k1_fused_filter_kernel(const __grid_constant__ FusedParams p) {
 
     WarpTopK<KPL> top;
     top.init(p.k, lane);
-    uint32_t* queue = s_queue[warp];
+    uint32_t* queue = sm.queue;
     int queued = 0;                                   // warp-uniform
 
     auto score_batch = [&](int first, int n_take) {   // rows queue[first .. first + n_take), n_take <= R
@@ -1024,38 +1038,35 @@ k1_fused_filter_kernel(const __grid_constant__ FusedParams p) {
         }
     };
 
-    // the wanted codes, replicated across a 32-bit word for the in-word compares
-    uint32_t want_w[kFusedMaxKeys];
-#pragma unroll
-    for (int u = 0; u < kFusedMaxKeys; ++u) {
-        const uint32_t w = static_cast<uint32_t>(p.want[u]);
-        want_w[u] = p.width[u] == 1 ? (w & 0xffu) * 0x01010101u : (w & 0xffffu) * 0x00010001u;
-    }
-    // codes of one stripe: two 16-byte slots per key (an int8 column uses the first only)
-    uint4 pf[kFusedMaxKeys][2];
+    // stage the codes of one stripe into this warp's shared memory: two 16-byte slots per key per lane (an int8
+    // column uses the first only); asynchronous, no registers held while the previous stripe's rows are gathered
     auto fetch = [&](int64_t st) {
         const int64_t r0 = st * kFusedStripe + 16 * lane;
 #pragma unroll
         for (int u = 0; u < kFusedMaxKeys; ++u) {
             if (u < p.n_used) {
                 if (p.width[u] == 1) {
-                    pf[u][0] = __ldg(reinterpret_cast<const uint4*>(static_cast<const uint8_t*>(p.cols[u]) + r0));
+                    cp_async_16(&sm.codes[u][0][lane], static_cast<const uint8_t*>(p.cols[u]) + r0);
                 } else {
-                    const uint4* src = reinterpret_cast<const uint4*>(static_cast<const uint16_t*>(p.cols[u]) + r0);
-                    pf[u][0] = __ldg(src);
-                    pf[u][1] = __ldg(src + 1);
+                    const uint16_t* src = static_cast<const uint16_t*>(p.cols[u]) + r0;
+                    cp_async_16(&sm.codes[u][0][lane], src);
+                    cp_async_16(&sm.codes[u][1][lane], src + 8);
                 }
             }
         }
+        asm volatile("cp.async.commit_group;" ::: "memory");
     };
-    // 16-bit pass mask of this lane's rows from the fetched codes
+    // 16-bit pass mask of this lane's rows from the staged codes
     auto evaluate = [&]() -> uint32_t {
+        asm volatile("cp.async.wait_group 0;" ::: "memory");
         uint32_t pass = 0xffffu;
 #pragma unroll
         for (int u = 0; u < kFusedMaxKeys; ++u) {
             if (u < p.n_used) {
-                if (p.width[u] == 1) pass &= eq_mask_bytes(pf[u][0], want_w[u]);
-                else pass &= eq_mask_halves(pf[u][0], want_w[u]) | (eq_mask_halves(pf[u][1], want_w[u]) << 8);
+                const uint32_t w = static_cast<uint32_t>(p.want[u]);
+                if (p.width[u] == 1) pass &= eq_mask_bytes(sm.codes[u][0][lane], (w & 0xffu) * 0x01010101u);
+                else pass &= eq_mask_halves(sm.codes[u][0][lane], (w & 0xffffu) * 0x00010001u) |
+                             (eq_mask_halves(sm.codes[u][1][lane], (w & 0xffffu) * 0x00010001u) << 8);
             }
         }
         return pass;
@@ -1085,6 +1096,7 @@ k1_fused_filter_kernel(const __grid_constant__ FusedParams p) {
     if (st < n_whole) fetch(st);
     for (; st < n_stripes; st += step) {
         uint32_t pass = st < n_whole ? evaluate() : evaluate_tail(st);
+        __syncwarp();
         if (st + step < n_whole) fetch(st + step);                // in flight while this stripe's survivors are gathered
         const int64_t r0 = st * kFusedStripe + 16 * lane;
         if (p.row_mask && pass) {
@@ -1122,6 +1134,7 @@ k1_fused_filter_kernel(const __grid_constant__ FusedParams p) {
         queued = rest;
         __syncwarp();
     }
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
     __syncwarp();
     if (queued > 0) score_batch(0, queued);
 

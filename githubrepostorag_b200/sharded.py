@@ -118,16 +118,17 @@ class NVLinkExchange:
             ex.peer_keys[p] = ptrs[p]
             ex.peer_counters[p] = ptrs[p] + 8 * 2 * self.world * self.cap_keys
         self.struct = ex
-        self.calls = 0
-        self.published = 0
+        import ctypes as C
+        self.state = (C.c_uint32 * 2)()      # {calls so far, queries published so far}; the C serving path updates it too
         dist.barrier(self.group)      # every rank's counters are zero before anyone publishes
 
     def next_call(self, batch: int) -> Tuple[int, int]:
         """(call_index, expected_total) of the next collective search of ``batch`` queries."""
-        self.published += batch
-        call = self.calls
-        self.calls += 1
-        return call & 0xFFFFFFFF, self.published & 0xFFFFFFFF
+        st = self.state
+        st[1] = (st[1] + batch) & 0xFFFFFFFF
+        call = st[0]
+        st[0] = (call + 1) & 0xFFFFFFFF
+        return call, st[1]
 
     def reset(self) -> None:
         """Collective: after a failed call (a rank lost or stalled, ``n_valid == -2``) the arrival counters and the
@@ -135,8 +136,7 @@ class NVLinkExchange:
         torch.cuda.synchronize(self.device)
         dist.barrier(self.group)
         self.buf.zero_()
-        self.calls = 0
-        self.published = 0
+        self.state[0] = self.state[1] = 0
         torch.cuda.synchronize(self.device)
         dist.barrier(self.group)
 

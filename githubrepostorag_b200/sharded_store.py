@@ -99,6 +99,16 @@ class ControlBlock:
     def name(self) -> str:
         return self.shm.name
 
+    def base_address(self) -> int:
+        return int(np.frombuffer(self.shm.buf, dtype=np.uint8).ctypes.data)
+
+    def c_layout(self, rank: int) -> "N.Ctl":
+        """``crb_ctl``: where the C serving path finds things in this block."""
+        c = N.Ctl()
+        c.seq_off, c.hdr_off, c.ack_off, c.status_off = 0, 8, self._o_ack, self._o_status
+        c.queries_off, c.filt_off, c.rank, c.world = self._o_q, self._o_filt, rank, self.world
+        return c
+
     def put_payload(self, obj: Any) -> int:
         raw = pickle.dumps(obj, protocol=pickle.HIGHEST_PROTOCOL)
         if len(raw) > self.payload_bytes:
@@ -211,6 +221,39 @@ class CudaRankEngine:
         if rc:
             N.check(rc)
         return out
+
+    # ---- the request path in C (crb_serve_post_search / crb_serve_next): no Python between the command word and the launch
+    def bind_control(self, ctl: "ControlBlock") -> None:
+        import ctypes as C
+        self._ctl_base = ctl.base_address()
+        self._ctl_layout = ctl.c_layout(self.rank)
+        self._ctl_ref = C.byref(self._ctl_layout)
+        self.ex_state = self.exchange.state
+
+    def post_search(self, queries: np.ndarray, k: int, metric: int, filt: Optional[np.ndarray], algo: int, seq_c,
+                    timeout_s: float):
+        """Rank 0: publish a plain search and run this rank's share; returns (scores, rows, n_valid), or the
+        integer 2 when a rank reported a failure of the previous command."""
+        import ctypes as C
+        b = queries.shape[0]
+        out = (np.empty((b, k), np.float32), np.empty((b, k), np.int64), np.empty((b,), np.int32))
+        self.exchange.struct.dest_mask = 1
+        rc = N.load().crb_serve_post_search(
+            self.shard._h, self._ctl_base, self._ctl_ref, queries.ctypes.data, b, k, metric,
+            None if filt is None else filt.ctypes.data, out[0].ctypes.data, out[1].ctypes.data, out[2].ctypes.data, algo,
+            self._ex_ref, C.addressof(self.ex_state), C.addressof(seq_c), timeout_s)
+        if rc == 2:
+            return 2
+        if rc:
+            N.check(rc)
+        return out
+
+    def serve_next(self, last_c) -> int:
+        """Ranks > 0: serve plain searches until a command needs the host side (0) or a search failed (-1)."""
+        import ctypes as C
+        self.exchange.struct.dest_mask = 1
+        return int(N.load().crb_serve_next(self.shard._h, self._ctl_base, self._ctl_ref, self._ex_ref,
+                                           C.addressof(self.ex_state), C.addressof(last_c)))
 
     def set_mask(self, mask_id: int, tree) -> None:
         self._masks[mask_id] = self.shard.pack_row_mask(self._eval(tree))
@@ -332,9 +375,12 @@ class ShardedB200VectorStore(B200VectorStore):
             dist.broadcast_object_list(names, src=0, group=group)
         if self.rank != 0:
             self.ctl = ControlBlock(self.world, st["dim"], max_batch, payload_mb << 20, reply, name=names[0])
-        self._seq = 0
+        import ctypes as C
+        self._seq_c = C.c_uint64(0)          # sequence number of the last command (shared with the C serving path)
         if hasattr(engine, "register_host"):
             engine.register_host(self.ctl.shm.buf)
+        if hasattr(engine, "bind_control"):
+            engine.bind_control(self.ctl)
         self._ack_peers = self.ctl.ack[1:self.world]
         self._status_peers = self.ctl.status[1:self.world]
         # every rank's row range
@@ -348,6 +394,14 @@ class ShardedB200VectorStore(B200VectorStore):
         self._rows.n_bulk = sum(s["n_rows"] for s in states)
         if self.world > 1:
             dist.barrier(group)
+
+    @property
+    def _seq(self) -> int:
+        return int(self._seq_c.value)
+
+    @_seq.setter
+    def _seq(self, v: int) -> None:
+        self._seq_c.value = v
 
     # ---- things the single-GPU store does with its own shard --------------------------------------
     def _ensure_built(self):
@@ -397,11 +451,21 @@ class ShardedB200VectorStore(B200VectorStore):
         if self.rank == 0:
             raise RuntimeError("rank 0 owns the store faces; serve_forever() is for the other ranks")
         ctl, last = self.ctl, self._seq
+        fast = hasattr(self.engine, "serve_next")
         while True:
-            _spin_until(lambda: int(ctl.seq[0]) != last, float("inf"), "a command")
-            last = int(ctl.seq[0])
+            failed = None
+            if fast:
+                # plain searches are served inside this call; it returns for every other command
+                if self.engine.serve_next(self._seq_c) < 0:
+                    failed = N.load().crb_last_error().decode("utf-8", "replace")
+                last = self._seq
+            else:
+                _spin_until(lambda: int(ctl.seq[0]) != last, float("inf"), "a command")
+                last = int(ctl.seq[0])
             cmd = int(ctl.hdr[0])
             try:
+                if failed is not None:
+                    raise RuntimeError(failed)
                 self._execute(cmd)
             except Exception as e:  # noqa: BLE001 - reported to rank 0 with the next command it posts
                 try:
@@ -508,6 +572,24 @@ class ShardedB200VectorStore(B200VectorStore):
         mids = None
         if any(extra for _, extra in split):
             mids = np.asarray([self._mask_id(extra) if extra else -1 for _, extra in split], dtype=np.int32)
+        if mids is None and hasattr(self.engine, "post_search"):
+            f32 = None if filt is None else np.ascontiguousarray(filt, dtype=np.int32)
+            with self._gate.read(), self._cmd_lock:
+                try:
+                    out = self.engine.post_search(q, k, self._metric_code(), f32, algo, self._seq_c, self.timeout_s)
+                    if isinstance(out, int):         # a rank failed the previous command: surface its message
+                        bad = [r for r in range(1, self.world) if self.ctl.status[r] != 0]
+                        err = self.ctl.get_reply(bad[0]) if bad else "unknown failure"
+                        for r in bad:
+                            self.ctl.status[r] = 0
+                        raise RuntimeError(f"sharded store: rank {bad[0] if bad else '?'} failed the previous command: {err}")
+                    return out
+                except RuntimeError:
+                    self._wait_acks()
+                    self._post(CMD_RESET)
+                    self._execute(CMD_RESET)
+                    self._wait_acks()
+                    raise
         with self._gate.read(), self._cmd_lock:
             ctl = self.ctl
             ctl.queries[:b * self.dim] = q.reshape(-1)

@@ -221,6 +221,28 @@ int crb_search_exchange_host(crb_index *index, const float *h_queries, int32_t b
                              float *h_scores, int64_t *h_rows, int32_t *h_n_valid, int32_t algo,
                              const crb_exchange *exchange, uint32_t call_index, uint32_t expected_total);
 
+/* The serving store's request path without the host language in it (no reference counterpart: the reference has one
+ * worker process and no second GPU).  The ranks of a box share one block of host memory (POSIX shared memory, laid out
+ * by the host side: githubrepostorag_b200/sharded_store.py::ControlBlock); `crb_ctl` says where things live in it.
+ *   crb_serve_post_search  rank 0: wait until every rank acknowledged the previous command, publish a plain SEARCH
+ *                          (queries, filter codes, k ...; bumps the sequence word), run this rank's share through
+ *                          crb_search_exchange_host and return the merged result.  Returns 2 when a rank reported a
+ *                          failure of the previous command (the host reads its reply).
+ *   crb_serve_next         ranks > 0: wait for the next command; run it and acknowledge it if it is a plain SEARCH, and
+ *                          go on waiting; return 0 when the command needs the host side (masks, writes, fetches ...,
+ *                          left unacknowledged, *last_seq = its sequence number), -1 on a failed search (unacknowledged).
+ * `call_state` is {calls so far, queries published so far} of this rank's exchange, shared with the host side. */
+typedef struct crb_ctl {
+    uint64_t seq_off, hdr_off, ack_off, status_off, queries_off, filt_off;
+    int32_t rank, world;
+} crb_ctl;
+int crb_serve_post_search(crb_index *index, void *ctl_base, const crb_ctl *ctl, const float *h_queries, int32_t batch,
+                          int32_t k, int32_t metric, const int32_t *h_filt, float *h_scores, int64_t *h_rows,
+                          int32_t *h_n_valid, int32_t algo, const crb_exchange *exchange, uint32_t *call_state,
+                          uint64_t *seq_state, double timeout_s);
+int crb_serve_next(crb_index *index, void *ctl_base, const crb_ctl *ctl, const crb_exchange *exchange,
+                   uint32_t *call_state, uint64_t *last_seq);
+
 /* Page-lock / release a host range the caller owns (no reference counterpart; plumbing of the serving store): the
  * shared-memory block its ranks exchange requests through is registered so that crb_search_exchange_host copies
  * large query batches to the GPU straight out of it.  Failure leaves the CUDA runtime's error state clean. */
