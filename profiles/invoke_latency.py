@@ -45,3 +45,11 @@ lat = []
 for i in range(200):
     t0 = time.perf_counter(); st._shard.search_host(q, 10); lat.append((time.perf_counter() - t0) * 1e3)
 print(json.dumps({"call": "crb_search_host batch 1 k=10 (1M x 384)", "p50_ms": round(float(np.median(lat[20:])), 4)}))
+# C1 (BASELINE.json config 1: 10k x 384, k=5, one query): the reference's own CPU-runnable case, through host buffers
+from githubrepostorag_b200.index import DeviceShard
+c1 = DeviceShard.from_host(S.corpus(1001, 10_000, d), None, device=0)
+lat = []
+for i in range(400):
+    t0 = time.perf_counter(); c1.search_host(q, 5); lat.append((time.perf_counter() - t0) * 1e6)
+print(json.dumps({"call": "C1 10k x 384 k=5 through crb_search_host", "p50_us": round(float(np.median(lat[50:])), 1),
+                  "p99_us": round(float(np.percentile(lat[50:], 99)), 1)}))

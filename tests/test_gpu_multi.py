@@ -242,3 +242,45 @@ def test_sharded_store_world_of_one():
     if p.is_alive():
         p.kill()
     assert res == [(0, "ok")], res
+
+
+def test_serve_entry_point_answers_json_lines(tmp_path):
+    """`python -m githubrepostorag_b200.serve --load <saved table>` with a world of one: the table is
+    saved in the streaming directory format, loaded as a sharded store, and requests on stdin come back as JSON lines
+    with the oracle's ids -- filtered, list-valued and unfiltered."""
+    import json
+    import subprocess
+    import sys
+
+    import oracle
+    from githubrepostorag_b200 import synthetic as S
+    from githubrepostorag_b200.vector_store import B200VectorStore
+    rng = np.random.default_rng(12)
+    n, d, k = 3000, 64, 5
+    emb = rng.standard_normal((n, d), dtype=np.float32).astype(np.float16).astype(np.float32)
+    metas = [{"namespace": "default", "repo": f"r{i % 4}", **({"topics": ["kafka"]} if i % 3 == 0 else {})} for i in range(n)]
+    ids = [S.row_id(i) for i in range(n)]
+    st = B200VectorStore(dim=d, scope="chunk")
+    st.add_embeddings(ids, emb, [f"text {i}" for i in range(n)], metas)
+    st.save(str(tmp_path / "table"))
+    st.close()
+    q = rng.standard_normal((3, d), dtype=np.float32)
+    reqs = [{"embedding": q[0].tolist(), "k": k}, {"embedding": q[1].tolist(), "k": k, "filter": {"repo": "r2"}},
+            {"embedding": q[2].tolist(), "k": k, "filter": {"topics": "kafka", "namespace": "default"}}, {"k": 1}]
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        port = s.getsockname()[1]
+    env = dict(os.environ, RANK="0", LOCAL_RANK="0", WORLD_SIZE="1", MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    out = subprocess.run([sys.executable, "-m", "githubrepostorag_b200.serve", "--load", str(tmp_path / "table")],
+                         input="\n".join(json.dumps(r) for r in reqs) + "\n", capture_output=True, text=True, env=env,
+                         cwd=root, timeout=300)
+    assert out.returncode == 0, out.stderr[-2000:]
+    lines = [json.loads(ln) for ln in out.stdout.splitlines() if ln.startswith("{")]
+    assert len(lines) == 4 and "error" in lines[3]                       # a bad request is answered, not fatal
+    for rep, req in zip(lines, reqs[:3]):
+        keep = oracle.prefilter_mask(metas, req.get("filter"))
+        s_ref, r_ref = oracle.query_vectorised(np.asarray(req["embedding"], np.float32), emb.astype(np.float16), k, keep=keep)
+        assert [h["id"] for h in rep["hits"]] == [ids[int(r)] for r in r_ref]
+        assert np.allclose([h["score"] for h in rep["hits"]], s_ref, rtol=1e-5, atol=2e-7)
+        assert rep["hits"][0]["text"] == f"text {int(r_ref[0])}"
