@@ -507,7 +507,7 @@ static int launch_k1_fused(const crb_index* ix, const float* d_query, int qi, in
         default: fn = CRB_FUSED(4, 4); break;
     }
 #undef CRB_FUSED
-    const size_t dyn = size_t(kK1Warps) * sizeof(FusedWarpSmem);
+    const size_t dyn = size_t(kK1Warps) * kFusedWarpSmem;
     static std::mutex mu;
     static std::map<std::pair<const void*, int>, int> cache;
     int occ = 0;

@@ -954,15 +954,24 @@ struct FusedParams {
 
 // Shared memory of the fused kernel, per warp: the survivor queue and the NEXT stripe's code words (staged with
 // cp.async, so the prefetch costs no registers and the registers go to rows in flight instead).
-// (Tried on top of this and dropped, profiles/README.md: four stripes of codes in flight instead of one -- no gain, the
-// scan is not what a selective search waits for; prefetching the survivors' rows into L2 when they are queued and
+// (Tried on top of this and dropped, profiles/README.md: prefetching the survivors' rows into L2 when they are queued and
 // scoring them one stripe later -- no gain at 1 %, 30-60 % slower from 10 % of the rows passing upwards.)
-struct FusedWarpSmem {
-    uint32_t queue[kFusedStripe + 32];
-    uint4 codes[kFusedMaxKeys][2][32];      // [key][16-byte slot][lane]
-};
+// `depth` stripes of codes are in flight per warp (a ring of stages, one cp.async group each): with one stripe in flight
+// the scan alone was a chain of ~8 dependent HBM round trips per warp -- a filter nothing passes took 24 us over 40 MB
+// of codes (ncu), a third of the whole C4 search.
+constexpr int kFusedQueue = kFusedStripe + 32;
+constexpr int kFusedCodeBytes = 8192;                   // staged code words per warp: `depth` stages of slots x 512 B
+constexpr size_t kFusedWarpSmem = kFusedQueue * 4 + kFusedCodeBytes;
 CRB_DEVINL void cp_async_16(void* smem_dst, const void* gmem_src) {
     asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" ::"r"(static_cast<uint32_t>(__cvta_generic_to_shared(smem_dst))), "l"(gmem_src) : "memory");
+}
+CRB_DEVINL void cp_async_wait_pending(int n) {      // wait until at most n of this thread's copy groups are pending
+    switch (n) {
+        case 0: asm volatile("cp.async.wait_group 0;" ::: "memory"); break;
+        case 1: asm volatile("cp.async.wait_group 1;" ::: "memory"); break;
+        case 2: asm volatile("cp.async.wait_group 2;" ::: "memory"); break;
+        default: asm volatile("cp.async.wait_group 3;" ::: "memory"); break;
+    }
 }
 
 template <int CH, int R, int KPL>
@@ -977,7 +986,14 @@ k1_fused_filter_kernel(const __grid_constant__ FusedParams p) {
     const int warp = threadIdx.x >> 5;
     const int chunks = p.dim >> 3;
     const bool cosine = (p.metric == 0);
-    FusedWarpSmem& sm = reinterpret_cast<FusedWarpSmem*>(fused_smem_raw)[warp];
+    uint8_t* my_smem = fused_smem_raw + static_cast<size_t>(warp) * kFusedWarpSmem;
+    uint32_t* queue = reinterpret_cast<uint32_t*>(my_smem);
+    uint4* codes = reinterpret_cast<uint4*>(my_smem + kFusedQueue * 4);      // [depth][slots][32 lanes]
+    // 16-byte slots one stripe needs per lane (an int8 column one, an int16 column two) and how many stripes fit
+    int slots = 0;
+#pragma unroll
+    for (int u = 0; u < kFusedMaxKeys; ++u) slots += u < p.n_used ? p.width[u] : 0;
+    const int depth = slots == 0 ? 1 : min(4, max(1, kFusedCodeBytes / (slots * 512)));
 
     float qr[CH][8];
 #pragma unroll
@@ -996,7 +1012,6 @@ k1_fused_filter_kernel(const __grid_constant__ FusedParams p) {
 
     WarpTopK<KPL> top;
     top.init(p.k, lane);
-    uint32_t* queue = sm.queue;
     int queued = 0;                                   // warp-uniform
 
     auto score_batch = [&](int first, int n_take) {   // rows queue[first .. first + n_take), n_take <= R
@@ -1038,67 +1053,65 @@ k1_fused_filter_kernel(const __grid_constant__ FusedParams p) {
         }
     };
 
-    // stage the codes of one stripe into this warp's shared memory: two 16-byte slots per key per lane (an int8
-    // column uses the first only); asynchronous, no registers held while the previous stripe's rows are gathered
-    auto fetch = [&](int64_t st) {
+    // stage the codes of stripe `st` into ring stage `stage` (always one commit group, empty past the last stripe); a
+    // lane whose 16 rows are not all inside the shard copies nothing
+    auto fetch = [&](int stage, int64_t st, bool live) {
         const int64_t r0 = st * kFusedStripe + 16 * lane;
+        if (live && r0 + 16 <= p.n_rows) {
+            uint4* dst = codes + static_cast<size_t>(stage) * slots * 32 + lane;
+            int slot = 0;
 #pragma unroll
-        for (int u = 0; u < kFusedMaxKeys; ++u) {
-            if (u < p.n_used) {
-                if (p.width[u] == 1) {
-                    cp_async_16(&sm.codes[u][0][lane], static_cast<const uint8_t*>(p.cols[u]) + r0);
-                } else {
-                    const uint16_t* src = static_cast<const uint16_t*>(p.cols[u]) + r0;
-                    cp_async_16(&sm.codes[u][0][lane], src);
-                    cp_async_16(&sm.codes[u][1][lane], src + 8);
+            for (int u = 0; u < kFusedMaxKeys; ++u) {
+                if (u < p.n_used) {
+                    if (p.width[u] == 1) {
+                        cp_async_16(dst + slot * 32, static_cast<const uint8_t*>(p.cols[u]) + r0);
+                        slot += 1;
+                    } else {
+                        const uint16_t* src = static_cast<const uint16_t*>(p.cols[u]) + r0;
+                        cp_async_16(dst + slot * 32, src);
+                        cp_async_16(dst + (slot + 1) * 32, src + 8);
+                        slot += 2;
+                    }
                 }
             }
         }
         asm volatile("cp.async.commit_group;" ::: "memory");
     };
     // 16-bit pass mask of this lane's rows from the staged codes
-    auto evaluate = [&]() -> uint32_t {
-        asm volatile("cp.async.wait_group 0;" ::: "memory");
+    auto evaluate = [&](int stage) -> uint32_t {
+        const uint4* src = codes + static_cast<size_t>(stage) * slots * 32 + lane;
         uint32_t pass = 0xffffu;
+        int slot = 0;
 #pragma unroll
         for (int u = 0; u < kFusedMaxKeys; ++u) {
             if (u < p.n_used) {
                 const uint32_t w = static_cast<uint32_t>(p.want[u]);
-                if (p.width[u] == 1) pass &= eq_mask_bytes(sm.codes[u][0][lane], (w & 0xffu) * 0x01010101u);
-                else pass &= eq_mask_halves(sm.codes[u][0][lane], (w & 0xffffu) * 0x00010001u) |
-                             (eq_mask_halves(sm.codes[u][1][lane], (w & 0xffffu) * 0x00010001u) << 8);
+                if (p.width[u] == 1) {
+                    pass &= eq_mask_bytes(src[slot * 32], (w & 0xffu) * 0x01010101u);
+                    slot += 1;
+                } else {
+                    pass &= eq_mask_halves(src[slot * 32], (w & 0xffffu) * 0x00010001u) |
+                            (eq_mask_halves(src[(slot + 1) * 32], (w & 0xffffu) * 0x00010001u) << 8);
+                    slot += 2;
+                }
             }
         }
         return pass;
     };
-    // the ragged last stripe: element-wise, bounds-checked
-    auto evaluate_tail = [&](int64_t st) -> uint32_t {
-        const int64_t r0 = st * kFusedStripe + 16 * lane;
-        uint32_t pass = 0u;
-        for (int j = 0; j < 16; ++j) {
-            const int64_t r = r0 + j;
-            if (r >= p.n_rows) break;
-            bool ok = true;
-            for (int u = 0; u < p.n_used; ++u) {
-                const int32_t c = p.width[u] == 1 ? static_cast<int32_t>(__ldg(static_cast<const int8_t*>(p.cols[u]) + r))
-                                                  : static_cast<int32_t>(__ldg(static_cast<const int16_t*>(p.cols[u]) + r));
-                ok = ok && (c == p.want[u]);
-            }
-            pass |= ok ? (1u << j) : 0u;
-        }
-        return pass;
-    };
-
     const int64_t n_stripes = (p.n_rows + kFusedStripe - 1) / kFusedStripe;
-    const int64_t n_whole = p.n_rows / kFusedStripe;              // stripes the vector loads may read completely
     const int64_t step = static_cast<int64_t>(gridDim.x) * kK1Warps;
-    int64_t st = static_cast<int64_t>(blockIdx.x) * kK1Warps + warp;
-    if (st < n_whole) fetch(st);
-    for (; st < n_stripes; st += step) {
-        uint32_t pass = st < n_whole ? evaluate() : evaluate_tail(st);
+    const int64_t st0 = static_cast<int64_t>(blockIdx.x) * kK1Warps + warp;
+    for (int d = 0; d < depth; ++d) fetch(d, st0 + d * step, st0 + d * step < n_stripes);
+    int it = 0;
+    for (int64_t st = st0; st < n_stripes; st += step, ++it) {
+        const int stage = it % depth;
+        cp_async_wait_pending(depth - 1);                          // this stage's group is the oldest one pending
         __syncwarp();
-        if (st + step < n_whole) fetch(st + step);                // in flight while this stripe's survivors are gathered
         const int64_t r0 = st * kFusedStripe + 16 * lane;
+        const uint32_t pass_all = evaluate(stage);
+        uint32_t pass = r0 + 16 <= p.n_rows ? pass_all : 0u;      // the shard's last n_rows % 16 rows: after the loop
+        __syncwarp();
+        fetch(stage, st + depth * step, st + depth * step < n_stripes);    // refill the stage: `depth` stripes ahead
         if (p.row_mask && pass) {
             // the lane's 16 rows are one half of a mask word (r0 is a multiple of 16)
             pass &= (__ldg(p.row_mask + (r0 >> 5)) >> (r0 & 31)) & 0xffffu;
@@ -1136,7 +1149,26 @@ k1_fused_filter_kernel(const __grid_constant__ FusedParams p) {
     }
     asm volatile("cp.async.wait_group 0;" ::: "memory");
     __syncwarp();
-    if (queued > 0) score_batch(0, queued);
+    // The shard's last n_rows % 16 rows belong to no whole 16-row lane group: one warp tests them, a row per lane.
+    // (As an element-wise pass over a whole ragged stripe inside the loop this was a chain of dependent loads.)
+    if (blockIdx.x == 0 && warp == 0) {
+        const int rem = static_cast<int>(p.n_rows & 15);
+        const int64_t r = p.n_rows - rem + lane;
+        bool ok = lane < rem;
+        for (int u = 0; u < p.n_used; ++u) {
+            if (lane < rem) {
+                const int32_t c = p.width[u] == 1 ? static_cast<int32_t>(__ldg(static_cast<const int8_t*>(p.cols[u]) + r))
+                                                  : static_cast<int32_t>(__ldg(static_cast<const int16_t*>(p.cols[u]) + r));
+                ok = ok && (c == p.want[u]);
+            }
+        }
+        if (ok && p.row_mask) ok = (__ldg(p.row_mask + (r >> 5)) >> (r & 31)) & 1u;
+        const uint32_t b = __ballot_sync(CRB_FULL_MASK, ok);
+        if (ok) queue[queued + __popc(b & ((1u << lane) - 1u))] = static_cast<uint32_t>(r);
+        queued += __popc(b);
+        __syncwarp();
+    }
+    for (int head = 0; head < queued; head += R) score_batch(head, min(R, queued - head));
 
     uint64_t* out = p.cand + static_cast<int64_t>(blockIdx.x) * p.k;
     block_extract_topk<KPL>(top, p.k, out, xchg, lane, warp, kK1Warps);

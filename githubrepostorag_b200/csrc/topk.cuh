@@ -153,20 +153,25 @@ struct TopKSink {
     }
 };
 
-// S-way merge of `n_lists` descending lists of k keys (list l starts at lists + l*stride) by k
-// rounds of "best head wins".  Thread t owns lists t, t+T, ...; LPT bounds lists per thread.
-// Heads are read with ld.cg (they were written by other CTAs of the same grid).
+// S-way merge of `n_lists` descending lists of k keys (list l starts at lists + l*stride), in two stages of
+// "best head wins" rounds that need no block barrier: (A) every warp merges its share of the lists -- warp w owns lists
+// w, w + nwarps, ...; a lane holds the heads of up to LPT of them -- into one sorted list in shared memory, all warps at
+// once; (B) warp 0 merges the nwarps lists.  (One block-wide stage cost a barrier per round: 6.8 us for 296 lists at
+// k = 20, a tenth of a selective filtered search -- in-kernel timestamps, profiles/README.md.)  Heads are read with
+// ld.cg (they were written by other CTAs of the same grid).
 template <int LPT>
 CRB_DEVINL void block_merge_sorted_lists(const uint64_t* __restrict__ lists, int n_lists, int k,
                                          int64_t stride, const TopKSink& sink,
                                          uint64_t (*xchg)[32], int lane, int warp, int nwarps) {
     __shared__ uint64_t s_win[kMaxTopK];
+    __shared__ uint64_t s_wl[8][kMaxTopK];          // stage A results (nwarps <= 8)
     const int T = nwarps * 32;
+    // ---- stage A ----
     uint64_t head[LPT], nxt[LPT];
     int pos[LPT];
 #pragma unroll
     for (int j = 0; j < LPT; ++j) {
-        const int l = threadIdx.x + j * T;
+        const int l = warp + nwarps * (lane + 32 * j);
         pos[j] = 0;
         head[j] = 0ull;
         nxt[j] = 0ull;
@@ -175,26 +180,47 @@ CRB_DEVINL void block_merge_sorted_lists(const uint64_t* __restrict__ lists, int
             if (k > 1) nxt[j] = ld_cg_u64(lists + l * stride + 1);
         }
     }
-    int r = 0;
-    for (; r < k; ++r) {
-        uint64_t m = head[0];
+    {
+        int r = 0;
+        for (; r < k; ++r) {
+            uint64_t m = head[0];
 #pragma unroll
-        for (int j = 1; j < LPT; ++j) m = head[j] > m ? head[j] : m;
-        const uint64_t best = block_max_u64(m, xchg, r, lane, warp, nwarps);
-        if (best == 0ull) break;
+            for (int j = 1; j < LPT; ++j) m = head[j] > m ? head[j] : m;
+            const uint64_t best = warp_max_u64(m);
+            if (best == 0ull) break;
 #pragma unroll
-        for (int j = 0; j < LPT; ++j) {
-            if (head[j] == best) {
-                const int l = threadIdx.x + j * T;
-                head[j] = nxt[j];
-                pos[j] += 1;
-                nxt[j] = (pos[j] + 1 < k) ? ld_cg_u64(lists + l * stride + pos[j] + 1) : 0ull;
+            for (int j = 0; j < LPT; ++j) {
+                if (head[j] == best) {
+                    const int l = warp + nwarps * (lane + 32 * j);
+                    head[j] = nxt[j];
+                    pos[j] += 1;
+                    nxt[j] = (pos[j] + 1 < k) ? ld_cg_u64(lists + l * stride + pos[j] + 1) : 0ull;
+                }
             }
+            if (lane == 0) s_wl[warp][r] = best;
         }
-        if (threadIdx.x == 0) s_win[r] = best;
+        if (lane == 0)
+            for (; r < k; ++r) s_wl[warp][r] = 0ull;
     }
-    const int nv = r;
     __syncthreads();
+    // ---- stage B ----
+    if (warp == 0) {
+        int p = 0;
+        uint64_t h = lane < nwarps ? s_wl[lane][0] : 0ull;
+        int r = 0;
+        for (; r < k; ++r) {
+            const uint64_t best = warp_max_u64(h);
+            if (best == 0ull) break;
+            if (h == best) {
+                p += 1;
+                h = p < k ? s_wl[lane][p] : 0ull;
+            }
+            if (lane == 0) s_win[r] = best;
+        }
+        if (lane == 0) xchg[0][0] = static_cast<uint64_t>(r);
+    }
+    __syncthreads();
+    const int nv = static_cast<int>(xchg[0][0]);
     // every rank of the result is written (and, in a sharded search, stored to the peers) by its own thread
     for (int i = threadIdx.x; i < k; i += T) {
         sink.emit(i, i < nv ? s_win[i] : 0ull);

@@ -3,7 +3,7 @@ import os, sys, numpy as np, torch
 sys.path.insert(0, ".")
 import bench
 from githubrepostorag_b200.index import DeviceShard
-n = int(os.environ.get("ROWS", 10_000_000)); d, k = 1024, 20
+n = int(os.environ.get("ROWS", 10_000_000)); d, k = 1024, int(os.environ.get("K", 20))
 rows = torch.randn((n, d), device="cuda").to(torch.float16)
 codes = bench.device_codes(torch, 0, n, 1004, torch.device("cuda"))
 if os.environ.get("WIDE"):
@@ -13,6 +13,8 @@ combo = (codes[0].to(torch.int64) * 2000 + codes[1].to(torch.int64)) * 2 + codes
 counts = torch.bincount(combo, minlength=16000).double()
 j = int(torch.argmin((counts / n - 0.01).abs()))
 filt = np.array([[j // 4000, (j // 2) % 2000, j % 2]], np.int32)
+if os.environ.get("EMPTY"):          # a filter (almost) nothing passes: the scan, the launch and the tail alone
+    j = int(torch.argmin(counts + (counts == 0) * 1e18)); filt = np.array([[j // 4000, (j // 2) % 2000, j % 2]], np.int32)
 print("selectivity", float(counts[j] / n), "filter", filt.tolist(), "widths", sh.code_widths)
 q = torch.randn((1, d), device="cuda")
 ws = sh.new_workspace(1, k, 1)
