@@ -175,7 +175,6 @@ class CudaRankEngine:
         self._ex_ref = C.byref(self.exchange.struct)
         self.limit = limit            # first global row this rank may NOT use (None = no bound but the 32-bit key)
         self._masks: Dict[int, Any] = {}
-        self._out: Dict[Tuple[int, int], tuple] = {}       # result arrays and their ctypes pointers per (batch, k)
         self._registered = None
 
     def register_host(self, buf) -> None:
@@ -203,8 +202,7 @@ class CudaRankEngine:
         receives = self.rank == dest_rank
         out, optr = None, (None, None, None)
         if receives:
-            # fresh arrays per call (the caller keeps them); their ctypes pointers are the cheap part to cache is not
-            # possible for fresh arrays, so allocate in one go
+            # fresh arrays per call: the caller keeps them
             out = (np.empty((b, k), np.float32), np.empty((b, k), np.int64), np.empty((b,), np.int32))
             optr = (out[0].ctypes.data, out[1].ctypes.data, out[2].ctypes.data)
         ptrs = None
