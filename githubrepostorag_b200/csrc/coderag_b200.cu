@@ -95,6 +95,7 @@ struct Tuning {
     int k2_gthr_every = 0;    // _K2_GTHR_EVERY: fixed re-read cadence of the bound (0 = schedule)
     int k2_prepass = 1;       // _K2_PREPASS: first accumulator tile read twice
     int zero_copy = 1;        // _ZEROCOPY: small results are written by the kernels straight into pinned host memory
+    int drop_trivial = 1;     // _DROP_TRIVIAL: drop filter codes that every row of the shard carries
     int k1_fold = 1;          // _K1_FOLD: sharded batch-1 calls merge in the streaming kernel's last CTA (one launch per rank)
     int k2_kprime = 16;       // candidates per list for k <= 10 (CRB_TUNING builds read _K2_KPRIME)
     int k2_prefetch = 0;      // CRB_TUNING builds only
@@ -116,6 +117,7 @@ struct Tuning {
         t.k1_fused = env("CODERAG_B200_K1_FUSED", t.k1_fused);
         t.k1_balanced = env("CODERAG_B200_K1_BALANCED", t.k1_balanced);
         t.k1_fold = env("CODERAG_B200_K1_FOLD", t.k1_fold);
+        t.drop_trivial = env("CODERAG_B200_DROP_TRIVIAL", t.drop_trivial);
         t.zero_copy = env("CODERAG_B200_ZEROCOPY", t.zero_copy);
         t.k2_pair = env("CODERAG_B200_K2_PAIR", t.k2_pair);
         t.k2_minner = env("CODERAG_B200_K2_MINNER", t.k2_minner);
@@ -890,6 +892,14 @@ static int search_impl(crb_index* ix, const float* d_queries, int batch, int k, 
             for (int m = 0; m < M && h_filt; ++m) {
                 f[m] = h_filt[size_t(b) * M + m];
                 if (f[m] < CRB_FILT_IMPOSSIBLE) return fail("filter code %d out of range", f[m]);
+                // a code that EVERY row of the shard carries constrains nothing (the reference's worker pins
+                // namespace = "default" on every request, agent_graph.py:198-239): drop it, so such a search takes
+                // the unfiltered plan.  Exact -- the histograms are counted over all n_rows at bind time, and deleted
+                // rows are excluded by their NaN norm, not by a code.
+                if (f[m] >= 0 && ix->tune.drop_trivial) {
+                    const std::vector<uint32_t>& h = ix->hist[m];
+                    if (size_t(f[m]) + 1 < h.size() && int64_t(h[size_t(f[m]) + 1]) == ix->n_rows) f[m] = CRB_FILT_ANY;
+                }
                 any |= (f[m] != CRB_FILT_ANY);
             }
             const uint32_t* rm = h_mask_ptrs ? h_mask_ptrs[b] : nullptr;
@@ -926,10 +936,8 @@ static int search_impl(crb_index* ix, const float* d_queries, int batch, int k, 
     // (profiles/group_width_probe.py, small_batch_dispatch.py).
     const int nq_group = std::max(1, std::min(nq_cap, ix->tune.k1_group > 0 ? ix->tune.k1_group : (ch > 4 ? 1 : 2)));
 
-    // one query under one satisfiable filter: filter and score in one pass, no survivor list.  OPT-IN
-    // (CODERAG_B200_K1_FUSED=1): measured 6 % faster than K3 + K1 at 1 % selectivity (10M x 1024: 84.8 vs 89.9 us)
-    // but slower when most rows pass (the scan and the scoring share one warp's registers and serialise their
-    // memory latencies), and the plan has no selectivity estimate to choose by.
+    // one query under one satisfiable filter: filter and score in one pass, no survivor list.  Chosen by the
+    // selectivity estimate below (CODERAG_B200_K1_FUSED=1 / 0 forces it on / off).
     // (measured, profiles/fused_sweep.py, fused vs K3 + K1: 10M x 1024 at 100 / 10 / 1 / 0.1 % passing 3.03 vs 3.44 ms, 368 vs
     //  394 us, 70 vs 83 us, 36 vs 48 us; 10M x 768: 2.32 vs 2.46 ms, 289 vs 289, 56 vs 65, 27 vs 40 us; 1M x 384: 195 vs 138,
     //  38 vs 35, 19.5 vs 24.8, 20 vs 25 us.)

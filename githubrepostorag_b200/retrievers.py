@@ -67,7 +67,7 @@ class EagerGraphRetriever:
     def invoke(self, query: str, filter: Optional[Dict[str, Any]] = None, **kwargs: Any) -> List[Document]:
         st = self.strategy
         k = int(kwargs.get("k", st.k))
-        qvec, found = self.store.search_with_embedding(query, k=st.start_k, filter=filter)
+        qvec, found = self.store.search_with_embedding(query, k=st.start_k, filter=filter, as_arrays=True)
         q = np.asarray(qvec, dtype=np.float32)
         seen: Dict[str, Tuple[Any, int]] = {}
         selected: List[str] = []
@@ -98,7 +98,7 @@ class EagerGraphRetriever:
                 break
             depth += 1
             frontier = []
-            for c in self.store.adjacent(new_edges, qvec, k=st.adjacent_k, filter=filter):
+            for c in self.store.adjacent(new_edges, q, k=st.adjacent_k, filter=filter, as_arrays=True):
                 if c.id not in seen:
                     seen[c.id] = (c, depth)
                     frontier.append(c)
@@ -106,7 +106,7 @@ class EagerGraphRetriever:
         # one matrix product for all selected rows (graph-retriever scores each node from its embedding)
         sims = {}
         if selected:
-            E = np.asarray([seen[rid][0].embedding for rid in selected], dtype=np.float32)
+            E = np.stack([np.asarray(seen[rid][0].embedding, dtype=np.float32) for rid in selected])
             den = np.linalg.norm(q) * np.linalg.norm(E, axis=1)
             dots = E @ q
             sims = {rid: (float(dots[i] / den[i]) if den[i] > 0 else 0.0) for i, rid in enumerate(selected)}

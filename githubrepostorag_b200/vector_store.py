@@ -106,55 +106,81 @@ class _WriteGate:
         self._depth = 0
         self._waiting_writers = 0
         self._local = threading.local()
+        self._read_hold = _ReadHold(self)
+        self._write_hold = _WriteHold(self)
 
-    def read(self):
-        gate = self
+    def read(self) -> "_ReadHold":
+        return self._read_hold
 
-        class _R:
-            def __enter__(self_inner):
-                me = threading.get_ident()
-                depth = getattr(gate._local, "reads", 0)
-                with gate._cv:
-                    if depth == 0 and gate._writer != me:
-                        while gate._writer is not None or gate._waiting_writers > 0:
-                            gate._cv.wait()
-                    gate._readers += 1
-                gate._local.reads = depth + 1
+    def write(self) -> "_WriteHold":
+        return self._write_hold
 
-            def __exit__(self_inner, *exc):
-                gate._local.reads -= 1
-                with gate._cv:
-                    gate._readers -= 1
-                    gate._cv.notify_all()
-        return _R()
+    def _enter_read(self) -> None:
+        me = threading.get_ident()
+        depth = getattr(self._local, "reads", 0)
+        with self._cv:
+            if depth == 0 and self._writer != me:
+                while self._writer is not None or self._waiting_writers > 0:
+                    self._cv.wait()
+            self._readers += 1
+        self._local.reads = depth + 1
 
-    def write(self):
-        gate = self
+    def _exit_read(self) -> None:
+        self._local.reads -= 1
+        with self._cv:
+            self._readers -= 1
+            if self._readers == 0 and self._waiting_writers:
+                self._cv.notify_all()
 
-        class _W:
-            def __enter__(self_inner):
-                me = threading.get_ident()
-                with gate._cv:
-                    if gate._writer == me:
-                        gate._depth += 1
-                        return
-                    if getattr(gate._local, "reads", 0):
-                        raise RuntimeError("internal: write requested while this thread holds a read")
-                    gate._waiting_writers += 1
-                    try:
-                        while gate._writer is not None or gate._readers > 0:
-                            gate._cv.wait()
-                    finally:
-                        gate._waiting_writers -= 1
-                    gate._writer, gate._depth = me, 1
+    def _enter_write(self) -> None:
+        me = threading.get_ident()
+        with self._cv:
+            if self._writer == me:
+                self._depth += 1
+                return
+            if getattr(self._local, "reads", 0):
+                raise RuntimeError("internal: write requested while this thread holds a read")
+            self._waiting_writers += 1
+            try:
+                while self._writer is not None or self._readers > 0:
+                    self._cv.wait()
+            finally:
+                self._waiting_writers -= 1
+            self._writer, self._depth = me, 1
 
-            def __exit__(self_inner, *exc):
-                with gate._cv:
-                    gate._depth -= 1
-                    if gate._depth == 0:
-                        gate._writer = None
-                        gate._cv.notify_all()
-        return _W()
+    def _exit_write(self) -> None:
+        with self._cv:
+            self._depth -= 1
+            if self._depth == 0:
+                self._writer = None
+                self._cv.notify_all()
+
+
+class _ReadHold:
+    """``with gate.read():`` -- stateless (the gate keeps the counts), so one object serves every thread."""
+    __slots__ = ("_gate",)
+
+    def __init__(self, gate: _WriteGate):
+        self._gate = gate
+
+    def __enter__(self):
+        self._gate._enter_read()
+
+    def __exit__(self, *exc):
+        self._gate._exit_read()
+
+
+class _WriteHold:
+    __slots__ = ("_gate",)
+
+    def __init__(self, gate: _WriteGate):
+        self._gate = gate
+
+    def __enter__(self):
+        self._gate._enter_write()
+
+    def __exit__(self, *exc):
+        self._gate._exit_write()
 
 
 class _Rows:
@@ -234,6 +260,7 @@ class B200VectorStore:
         self.multi_valued_keys = tuple(k for k in multi_valued_keys if k not in self.dictionary.keys)
         self._postings: Dict[Tuple[str, str], List[int]] = {}
         self._mask_cache: Dict[Any, Any] = {}
+        self._filter_cache: Dict[Any, Any] = {}
         self._mask_lock = threading.Lock()
         self._hist = _retrieval_histogram()
 
@@ -542,10 +569,14 @@ class B200VectorStore:
             raise ValueError("k must be >= 1")
         if k > N.MAX_TOPK:
             raise ValueError(f"k={k} exceeds the supported maximum {N.MAX_TOPK}")
-        split = [self._split_filter(f) for f in filters]
+        compiled = [self._compile_filter(f) for f in filters]
+        split = [(eq, extra) for eq, extra, _ in compiled]
         filt = None
-        if any(eq for eq, _ in split):
-            filt = np.stack([self.dictionary.encode_filter(eq) for eq, _ in split])
+        if any(row is not None for _, _, row in compiled):
+            filt = np.full((len(compiled), self.dictionary.n_keys), N.FILT_ANY, dtype=np.int32)
+            for i, (_, _, row) in enumerate(compiled):
+                if row is not None:
+                    filt[i] = row
         import time
         t0 = time.perf_counter()
         try:
@@ -603,6 +634,29 @@ class B200VectorStore:
             else:
                 items.append((str(key), ("eq", str(val))))
         return tuple(sorted(items, key=repr))
+
+    def _compile_filter(self, flt: Optional[Mapping[str, Any]]):
+        """filter dict -> ``(eq, extra, codes)``: :meth:`_split_filter`'s two parts and the equalities as one int32
+        code per key (None without equalities).  Remembered per distinct filter: the worker repeats a handful of
+        filters per request (``agent_graph.py:198-239``) and ``adjacent`` one per edge.  A filter naming a value the
+        dictionary does not know yet is not remembered (a later write may introduce the value)."""
+        if not flt:
+            return None, (), None
+        try:
+            key = tuple(flt.items())
+            hit = self._filter_cache.get(key)
+        except TypeError:                      # an unhashable value (("in", [..]) lists, __any_of__ groups)
+            key, hit = None, None
+        if hit is not None:
+            return hit
+        eq, extra = self._split_filter(flt)
+        row = self.dictionary.encode_filter(eq) if eq else None
+        hit = (eq, extra, row)
+        if key is not None and (row is None or int(row.min()) > N.FILT_IMPOSSIBLE):
+            if len(self._filter_cache) >= 4096:
+                self._filter_cache.clear()
+            self._filter_cache[key] = hit
+        return hit
 
     def _split_filter(self, flt: Optional[Mapping[str, Any]]):
         """filter dict -> (equalities on coded keys -- they go to the filter kernel as codes --, extra
@@ -823,19 +877,22 @@ class B200VectorStore:
         return B200Retriever(self, **kwargs)
 
     # ------------------------------------------------------------------ face B': graph-retriever Adapter
-    def _content(self, r: int, vec: np.ndarray) -> Content:
-        return Content(id=self._rows.id(r), content=self._rows.text(r), embedding=vec.tolist(),
+    def _content(self, r: int, vec: np.ndarray, as_arrays: bool = False) -> Content:
+        return Content(id=self._rows.id(r), content=self._rows.text(r), embedding=vec if as_arrays else vec.tolist(),
                        metadata=self._rows.meta(r))
 
     def search_with_embedding(self, query: str, k: int = 4, filter: Optional[Dict[str, Any]] = None, **kw
                               ) -> Tuple[List[float], List[Content]]:
         qvec = self._embed_query(query)
-        return qvec, self.search(qvec, k=k, filter=filter)
+        return qvec, self.search(qvec, k=k, filter=filter, **kw)
 
     @_reading
-    def search(self, embedding: Sequence[float], k: int = 4, filter: Optional[Dict[str, Any]] = None, **kw) -> List[Content]:
+    def search(self, embedding: Sequence[float], k: int = 4, filter: Optional[Dict[str, Any]] = None, *,
+               as_arrays: bool = False, **kw) -> List[Content]:
+        """``as_arrays``: leave ``Content.embedding`` as the fp32 array the device returned instead of a list of
+        floats (the in-repo traversal scores from arrays; graph-retriever's own callers get the list)."""
         hits, vecs = self._hits_with_vectors(embedding, k, filter)
-        return [self._content(r, vecs[i]) for i, (r, _) in enumerate(hits)]
+        return [self._content(r, vecs[i], as_arrays) for i, (r, _) in enumerate(hits)]
 
     @_reading
     def get(self, ids: Sequence[str], filter: Optional[Dict[str, Any]] = None, **kw) -> List[Content]:
@@ -852,7 +909,7 @@ class B200VectorStore:
 
     @_reading
     def adjacent(self, edges: Iterable[Any], query_embedding: Sequence[float], k: int,
-                 filter: Optional[Dict[str, Any]] = None, **kw) -> List[Content]:
+                 filter: Optional[Dict[str, Any]] = None, *, as_arrays: bool = False, **kw) -> List[Content]:
         """All rows adjacent through ``edges`` -- one filtered top-k per distinct
         ``(field, value)`` edge, same query vector -- issued as ONE batched search (the
         reference's adapter issues one CQL query per edge), then merged:
@@ -881,15 +938,19 @@ class B200VectorStore:
         flts = list({tuple(sorted((str(a), str(b)) for a, b in f.items())): f for f in flts}.values())
         q = np.repeat(np.asarray(query_embedding, dtype=np.float32)[None, :], len(flts), axis=0)
         scores, rows, n_valid, vecs = self._search(q, k, flts, vectors=True)
-        best: Dict[int, Tuple[float, int, int]] = {}
-        for i in range(len(flts)):
-            for j in range(int(n_valid[i])):
-                r = int(rows[i, j])
-                s = float(scores[i, j])
-                if r not in best or s > best[r][0]:
-                    best[r] = (s, i, j)
-        top = sorted(best.items(), key=lambda t: (-t[1][0], -t[0]))[:k]
-        return [self._content(r, vecs[i, j]) for r, (_, i, j) in top]
+        # merge the per-edge lists: one entry per row (its best score), best k by (score desc, row desc)
+        valid = (np.arange(rows.shape[1])[None, :] < np.asarray(n_valid)[:, None]).ravel()
+        slot = np.nonzero(valid)[0]
+        if not len(slot):
+            return []
+        fr, fs = rows.ravel()[slot], scores.ravel()[slot]
+        order = np.lexsort((-fs, fr))
+        lead = np.ones(len(order), dtype=bool)
+        lead[1:] = fr[order][1:] != fr[order][:-1]
+        cand = order[lead]
+        top = cand[np.lexsort((-fr[cand], -fs[cand]))[:k]]
+        flat = vecs.reshape(-1, vecs.shape[-1])
+        return [self._content(int(fr[t]), flat[slot[t]], as_arrays) for t in top]
 
 
 class B200Retriever:

@@ -248,3 +248,54 @@ def test_narrow_code_columns_equal_the_int32_matrix_and_widen_on_append():
         assert int(v_[0]) == len(r_ref) and r_[0, :len(r_ref)].tolist() == r_ref.tolist(), want
     wide.close()
     slim.close()
+
+
+def test_a_code_every_row_carries_is_dropped_from_the_filter(monkeypatch):
+    """The worker pins `namespace` on every request (agent_graph.py:198-239); in a single-namespace table that
+    predicate is true of every row.  The plan drops it (histograms of the code columns, exact): same result bit for
+    bit as with the elimination switched off, as the unfiltered search and as the oracle -- with the unfiltered plan's launches, no
+    filter pass; deleted rows stay excluded; an append that ends the uniformity ends the elimination."""
+    from githubrepostorag_b200 import _native as N
+    from githubrepostorag_b200.index import DeviceShard
+    rng = np.random.default_rng(5)
+    n, d, k = 60_000, 384, 10
+    rows16 = rng.standard_normal((n, d), dtype=np.float32).astype(np.float16)
+    codes = np.stack([np.zeros(n, np.int32), rng.integers(0, 40, n).astype(np.int32)])
+    sh = DeviceShard.from_host(rows16, codes, device=0, capacity=n + 16)
+    q = rng.standard_normal((1, d), dtype=np.float32)
+
+    def run(filt):
+        before = N.launch_count()
+        s_, r_, v_ = sh.search_host(q, k, filt=None if filt is None else np.asarray([filt], np.int32))
+        return s_.copy(), r_.copy(), v_.copy(), N.launch_count() - before
+
+    s0, r0, v0, l0 = run(None)
+    s1, r1, v1, l1 = run([0, -1])
+    assert l1 == l0 and np.array_equal(r0, r1) and np.array_equal(s0.view(np.int32), s1.view(np.int32))
+    s2, r2, v2, l2 = run([0, 7])                       # the second key still filters; one key left for the filter pass
+    keep = codes[1] == 7
+    s_ref, r_ref = oracle.query_vectorised(q[0], rows16, k, keep=keep)
+    assert r2[0].tolist() == r_ref.tolist()
+    monkeypatch.setenv("CODERAG_B200_DROP_TRIVIAL", "0")
+    sh.reload_tuning()
+    s3, r3, v3, l3 = run([0, -1])
+    s4, r4, v4, _ = run([0, 7])
+    assert l3 > l1 and np.array_equal(r3, r1) and np.array_equal(s3.view(np.int32), s1.view(np.int32))
+    assert np.array_equal(r4, r2) and np.array_equal(s4.view(np.int32), s2.view(np.int32))
+    monkeypatch.delenv("CODERAG_B200_DROP_TRIVIAL")
+    sh.reload_tuning()
+    # a deleted row never comes back, filter dropped or not
+    top = int(r1[0, 0])
+    sh.tombstone([top])
+    _, r5, _, l5 = run([0, -1])
+    live = np.ones(n, bool)
+    live[top] = False
+    assert l5 == l0 and r5[0].tolist() == oracle.query_vectorised(q[0], rows16, k, keep=live)[1].tolist()
+    # one row of another namespace: the predicate constrains again, and that row is filtered out
+    extra = (q[0] * 3).astype(np.float16)[None, :]     # would be the best hit
+    sh.append(extra, np.asarray([[1], [7]], np.int32))
+    _, r6, _, l6 = run([0, -1])
+    assert l6 > l0 and n not in r6[0].tolist() and r6[0].tolist() == r5[0].tolist()
+    _, r7, _, _ = run([1, -1])
+    assert r7[0, 0] == n
+    sh.close()
