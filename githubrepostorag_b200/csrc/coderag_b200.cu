@@ -871,6 +871,55 @@ static int launch_k2(crb_index* ix, const float* d_queries, int batch, int k, in
 // ---------------------------------------------------------------------------------------------
 // the search plan: dedup filters, build survivor lists, group queries, choose K1 / K2, launch
 // ---------------------------------------------------------------------------------------------
+// The filter pass: survivor lists (and, for the tensor-core plan, pass-bit masks) of `n` filters into the workspace.
+// any_of: the filters are alternatives of ONE row set -- a row that passes any of them lands in list 0, once.
+static int launch_k3(const crb_index* ix, const std::array<int32_t, kMaxKeys>* filters, const uint32_t* const* filter_masks,
+                     int n, bool any_of, uint8_t* ws, uint32_t* lists, uint32_t* masks, cudaStream_t stream) {
+    const int M = ix->n_keys;
+    K3Params kp;
+    memset(&kp, 0, sizeof kp);
+    for (int m = 0; m < M; ++m) {
+        kp.cols[m] = ix->cols[m];
+        kp.width[m] = ix->width[m];
+        kp.vec_ok[m] = reinterpret_cast<uintptr_t>(ix->cols[m]) % 16 == 0 ? 1 : 0;
+    }
+    kp.lists = lists;
+    kp.counts = reinterpret_cast<uint32_t*>(ws + kWsCountsOffset);
+    kp.masks = masks;
+    kp.mask_stride = mask_stride_of(ix);
+    kp.n_rows = ix->n_rows;
+    kp.list_stride = list_stride_of(ix);
+    kp.n_keys = M;
+    kp.n_filters = n;
+    kp.any_of = any_of ? 1 : 0;
+    for (int f = 0; f < n; ++f) {
+        kp.extra[f] = filter_masks ? filter_masks[f] : nullptr;
+        for (int m = 0; m < kMaxKeys; ++m) {
+            kp.want[f][m] = m < M ? filters[f][m] : CRB_FILT_ANY;
+            if (m < M && filters[f][m] != CRB_FILT_ANY) kp.used_keys |= (1u << m);
+        }
+    }
+    for (int m = 0; m < M; ++m)
+        if ((kp.used_keys >> m) & 1u) kp.ukeys[kp.n_used++] = static_cast<uint8_t>(m);
+    CRB_CUDA(cudaMemsetAsync(ws + kWsCountsOffset, 0, kMaxFilters * sizeof(uint32_t), stream));
+    const int64_t rows_per_block = int64_t(kK3Threads) * kK3RowsPerThread;
+    const unsigned blocks = static_cast<unsigned>((ix->n_rows + rows_per_block - 1) / rows_per_block);
+    if (blocks > 0) {
+        k3_filter_kernel<<<blocks, kK3Threads, 0, stream>>>(kp);
+        CRB_LAUNCH_CHECK();
+    }
+    return 0;
+}
+
+// A filter code that EVERY row of the shard carries constrains nothing (the reference's worker pins namespace = "default"
+// on every request, agent_graph.py:198-239): such a search takes the unfiltered plan.  Exact -- the histograms are
+// counted over all n_rows at bind time, and deleted rows are excluded by their NaN norm, not by a code.
+static bool code_is_trivial(const crb_index* ix, int m, int32_t code) {
+    if (code < 0 || !ix->tune.drop_trivial) return false;
+    const std::vector<uint32_t>& h = ix->hist[m];
+    return size_t(code) + 1 < h.size() && int64_t(h[size_t(code) + 1]) == ix->n_rows;
+}
+
 static int search_impl(crb_index* ix, const float* d_queries, int batch, int k, int metric,
                        const int32_t* h_filt, float* d_scores, int64_t* d_rows,
                        int32_t* d_n_valid, uint64_t* d_keys, void* d_workspace,
@@ -892,14 +941,7 @@ static int search_impl(crb_index* ix, const float* d_queries, int batch, int k, 
             for (int m = 0; m < M && h_filt; ++m) {
                 f[m] = h_filt[size_t(b) * M + m];
                 if (f[m] < CRB_FILT_IMPOSSIBLE) return fail("filter code %d out of range", f[m]);
-                // a code that EVERY row of the shard carries constrains nothing (the reference's worker pins
-                // namespace = "default" on every request, agent_graph.py:198-239): drop it, so such a search takes
-                // the unfiltered plan.  Exact -- the histograms are counted over all n_rows at bind time, and deleted
-                // rows are excluded by their NaN norm, not by a code.
-                if (f[m] >= 0 && ix->tune.drop_trivial) {
-                    const std::vector<uint32_t>& h = ix->hist[m];
-                    if (size_t(f[m]) + 1 < h.size() && int64_t(h[size_t(f[m]) + 1]) == ix->n_rows) f[m] = CRB_FILT_ANY;
-                }
+                if (code_is_trivial(ix, m, f[m])) f[m] = CRB_FILT_ANY;
                 any |= (f[m] != CRB_FILT_ANY);
             }
             const uint32_t* rm = h_mask_ptrs ? h_mask_ptrs[b] : nullptr;
@@ -992,38 +1034,10 @@ static int search_impl(crb_index* ix, const float* d_queries, int batch, int k, 
         }
 
         if (f_hi > f_lo) {
-            K3Params kp;
-            memset(&kp, 0, sizeof kp);
-            for (int m = 0; m < M; ++m) {
-                kp.cols[m] = ix->cols[m];
-                kp.width[m] = ix->width[m];
-                kp.vec_ok[m] = reinterpret_cast<uintptr_t>(ix->cols[m]) % 16 == 0 ? 1 : 0;
-            }
-            kp.lists = lists;
-            kp.counts = reinterpret_cast<uint32_t*>(ws + kWsCountsOffset);
-            kp.masks = any_k2_filtered ? masks : nullptr;
-            kp.mask_stride = mstride;
-            kp.n_rows = ix->n_rows;
-            kp.list_stride = stride;
-            kp.n_keys = M;
-            kp.n_filters = f_hi - f_lo;
-            for (int f = f_lo; f < f_hi; ++f) {
-                slot_of_filter[f] = f - f_lo;
-                kp.extra[f - f_lo] = filter_masks[f];
-                for (int m = 0; m < kMaxKeys; ++m) {
-                    kp.want[f - f_lo][m] = m < M ? filters[f][m] : CRB_FILT_ANY;
-                    if (m < M && filters[f][m] != CRB_FILT_ANY) kp.used_keys |= (1u << m);
-                }
-            }
-            for (int m = 0; m < M; ++m)
-                if ((kp.used_keys >> m) & 1u) kp.ukeys[kp.n_used++] = static_cast<uint8_t>(m);
-            CRB_CUDA(cudaMemsetAsync(ws + kWsCountsOffset, 0, kMaxFilters * sizeof(uint32_t), stream));
-            const int64_t rows_per_block = int64_t(kK3Threads) * kK3RowsPerThread;
-            const unsigned blocks = static_cast<unsigned>((ix->n_rows + rows_per_block - 1) / rows_per_block);
-            if (blocks > 0) {
-                k3_filter_kernel<<<blocks, kK3Threads, 0, stream>>>(kp);
-                CRB_LAUNCH_CHECK();
-            }
+            for (int f = f_lo; f < f_hi; ++f) slot_of_filter[f] = f - f_lo;
+            if (int rc = launch_k3(ix, filters.data() + f_lo, filter_masks.data() + f_lo, f_hi - f_lo, false, ws, lists,
+                                   any_k2_filtered ? masks : nullptr, stream))
+                return rc;
         }
 
         // A filtered row set is worth the tensor-core kernel (which scans the whole shard under a
@@ -1108,6 +1122,60 @@ static int search_impl(crb_index* ix, const float* d_queries, int batch, int k, 
         f_lo = f_hi;
     }
     return 0;
+}
+
+// One query under a DISJUNCTION of filters: a row passes when ANY of the n_alt alternatives (each an AND of equalities)
+// passes.  This is the adapter's adjacent(): one query vector, one row set per edge, the best k of their union
+// (graph_rag_retrievers.py:82-134 hands the edges to graph-retriever, whose adapter runs one filtered search per edge and
+// keeps the best k of the merged, de-duplicated hits).  The top k of a union is the top k of the per-set top k's, so one
+// search over the union returns the same rows -- and a row in several sets (a file's rows are its module's and its
+// repository's too) is read and scored once.
+static int search_any_of_impl(crb_index* ix, const float* d_query, int n_alt, const int32_t* h_filt, int k, int metric,
+                              float* d_scores, int64_t* d_rows, int32_t* d_n_valid, void* d_workspace,
+                              size_t workspace_bytes, cudaStream_t stream) {
+    const int M = ix->n_keys;
+    std::vector<std::array<int32_t, kMaxKeys>> alts;
+    bool everything = false;
+    for (int a = 0; a < n_alt && !everything; ++a) {
+        std::array<int32_t, kMaxKeys> f;
+        f.fill(CRB_FILT_ANY);
+        bool any = false, impossible = false;
+        for (int m = 0; m < M; ++m) {
+            f[m] = h_filt[size_t(a) * M + m];
+            if (f[m] < CRB_FILT_IMPOSSIBLE) return fail("filter code %d out of range", f[m]);
+            impossible |= (f[m] == CRB_FILT_IMPOSSIBLE);
+            if (code_is_trivial(ix, m, f[m])) f[m] = CRB_FILT_ANY;
+            any |= (f[m] != CRB_FILT_ANY);
+        }
+        if (impossible) continue;                     // matches no row: adds nothing to the union
+        if (!any) { everything = true; break; }       // matches every row: the union is the shard
+        if (std::find(alts.begin(), alts.end(), f) == alts.end()) alts.push_back(f);
+    }
+    if (everything)
+        return search_impl(ix, d_query, 1, k, metric, nullptr, d_scores, d_rows, d_n_valid, nullptr, d_workspace,
+                           workspace_bytes, 0, stream);
+    if (alts.size() <= 1) {
+        std::array<int32_t, kMaxKeys> f;
+        f.fill(CRB_FILT_IMPOSSIBLE);
+        if (!alts.empty()) f = alts[0];
+        return search_impl(ix, d_query, 1, k, metric, f.data(), d_scores, d_rows, d_n_valid, nullptr, d_workspace,
+                           workspace_bytes, 0, stream);
+    }
+    if (alts.size() > size_t(kMaxFilters))
+        return fail("at most %d distinct alternatives per call (got %zu)", kMaxFilters, alts.size());
+    uint8_t* ws = static_cast<uint8_t*>(d_workspace);
+    const WsLayout L = ws_layout(ix, 1, k);
+    if (workspace_bytes < L.filt + L.per_filter)
+        return fail("workspace too small for one survivor list: need %zu bytes", L.filt + L.per_filter);
+    uint32_t* lists = reinterpret_cast<uint32_t*>(ws + L.filt);
+    if (int rc = launch_k3(ix, alts.data(), nullptr, static_cast<int>(alts.size()), true, ws, lists, nullptr, stream))
+        return rc;
+    std::vector<QueryGroup> groups(1);
+    groups[0].filter = 0;
+    groups[0].queries.assign(1, 0);
+    const std::vector<int> slot_of_filter(1, 0);
+    return launch_k1(ix, d_query, k, metric, groups, slot_of_filter, 1, ws, lists, d_scores, d_rows, d_n_valid, nullptr,
+                     stream);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -1565,7 +1633,8 @@ namespace crb {
 // crb_search_host and crb_search_host_vectors: host buffers in, host buffers out, one lane per caller
 static int search_host_impl(crb_index* ix, const float* h_queries, int32_t batch, int32_t k, int32_t metric,
                             const int32_t* h_filt, float* h_scores, int64_t* h_rows, int32_t* h_n_valid,
-                            float* h_vectors, int32_t algo) {
+                            float* h_vectors, int32_t algo, int32_t n_alt = 0) {
+    // n_alt > 0: ONE query (batch == 1) under a disjunction of n_alt filter rows (crb_search_host_any_of)
     if (int rc = validate_search(ix, batch, k, metric)) return rc;
     if (!h_queries || !h_scores || !h_rows || !h_n_valid) return fail("NULL host pointer passed to crb_search_host");
     DeviceGuard guard(ix->device);
@@ -1584,7 +1653,7 @@ static int search_host_impl(crb_index* ix, const float* h_queries, int32_t batch
     const size_t off_valid = off_scores + round_up(s_bytes, 256);
     const size_t off_vec = off_valid + round_up(v_bytes, 256);
     const size_t io_bytes = off_vec + round_up(e_bytes, 256);
-    const size_t ws_bytes = crb_workspace_bytes(ix, batch, k, count_distinct_filters(h_filt, batch, ix->n_keys));
+    const size_t ws_bytes = crb_workspace_bytes(ix, batch, k, n_alt > 0 ? 1 : count_distinct_filters(h_filt, batch, ix->n_keys));
     if (int rc = lane_reserve(l, ws_bytes, io_bytes, io_bytes)) return rc;
 
     uint8_t* d_io = static_cast<uint8_t*>(l->d_io);
@@ -1593,11 +1662,15 @@ static int search_host_impl(crb_index* ix, const float* h_queries, int32_t batch
     CRB_CUDA(cudaMemcpyAsync(d_io, h_io, q_bytes, cudaMemcpyHostToDevice, l->stream));
     const bool zc = ix->tune.zero_copy && !h_vectors && (io_bytes - off_rows) <= kZeroCopyMaxBytes;
     uint8_t* o_io = zc ? h_io : d_io;          // where the kernels write the result
-    int rc = search_impl(ix, reinterpret_cast<const float*>(d_io), batch, k, metric, h_filt,
-                         reinterpret_cast<float*>(o_io + off_scores),
-                         reinterpret_cast<int64_t*>(o_io + off_rows),
-                         reinterpret_cast<int32_t*>(o_io + off_valid), nullptr, l->d_ws, l->ws_cap,
-                         algo, l->stream);
+    int rc = n_alt > 0
+        ? search_any_of_impl(ix, reinterpret_cast<const float*>(d_io), n_alt, h_filt, k, metric,
+                             reinterpret_cast<float*>(o_io + off_scores), reinterpret_cast<int64_t*>(o_io + off_rows),
+                             reinterpret_cast<int32_t*>(o_io + off_valid), l->d_ws, l->ws_cap, l->stream)
+        : search_impl(ix, reinterpret_cast<const float*>(d_io), batch, k, metric, h_filt,
+                      reinterpret_cast<float*>(o_io + off_scores),
+                      reinterpret_cast<int64_t*>(o_io + off_rows),
+                      reinterpret_cast<int32_t*>(o_io + off_valid), nullptr, l->d_ws, l->ws_cap,
+                      algo, l->stream);
     if (rc) { cudaStreamSynchronize(l->stream); return rc; }
     if (zc) {
         if (int rs = lane_signal(l)) { cudaStreamSynchronize(l->stream); return rs; }
@@ -1638,6 +1711,14 @@ extern "C" int crb_search_host_vectors(crb_index* ix, const float* h_queries, in
                                        int64_t* h_rows, int32_t* h_n_valid, float* h_vectors, int32_t algo) {
     if (!h_vectors) return fail("NULL vector buffer passed to crb_search_host_vectors");
     return search_host_impl(ix, h_queries, batch, k, metric, h_filt, h_scores, h_rows, h_n_valid, h_vectors, algo);
+}
+
+extern "C" int crb_search_host_any_of(crb_index* ix, const float* h_query, int32_t n_alt, const int32_t* h_filt,
+                                      int32_t k, int32_t metric, float* h_scores, int64_t* h_rows,
+                                      int32_t* h_n_valid, float* h_vectors) {
+    if (n_alt < 1) return fail("n_alt must be >= 1");
+    if (!h_filt) return fail("NULL filter pointer passed to crb_search_host_any_of");
+    return search_host_impl(ix, h_query, 1, k, metric, h_filt, h_scores, h_rows, h_n_valid, h_vectors, 0, n_alt);
 }
 
 extern "C" int crb_merge_keys(const uint64_t* d_keys_in, int32_t n_lists, int32_t batch, int32_t k,

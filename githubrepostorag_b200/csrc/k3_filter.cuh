@@ -32,6 +32,7 @@ struct K3Params {
     int64_t list_stride;
     int32_t n_keys;
     int32_t n_filters;
+    int32_t any_of;        // 1: the filters are ALTERNATIVES -- a row that passes any of them goes to list 0 (once)
     uint32_t used_keys;    // bit m set when any filter constrains key m
     int32_t n_used;        // the constrained keys, compacted (host-filled)
     uint8_t ukeys[kMaxKeys];
@@ -156,10 +157,16 @@ __global__ void __launch_bounds__(kK3Threads) k3_filter_kernel(const __grid_cons
         for (int j = 0; j < kK3RowsPerThread; ++j)
             if (!((half >> j) & 1u)) pass[j] &= ~(1u << f);
     }
+    // alternatives (one query vector, the union of several edges' row sets -- the adapter's adjacent()): one list
+    const int n_out = p.any_of ? 1 : p.n_filters;
+    if (p.any_of) {
+#pragma unroll
+        for (int j = 0; j < kK3RowsPerThread; ++j) pass[j] = pass[j] ? 1u : 0u;
+    }
     __syncthreads();
 
     // per filter: this thread's 16-bit survivor mask; the warp's total claims the warp's place in the block
-    for (int f = 0; f < p.n_filters; ++f) {
+    for (int f = 0; f < n_out; ++f) {
         uint32_t pm = 0u;
 #pragma unroll
         for (int j = 0; j < kK3RowsPerThread; ++j) pm |= ((pass[j] >> f) & 1u) << j;
@@ -173,13 +180,13 @@ __global__ void __launch_bounds__(kK3Threads) k3_filter_kernel(const __grid_cons
         }
     }
     __syncthreads();
-    if (threadIdx.x < p.n_filters) {
+    if (threadIdx.x < n_out) {
         const uint32_t c = s_cnt[threadIdx.x];
         s_base[threadIdx.x] = c ? atomicAdd(&p.counts[threadIdx.x], c) : 0u;
     }
     __syncthreads();
 
-    for (int f = 0; f < p.n_filters; ++f) {
+    for (int f = 0; f < n_out; ++f) {
         uint32_t pm = 0u;
 #pragma unroll
         for (int j = 0; j < kK3RowsPerThread; ++j) pm |= ((pass[j] >> f) & 1u) << j;

@@ -422,6 +422,27 @@ class DeviceShard:
         N.check(self._lib.crb_search_host(self._h, pq, b, k, m, pf, ps, pr, pv, algo))
         return s_scores.copy(), s_rows.copy(), s_valid.copy()
 
+    def search_host_any_of(self, query: np.ndarray, filt: np.ndarray, k: int, *, metric: str | int = "cosine",
+                           vectors: bool = False):
+        """ONE query under a disjunction of filters (``crb_search_host_any_of``): ``filt`` int32 ``[n_alt, n_keys]``, a row
+        passes when any of its rows passes -- the traversal's ``adjacent`` step in one search over the union of the
+        edges' row sets.  Returns ``(scores [k], rows [k], n_valid)`` and, with ``vectors``, the hits' rows ``[k, dim]``."""
+        q = np.ascontiguousarray(query, dtype=np.float32).reshape(-1)
+        if q.shape[0] != self.dim:
+            raise ValueError(f"query dimension {q.shape[0]} != index dimension {self.dim}")
+        f = np.ascontiguousarray(filt, dtype=np.int32)
+        if f.ndim != 2 or f.shape[0] < 1 or f.shape[1] != self.n_keys:
+            raise ValueError(f"filt must be [n_alt >= 1, {self.n_keys}] (got {f.shape})")
+        k = int(k)
+        scores = np.empty((k,), dtype=np.float32)
+        rows = np.empty((k,), dtype=np.int64)
+        n_valid = np.empty((1,), dtype=np.int32)
+        vecs = np.empty((k, self.dim), dtype=np.float32) if vectors else None
+        N.check(self._lib.crb_search_host_any_of(self._h, q.ctypes.data, f.shape[0], f.ctypes.data if f.size else None, k,
+                                                 self._metric(metric), _addr(scores), _addr(rows), _addr(n_valid),
+                                                 None if vecs is None else _addr(vecs)))
+        return (scores, rows, int(n_valid[0]), vecs) if vectors else (scores, rows, int(n_valid[0]))
+
     def workspace_bytes(self, batch: int, k: int, n_filters: int) -> int:
         return int(self._lib.crb_workspace_bytes(self._h, batch, k, n_filters))
 

@@ -337,6 +337,10 @@ class ShardedB200VectorStore(B200VectorStore):
     """Collective constructor (every rank calls it); afterwards rank 0 uses the faces of :class:`B200VectorStore`
     and every other rank calls :meth:`serve_forever`.  ``close()`` on rank 0 ends the peers' loops."""
 
+    def _search_any_of(self, q, k, flts):
+        # the union search is a single-shard call; a sharded adjacent() step stays one batched, exchanged search
+        return None
+
     def __init__(self, engine, *, dictionary: Optional[MetadataDictionary] = None, embedding: Any = None,
                  id_fn: Optional[Callable[[int], str]] = None, meta_fn: Optional[Callable[[int], Dict[str, Any]]] = None,
                  text_fn: Optional[Callable[[int], str]] = None, metric: str = "cosine", table_name: str = "embeddings",

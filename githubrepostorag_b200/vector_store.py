@@ -907,13 +907,38 @@ class B200VectorStore:
         vecs = self._fetch_vectors(rows)
         return [self._content(r, vecs[i]) for i, r in enumerate(rows)]
 
+    MAX_ALTERNATIVES = 32            # distinct edge filters one crb_search_host_any_of call takes
+
+    def _search_any_of(self, q: np.ndarray, k: int, flts: Sequence[Mapping[str, Any]]):
+        """The edges of one ``adjacent`` step as ONE search over the union of their row sets: the best ``k`` of a union
+        is the best ``k`` of the per-edge best ``k``'s (what the adapter computes), and a row in several sets is scored
+        once.  ``(rows, vectors, n_valid)``, or None when an edge needs more than coded equalities (list-valued keys,
+        IN, OR: those ride on row masks) -- the caller then issues the per-edge batch."""
+        compiled = [self._compile_filter(f) for f in flts]
+        if any(extra or row is None for _, extra, row in compiled):
+            return None
+        import time
+        t0 = time.perf_counter()
+        try:
+            with self._gate.read():
+                alts = np.concatenate([row for _, _, row in compiled]).reshape(len(compiled), -1)
+                _, rows, nv, vecs = self._shard.search_host_any_of(q, alts, k, metric=self.metric, vectors=True)
+                off = self._shard.row_offset
+                if off:
+                    rows = np.where(rows >= 0, rows - off, rows)
+                return rows, vecs, nv
+        finally:
+            if self._hist is not None:
+                self._hist.labels(self.table_name, "any_of").observe(time.perf_counter() - t0)
+
     @_reading
     def adjacent(self, edges: Iterable[Any], query_embedding: Sequence[float], k: int,
                  filter: Optional[Dict[str, Any]] = None, *, as_arrays: bool = False, **kw) -> List[Content]:
-        """All rows adjacent through ``edges`` -- one filtered top-k per distinct
-        ``(field, value)`` edge, same query vector -- issued as ONE batched search (the
-        reference's adapter issues one CQL query per edge), then merged:
-        de-duplicated by row, best ``k`` by similarity."""
+        """The best ``k`` rows adjacent through ``edges`` (the reference's adapter issues one CQL query per
+        ``(field, value)`` edge with the same query vector, merges the hits, de-duplicates them and keeps the best
+        ``k`` by similarity).  Edges that are coded equalities go out as ONE search over the union of
+        their row sets (:meth:`_search_any_of` -- same rows, a row shared by several edges scored once); otherwise as
+        one batched search, a query per distinct edge, merged here."""
         pairs = []
         for e in edges:
             if isinstance(e, tuple):
@@ -935,8 +960,16 @@ class B200VectorStore:
                 flts.append({**base, fld: val})
         # edges that resolve to the same filter (an edge on a key the caller's filter already pins) are one search:
         # the results are merged by row below, and single-query groups keep the fan-out on the balanced kernel
-        flts = list({tuple(sorted((str(a), str(b)) for a, b in f.items())): f for f in flts}.values())
-        q = np.repeat(np.asarray(query_embedding, dtype=np.float32)[None, :], len(flts), axis=0)
+        try:
+            flts = list({tuple(f.items()): f for f in flts}.values())        # (base's items first, then the edge's: one order)
+        except TypeError:                                                    # an unhashable value in the caller's filter
+            flts = list({tuple(sorted((str(a), str(b)) for a, b in f.items())): f for f in flts}.values())
+        qv = np.asarray(query_embedding, dtype=np.float32)
+        union = self._search_any_of(qv, k, flts) if 2 <= len(flts) <= self.MAX_ALTERNATIVES else None
+        if union is not None:
+            rows1, vecs1, nv = union
+            return [self._content(int(rows1[j]), vecs1[j], as_arrays) for j in range(nv)]
+        q = np.repeat(qv[None, :], len(flts), axis=0)
         scores, rows, n_valid, vecs = self._search(q, k, flts, vectors=True)
         # merge the per-edge lists: one entry per row (its best score), best k by (score desc, row desc)
         valid = (np.arange(rows.shape[1])[None, :] < np.asarray(n_valid)[:, None]).ravel()

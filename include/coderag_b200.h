@@ -168,6 +168,19 @@ int crb_search_host_vectors(crb_index *index, const float *h_queries, int32_t ba
                             int32_t metric, const int32_t *h_filt, float *h_scores, int64_t *h_rows,
                             int32_t *h_n_valid, float *h_vectors, int32_t algo);
 
+/* ONE query under a DISJUNCTION of filters: h_filt int32 [n_alt, n_keys], a row passes when ANY of the n_alt rows (each an
+ * AND of equalities, as in crb_search_host) passes; at most 32 distinct alternatives.  Replaces the per-edge searches of
+ * the graph traversal's adjacent step: rag_worker/src/worker/services/graph_rag_retrievers.py:82-134 gives the
+ * retriever its edges ((repo, repo), (module, module), (file_path, file_path) ...), and graph-retriever's store adapter
+ * runs one filtered search per (field, value) edge with the same query vector, then keeps the best k of the merged,
+ * de-duplicated hits.  The best k of a union equals the best k of the per-set best k's, so this call returns exactly
+ * those rows while reading and scoring a row that lies in several sets (a file's rows are its module's and its
+ * repository's) once.  Results for the one query: h_scores fp32 [k], h_rows int64 [k], h_n_valid int32 [1];
+ * h_vectors fp32 [k, dim] (the hits' stored vectors) or NULL. */
+int crb_search_host_any_of(crb_index *index, const float *h_query, int32_t n_alt, const int32_t *h_filt,
+                           int32_t k, int32_t metric, float *h_scores, int64_t *h_rows,
+                           int32_t *h_n_valid, float *h_vectors);
+
 /* Cross-shard merge (no reference counterpart in-tree: the reference runs `replicas: 1`,
  * helm/values.yaml:113; this is the k-way merge a row-sharded store needs after the
  * all-gather of per-shard keys).  d_keys_in uint64 [n_lists, batch, k] -> the best k per

@@ -299,3 +299,108 @@ def test_a_code_every_row_carries_is_dropped_from_the_filter(monkeypatch):
     _, r7, _, _ = run([1, -1])
     assert r7[0, 0] == n
     sh.close()
+
+
+@pytest.mark.parametrize("d", [384, 768])
+def test_one_search_over_the_union_of_alternative_filters(d):
+    """crb_search_host_any_of: one query, a row passes when ANY alternative passes -- the adjacent() step of the graph
+    traversal.  Equal to the oracle under the OR of the alternatives' masks, and (ids, scores, vectors) to the
+    per-edge batch merged on the host; nested and overlapping sets, an alternative no row matches, one every row
+    matches, the 32-alternative limit, deleted rows, both metrics."""
+    from githubrepostorag_b200.index import DeviceShard
+    rng = np.random.default_rng(d)
+    n, k = 80_003, 8
+    rows16 = rng.standard_normal((n, d), dtype=np.float32).astype(np.float16)
+    repo = rng.integers(0, 6, n)
+    module = repo * 50 + rng.integers(0, 50, n)                 # a module lies in one repo
+    fpath = module * 200 + rng.integers(0, 200, n)              # a file in one module (60k values: an int32 column)
+    codes = np.stack([np.zeros(n, np.int64), repo, module, fpath]).astype(np.int32)
+    sh = DeviceShard.from_host(rows16, codes, device=0)
+    assert sh.code_widths == [1, 1, 2, 4]
+    q = rng.standard_normal(d, dtype=np.float32)
+    r0 = int(np.argmax(rows16.astype(np.float32) @ q))           # a strong hit: its repo / module / file are the edges
+
+    def mask_of(alt):
+        keep = np.ones(n, bool)
+        for m, w in enumerate(alt):
+            if w == -2:
+                keep[:] = False
+            elif w >= 0:
+                keep &= codes[m] == w
+        return keep
+
+    nested = [[0, repo[r0], -1, -1], [0, -1, module[r0], -1], [0, -1, -1, fpath[r0]]]
+    cases = {
+        "nested": nested,
+        "overlapping": [[-1, 1, -1, -1], [-1, -1, module[r0], -1], [-1, 2, -1, -1], [-1, 1, int(module[r0]), -1]],
+        "with an impossible one": nested + [[-2, -1, -1, -1]],
+        "all impossible": [[-2, -1, -1, -1], [-1, -2, -1, -1]],
+        "one matches everything": nested + [[0, -1, -1, -1]],
+        "single": [[-1, 3, -1, -1]],
+        "duplicates": [nested[1], nested[1], nested[2]],
+        "32 files": [[-1, -1, -1, int(v)] for v in np.unique(fpath)[:32]],
+    }
+    for metric, mode in (("cosine", oracle.MODE_COSINE), ("ip", oracle.MODE_DOT)):
+        for name, alts in cases.items():
+            f = np.asarray(alts, np.int32)
+            s_, r_, nv, vec = sh.search_host_any_of(q, f, k, metric=metric, vectors=True)
+            keep = np.zeros(n, bool)
+            for alt in alts:
+                keep |= mask_of(alt)
+            s_ref, r_ref = oracle.query_vectorised(q, rows16, k, keep=keep, mode=mode)
+            assert nv == len(r_ref) and r_[:nv].tolist() == r_ref.tolist(), (name, metric)
+            tol = 2e-6 * (1.0 if metric == "cosine" or not nv else float(np.abs(s_ref).max()) + 1.0)
+            assert np.allclose(s_[:nv], s_ref, rtol=1e-5, atol=tol)
+            assert np.array_equal(vec[:nv], rows16[r_[:nv]].astype(np.float32)) and not vec[nv:].any()
+            # the per-edge batch, merged as the adapter merges: same rows, same score bits
+            bs, br, bv = sh.search_host(np.repeat(q[None, :], len(alts), 0), k, metric=metric, filt=f)
+            best = {}
+            for i in range(len(alts)):
+                for j in range(int(bv[i])):
+                    best[int(br[i, j])] = bs[i, j]
+            top = sorted(best.items(), key=lambda t: (-t[1], -t[0]))[:k]
+            assert [r for r, _ in top] == r_[:nv].tolist(), (name, metric)
+            assert np.array_equal(np.asarray([s for _, s in top], np.float32).view(np.int32), s_[:nv].view(np.int32)), (name, metric)
+    with pytest.raises(RuntimeError, match="at most 32"):
+        sh.search_host_any_of(q, np.asarray([[-1, -1, -1, int(v)] for v in np.unique(fpath)[:33]], np.int32), k)
+    # a deleted row leaves the union
+    _, r_, nv, _ = sh.search_host_any_of(q, np.asarray(nested, np.int32), k, vectors=True)
+    sh.tombstone([int(r_[0])])
+    _, r2, nv2, _ = sh.search_host_any_of(q, np.asarray(nested, np.int32), k, vectors=True)
+    keep = mask_of(nested[0]) | mask_of(nested[1]) | mask_of(nested[2])
+    keep[int(r_[0])] = False
+    assert r2[:nv2].tolist() == oracle.query_vectorised(q, rows16, k, keep=keep)[1].tolist()
+    sh.close()
+
+
+def test_adjacent_takes_the_union_search_and_equals_the_per_edge_batch(monkeypatch):
+    """B200VectorStore.adjacent(): coded-equality edges go out as one union search; edges on list-valued keys keep the
+    per-edge batch.  Same Content list either way."""
+    from githubrepostorag_b200.vector_store import B200VectorStore
+    n, d, k = 6000, 64, 7
+    rng, emb, metas, ids = _corpus(23, n, d)
+    st = B200VectorStore(dim=d)
+    st.add_embeddings(ids, emb, [f"t{i}" for i in range(n)], metas)
+    q = rng.standard_normal(d, dtype=np.float32)
+    calls = []
+    real = B200VectorStore._search_any_of
+
+    def spy(self, *a, **kw):
+        out = real(self, *a, **kw)
+        calls.append(out is not None)
+        return out
+    monkeypatch.setattr(B200VectorStore, "_search_any_of", spy)
+    for edges, base in (([("repo", "r2"), ("module", "m5"), ("file_path", "src/f7.py")], {"namespace": "default"}),
+                        ([("owner", "o1"), ("symbol", "fn3"), ("repo", "r6")], None),
+                        ([("repo", "r2"), ("topics", "kafka")], {"namespace": "default"})):
+        calls.clear()
+        got = st.adjacent(edges, q.tolist(), k=k, filter=base)
+        took_union = calls == [True]
+        assert took_union == all(fld != "topics" for fld, _ in edges)
+        monkeypatch.setattr(B200VectorStore, "MAX_ALTERNATIVES", 0)
+        want = st.adjacent(edges, q.tolist(), k=k, filter=base)
+        monkeypatch.setattr(B200VectorStore, "MAX_ALTERNATIVES", 32)
+        assert [c.id for c in got] == [c.id for c in want] and [c.embedding for c in got] == [c.embedding for c in want]
+        flt = {"__any_of__": [[{fld: val} for fld, val in edges]], **(base or {})}
+        assert [c.id for c in got] == _expect(q, emb, metas, ids, k, flt)[0]
+    st.close()

@@ -210,13 +210,32 @@ def test_adjacent_searches_each_distinct_filter_once(lib, monkeypatch):
         return scores, rows, nv, np.zeros((b, k, 8), np.float32)
 
     class FakeShard:
+        row_offset = 0
+
         def fetch_rows(self, rows):
             return np.zeros((len(rows), 8), np.float32)
+
+        def search_host_any_of(self, q, filt, k, metric="cosine", vectors=False):
+            # the union search: rows passing ANY alternative (codes: -1 any, -2 impossible), best k
+            seen["alternatives"] = np.asarray(filt).copy()
+            codes = st.dictionary.encode_rows([st._rows.meta(r) for r in range(6)])
+            hit = [r for r in range(6) if any(all(w == -1 or (w >= 0 and codes[m, r] == w) for m, w in enumerate(alt))
+                                              for alt in filt)][:k]
+            rows = np.full(k, -1, np.int64)
+            rows[:len(hit)] = hit
+            return np.zeros(k, np.float32), rows, len(hit), np.zeros((k, 8), np.float32)
 
     monkeypatch.setattr(st, "_ensure_built", lambda: None)
     monkeypatch.setattr(st, "_search", fake_search)
     monkeypatch.setattr(st, "_shard", FakeShard(), raising=False)
     edges = [("namespace", "ns"), ("repo", "a"), ("repo", "a"), ("namespace", "other"), ("repo", "b")]
+    # coded-equality edges leave as ONE union search: four distinct alternatives, the contradicting one impossible
+    out = st.adjacent(edges, [0.5] * 8, k=4, filter={"namespace": "ns"})
+    alts = seen["alternatives"]
+    assert alts.shape == (4, st.dictionary.n_keys) and sum((a == -2).any() for a in alts) == 1
+    assert [c.id for c in out] == ["n0", "n1", "n2", "n3"] and "filters" not in seen
+    # the per-edge batch (what an edge on a list-valued key, or more than 32 edges, falls back to)
+    monkeypatch.setattr(st, "MAX_ALTERNATIVES", 0, raising=False)
     out = st.adjacent(edges, [0.5] * 8, k=4, filter={"namespace": "ns"})
     flt = seen["filters"]
     assert len(flt) == 4                                            # 5 edges: one repeated, none merged wrongly
