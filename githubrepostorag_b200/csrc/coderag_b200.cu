@@ -1717,7 +1717,8 @@ extern "C" int crb_search_host_any_of(crb_index* ix, const float* h_query, int32
                                       int32_t k, int32_t metric, float* h_scores, int64_t* h_rows,
                                       int32_t* h_n_valid, float* h_vectors) {
     if (n_alt < 1) return fail("n_alt must be >= 1");
-    if (!h_filt) return fail("NULL filter pointer passed to crb_search_host_any_of");
+    if (!ix) return fail("index is NULL");
+    if (!h_filt && ix->n_keys > 0) return fail("NULL filter pointer passed to crb_search_host_any_of");
     return search_host_impl(ix, h_query, 1, k, metric, h_filt, h_scores, h_rows, h_n_valid, h_vectors, 0, n_alt);
 }
 
