@@ -66,6 +66,7 @@ PROTOTYPES = {
                                        _vp, C.c_uint32, C.c_uint32]),
     "crb_search_exchange_host": (C.c_int, [_vp, _vp, _i32, _i32, _i32, _vp, _vp, _vp, _vp, _vp, _i32, _vp,
                                             C.c_uint32, C.c_uint32]),
+    "crb_search_exchange_host_any_of": (C.c_int, [_vp, _vp, _i32, _vp, _i32, _i32, _vp, _vp, _vp, _vp, C.c_uint32, C.c_uint32]),
     "crb_serve_post_search": (C.c_int, [_vp, _vp, _vp, _vp, _i32, _i32, _i32, _vp, _vp, _vp, _vp, _i32, _vp, _vp, _vp,
                                          C.c_double]),
     "crb_serve_next": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp]),

@@ -1132,7 +1132,8 @@ static int search_impl(crb_index* ix, const float* d_queries, int batch, int k, 
 // repository's too) is read and scored once.
 static int search_any_of_impl(crb_index* ix, const float* d_query, int n_alt, const int32_t* h_filt, int k, int metric,
                               float* d_scores, int64_t* d_rows, int32_t* d_n_valid, void* d_workspace,
-                              size_t workspace_bytes, cudaStream_t stream) {
+                              size_t workspace_bytes, cudaStream_t stream, const ExchangeDev* ex = nullptr,
+                              bool* folded = nullptr) {
     const int M = ix->n_keys;
     std::vector<std::array<int32_t, kMaxKeys>> alts;
     bool everything = false;
@@ -1153,13 +1154,13 @@ static int search_any_of_impl(crb_index* ix, const float* d_query, int n_alt, co
     }
     if (everything)
         return search_impl(ix, d_query, 1, k, metric, nullptr, d_scores, d_rows, d_n_valid, nullptr, d_workspace,
-                           workspace_bytes, 0, stream);
+                           workspace_bytes, 0, stream, ex, nullptr, folded);
     if (alts.size() <= 1) {
         std::array<int32_t, kMaxKeys> f;
         f.fill(CRB_FILT_IMPOSSIBLE);
         if (!alts.empty()) f = alts[0];
         return search_impl(ix, d_query, 1, k, metric, f.data(), d_scores, d_rows, d_n_valid, nullptr, d_workspace,
-                           workspace_bytes, 0, stream);
+                           workspace_bytes, 0, stream, ex, nullptr, folded);
     }
     if (alts.size() > size_t(kMaxFilters))
         return fail("at most %d distinct alternatives per call (got %zu)", kMaxFilters, alts.size());
@@ -1174,8 +1175,16 @@ static int search_any_of_impl(crb_index* ix, const float* d_query, int n_alt, co
     groups[0].filter = 0;
     groups[0].queries.assign(1, 0);
     const std::vector<int> slot_of_filter(1, 0);
+    // sharded: the one streaming launch also waits for the peers and merges (as a batch-1 search does)
+    ExchangeDev ex_fold;
+    if (ex && folded && ix->tune.k1_fold) {
+        ex_fold = *ex;
+        ex_fold.fold = 1;
+        ex = &ex_fold;
+        *folded = true;
+    }
     return launch_k1(ix, d_query, k, metric, groups, slot_of_filter, 1, ws, lists, d_scores, d_rows, d_n_valid, nullptr,
-                     stream);
+                     stream, ex);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -1804,11 +1813,13 @@ extern "C" int crb_search_exchange(crb_index* ix, const float* d_queries, int32_
                              expected_total, stream);
 }
 
-extern "C" int crb_search_exchange_host(crb_index* ix, const float* h_queries, int32_t batch, int32_t k,
-                                        int32_t metric, const int32_t* h_filt,
-                                        const uint32_t* const* h_row_mask_ptrs, float* h_scores, int64_t* h_rows,
-                                        int32_t* h_n_valid, int32_t algo, const crb_exchange* exch,
-                                        uint32_t call_index, uint32_t expected_total) {
+namespace crb {
+// n_alt > 0: ONE query (batch == 1) under a disjunction of n_alt filter rows (crb_search_exchange_host_any_of)
+static int search_exchange_host_impl(crb_index* ix, const float* h_queries, int32_t batch, int32_t k,
+                                     int32_t metric, const int32_t* h_filt,
+                                     const uint32_t* const* h_row_mask_ptrs, float* h_scores, int64_t* h_rows,
+                                     int32_t* h_n_valid, int32_t algo, const crb_exchange* exch,
+                                     uint32_t call_index, uint32_t expected_total, int32_t n_alt) {
     if (int rc = validate_search(ix, batch, k, metric)) return rc;
     if (!h_queries) return fail("NULL query pointer passed to crb_search_exchange_host");
     ExchangeDev ex;
@@ -1829,7 +1840,7 @@ extern "C" int crb_search_exchange_host(crb_index* ix, const float* h_queries, i
     const size_t off_scores = off_rows + round_up(r_bytes, 256);
     const size_t off_valid = off_scores + round_up(s_bytes, 256);
     const size_t io_bytes = off_valid + round_up(v_bytes, 256);
-    int n_filters = count_distinct_filters(h_filt, batch, ix->n_keys);
+    int n_filters = n_alt > 0 ? 1 : count_distinct_filters(h_filt, batch, ix->n_keys);
     if (h_row_mask_ptrs) n_filters = std::min<int>(kMaxFilters, n_filters + batch);   // masks split filter classes further
     const size_t ws_bytes = crb_workspace_bytes(ix, batch, k, n_filters);
     if (int rc = lane_reserve(l, ws_bytes, io_bytes, io_bytes)) return rc;
@@ -1850,8 +1861,11 @@ extern "C" int crb_search_exchange_host(crb_index* ix, const float* h_queries, i
     int64_t* d_rows = reinterpret_cast<int64_t*>(o_io + off_rows);
     int32_t* d_valid = reinterpret_cast<int32_t*>(o_io + off_valid);
     bool folded = false;
-    int rc = search_impl(ix, d_q, batch, k, metric, h_filt, d_scores, d_rows, d_valid, nullptr, l->d_ws, l->ws_cap,
-                         algo, l->stream, &ex, h_row_mask_ptrs, &folded);
+    int rc = n_alt > 0
+        ? search_any_of_impl(ix, d_q, n_alt, h_filt, k, metric, d_scores, d_rows, d_valid, l->d_ws, l->ws_cap, l->stream,
+                             &ex, &folded)
+        : search_impl(ix, d_q, batch, k, metric, h_filt, d_scores, d_rows, d_valid, nullptr, l->d_ws, l->ws_cap,
+                      algo, l->stream, &ex, h_row_mask_ptrs, &folded);
     if (!rc && !folded) rc = launch_merge_wait(ix, exch, ex, d_q, batch, k, metric, d_scores, d_rows, d_valid, nullptr,
                                                expected_total, l->stream);
     if (rc) { cudaStreamSynchronize(l->stream); return rc; }
@@ -1874,6 +1888,28 @@ extern "C" int crb_search_exchange_host(crb_index* ix, const float* h_queries, i
                             "the exchange counters are out of step -- reset the exchange on every rank", b);
     }
     return 0;
+}
+
+}  // namespace crb
+
+extern "C" int crb_search_exchange_host(crb_index* ix, const float* h_queries, int32_t batch, int32_t k,
+                                        int32_t metric, const int32_t* h_filt,
+                                        const uint32_t* const* h_row_mask_ptrs, float* h_scores, int64_t* h_rows,
+                                        int32_t* h_n_valid, int32_t algo, const crb_exchange* exch,
+                                        uint32_t call_index, uint32_t expected_total) {
+    return crb::search_exchange_host_impl(ix, h_queries, batch, k, metric, h_filt, h_row_mask_ptrs, h_scores, h_rows,
+                                          h_n_valid, algo, exch, call_index, expected_total, 0);
+}
+
+extern "C" int crb_search_exchange_host_any_of(crb_index* ix, const float* h_query, int32_t n_alt, const int32_t* h_filt,
+                                               int32_t k, int32_t metric, float* h_scores, int64_t* h_rows,
+                                               int32_t* h_n_valid, const crb_exchange* exch, uint32_t call_index,
+                                               uint32_t expected_total) {
+    if (n_alt < 1) return crb::fail("n_alt must be >= 1");
+    if (!ix) return crb::fail("index is NULL");
+    if (!h_filt && ix->n_keys > 0) return crb::fail("NULL filter pointer passed to crb_search_exchange_host_any_of");
+    return crb::search_exchange_host_impl(ix, h_query, 1, k, metric, h_filt, nullptr, h_scores, h_rows, h_n_valid, 0, exch,
+                                          call_index, expected_total, n_alt);
 }
 
 // ---------------------------------------------------------------------------------------------

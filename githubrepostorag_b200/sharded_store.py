@@ -40,7 +40,7 @@ from .index import MetadataDictionary
 from .vector_store import B200VectorStore, _Rows
 
 (CMD_SEARCH, CMD_SET_MASK, CMD_DROP_MASKS, CMD_FETCH, CMD_APPEND, CMD_TOMBSTONE, CMD_RESET, CMD_SHUTDOWN, CMD_STATE,
- CMD_RELEASE) = range(1, 11)
+ CMD_RELEASE, CMD_SEARCH_ANY) = range(1, 12)
 
 _HDR_WORDS = 32            # int32 header words after the sequence number
 _MAX_RANKS = N.MAX_PEERS
@@ -220,6 +220,24 @@ class CudaRankEngine:
             N.check(rc)
         return out
 
+    def search_any_of(self, query: np.ndarray, alts: np.ndarray, k: int, metric: int, dest_rank: int):
+        """Collective: ONE query, a row passes when any row of ``alts`` (int32 ``[n_alt, n_keys]``) passes
+        (``crb_search_exchange_host_any_of``).  ``(scores [1, k], rows [1, k], n_valid [1])`` on ``dest_rank``."""
+        lib, ex = N.load(), self.exchange
+        out, optr = None, (None, None, None)
+        if self.rank == dest_rank:
+            out = (np.empty((1, k), np.float32), np.empty((1, k), np.int64), np.empty((1,), np.int32))
+            optr = (out[0].ctypes.data, out[1].ctypes.data, out[2].ctypes.data)
+        q = np.ascontiguousarray(query, dtype=np.float32).reshape(-1)
+        a = np.ascontiguousarray(alts, dtype=np.int32)
+        ex.struct.dest_mask = 1 << dest_rank
+        call, total = ex.next_call(1)
+        rc = lib.crb_search_exchange_host_any_of(self.shard._h, q.ctypes.data, a.shape[0], a.ctypes.data if a.size else None,
+                                                 k, metric, optr[0], optr[1], optr[2], self._ex_ref, call, total)
+        if rc:
+            N.check(rc)
+        return out
+
     # ---- the request path in C (crb_serve_post_search / crb_serve_next): no Python between the command word and the launch
     def bind_control(self, ctl: "ControlBlock") -> None:
         import ctypes as C
@@ -338,8 +356,31 @@ class ShardedB200VectorStore(B200VectorStore):
     and every other rank calls :meth:`serve_forever`.  ``close()`` on rank 0 ends the peers' loops."""
 
     def _search_any_of(self, q, k, flts):
-        # the union search is a single-shard call; a sharded adjacent() step stays one batched, exchanged search
-        return None
+        """The union search over every rank's shard (``crb_search_exchange_host_any_of``), the hits' vectors fetched
+        from the ranks that hold them.  None (-> the per-edge batch) when an edge needs a row mask, the engine has no
+        union search, or the alternatives do not fit the command block."""
+        compiled = [self._compile_filter(f) for f in flts]
+        if any(extra or row is None for _, extra, row in compiled) or not hasattr(self.engine, "search_any_of") \
+                or len(compiled) > self.ctl.max_batch:
+            return None
+        alts = np.concatenate([row for _, _, row in compiled])
+        with self._gate.read(), self._cmd_lock:
+            ctl = self.ctl
+            ctl.queries[:self.dim] = np.asarray(q, dtype=np.float32).reshape(-1)
+            ctl.filt[:alts.size] = alts
+            self._post(CMD_SEARCH_ANY, batch=len(compiled), k=int(k), metric=self._metric_code())
+            try:
+                _, rows, nv = self._execute(CMD_SEARCH_ANY)
+            except RuntimeError:
+                # a peer that never published leaves the arrival counters out of step: realign before the next call
+                self._wait_acks()
+                self._post(CMD_RESET)
+                self._execute(CMD_RESET)
+                self._wait_acks()
+                raise
+        n = int(nv[0])
+        vecs = self._fetch_vectors([int(r) for r in rows[0, :n]])
+        return rows[0], vecs, n
 
     def __init__(self, engine, *, dictionary: Optional[MetadataDictionary] = None, embedding: Any = None,
                  id_fn: Optional[Callable[[int], str]] = None, meta_fn: Optional[Callable[[int], Dict[str, Any]]] = None,
@@ -499,6 +540,11 @@ class ShardedB200VectorStore(B200VectorStore):
             filt = ctl.filt[:b * nk].reshape(b, nk) if h[5] else None
             mids = ctl.mask_ids[:b] if h[6] else None
             return eng.search(q, k, h[3], filt, mids, h[4], 0)
+        if cmd == CMD_SEARCH_ANY:
+            # one query (the first of the query area), `batch` alternative filter rows: a row passes when any does
+            n_alt, k = h[1], h[2]
+            nk = self.dictionary.n_keys
+            return eng.search_any_of(ctl.queries[:self.dim], ctl.filt[:n_alt * nk].reshape(n_alt, nk), k, h[3], 0)
         if cmd == CMD_SET_MASK:
             trees = ctl.get_payload(int(h[7]))
             eng.set_mask(int(h[8]), trees[self.rank] if isinstance(trees, dict) else trees)

@@ -234,6 +234,14 @@ int crb_search_exchange_host(crb_index *index, const float *h_queries, int32_t b
                              float *h_scores, int64_t *h_rows, int32_t *h_n_valid, int32_t algo,
                              const crb_exchange *exchange, uint32_t call_index, uint32_t expected_total);
 
+/* crb_search_host_any_of over a row-sharded store: ONE query, a row passes when any of the n_alt filter rows passes;
+ * every rank searches the union inside its shard and the keys are exchanged and merged as in crb_search_exchange_host
+ * (one query per call: expected_total advances by 1). */
+int crb_search_exchange_host_any_of(crb_index *index, const float *h_query, int32_t n_alt, const int32_t *h_filt,
+                                    int32_t k, int32_t metric, float *h_scores, int64_t *h_rows,
+                                    int32_t *h_n_valid, const crb_exchange *exchange, uint32_t call_index,
+                                    uint32_t expected_total);
+
 /* The serving store's request path without the host language in it (no reference counterpart: the reference has one
  * worker process and no second GPU).  The ranks of a box share one block of host memory (POSIX shared memory, laid out
  * by the host side: githubrepostorag_b200/sharded_store.py::ControlBlock); `crb_ctl` says where things live in it.

@@ -157,6 +157,21 @@ def _store_worker(rank, world, port, out):
         assert [c.id for c in adj] == want
         for c in adj:
             assert np.array_equal(np.asarray(c.embedding, np.float32), rows16[int(c.id[4:])].astype(np.float32))
+        # edges that are coded equalities go out as ONE union search over every shard (crb_search_exchange_host_any_of):
+        # the same rows as the per-edge batch, and as the oracle under the OR of the edges
+        edges = [("repo", "r1"), ("module", "m17"), ("repo", "r4"), ("owner", "o0")]
+        adj = st.adjacent(edges, q[1].tolist(), k=k, filter={"owner": "o0"})
+        assert [c.id for c in adj] == expect(q[1], {"owner": "o0"})[0]                 # the owner edge is the caller's filter
+        adj = st.adjacent(edges[:3], q[1].tolist(), k=k, filter={"owner": "o0"})
+        want = expect(q[1], {"owner": "o0", "__any_of__": [[{"repo": "r1"}, {"module": "m17"}, {"repo": "r4"}]]})[0]
+        assert [c.id for c in adj] == want
+        for c in adj:
+            assert np.array_equal(np.asarray(c.embedding, np.float32), rows16[int(c.id[4:])].astype(np.float32))
+        type(st).MAX_ALTERNATIVES, keep_max = 0, type(st).MAX_ALTERNATIVES            # the per-edge batch
+        try:
+            assert [c.id for c in st.adjacent(edges[:3], q[1].tolist(), k=k, filter={"owner": "o0"})] == want
+        finally:
+            type(st).MAX_ALTERNATIVES = keep_max
         # the graph retriever over the sharded store (the reference's retriever.invoke(q, filter=...))
         from githubrepostorag_b200.retrievers import Eager, EagerGraphRetriever
 

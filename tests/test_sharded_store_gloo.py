@@ -61,6 +61,33 @@ class NumpyEngine:
             scores[i, :len(r)], rows[i, :len(r)], nv[i] = s, r, len(r)
         return scores, rows, nv
 
+    def search_any_of(self, q, alts, k, metric, dest):
+        keep = np.zeros(len(self.rows16), bool)
+        for alt in alts:
+            one = ~self.dead
+            for m, c in enumerate(alt):
+                if c == -2:
+                    one = np.zeros_like(one)
+                elif c >= 0:
+                    one = one & (self.codes[m] == c)
+            keep |= one
+        s, r = oracle.query_vectorised(np.asarray(q, np.float32), self.rows16, k, keep=keep, row_offset=self.off,
+                                       mode=oracle.MODE_COSINE if metric == 0 else oracle.MODE_DOT)
+        keys = np.zeros((1, k), np.int64)
+        keys[0, :len(r)] = pack_keys(s, r)
+        import torch
+        gathered = [torch.zeros((1, k), dtype=torch.int64) for _ in range(self.world)] if self.rank == dest else None
+        dist.gather(torch.from_numpy(keys), gathered, dst=dest)
+        if self.rank != dest:
+            return None
+        cand = np.sort(np.stack([g.numpy() for g in gathered]).view(np.uint64).reshape(-1))[::-1]
+        cand = cand[cand != 0][:k]
+        s, r = unpack_keys(cand.view(np.int64))
+        scores = np.full((1, k), -np.inf, np.float32)
+        rows = np.full((1, k), -1, np.int64)
+        scores[0, :len(r)], rows[0, :len(r)] = s, r
+        return scores, rows, np.asarray([len(r)], np.int32)
+
     def _eval(self, tree):
         n = len(self.rows16)
         kind = tree[0]
@@ -169,6 +196,13 @@ def _worker(rank, world, port, out):
         assert {int(i[4:]) >= hi for _, _, i in trip} == {True, False} or world == 1     # both shards contribute
         adj = st.adjacent({("repo", "r1"), ("topics", "kafka")}, q[2].tolist(), k=k)
         assert [c.id for c in adj] == expect(q[2], {"__any_of__": [[{"repo": "r1"}, {"topics": "kafka"}]]})[0]
+        # edges that are coded equalities travel as ONE union search (CMD_SEARCH_ANY), vectors fetched from their ranks
+        adj = st.adjacent([("repo", "r1"), ("owner", "o2"), ("repo", "r3")], q[3].tolist(), k=k, filter={"owner": "o2"})
+        want = expect(q[3], {"owner": "o2"})[0]              # (the owner edge repeats the caller's filter: the union is it)
+        assert [c.id for c in adj] == want
+        assert all(np.array_equal(np.asarray(c.embedding, np.float32), emb16[int(c.id[4:])].astype(np.float32)) for c in adj)
+        adj = st.adjacent([("repo", "r1"), ("repo", "r3")], q[3].tolist(), k=k)
+        assert [c.id for c in adj] == expect(q[3], {"__any_of__": [[{"repo": "r1"}, {"repo": "r3"}]]})[0]
         assert st.get([S.row_id(7), S.row_id(n - 1), "nope"])[1].content == f"text {n - 1}"
         st.release_peers()
         # writes: new rows go to the rank with room (the last one: the first is bounded by its neighbour's range)
