@@ -95,6 +95,7 @@ struct Tuning {
     int k2_gthr_every = 0;    // _K2_GTHR_EVERY: fixed re-read cadence of the bound (0 = schedule)
     int k2_prepass = 1;       // _K2_PREPASS: first accumulator tile read twice
     int zero_copy = 1;        // _ZEROCOPY: small results are written by the kernels straight into pinned host memory
+    int zone_maps = 1;        // _ZONE_MAPS: a single filtered row set is searched inside the row range its codes occupy
     int drop_trivial = 1;     // _DROP_TRIVIAL: drop filter codes that every row of the shard carries
     int k1_fold = 1;          // _K1_FOLD: sharded batch-1 calls merge in the streaming kernel's last CTA (one launch per rank)
     int k2_kprime = 16;       // candidates per list for k <= 10 (CRB_TUNING builds read _K2_KPRIME)
@@ -118,6 +119,7 @@ struct Tuning {
         t.k1_balanced = env("CODERAG_B200_K1_BALANCED", t.k1_balanced);
         t.k1_fold = env("CODERAG_B200_K1_FOLD", t.k1_fold);
         t.drop_trivial = env("CODERAG_B200_DROP_TRIVIAL", t.drop_trivial);
+        t.zone_maps = env("CODERAG_B200_ZONE_MAPS", t.zone_maps);
         t.zero_copy = env("CODERAG_B200_ZEROCOPY", t.zero_copy);
         t.k2_pair = env("CODERAG_B200_K2_PAIR", t.k2_pair);
         t.k2_minner = env("CODERAG_B200_K2_MINNER", t.k2_minner);
@@ -182,6 +184,10 @@ struct crb_index {
     // rows per code of the narrow columns (bin code + 1; bin 0 = key absent), counted when the columns are bound:
     // the plan's selectivity estimate (product of the constrained keys' frequencies)
     std::vector<uint32_t> hist[CRB_MAX_KEYS];
+    // first / last row carrying each code (same bins; valid where hist > 0): a filter's survivors lie inside the
+    // intersection of its codes' row ranges, and a code whose rows are one contiguous run (hist == last - first + 1: rows
+    // written repository by repository, or a shard clustered by its keys) needs no filter pass at all
+    std::vector<uint32_t> zone_first[CRB_MAX_KEYS], zone_last[CRB_MAX_KEYS];
     int64_t n_rows = 0;
     int32_t dim = 0;
     int32_t n_keys = 0;
@@ -235,23 +241,39 @@ static WsLayout ws_layout(const crb_index* ix, int batch, int k) {
     return L;
 }
 
-// Rows per code of one narrow column: hist[code + 1] (code -1 = key absent -> bin 0).
+// Per code of one narrow column (bin = code + 1; code -1 = key absent -> bin 0): how many rows carry it, the first and
+// the last such row.  One pass; int8 columns accumulate in shared memory.
 __global__ void __launch_bounds__(256) code_histogram_kernel(const void* __restrict__ col, int width, int64_t n,
-                                                             unsigned* __restrict__ hist) {
-    __shared__ unsigned s_h[130];
+                                                             unsigned* __restrict__ hist, unsigned* __restrict__ first,
+                                                             unsigned* __restrict__ last) {
+    __shared__ unsigned s_h[130], s_lo[130], s_hi[130];
     if (width == 1) {
-        for (int i = threadIdx.x; i < 130; i += blockDim.x) s_h[i] = 0u;
+        for (int i = threadIdx.x; i < 130; i += blockDim.x) { s_h[i] = 0u; s_lo[i] = 0xffffffffu; s_hi[i] = 0u; }
         __syncthreads();
     }
     for (int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < n;
          i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
-        if (width == 1) atomicAdd(&s_h[static_cast<int>(static_cast<const int8_t*>(col)[i]) + 1], 1u);
-        else atomicAdd(&hist[static_cast<int>(static_cast<const int16_t*>(col)[i]) + 1], 1u);
+        const unsigned r = static_cast<unsigned>(i);
+        if (width == 1) {
+            const int b = static_cast<int>(static_cast<const int8_t*>(col)[i]) + 1;
+            atomicAdd(&s_h[b], 1u);
+            atomicMin(&s_lo[b], r);
+            atomicMax(&s_hi[b], r);
+        } else {
+            const int b = static_cast<int>(static_cast<const int16_t*>(col)[i]) + 1;
+            atomicAdd(&hist[b], 1u);
+            atomicMin(&first[b], r);
+            atomicMax(&last[b], r);
+        }
     }
     if (width == 1) {
         __syncthreads();
         for (int i = threadIdx.x; i < 130; i += blockDim.x)
-            if (s_h[i]) atomicAdd(&hist[i], s_h[i]);
+            if (s_h[i]) {
+                atomicAdd(&hist[i], s_h[i]);
+                atomicMin(&first[i], s_lo[i]);
+                atomicMax(&last[i], s_hi[i]);
+            }
     }
 }
 
@@ -269,6 +291,37 @@ static double estimate_selectivity(const crb_index* ix, const int32_t* want) {
         sel *= bin < h.size() ? double(h[bin]) / double(ix->n_rows) : 0.0;
     }
     return sel;
+}
+
+// The rows a filter can match, from the per-code row ranges taken at bind time: survivors lie in [lo, hi) -- the
+// intersection of the constrained codes' ranges.  `exact`: every constrained code's rows are one contiguous run, so every
+// row of the intersection passes and the search is an UNFILTERED pass over [lo, hi) (no filter pass, no gather).  Rows
+// arrive repository by repository (ingest) or the shard was clustered by its keys (B200VectorStore.compact(cluster_by=));
+// on rows in random order the window is the whole shard and nothing changes.
+struct RowWindow {
+    int64_t lo = 0, hi = 0;
+    bool exact = false;
+};
+static RowWindow filter_window(const crb_index* ix, const int32_t* want) {
+    RowWindow w;
+    w.hi = ix->n_rows;
+    bool exact = true, any = false;
+    for (int m = 0; m < ix->n_keys; ++m) {
+        if (want[m] == CRB_FILT_ANY) continue;
+        any = true;
+        if (want[m] < 0) { w.lo = w.hi = 0; w.exact = true; return w; }       // impossible: no row
+        const std::vector<uint32_t>& h = ix->hist[m];
+        if (h.empty() || ix->zone_first[m].size() != h.size()) { exact = false; continue; }   // no ranges for this key
+        const size_t bin = size_t(want[m]) + 1;
+        if (bin >= h.size() || h[bin] == 0) { w.lo = w.hi = 0; w.exact = true; return w; }     // no row carries the code
+        const int64_t lo = ix->zone_first[m][bin], hi = int64_t(ix->zone_last[m][bin]) + 1;
+        w.lo = std::max(w.lo, lo);
+        w.hi = std::min(w.hi, hi);
+        if (int64_t(h[bin]) != hi - lo) exact = false;
+    }
+    if (w.hi < w.lo) w.hi = w.lo;
+    w.exact = any && exact;
+    return w;
 }
 
 // cuTensorMapEncodeTiled through the runtime's driver entry point (no link-time libcuda).
@@ -426,7 +479,10 @@ struct QueryGroup {
 static int launch_k1(const crb_index* ix, const float* d_queries, int k, int metric,
                      const std::vector<QueryGroup>& groups, const std::vector<int>& slot_of_filter,
                      int nq, uint8_t* ws, const uint32_t* lists, float* d_scores, int64_t* d_rows,
-                     int32_t* d_n_valid, uint64_t* d_keys, cudaStream_t stream, const ExchangeDev* ex = nullptr) {
+                     int32_t* d_n_valid, uint64_t* d_keys, cudaStream_t stream, const ExchangeDev* ex = nullptr,
+                     const RowWindow* win = nullptr) {
+    // win: the launch sees rows [lo, hi) as its shard (list entries, if any, are relative to lo)
+    const int64_t w_lo = win ? win->lo : 0, w_rows = win ? win->hi - win->lo : ix->n_rows;
     K1Choice c;
     if (int rc = k1_choose(ix, nq, k, &c)) return rc;
     const K1Fn fn = c.fn;
@@ -439,8 +495,8 @@ static int launch_k1(const crb_index* ix, const float* d_queries, int k, int met
         const int ng = static_cast<int>(std::min<size_t>(kMaxGroups, groups.size() - g0));
         K1Params p;
         memset(&p, 0, sizeof p);
-        p.rows = ix->rows;
-        p.inv_norm = ix->inv_norm;
+        p.rows = ix->rows + w_lo * ix->dim;
+        p.inv_norm = ix->inv_norm + w_lo;
         p.queries = d_queries;
         p.lists = lists;
         p.list_counts = reinterpret_cast<const uint32_t*>(ws + kWsCountsOffset);
@@ -450,9 +506,9 @@ static int launch_k1(const crb_index* ix, const float* d_queries, int k, int met
         p.out_rows = d_rows;
         p.out_nvalid = d_n_valid;
         p.out_keys = d_keys;
-        p.n_rows = ix->n_rows;
+        p.n_rows = w_rows;
         p.list_stride = list_stride_of(ix);
-        p.row_offset = static_cast<uint32_t>(ix->row_offset);
+        p.row_offset = static_cast<uint32_t>(ix->row_offset + w_lo);
         p.dim = ix->dim;
         p.k = k;
         p.metric = metric;
@@ -465,7 +521,7 @@ static int launch_k1(const crb_index* ix, const float* d_queries, int k, int met
         }
         // grid.x: fill the machine once across all groups, but never more CTAs than there is
         // work for, and never more per-CTA lists than the scratch region or the merge can hold.
-        const int64_t work = (ix->n_rows + int64_t(kK1Warps) * rows_per_warp_iter * 2 - 1) /
+        const int64_t work = (w_rows + int64_t(kK1Warps) * rows_per_warp_iter * 2 - 1) /
                              (int64_t(kK1Warps) * rows_per_warp_iter * 2);
         int64_t gx = std::max<int64_t>(resident / ng, 16);
         gx = std::min<int64_t>(gx, std::max<int64_t>(work, 1));
@@ -874,26 +930,29 @@ static int launch_k2(crb_index* ix, const float* d_queries, int batch, int k, in
 // The filter pass: survivor lists (and, for the tensor-core plan, pass-bit masks) of `n` filters into the workspace.
 // any_of: the filters are alternatives of ONE row set -- a row that passes any of them lands in list 0, once.
 static int launch_k3(const crb_index* ix, const std::array<int32_t, kMaxKeys>* filters, const uint32_t* const* filter_masks,
-                     int n, bool any_of, uint8_t* ws, uint32_t* lists, uint32_t* masks, cudaStream_t stream) {
+                     int n, bool any_of, uint8_t* ws, uint32_t* lists, uint32_t* masks, cudaStream_t stream,
+                     const RowWindow* win = nullptr) {
+    // win (lo a multiple of 32; no K2 masks): only rows [lo, hi) are tested, the list entries are relative to lo
+    const int64_t w_lo = win ? win->lo : 0, w_rows = win ? win->hi - win->lo : ix->n_rows;
     const int M = ix->n_keys;
     K3Params kp;
     memset(&kp, 0, sizeof kp);
     for (int m = 0; m < M; ++m) {
-        kp.cols[m] = ix->cols[m];
+        kp.cols[m] = ix->cols[m] ? static_cast<const uint8_t*>(ix->cols[m]) + w_lo * ix->width[m] : nullptr;
         kp.width[m] = ix->width[m];
-        kp.vec_ok[m] = reinterpret_cast<uintptr_t>(ix->cols[m]) % 16 == 0 ? 1 : 0;
+        kp.vec_ok[m] = reinterpret_cast<uintptr_t>(kp.cols[m]) % 16 == 0 ? 1 : 0;
     }
     kp.lists = lists;
     kp.counts = reinterpret_cast<uint32_t*>(ws + kWsCountsOffset);
     kp.masks = masks;
     kp.mask_stride = mask_stride_of(ix);
-    kp.n_rows = ix->n_rows;
+    kp.n_rows = w_rows;
     kp.list_stride = list_stride_of(ix);
     kp.n_keys = M;
     kp.n_filters = n;
     kp.any_of = any_of ? 1 : 0;
     for (int f = 0; f < n; ++f) {
-        kp.extra[f] = filter_masks ? filter_masks[f] : nullptr;
+        kp.extra[f] = filter_masks && filter_masks[f] ? filter_masks[f] + (w_lo >> 5) : nullptr;
         for (int m = 0; m < kMaxKeys; ++m) {
             kp.want[f][m] = m < M ? filters[f][m] : CRB_FILT_ANY;
             if (m < M && filters[f][m] != CRB_FILT_ANY) kp.used_keys |= (1u << m);
@@ -903,7 +962,7 @@ static int launch_k3(const crb_index* ix, const std::array<int32_t, kMaxKeys>* f
         if ((kp.used_keys >> m) & 1u) kp.ukeys[kp.n_used++] = static_cast<uint8_t>(m);
     CRB_CUDA(cudaMemsetAsync(ws + kWsCountsOffset, 0, kMaxFilters * sizeof(uint32_t), stream));
     const int64_t rows_per_block = int64_t(kK3Threads) * kK3RowsPerThread;
-    const unsigned blocks = static_cast<unsigned>((ix->n_rows + rows_per_block - 1) / rows_per_block);
+    const unsigned blocks = static_cast<unsigned>((w_rows + rows_per_block - 1) / rows_per_block);
     if (blocks > 0) {
         k3_filter_kernel<<<blocks, kK3Threads, 0, stream>>>(kp);
         CRB_LAUNCH_CHECK();
@@ -983,13 +1042,48 @@ static int search_impl(crb_index* ix, const float* d_queries, int batch, int k, 
     // (measured, profiles/fused_sweep.py, fused vs K3 + K1: 10M x 1024 at 100 / 10 / 1 / 0.1 % passing 3.03 vs 3.44 ms, 368 vs
     //  394 us, 70 vs 83 us, 36 vs 48 us; 10M x 768: 2.32 vs 2.46 ms, 289 vs 289, 56 vs 65, 27 vs 40 us; 1M x 384: 195 vs 138,
     //  38 vs 35, 19.5 vs 24.8, 20 vs 25 us.)
+    // ONE filtered row set for the whole call (a filtered query, or a group of queries under one filter): search inside
+    // the row range its codes occupy.  Where every row of that range passes (each code's rows are one contiguous run),
+    // the search is an unfiltered streaming pass over the range: no filter pass, no gather.
+    RowWindow win;
+    const RowWindow* winp = nullptr;
+    bool one_row_set = F == 1 && batch <= nq_group && algo != 2 && ix->n_rows > 0 && ix->tune.zone_maps;
+    for (int b = 0; b < batch && one_row_set; ++b) one_row_set = fid[b] == 0;
+    if (one_row_set) {
+        win = filter_window(ix, filters[0].data());
+        if (filter_masks[0]) win.exact = false;
+        if (win.exact) {
+            std::vector<QueryGroup> groups(1);
+            groups[0].filter = -1;
+            for (int b = 0; b < batch; ++b) groups[0].queries.push_back(b);
+            ExchangeDev ex_fold;
+            const ExchangeDev* ex_k1 = ex;
+            if (ex && folded && ix->tune.k1_fold) {       // sharded: this one launch also waits for the peers and merges
+                ex_fold = *ex;
+                ex_fold.fold = 1;
+                ex_k1 = &ex_fold;
+                *folded = true;
+            }
+            return launch_k1(ix, d_queries, k, metric, groups, std::vector<int>(), batch <= 1 ? 1 : (batch <= 2 ? 2 : 4), ws,
+                             lists, d_scores, d_rows, d_n_valid, d_keys, stream, ex_k1, &win);
+        }
+        // a range that leaves out at least half the shard (codes in random order span all of it: nothing to gain, and
+        // the fused kernel below is the better plan there)
+        if ((win.hi - win.lo) * 2 <= ix->n_rows) {
+            win.lo &= ~int64_t(511);           // whole mask words / 16-byte column loads
+            winp = &win;
+        }
+    }
+    // (inside a narrowed row range the survivors tend to come in runs -- that is why the range is narrow -- and the fused
+    //  kernel hands whole 512-row stripes to single warps: 10M x 1024 clustered by its filter keys, 1 % passing as ONE run
+    //  inside a 17 % range: 258 us fused against the list path's even split.  A narrowed range takes the filter pass + gather.)
     bool use_fused = false;
-    if (batch == 1 && F == 1 && ch <= 4 && algo != 2 && ix->n_rows > 0 && ix->tune.k1_fused != 0 &&
+    if (batch == 1 && F == 1 && ch <= 4 && algo != 2 && ix->n_rows > 0 && ix->tune.k1_fused != 0 && !winp &&
         fused_eligible(ix, filters[0].data())) {
         if (ix->tune.k1_fused > 0) use_fused = true;
         else {
             // wide rows (dim > 512): the fused kernel wins at every selectivity measured; short rows: only when
-            // few rows pass (its per-row queueing costs more than the streaming kernel's whole row step)
+            // few of the scanned rows pass (its per-row queueing costs more than the streaming kernel's whole row step)
             const double est = estimate_selectivity(ix, filters[0].data());
             use_fused = est >= 0.0 && est <= (ch >= 3 ? 1.0 : 0.03);
         }
@@ -1036,7 +1130,7 @@ static int search_impl(crb_index* ix, const float* d_queries, int batch, int k, 
         if (f_hi > f_lo) {
             for (int f = f_lo; f < f_hi; ++f) slot_of_filter[f] = f - f_lo;
             if (int rc = launch_k3(ix, filters.data() + f_lo, filter_masks.data() + f_lo, f_hi - f_lo, false, ws, lists,
-                                   any_k2_filtered ? masks : nullptr, stream))
+                                   any_k2_filtered ? masks : nullptr, stream, winp))
                 return rc;
         }
 
@@ -1115,7 +1209,7 @@ static int search_impl(crb_index* ix, const float* d_queries, int batch, int k, 
             int rc = balanced ? launch_k1_balanced(ix, d_queries, k, metric, groups, slot_of_filter, ws, lists, d_scores,
                                                    d_rows, d_n_valid, d_keys, stream, ex)
                               : launch_k1(ix, d_queries, k, metric, groups, slot_of_filter, nq, ws, lists, d_scores,
-                                          d_rows, d_n_valid, d_keys, stream, ex_k1);
+                                          d_rows, d_n_valid, d_keys, stream, ex_k1, winp);
             if (rc) return rc;
         }
         first = false;
@@ -1169,10 +1263,42 @@ static int search_any_of_impl(crb_index* ix, const float* d_query, int n_alt, co
     if (workspace_bytes < L.filt + L.per_filter)
         return fail("workspace too small for one survivor list: need %zu bytes", L.filt + L.per_filter);
     uint32_t* lists = reinterpret_cast<uint32_t*>(ws + L.filt);
-    if (int rc = launch_k3(ix, alts.data(), nullptr, static_cast<int>(alts.size()), true, ws, lists, nullptr, stream))
-        return rc;
+    // the union lies inside the hull of the alternatives' row ranges; when every alternative is a contiguous run and the
+    // runs join up into one (a file inside its module inside its repository), the union IS that range
+    RowWindow hull;
+    const RowWindow* winp = nullptr;
+    bool exact_union = false;
+    if (ix->tune.zone_maps && ix->n_rows > 0) {
+        std::vector<std::pair<int64_t, int64_t>> runs;
+        bool all_exact = true;
+        hull.lo = ix->n_rows;
+        hull.hi = 0;
+        for (const auto& a : alts) {
+            const RowWindow w = filter_window(ix, a.data());
+            if (w.hi <= w.lo) continue;                       // this alternative matches no row
+            all_exact &= w.exact;
+            runs.emplace_back(w.lo, w.hi);
+            hull.lo = std::min(hull.lo, w.lo);
+            hull.hi = std::max(hull.hi, w.hi);
+        }
+        if (runs.empty()) { hull.lo = hull.hi = 0; exact_union = true; }
+        else if (all_exact) {
+            std::sort(runs.begin(), runs.end());
+            int64_t reach = runs[0].second;
+            exact_union = true;
+            for (size_t i = 1; i < runs.size() && exact_union; ++i) {
+                if (runs[i].first > reach) exact_union = false;          // a gap: rows between the runs do not pass
+                reach = std::max(reach, runs[i].second);
+            }
+        }
+        if (!exact_union) hull.lo &= ~int64_t(511);
+        if (exact_union || (hull.hi - hull.lo) * 2 <= ix->n_rows) winp = &hull;
+    }
+    if (!exact_union)
+        if (int rc = launch_k3(ix, alts.data(), nullptr, static_cast<int>(alts.size()), true, ws, lists, nullptr, stream, winp))
+            return rc;
     std::vector<QueryGroup> groups(1);
-    groups[0].filter = 0;
+    groups[0].filter = exact_union ? -1 : 0;
     groups[0].queries.assign(1, 0);
     const std::vector<int> slot_of_filter(1, 0);
     // sharded: the one streaming launch also waits for the peers and merges (as a batch-1 search does)
@@ -1184,7 +1310,7 @@ static int search_any_of_impl(crb_index* ix, const float* d_query, int n_alt, co
         *folded = true;
     }
     return launch_k1(ix, d_query, k, metric, groups, slot_of_filter, 1, ws, lists, d_scores, d_rows, d_n_valid, nullptr,
-                     stream, ex);
+                     stream, ex, winp);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -1387,6 +1513,8 @@ static int bind_buffers(crb_index* ix, const void* d_rows_f16, const float* d_in
         ix->cols[m] = d_codes ? d_codes + int64_t(m) * code_stride : nullptr;
         ix->width[m] = 4;
         ix->hist[m].clear();
+        ix->zone_first[m].clear();
+        ix->zone_last[m].clear();
     }
     ix->n_rows = n_rows;
     ix->k2_ok = false;
@@ -1492,25 +1620,38 @@ extern "C" int crb_index_rebind_columns(crb_index* ix, const void* d_rows_f16, c
     DeviceGuard guard(ix->device);
     CRB_CUDA(guard.status);
     if (int rc = bind_buffers(ix, d_rows_f16, d_inv_norm, nullptr, n_rows, n_rows)) return rc;
-    unsigned* d_hist = nullptr;
+    unsigned* d_hist = nullptr;            // [3][bins]: counts, first rows, last rows
+    constexpr size_t kMaxBins = 32770;
     for (int m = 0; m < ix->n_keys; ++m) {
         ix->cols[m] = h_code_cols[m];
         ix->width[m] = static_cast<uint8_t>(h_code_widths[m]);
         ix->hist[m].clear();
+        ix->zone_first[m].clear();
+        ix->zone_last[m].clear();
         if (h_code_widths[m] > 2 || n_rows == 0) continue;
-        const size_t bins = h_code_widths[m] == 1 ? 130 : 32770;
-        if (!d_hist) CRB_CUDA(cudaMalloc(&d_hist, 32770 * sizeof(unsigned)));
+        const size_t bins = h_code_widths[m] == 1 ? 130 : kMaxBins;
+        if (!d_hist) CRB_CUDA(cudaMalloc(&d_hist, 3 * kMaxBins * sizeof(unsigned)));
         cudaError_t e = cudaMemset(d_hist, 0, bins * sizeof(unsigned));
+        if (e == cudaSuccess) e = cudaMemset(d_hist + kMaxBins, 0xff, bins * sizeof(unsigned));
+        if (e == cudaSuccess) e = cudaMemset(d_hist + 2 * kMaxBins, 0, bins * sizeof(unsigned));
         if (e == cudaSuccess) {
             code_histogram_kernel<<<static_cast<unsigned>(std::min<int64_t>((n_rows + 255) / 256, int64_t(ix->sm_count) * 8)), 256>>>(
-                h_code_cols[m], h_code_widths[m], n_rows, d_hist);
+                h_code_cols[m], h_code_widths[m], n_rows, d_hist, d_hist + kMaxBins, d_hist + 2 * kMaxBins);
             g_launches.fetch_add(1, std::memory_order_relaxed);
             ix->hist[m].resize(bins);
+            ix->zone_first[m].resize(bins);
+            ix->zone_last[m].resize(bins);
             e = cudaMemcpy(ix->hist[m].data(), d_hist, bins * sizeof(unsigned), cudaMemcpyDeviceToHost);
+            if (e == cudaSuccess)
+                e = cudaMemcpy(ix->zone_first[m].data(), d_hist + kMaxBins, bins * sizeof(unsigned), cudaMemcpyDeviceToHost);
+            if (e == cudaSuccess)
+                e = cudaMemcpy(ix->zone_last[m].data(), d_hist + 2 * kMaxBins, bins * sizeof(unsigned), cudaMemcpyDeviceToHost);
         }
         if (e != cudaSuccess) {
             cudaFree(d_hist);
             ix->hist[m].clear();
+            ix->zone_first[m].clear();
+            ix->zone_last[m].clear();
             return fail("code histogram failed: %s", cudaGetErrorString(e));
         }
     }

@@ -453,7 +453,7 @@ class ShardedB200VectorStore(B200VectorStore):
     def __len__(self) -> int:
         return len(self._rows) - self._rows.n_dead
 
-    def compact(self) -> None:
+    def compact(self, cluster_by=None) -> None:
         raise NotImplementedError("compaction of a sharded store is not implemented (tombstoned rows are never returned)")
 
     def save(self, path: str) -> None:

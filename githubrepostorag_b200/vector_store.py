@@ -377,18 +377,33 @@ class B200VectorStore:
         if r.n_dead > 1024 and r.n_dead > len(r.ids) - r.n_dead:
             self.compact()
 
-    def compact(self) -> None:
-        """Drop tombstoned rows (device-side gather of the live rows into fresh buffers)."""
+    def compact(self, cluster_by: Optional[Sequence[str]] = None) -> None:
+        """Drop tombstoned rows (device-side gather of the live rows into fresh buffers).
+
+        ``cluster_by``: also ORDER the rows by these coded keys, outermost first (``("repo", "module", "file_path")``;
+        ties keep their insertion order).  Rows that share a code then form one contiguous run, the shard's per-code
+        row ranges (taken when the columns are bound) become exact, and a search filtered on such keys -- every
+        traversal edge of the reference is one -- is an unfiltered streaming pass over the run: no filter pass, no
+        gather.  Row numbers change, ids do not; rows appended later land at the end and merely widen a range."""
         import torch
         with self._gate.write():
             r = self._rows
             if self._pending_emb or self._pending_dead:
                 self._flush()
-            if r.id_fn or self._shard is None or r.n_dead == 0:
+            if r.id_fn or self._shard is None or (r.n_dead == 0 and not cluster_by):
                 return
             live = [i for i, rid in enumerate(r.ids) if rid is not None]
-            idx = torch.as_tensor(live, dtype=torch.int64, device=self._shard.device)
             old = self._shard
+            if cluster_by and live and old.codes is not None:
+                cols = []
+                for key in cluster_by:
+                    pos = self.dictionary._pos.get(key)
+                    if pos is None:
+                        raise ValueError(f"cluster_by: {key!r} is not a coded key of this store ({self.dictionary.keys})")
+                    cols.append(old.codes[pos][:old.n_rows].cpu().numpy()[live])
+                order = np.lexsort(tuple(reversed(cols)))            # last key of lexsort is the primary one
+                live = [live[i] for i in order]
+            idx = torch.as_tensor(live, dtype=torch.int64, device=self._shard.device)
             rows = old.rows.index_select(0, idx).contiguous()
             inv = old.inv_norm.index_select(0, idx).contiguous()
             codes = None if old.codes is None else [c.index_select(0, idx).contiguous() for c in old.codes]

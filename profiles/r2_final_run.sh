@@ -1,6 +1,11 @@
 set -x
-timeout 900 python -m pytest tests -m gpu -x -q > gpurun_out/r2b_pytest.log 2>&1; echo "pytest rc=$?" >> gpurun_out/r2b_pytest.log
-tail -5 gpurun_out/r2b_pytest.log
-timeout 300 python profiles/invoke_latency.py > gpurun_out/r2b_invoke_latency.jsonl 2> gpurun_out/r2b_invoke_latency.err; cat gpurun_out/r2b_invoke_latency.jsonl
-timeout 250 python profiles/invoke_split.py > gpurun_out/r2b_invoke_split.jsonl 2> gpurun_out/r2b_invoke_split.err; cat gpurun_out/r2b_invoke_split.jsonl
-timeout 100 python profiles/invoke_once.py && timeout 300 ncu --metrics gpu__time_duration.sum --clock-control none -c 3000 --csv --log-file gpurun_out/r2b_invoke_launches.csv python profiles/invoke_once.py > gpurun_out/r2b_invoke_ncu.log 2>&1
+timeout 900 python -m pytest tests -m gpu -x -q > gpurun_out/r2c_pytest.log 2>&1; echo "pytest rc=$?" >> gpurun_out/r2c_pytest.log
+tail -4 gpurun_out/r2c_pytest.log
+timeout 200 python profiles/zone_probe.py > gpurun_out/r2c_zone_probe.json 2> gpurun_out/r2c_zone_probe.err; cat gpurun_out/r2c_zone_probe.json; tail -2 gpurun_out/r2c_zone_probe.err
+timeout 600 python bench.py > gpurun_out/r2c_bench_n1.json 2> gpurun_out/r2c_bench_n1.err; python - <<'PY'
+import json
+d=json.loads(open('gpurun_out/r2c_bench_n1.json').read().strip().splitlines()[-1])
+print(d['value'], d['ms_per_step'], d['e2e']['value'], d.get('parity_check'), d['roofline']['frac'], d.get('clocks'))
+for k,v in d.get('configs',{}).items(): print(k, v['ms_median'], v['roofline']['frac'], v['parity_check']['ok'], v['gpu_launches'])
+PY
+tail -3 gpurun_out/r2c_bench_n1.err

@@ -277,12 +277,14 @@ def test_a_code_every_row_carries_is_dropped_from_the_filter(monkeypatch):
     s_ref, r_ref = oracle.query_vectorised(q[0], rows16, k, keep=keep)
     assert r2[0].tolist() == r_ref.tolist()
     monkeypatch.setenv("CODERAG_B200_DROP_TRIVIAL", "0")
+    monkeypatch.setenv("CODERAG_B200_ZONE_MAPS", "0")          # (a code's row range covering the shard says the same thing)
     sh.reload_tuning()
     s3, r3, v3, l3 = run([0, -1])
     s4, r4, v4, _ = run([0, 7])
     assert l3 > l1 and np.array_equal(r3, r1) and np.array_equal(s3.view(np.int32), s1.view(np.int32))
     assert np.array_equal(r4, r2) and np.array_equal(s4.view(np.int32), s2.view(np.int32))
     monkeypatch.delenv("CODERAG_B200_DROP_TRIVIAL")
+    monkeypatch.delenv("CODERAG_B200_ZONE_MAPS")
     sh.reload_tuning()
     # a deleted row never comes back, filter dropped or not
     top = int(r1[0, 0])
@@ -294,8 +296,14 @@ def test_a_code_every_row_carries_is_dropped_from_the_filter(monkeypatch):
     # one row of another namespace: the predicate constrains again, and that row is filtered out
     extra = (q[0] * 3).astype(np.float16)[None, :]     # would be the best hit
     sh.append(extra, np.asarray([[1], [7]], np.int32))
-    _, r6, _, l6 = run([0, -1])
-    assert l6 > l0 and n not in r6[0].tolist() and r6[0].tolist() == r5[0].tolist()
+    _, r6, _, l6 = run([0, -1])          # (namespace 0 is still one run, rows [0, n): a streaming pass over it)
+    assert l6 == l0 and n not in r6[0].tolist() and r6[0].tolist() == r5[0].tolist()
+    monkeypatch.setenv("CODERAG_B200_ZONE_MAPS", "0")          # without row ranges the filter pass is back
+    sh.reload_tuning()
+    _, r6b, _, l6b = run([0, -1])
+    monkeypatch.delenv("CODERAG_B200_ZONE_MAPS")
+    sh.reload_tuning()
+    assert l6b > l0 and r6b[0].tolist() == r6[0].tolist()
     _, r7, _, _ = run([1, -1])
     assert r7[0, 0] == n
     sh.close()
@@ -403,4 +411,139 @@ def test_adjacent_takes_the_union_search_and_equals_the_per_edge_batch(monkeypat
         assert [c.id for c in got] == [c.id for c in want] and [c.embedding for c in got] == [c.embedding for c in want]
         flt = {"__any_of__": [[{fld: val} for fld, val in edges]], **(base or {})}
         assert [c.id for c in got] == _expect(q, emb, metas, ids, k, flt)[0]
+    st.close()
+
+
+def _clustered(rng, n, d):
+    """Rows ordered repository by repository (a module lies in one repository, a file in one module), plus a key that
+    is scattered (`kind`) and one with a single value (`namespace`)."""
+    rows16 = rng.standard_normal((n, d), dtype=np.float32).astype(np.float16)
+    repo = rng.integers(0, 12, n)
+    module = repo * 40 + rng.integers(0, 40, n)
+    order = np.lexsort((module, repo))
+    repo, module = repo[order], module[order]
+    kind = rng.integers(0, 3, n)
+    codes = np.stack([np.zeros(n, np.int64), repo, module, kind]).astype(np.int32)
+    return rows16, codes
+
+
+@pytest.mark.parametrize("d", [384, 1024])
+def test_filters_on_contiguous_codes_are_range_scans(d, monkeypatch):
+    """Per-code row ranges (taken at bind time): a filter whose codes each occupy one contiguous run is an UNFILTERED
+    pass over the intersection of the runs -- no filter pass (launch counts), same bits as with the ranges switched off,
+    same rows as the oracle; a filter that also names a scattered key is filtered inside the range; unions of runs that
+    join up are one range; an append at the end widens a range and everything stays right."""
+    from githubrepostorag_b200 import _native as N
+    from githubrepostorag_b200.index import DeviceShard
+    rng = np.random.default_rng(d + 1)
+    n, k = 120_007, 10
+    rows16, codes = _clustered(rng, n, d)
+    sh = DeviceShard.from_host(rows16, codes, device=0, capacity=n + 64)
+    q = rng.standard_normal((2, d), dtype=np.float32)
+
+    def keep_of(want, cds=codes):
+        keep = np.ones(cds.shape[1], bool)
+        for m, w in enumerate(want):
+            if w >= 0:
+                keep &= cds[m] == w
+        return keep
+
+    def run(fn):
+        out = {}
+        for z in ("1", "0"):
+            monkeypatch.setenv("CODERAG_B200_ZONE_MAPS", z)
+            sh.reload_tuning()
+            before = N.launch_count()
+            res = fn()
+            out[z] = (res, N.launch_count() - before)
+        monkeypatch.delenv("CODERAG_B200_ZONE_MAPS")
+        sh.reload_tuning()
+        return out
+
+    plain = run(lambda: sh.search_host(q[:1], k))["1"][1]            # launches of an unfiltered host search
+    r5, m5 = 5, int(codes[2][codes[1] == 5][100])
+    cases = [([0, r5, -1, -1], True), ([-1, r5, m5, -1], True), ([-1, -1, m5, -1], True), ([-1, r5, -1, 2], False),
+             ([-1, -1, m5, 1], False), ([-1, 3, m5, -1], True),      # a module of another repository: empty intersection
+             ([-1, 11, -1, -1], True), ([-1, 0, -1, 0], False)]
+    for want, exact in cases:
+        for b in (1, 2):
+            f = np.tile(np.asarray([want], np.int32), (b, 1))
+            out = run(lambda: sh.search_host(q[:b], k, filt=f))
+            (s1, r1, v1), l1 = out["1"]
+            (s0, r0, v0), l0 = out["0"]
+            assert np.array_equal(r1, r0) and np.array_equal(v1, v0) and np.array_equal(s1.view(np.int32), s0.view(np.int32)), want
+            for i in range(b):
+                s_ref, r_ref = oracle.query_vectorised(q[i], rows16, k, keep=keep_of(want))
+                assert int(v1[i]) == len(r_ref) and r1[i, :len(r_ref)].tolist() == r_ref.tolist(), (want, b)
+            if exact:
+                assert l1 == plain and l0 >= plain, (want, b, l1, l0, plain)      # (the fused kernel is one launch too)
+    # device path with a caller's row mask: filtered inside the range, never "exact"
+    import torch
+    extra = rng.random(n) < 0.5
+    mask = sh.pack_row_mask(torch.from_numpy(extra).cuda())
+    for want in ([-1, r5, -1, -1], [-1, r5, -1, 2]):
+        f = np.asarray([want], np.int32)
+        out = run(lambda: [t.cpu().numpy() for t in sh.search_device(torch.from_numpy(q[:1]).cuda(), k, filt=f, row_masks=[mask])])
+        assert all(np.array_equal(a, b_) for a, b_ in zip(out["1"][0], out["0"][0]))
+        s_ref, r_ref = oracle.query_vectorised(q[0], rows16, k, keep=keep_of(want) & extra)
+        assert out["1"][0][1][0, :len(r_ref)].tolist() == r_ref.tolist()
+    # unions: nested runs and neighbouring runs are one range (no filter pass); runs with a gap are filtered inside the hull
+    m_next = int(codes[2][np.searchsorted(codes[2], m5, side="right")])        # the module stored right after m5
+    for alts, exact in (([[-1, r5, -1, -1], [-1, -1, m5, -1]], True), ([[-1, -1, m5, -1], [-1, -1, m_next, -1]], True),
+                        ([[-1, 2, -1, -1], [-1, 7, -1, -1]], False), ([[-1, 2, -1, -1], [-1, 3, -1, 1]], False),
+                        ([[-1, 4, 9999, -1], [-1, 3, m5, -1]], True)):
+        f = np.asarray(alts, np.int32)
+        out = run(lambda: sh.search_host_any_of(q[0], f, k, vectors=True))
+        (s1, r1, v1, e1), l1 = out["1"]
+        (s0, r0, v0, e0), l0 = out["0"]
+        assert v1 == v0 and np.array_equal(r1, r0) and np.array_equal(s1.view(np.int32), s0.view(np.int32)) and np.array_equal(e1, e0)
+        keep = np.zeros(n, bool)
+        for a in alts:
+            keep |= keep_of(a)
+        assert r1[:v1].tolist() == oracle.query_vectorised(q[0], rows16, k, keep=keep)[1].tolist(), alts
+        if exact:
+            assert l1 < l0, (alts, l1, l0)
+    # an append lands at the end: repository 5's rows are no longer one run; results stay the oracle's
+    more = rng.standard_normal((3, d), dtype=np.float32).astype(np.float16)
+    more_codes = np.asarray([[0, 0, 0], [r5, r5, 0], [m5, m5, 1], [1, 1, 1]], np.int32)
+    sh.append(more, more_codes)
+    allrows, allcodes = np.concatenate([rows16, more]), np.concatenate([codes, more_codes], axis=1)
+    for want in ([-1, r5, -1, -1], [-1, -1, m5, -1], [-1, 0, -1, -1], [-1, r5, -1, 1]):
+        out = run(lambda: sh.search_host(q[:1], k, filt=np.asarray([want], np.int32)))
+        (s1, r1, v1), _ = out["1"]
+        assert np.array_equal(r1, out["0"][0][1])
+        assert r1[0, :int(v1[0])].tolist() == oracle.query_vectorised(q[0], allrows, k, keep=keep_of(want, allcodes))[1].tolist()
+    sh.close()
+
+
+def test_store_clustered_by_its_keys_returns_the_same_documents():
+    """B200VectorStore.compact(cluster_by=...): rows are re-ordered (a repository's rows, inside them a module's, become
+    one run), ids / text / metadata follow, every face answers as before."""
+    from githubrepostorag_b200.vector_store import B200VectorStore
+    n, d, k = 5000, 64, 9
+    rng, emb, metas, ids = _corpus(31, n, d)
+    st = B200VectorStore(dim=d)
+    st.add_embeddings(ids, emb, [f"t{i}" for i in range(n)], metas)
+    st.delete(ids[7])
+    q = rng.standard_normal(d, dtype=np.float32)
+    flts = [None, {"repo": "r3"}, {"repo": "r3", "module": "m5"}, {"namespace": "default", "repo": "r2", "owner": "o1"},
+            {"topics": "kafka", "repo": "r1"}, {"module": "m11"}]
+    before = [[(i, round(s, 6)) for _, s, i in st.similarity_search_with_score_id_by_vector(q.tolist(), k=k, filter=f)] for f in flts]
+    adj_before = [c.id for c in st.adjacent([("repo", "r3"), ("module", "m5")], q.tolist(), k=k, filter={"namespace": "default"})]
+    st.compact(cluster_by=("repo", "module"))
+    sh = st._shard
+    repo_col = sh.codes[st.dictionary.keys.index("repo")].cpu().numpy()
+    assert (np.diff(repo_col) >= 0).all() and len(st) == n - 1
+    after = [[(i, round(s, 6)) for _, s, i in st.similarity_search_with_score_id_by_vector(q.tolist(), k=k, filter=f)] for f in flts]
+    assert after == before
+    assert [c.id for c in st.adjacent([("repo", "r3"), ("module", "m5")], q.tolist(), k=k, filter={"namespace": "default"})] == adj_before
+    live = np.ones(n, bool)
+    live[7] = False
+    assert [i for i, _ in after[1]] == _expect(q, emb[live], [m for j, m in enumerate(metas) if j != 7],
+                                               [x for j, x in enumerate(ids) if j != 7], k, {"repo": "r3"})[0]
+    doc = st.get_by_document_id(ids[11])
+    assert doc.page_content == "t11" and doc.metadata["repo"] == metas[11]["repo"] and st.get([ids[7]]) == []
+    st.add_embeddings(["late"], emb[:1], ["x"], [{"repo": "r3", "module": "m5"}])      # lands at the end: ranges widen
+    got = st.similarity_search_with_score_id_by_vector(emb[0].tolist(), k=2, filter={"repo": "r3", "module": "m5"})
+    assert "late" in [i for _, _, i in got]
     st.close()
