@@ -465,3 +465,56 @@ def test_c2_1m_x768_k10_full_size(torch_cuda):
     assert rows[:, 0].tolist() == planted.tolist()      # size-independent property: planted top-1
     assert np.all(scores[:, 0] > 0.99)
     sh.close()
+
+
+def test_replayed_host_call_equals_the_enqueued_one(torch_cuda, monkeypatch):
+    """The one-query unfiltered host call is recorded as a graph on its second occurrence and replayed afterwards: same
+    bits as the enqueued form and the device path, across a change of k, of the metric, an append (re-bind), a
+    tombstone, filtered calls in between -- and the launch count per call does not change."""
+    from githubrepostorag_b200 import _native as N
+    torch = torch_cuda
+    n, d = 30_011, 768
+    rows16 = S.corpus(21, n, d)
+    sh = _shard(torch, rows16, (np.arange(n) % 5).astype(np.int32)[None, :].copy())
+    qs = S.queries(21, 6, d)
+
+    def both(q, k, metric="cosine", filt=None):
+        out = []
+        for g in ("1", "0"):
+            monkeypatch.setenv("CODERAG_B200_HOST_GRAPH", g)
+            sh.reload_tuning()
+            res = []
+            for _ in range(3):                      # enqueued, recorded + replayed, replayed
+                before = N.launch_count()
+                r = sh.search_host(q, k, metric=metric, filt=filt)
+                res.append(([a.copy() for a in r], N.launch_count() - before))
+            out.append(res)
+        monkeypatch.delenv("CODERAG_B200_HOST_GRAPH")
+        sh.reload_tuning()
+        base = out[1][0][0]
+        for res in out:
+            for r, launches in res:
+                assert launches == out[1][0][1]
+                assert np.array_equal(r[1], base[1]) and np.array_equal(r[2], base[2]) and np.array_equal(r[0].view(np.int32), base[0].view(np.int32))
+        return base
+
+    for i, (k, metric) in enumerate(((10, "cosine"), (64, "cosine"), (10, "ip"), (10, "cosine"))):
+        s_, r_, v_ = both(qs[i:i + 1], k, metric)
+        ds, dr, dv = sh.search_device(torch.from_numpy(qs[i:i + 1]).cuda(), k, metric=metric)
+        torch.cuda.synchronize()
+        assert np.array_equal(r_, dr.cpu().numpy()) and np.array_equal(s_.view(np.int32), ds.cpu().numpy().view(np.int32))
+    # the graph stays valid across filtered calls, dies with a re-bind, and sees a tombstone (same buffers, new contents)
+    for _ in range(3):
+        sh.search_host(qs[:1], 10)
+    top = int(sh.search_host(qs[:1], 10)[1][0, 0])
+    sh.search_host(qs[:1], 10, filt=np.asarray([[3]], np.int32))
+    sh.tombstone([top])
+    assert top not in sh.search_host(qs[:1], 10)[1][0].tolist()
+    more = (qs[0] * 2).astype(np.float16)[None, :]
+    sh.append(more, np.asarray([[1]], np.int32))
+    for _ in range(3):
+        assert int(sh.search_host(qs[:1], 10)[1][0, 0]) == n          # the appended row is the best hit now
+    live = np.ones(n + 1, bool)
+    live[top] = False
+    _check(qs[:1], np.concatenate([rows16, more]), *sh.search_host(qs[:1], 10), 10, oracle.MODE_COSINE, keep=live, what="after append")
+    sh.close()
