@@ -293,3 +293,91 @@ def test_llamaindex_filters_or_nested_in(lib):
     eq, extra = st._split_filter({"topics": ("in", ["b", "a"]), "symbol": "f"})
     assert eq == {"symbol": "f"} and extra == (("topics", ("in", ("a", "b"))),)
     hash(extra)     # the mask cache key
+
+
+def test_compiled_filters_are_remembered_only_when_every_value_is_known(lib):
+    """The store remembers the compiled form of a filter dict (the worker repeats a handful per request); a filter naming
+    a value the dictionary has not seen compiles to the impossible filter and is NOT remembered, so a later write that
+    introduces the value is found."""
+    from githubrepostorag_b200 import _native as N
+    from githubrepostorag_b200.vector_store import B200VectorStore
+    st = B200VectorStore(dim=8)
+    st.add_embeddings(["a0"], np.ones((1, 8), np.float32), ["t"], [{"repo": "a", "namespace": "ns"}])
+    eq, extra, row = st._compile_filter({"repo": "b"})
+    assert extra == () and (row == N.FILT_IMPOSSIBLE).any() and not st._filter_cache
+    st.add_embeddings(["b0"], np.ones((1, 8), np.float32), ["t"], [{"repo": "b", "namespace": "ns"}])
+    hit = st._compile_filter({"repo": "b"})
+    pos = st.dictionary.keys.index("repo")
+    assert hit[2][pos] == st.dictionary.values[pos]["b"] and st._compile_filter({"repo": "b"}) is hit
+    # list-valued keys, IN and OR ride on row masks (extra), unhashable values are compiled without being remembered
+    eq, extra, row = st._compile_filter({"repo": "a", "topics": "kafka"})
+    assert eq == {"repo": "a"} and extra and row is not None
+    n_cached = len(st._filter_cache)
+    eq, extra, row = st._compile_filter({"repo": ("in", ["a", "b"])})
+    assert eq is None and extra and row is None and len(st._filter_cache) == n_cached
+    assert st._compile_filter(None) == (None, (), None) and st._compile_filter({}) == (None, (), None)
+
+
+def test_write_gate_readers_share_writers_exclude(lib):
+    """Searches (readers) run concurrently and re-entrantly; a writer waits for them, excludes them, and is not starved
+    by a stream of new readers."""
+    import threading
+    import time
+    from githubrepostorag_b200.vector_store import _WriteGate
+    gate = _WriteGate()
+    log, inside = [], []
+    start = threading.Barrier(4)
+
+    def reader(i):
+        start.wait()
+        with gate.read():
+            with gate.read():                      # re-entrant
+                inside.append(i)
+                time.sleep(0.05)
+        log.append(("r", i))
+
+    def writer():
+        start.wait()
+        time.sleep(0.01)                           # the readers are inside by now
+        with gate.write():
+            assert gate._readers == 0
+            log.append(("w", len(inside)))
+            with gate.write():                     # re-entrant
+                pass
+
+    ts = [threading.Thread(target=reader, args=(i,)) for i in range(3)] + [threading.Thread(target=writer)]
+    [t.start() for t in ts]
+    [t.join(timeout=10) for t in ts]
+    assert not any(t.is_alive() for t in ts)
+    assert ("w", 3) in log and sorted(x for x in log if x[0] == "r") == [("r", 0), ("r", 1), ("r", 2)]
+    # a reader arriving while a writer waits queues behind it
+    order = []
+    hold = threading.Event()
+
+    def long_reader():
+        with gate.read():
+            hold.wait(5)
+        order.append("r1")
+
+    def late_reader():
+        with gate.read():
+            order.append("r2")
+
+    def w2():
+        with gate.write():
+            order.append("w")
+
+    a = threading.Thread(target=long_reader); a.start()
+    time.sleep(0.02)
+    b = threading.Thread(target=w2); b.start()
+    time.sleep(0.02)
+    c = threading.Thread(target=late_reader); c.start()
+    time.sleep(0.02)
+    assert order == []                             # writer waits for r1, the late reader waits for the writer
+    hold.set()
+    [t.join(timeout=10) for t in (a, b, c)]
+    assert order.index("w") < order.index("r2")
+    with pytest.raises(RuntimeError):
+        with gate.read():
+            with gate.write():
+                pass
