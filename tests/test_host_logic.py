@@ -320,43 +320,55 @@ def test_compiled_filters_are_remembered_only_when_every_value_is_known(lib):
 
 def test_write_gate_readers_share_writers_exclude(lib):
     """Searches (readers) run concurrently and re-entrantly; a writer waits for them, excludes them, and is not starved
-    by a stream of new readers."""
+    by a stream of new readers.  (Event-driven: no outcome depends on how fast a thread gets scheduled.)"""
     import threading
     import time
     from githubrepostorag_b200.vector_store import _WriteGate
+
+    def wait_for(cond, what):
+        t0 = time.time()
+        while not cond():
+            assert time.time() - t0 < 20, f"timed out waiting for {what}"
+            time.sleep(0.001)
+
     gate = _WriteGate()
     log, inside = [], []
-    start = threading.Barrier(4)
+    release = threading.Event()
 
     def reader(i):
-        start.wait()
         with gate.read():
             with gate.read():                      # re-entrant
                 inside.append(i)
-                time.sleep(0.05)
+                release.wait(20)
         log.append(("r", i))
 
     def writer():
-        start.wait()
-        time.sleep(0.01)                           # the readers are inside by now
         with gate.write():
             assert gate._readers == 0
             log.append(("w", len(inside)))
             with gate.write():                     # re-entrant
                 pass
 
-    ts = [threading.Thread(target=reader, args=(i,)) for i in range(3)] + [threading.Thread(target=writer)]
-    [t.start() for t in ts]
-    [t.join(timeout=10) for t in ts]
-    assert not any(t.is_alive() for t in ts)
+    rs = [threading.Thread(target=reader, args=(i,)) for i in range(3)]
+    [t.start() for t in rs]
+    wait_for(lambda: len(inside) == 3, "three concurrent readers")          # readers share the gate
+    w = threading.Thread(target=writer)
+    w.start()
+    wait_for(lambda: gate._waiting_writers == 1, "the writer to queue")
+    assert not any(x[0] == "w" for x in log)                                 # ... and exclude the writer
+    release.set()
+    [t.join(timeout=20) for t in rs + [w]]
+    assert not any(t.is_alive() for t in rs + [w])
     assert ("w", 3) in log and sorted(x for x in log if x[0] == "r") == [("r", 0), ("r", 1), ("r", 2)]
     # a reader arriving while a writer waits queues behind it
     order = []
     hold = threading.Event()
+    r1_in = threading.Event()
 
     def long_reader():
         with gate.read():
-            hold.wait(5)
+            r1_in.set()
+            hold.wait(20)
         order.append("r1")
 
     def late_reader():
@@ -367,16 +379,19 @@ def test_write_gate_readers_share_writers_exclude(lib):
         with gate.write():
             order.append("w")
 
-    a = threading.Thread(target=long_reader); a.start()
-    time.sleep(0.02)
-    b = threading.Thread(target=w2); b.start()
-    time.sleep(0.02)
-    c = threading.Thread(target=late_reader); c.start()
-    time.sleep(0.02)
-    assert order == []                             # writer waits for r1, the late reader waits for the writer
+    a = threading.Thread(target=long_reader)
+    a.start()
+    assert r1_in.wait(20)
+    b = threading.Thread(target=w2)
+    b.start()
+    wait_for(lambda: gate._waiting_writers == 1, "the second writer to queue")
+    c = threading.Thread(target=late_reader)
+    c.start()
+    time.sleep(0.05)
+    assert order == []                             # the writer waits for r1; the late reader (if it got that far) for the writer
     hold.set()
-    [t.join(timeout=10) for t in (a, b, c)]
-    assert order.index("w") < order.index("r2")
+    [t.join(timeout=20) for t in (a, b, c)]
+    assert not any(t.is_alive() for t in (a, b, c)) and order.index("w") < order.index("r2")
     with pytest.raises(RuntimeError):
         with gate.read():
             with gate.write():
